@@ -1,0 +1,21 @@
+#!/bin/bash
+# TEST INFRASTRUCTURE ONLY.  Builds the reference's own sw runtime (python_sw) for the
+# five in-scope networks from the UNMODIFIED sources where they lie under
+# /root/reference, with the make-sw.sh:114 flags, against oracle/shim stand-in headers.
+# Outputs only into oracle/_ref/ (git-ignored).  Usage: oracle/build_ref.sh [net ...]
+set -e
+HERE="$(cd "$(dirname "$0")" && pwd)"
+REF=${BNN_REFERENCE:-/root/reference}
+SRC=$REF/bnn/src
+OUT=$HERE/_ref
+mkdir -p "$OUT"
+NETS=${@:-cnvW1A1 cnvW1A2 cnvW2A2 lfcW1A1 lfcW1A2}
+OPT=${REF_OPT:--O2}
+for n in $NETS; do
+  ( g++ -g0 -DOFFLOAD -DRAWHLS -std=c++14 -pthread $OPT -fPIC -shared -w \
+      $SRC/library/host/foldedmv-offload.cpp $SRC/library/host/rawhls-offload.cpp \
+      $SRC/network/$n/hw/top.cpp $SRC/network/$n/sw/main_python.cpp $HERE/shim/bbj_forward.cpp \
+      -I$HERE/shim -I$SRC/library/host -I$SRC/library/finn-hlslib -I$SRC/network/$n/hw \
+      -o $OUT/python_sw-$n.so && echo "built $OUT/python_sw-$n.so" ) &
+done
+wait
