@@ -14,7 +14,7 @@ OPT=${REF_OPT:--O2}
 for n in $NETS; do
   ( g++ -g0 -DOFFLOAD -DRAWHLS -std=c++14 -pthread $OPT -fPIC -shared -w \
       $SRC/library/host/foldedmv-offload.cpp $SRC/library/host/rawhls-offload.cpp \
-      $SRC/network/$n/hw/top.cpp $SRC/network/$n/sw/main_python.cpp $HERE/shim/bbj_forward.cpp \
+      $SRC/network/$n/hw/top.cpp $SRC/network/$n/sw/main_python.cpp $HERE/shim/bbj_forward.cpp $HERE/shim/ref_hooks.cpp \
       -I$HERE/shim -I$SRC/library/host -I$SRC/library/finn-hlslib -I$SRC/network/$n/hw \
       -o $OUT/python_sw-$n.so && echo "built $OUT/python_sw-$n.so" ) &
 done
