@@ -1,0 +1,89 @@
+// The CUDA runtime behind the C ABI: per-device replicated parameters, activation buffers sized to stay L2-resident,
+// stream-ordered fault epochs, and contiguous sharding of an image batch over the visible GPUs (no collective).
+// Replaces the host library's accelerator glue: FoldedMVInit/Deinit, FoldedMVOffloadBinarized (rawhls-offload.cpp:54-94),
+// testPrebuiltCIFAR10_multiple_images / _from_image (foldedmv-offload.h:316-416),
+// testPrebinarized_nolabel(_multiple_images) (foldedmv-offload.cpp:114-224) and BlackBoxJam's dispatch (top.cpp:238-291).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+#include "kernels.cuh"
+#include "netdesc.hpp"
+#include "params.hpp"
+
+namespace bnnb {
+
+struct DeviceState;
+
+class Engine {
+ public:
+  explicit Engine(const NetDesc& net);
+  ~Engine();
+  const NetDesc& net() const { return net_; }
+  const std::string& last_error() const { return err_; }
+
+  // Devices used for sharding (default: every visible device, or BNN_B200_DEVICES="0,1,..").
+  int set_devices(const int* ids, int n);
+  int num_devices() const { return (int)dev_.size(); }
+
+  int load_parameters(const std::string& dir);
+  bool loaded() const { return loaded_; }
+  ParamMirror& mirror() { return *pm_; }
+
+  // Host-buffer inference.  `input`: CNV n x 3073-byte CIFAR records, LFC n x 784 pixel bytes.
+  // classes (n, multi-image rule) / scores (CNV: n x 64 int16) / words (LFC: n x uint64) may be null.
+  // usec_per_image: device time of the inference kernels only, max over devices (the reference's timed region,
+  // foldedmv-offload.h:389-392), measured with CUDA events on the launching streams.
+  int infer_host(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, float* usec_per_image);
+
+  // Same, with faults applied between image segments ("epochs"): every fault with time i is applied before image i,
+  // cumulatively, and they persist afterwards (faults.h:115-148).  All devices apply every fault; each runs only its shard.
+  int infer_host_with_faults(const uint8_t* input, int n, int ncls, const std::vector<Fault>& faults, int* classes,
+                             float* usec_per_image);
+
+  // Device-resident inference on device slot `slot` (index into the device list): `d_in` is the layer-0 input exactly as
+  // BlackBoxJam reads it (CNV int8 HWC 3072 B/img; LFC 104 B/img), `d_out` what it writes (CNV 64 x int16; LFC uint64),
+  // `d_classes` optional int32 (CNV only).  Enqueued on `stream` (0 = the engine's own stream); returns without syncing.
+  int infer_device(int slot, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t stream);
+  // raw records / pixels (device) -> layer-0 input (device)
+  int prep_device(int slot, const void* d_raw, int n, void* d_in, cudaStream_t stream);
+  int sync(int slot);
+  // Number of kernels the last infer_device call enqueued (per call; for bench.py's gpu_launches).
+  int last_launches() const { return last_launches_; }
+
+  // Debug taps for parity tests: per image, concatenated over layers, int32 accumulators [ofm^2][N] and the layer outputs
+  // after pooling as int8 values [out_dim^2][N] (last CNV layer: low 8 bits of the score).
+  int tap_host(const uint8_t* input, int n, int32_t* acc, int8_t* act);
+  size_t tap_acc_size() const;
+  size_t tap_act_size() const;
+
+  // Deterministic fault door (inject_fault's arguments) and accelerator-memory access (FoldedMVMemRead/MemSet).
+  int inject_fault(uint32_t target, uint32_t layer, uint32_t bit, uint32_t word_size);
+  uint64_t mem_read(unsigned tl, unsigned mem, unsigned ind, unsigned thresh);
+  int mem_set(unsigned tl, unsigned mem, unsigned ind, unsigned thresh, uint64_t val);
+
+  void* alloc_pinned(size_t bytes);
+  void free_pinned(void* p);
+
+ private:
+  int ensure_devices();
+  int upload_all();
+  int apply_patches(const std::vector<Patch>& patches);                 // all devices, stream-ordered
+  void enqueue_patches(DeviceState& ds, const std::vector<Patch>& p, cudaStream_t s);
+  int run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s,
+                int32_t* tap_acc, uint32_t** bufs);
+  int chunk_images() const;
+  bool fail(const std::string& m) { err_ = m; return false; }
+
+  NetDesc net_;
+  std::unique_ptr<ParamMirror> pm_;
+  std::vector<std::unique_ptr<DeviceState>> dev_;
+  std::vector<int> dev_ids_;
+  bool loaded_ = false;
+  int last_launches_ = 0;
+  std::string err_;
+};
+
+}  // namespace bnnb

@@ -1,0 +1,53 @@
+// Device-side data layout and kernel launch wrappers (sm_100a).  See DESIGN.md "Data layout in HBM".
+//
+//  activations, 1 bit   : uint32 [img][pixel][C/32]            bit b of word j = channel 32j+b (1 <-> +1)
+//  activations, ternary : uint32 [img][pixel][2][C/32]         plane 0 = nz (value != 0), plane 1 = pos (value == +1)
+//  CNV input            : int8   [img][32][32][3]              quantiseAndPack<8,1> output (foldedmv-offload.h:129-144)
+//  LFC input            : uint32 [img][26]                     binarizeAndPack output, 832 bits (foldedmv-offload.cpp:82-98)
+//  CNV output           : int16  [img][64]                     PassThroughActivation scores (what Stream2Mem_Batch<64,128> writes)
+//  LFC output           : uint64 [img]
+//  weights (popc path)  : uint32 [plane][K/32][N]              K-major bit planes; W1: plane 0 = bit(+1); W2: plane 0 = lsb, 1 = sign
+//  weights layer 0      : uint32 [64][8]                       int8x4 words, K = 27 padded to 32, values +-1 (W1) or -2..1 (W2)
+//  weights (mma path)   : int8   [N][Kpad]                     values, K contiguous ("col" B operand of mma.m16n8k32)
+//  thresholds           : int32  [N][2]                        sign-extended int16 (layer 0: raw ap_fixed<24,16>); unused slots INT_MAX
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "netdesc.hpp"
+
+namespace bnnb {
+
+struct DevLayer {
+  LayerDesc d;
+  const uint64_t* wf;   // folded weight memory  [pe][wmem]   (device copy of the reference-coordinates mirror)
+  const int32_t* tf;    // folded threshold memory [pe][tmem][nthr]
+  uint32_t* wp;         // popc-path planes (or layer-0 int8x4 words)
+  int8_t* w8;           // mma-path int8 B operand (may be null)
+  int32_t* thr;         // [N][2]
+  int kwords;           // K/32
+  int kpad;             // K padded to a multiple of 32 (mma path)
+};
+
+// ---- parameter re-pack (runs once per load_parameters and after every fault epoch for the touched layers) ----
+void launch_repack(const DevLayer& L, int is_cnv_layer0, cudaStream_t s);
+// writes patch values into the folded device mirrors: entries {layer,is_thr,pe,ind,thresh,pad,value}
+struct DevPatch { uint32_t layer, is_thr, pe, ind, thresh, pad; uint64_t value; };
+struct DevFolded { uint64_t* wf[9]; int32_t* tf[9]; int wmem[9], tmem[9], nthr[9]; };
+void launch_patch(const DevFolded& f, const DevPatch* patches, int n, cudaStream_t s);
+
+// ---- input preparation ----
+void launch_prep_cifar(const uint8_t* records, int8_t* q, int n, cudaStream_t s);   // 3073-byte records -> int8 HWC
+void launch_prep_mnist(const uint8_t* pixels, uint32_t* bits, int n, cudaStream_t s);  // 784 bytes -> 832 bits
+
+// ---- layers (LOP3+POPC CUDA-core path) ----
+// tap_acc (optional): int32 [img][ofm_dim^2][N] pre-threshold accumulators.
+void launch_conv0(const DevLayer& L, const int8_t* in, uint32_t* out, int n_img, int32_t* tap_acc, int num_sms, cudaStream_t s);
+void launch_layer_popc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int32_t* tap_acc, int num_sms, cudaStream_t s);
+
+// ---- class decode for CNV (multi-image rule, foldedmv-offload.h:398-406) ----
+void launch_cnv_classes(const int16_t* scores, int n, int ncls, int* classes, cudaStream_t s);
+
+// opt-in to large dynamic shared memory for every kernel (call once per device)
+void kernels_init_device();
+
+}  // namespace bnnb

@@ -1,0 +1,113 @@
+/* bnn_b200 -- C ABI of the B200 (sm_100a) runtime for BNN-PYNQ's CNV / LFC networks.
+ *
+ * Two layers of entry points, both plain C (pointers and sizes only):
+ *
+ * (1) The six per-network symbols that bnn/bnn.py binds through cffi (cdef at bnn/bnn.py:69-76).  They are exported,
+ *     with exactly these names, by one shared object per network, lib/python_cuda-<network>.so, next to the
+ *     reference's python_hw-<network>-<platform>.so and python_sw-<network>-<platform>.so.  They replace the definitions in
+ *     bnn/src/network/<network>/sw/main_python.cpp (cnvW1A1: :67,120,141,171,225,229; lfcW1A1: :65,112,135,158,210,214).
+ *
+ * (2) A handle-based superset (bnnb_*), exported by lib/libbnn_b200.so, which the per-network objects are thin shims over:
+ *     in-memory inputs (no temp files), 16-bit scores / raw LFC words, deterministic fault lists, accelerator-memory access
+ *     (FoldedMVMemRead/MemSet, rawhls-offload.cpp:76-88), per-layer taps, and device-resident inference for benchmarks.
+ *
+ * Error behaviour: the reference throws string literals through the extern "C" frame and terminates the process
+ * (foldedmv-offload.cpp:321-323, foldedmv-offload.h:373-376).  This library never throws across the boundary: functions
+ * return -1 / NULL and bnnb_last_error() holds the message; the six bnn.py symbols also print it to stderr.
+ * There is no CPU fallback: without a CUDA device every compute call fails.
+ */
+#ifndef BNN_B200_H
+#define BNN_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * (1) bnn.py's cffi surface -- exported by lib/python_cuda-<network>.so
+ * ------------------------------------------------------------------------------------------------------------------ */
+/* <net>/sw/main_python.cpp:67 -- reads <path>/<L>-<PE>-weights.bin and <L>-<PE>-thres.bin (FoldedMVLoadLayerMem,
+ * foldedmv-offload.cpp:315-336), re-packs them on every visible GPU; discards previously injected faults. */
+void load_parameters(const char* path);
+/* :120 -- first CIFAR record (CNV) / first idx3 image (LFC) of the file.  results may be NULL; CNV: number_class scores,
+ * class = first maximum (std::max_element, :138); LFC: 64-entry one-hot at round(log2(word)) (foldedmv-offload.cpp:155-166). */
+int inference(const char* path, int results[64], int number_class, float* usecPerImage);
+/* :141 -- every record of the file.  Returns new int[N] class ids, or (CNV, enable_detail != 0) new int[N*number_class] scores.
+ * CNV class = first score strictly above a running maximum that starts at 0 (foldedmv-offload.h:398-406);
+ * LFC class = index of the highest set bit of (word & mask(number_class)), 0 if none (foldedmv-offload.cpp:202-220). */
+int* inference_multiple(const char* path, int number_class, int* image_number, float* usecPerImage, int enable_detail);
+/* :171 -- as inference_multiple (class ids only) with flip_count random parameter faults scheduled over the batch
+ * (faults.h:60-148).  target: <0 any, 0 weights, >0 thresholds; target_layers may be NULL (= all layers). */
+int* inference_multiple_with_faults(const char* path, int number_class, int* image_number, float* usecPerImage,
+                                    unsigned int flip_count, int word_size, int target, int* target_layers,
+                                    unsigned int num_targets);
+/* :225 */
+void free_results(int* result);
+/* :229 -- releases nothing the next call cannot rebuild: every entry point re-initialises on demand (FoldedMVInit). */
+void deinit(void);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * (2) handle-based API -- exported by lib/libbnn_b200.so
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct bnnb_ctx bnnb_ctx;
+
+/* network: "cnvW1A1" | "cnvW1A2" | "cnvW2A2" | "lfcW1A1" | "lfcW1A2".  NULL for an unknown name. */
+bnnb_ctx* bnnb_open(const char* network);
+void bnnb_close(bnnb_ctx* c);
+const char* bnnb_last_error(bnnb_ctx* c);
+/* GPUs the image batch is sharded over (contiguous ranges, parameters replicated, no collective).  Default: all visible
+ * devices or the comma list in $BNN_B200_DEVICES.  Must precede the first load/inference. */
+int bnnb_set_devices(bnnb_ctx* c, const int* device_ids, int n);
+int bnnb_num_devices(bnnb_ctx* c);
+int bnnb_load_parameters(bnnb_ctx* c, const char* dir);
+
+/* Host-buffer inference.  records: n x 3073 bytes (label + planar RGB, the CIFAR-10 binary record bnn.py writes, bnn/bnn.py:226-242);
+ * pixels: n x 784 bytes (idx3 payload).  Output pointers may be NULL.  scores: n x 64 int16 (what BlackBoxJam writes per image);
+ * words: n x uint64.  classes use the multi-image rules above.  usec_per_image: device time of the inference kernels only. */
+int bnnb_classify_cifar(bnnb_ctx* c, const uint8_t* records, int n, int number_class, int* classes, int16_t* scores, float* usec_per_image);
+int bnnb_classify_mnist(bnnb_ctx* c, const uint8_t* pixels, int n, int number_class, int* classes, uint64_t* words, float* usec_per_image);
+
+/* Deterministic fault list: nf x 5 uint32 {time, target (1 weights | 2 thresholds), layer, bit, word_size}, the arguments of the
+ * reference's inject_fault (foldedmv-offload.h:169-214); a fault with time i is applied before image i, cumulatively (faults.h:138-146).
+ * word_size is used as given (the reference's bool collapse, faults.h:42, is applied by bnnb_schedule_faults only). */
+int bnnb_classify_with_fault_list(bnnb_ctx* c, const uint8_t* input, int n, int number_class, const uint32_t* faults, int nf,
+                                  int* classes, float* usec_per_image);
+/* Draws the reference's random schedule (faults.h:60-94,123-133; topology.h:108-160) into out (cap x 5 uint32); returns the count.
+ * seed < 0: std::random_device, as the reference. */
+int bnnb_schedule_faults(bnnb_ctx* c, unsigned num_images, unsigned flip_count, int word_size, int target, const int* target_layers,
+                         unsigned num_targets, long long seed, uint32_t* out, int cap);
+/* One fault now (persists until the next load). */
+int bnnb_inject_fault(bnnb_ctx* c, unsigned target, unsigned layer, unsigned bit, unsigned word_size);
+/* FoldedMVMemRead / FoldedMVMemSet (rawhls-offload.cpp:76-88 -> DoMemRead/DoMemInit, cnvW1A1/hw/top.cpp:78-178):
+ * target_layer = 2*L (weights) or 2*L+1 (thresholds). */
+uint64_t bnnb_mem_read(bnnb_ctx* c, unsigned target_layer, unsigned mem, unsigned ind, unsigned thresh);
+int bnnb_mem_set(bnnb_ctx* c, unsigned target_layer, unsigned mem, unsigned ind, unsigned thresh, uint64_t val);
+unsigned bnnb_weight_layer_bits(bnnb_ctx* c, int layer);   /* topology.h:55-62 */
+unsigned bnnb_thresh_layer_bits(bnnb_ctx* c, int layer);   /* topology.h:63-70 */
+
+/* Per-layer taps (parity tests): per image, concatenated over layers: int32 accumulators [ofm_dim^2][N] before the threshold,
+ * and int8 layer outputs [out_dim^2][N] after the layer's max-pool (values 0/1, -1/0/+1, or the low byte of the score). */
+size_t bnnb_tap_acc_size(bnnb_ctx* c);
+size_t bnnb_tap_act_size(bnnb_ctx* c);
+int bnnb_tap(bnnb_ctx* c, const uint8_t* input, int n, int32_t* acc, int8_t* act);
+
+/* Device-resident inference (the reference's timed region: BlackBoxJam on inputs already in accelerator memory,
+ * foldedmv-offload.h:389-392).  d_in: CNV int8 HWC 3072 B/img, LFC 104 B/img; d_out: CNV 64 x int16, LFC uint64 per image;
+ * d_classes: optional int32 (CNV).  All device pointers on device slot `slot`; stream: a cudaStream_t (NULL = the library's).
+ * Asynchronous: call bnnb_sync or synchronise the stream.  bnnb_last_launches: kernels enqueued by the last call. */
+int bnnb_infer_device(bnnb_ctx* c, int slot, const void* d_in, int n, void* d_out, int* d_classes, int number_class, void* stream);
+int bnnb_prep_device(bnnb_ctx* c, int slot, const void* d_raw, int n, void* d_in, void* stream);  /* records/pixels -> layer-0 input */
+int bnnb_sync(bnnb_ctx* c, int slot);
+int bnnb_last_launches(bnnb_ctx* c);
+int bnnb_in_bytes(bnnb_ctx* c);    /* per image: 3072 | 104 */
+int bnnb_out_bytes(bnnb_ctx* c);   /* per image: 128 | 8 */
+
+/* Pinned host memory for full-rate asynchronous copies. */
+void* bnnb_alloc_host(size_t bytes);
+void bnnb_free_host(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
