@@ -1,0 +1,223 @@
+"""ctypes binding of the handle-based C ABI (include/bnn_b200.h, section 2) exported by lib/libbnn_b200.so.
+In-memory entry points for callers that already hold the images (no temp-file round trip), deterministic fault lists,
+accelerator-memory access and device-resident inference.  There is no CPU fallback: every call needs the built library."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.realpath(__file__))
+LIB_DIR = os.environ.get("BNN_B200_LIB_DIR", os.path.join(os.path.dirname(_HERE), "lib"))
+_lib = None
+
+_SIGS = {
+    "bnnb_open": (C.c_void_p, [C.c_char_p]),
+    "bnnb_close": (None, [C.c_void_p]),
+    "bnnb_last_error": (C.c_char_p, [C.c_void_p]),
+    "bnnb_set_devices": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "bnnb_num_devices": (C.c_int, [C.c_void_p]),
+    "bnnb_load_parameters": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "bnnb_classify_cifar": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "bnnb_classify_mnist": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "bnnb_classify_with_fault_list": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "bnnb_schedule_faults": (C.c_int, [C.c_void_p, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_void_p, C.c_uint, C.c_longlong, C.c_void_p, C.c_int]),
+    "bnnb_inject_fault": (C.c_int, [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_uint]),
+    "bnnb_mem_read": (C.c_uint64, [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_uint]),
+    "bnnb_mem_set": (C.c_int, [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint64]),
+    "bnnb_weight_layer_bits": (C.c_uint, [C.c_void_p, C.c_int]),
+    "bnnb_thresh_layer_bits": (C.c_uint, [C.c_void_p, C.c_int]),
+    "bnnb_tap_acc_size": (C.c_size_t, [C.c_void_p]),
+    "bnnb_tap_act_size": (C.c_size_t, [C.c_void_p]),
+    "bnnb_tap": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "bnnb_infer_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "bnnb_prep_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "bnnb_sync": (C.c_int, [C.c_void_p, C.c_int]),
+    "bnnb_last_launches": (C.c_int, [C.c_void_p]),
+    "bnnb_in_bytes": (C.c_int, [C.c_void_p]),
+    "bnnb_out_bytes": (C.c_int, [C.c_void_p]),
+    "bnnb_profile_enable": (C.c_int, [C.c_void_p, C.c_int]),
+    "bnnb_profile_collect": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "bnnb_microbench": (C.c_double, [C.c_int, C.c_void_p]),
+    "bnnb_alloc_host": (C.c_void_p, [C.c_size_t]),
+    "bnnb_free_host": (None, [C.c_void_p]),
+}
+
+
+def lib_path():
+    return os.path.join(LIB_DIR, "libbnn_b200.so")
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise RuntimeError("%s is missing: build it with `make -C bnn-pynq_b200`; this runtime has no CPU fallback" % p)
+        L = C.CDLL(p)
+        for name, (res, args) in _SIGS.items():
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Runtime:
+    """One network on the visible GPUs."""
+
+    def __init__(self, network, params_dir=None, devices=None):
+        self.L = lib()
+        self.network = network
+        self.is_cnv = network.startswith("cnv")
+        self.h = self.L.bnnb_open(network.encode())
+        if not self.h:
+            raise ValueError("unknown network %r" % network)
+        if devices is not None:
+            ids = np.ascontiguousarray(devices, np.int32)
+            self._ck(self.L.bnnb_set_devices(self.h, _p(ids), len(ids)))
+        if params_dir is not None:
+            self.load_parameters(params_dir)
+
+    def close(self):
+        if self.h:
+            self.L.bnnb_close(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RuntimeError("bnn_b200[%s]: %s" % (self.network, self.L.bnnb_last_error(self.h).decode()))
+
+    def load_parameters(self, params_dir):
+        self._ck(self.L.bnnb_load_parameters(self.h, params_dir.encode()))
+
+    @property
+    def usec_per_image(self):
+        return self._usec
+
+    def classify_cifar(self, records, number_class=10, want_scores=False):
+        """records: uint8 [n, 3073].  Returns classes (and int16 scores [n, 64])."""
+        rec = np.ascontiguousarray(records, np.uint8).reshape(-1, 3073)
+        n = rec.shape[0]
+        cls = np.zeros(n, np.int32)
+        sc = np.zeros((n, 64), np.int16) if want_scores else None
+        us = C.c_float(0)
+        self._ck(self.L.bnnb_classify_cifar(self.h, _p(rec), n, number_class, _p(cls), _p(sc), C.byref(us)))
+        self._usec = us.value
+        return (cls, sc) if want_scores else cls
+
+    def classify_mnist(self, pixels, number_class=10, want_words=False):
+        px = np.ascontiguousarray(pixels, np.uint8).reshape(-1, 784)
+        n = px.shape[0]
+        cls = np.zeros(n, np.int32)
+        words = np.zeros(n, np.uint64) if want_words else None
+        us = C.c_float(0)
+        self._ck(self.L.bnnb_classify_mnist(self.h, _p(px), n, number_class, _p(cls), _p(words), C.byref(us)))
+        self._usec = us.value
+        return (cls, words) if want_words else cls
+
+    def classify(self, data, number_class=10):
+        return self.classify_cifar(data, number_class) if self.is_cnv else self.classify_mnist(data, number_class)
+
+    def classify_with_fault_list(self, data, faults, number_class=10):
+        w = 3073 if self.is_cnv else 784
+        d = np.ascontiguousarray(data, np.uint8).reshape(-1, w)
+        fl = np.ascontiguousarray(faults, np.uint32).reshape(-1, 5)
+        cls = np.zeros(d.shape[0], np.int32)
+        us = C.c_float(0)
+        self._ck(self.L.bnnb_classify_with_fault_list(self.h, _p(d), d.shape[0], number_class, _p(fl), fl.shape[0], _p(cls), C.byref(us)))
+        self._usec = us.value
+        return cls
+
+    def schedule_faults(self, num_images, flip_count, word_size=1, target=-1, target_layers=None, seed=-1):
+        out = np.zeros((max(flip_count, 1), 5), np.uint32)
+        tl = None if not target_layers else np.ascontiguousarray(target_layers, np.int32)
+        m = self.L.bnnb_schedule_faults(self.h, num_images, flip_count, word_size, target, _p(tl), 0 if tl is None else len(tl), seed, _p(out), flip_count)
+        if m < 0:
+            self._ck(m)
+        return out[:m]
+
+    def inject_fault(self, target, layer, bit, word_size=1):
+        self._ck(self.L.bnnb_inject_fault(self.h, target, layer, bit, word_size))
+
+    def mem_read(self, tl, mem, ind, th):
+        return self.L.bnnb_mem_read(self.h, tl, mem, ind, th)
+
+    def mem_set(self, tl, mem, ind, th, val):
+        self._ck(self.L.bnnb_mem_set(self.h, tl, mem, ind, th, val & 0xFFFFFFFFFFFFFFFF))
+
+    def weight_layer_bits(self, l):
+        return self.L.bnnb_weight_layer_bits(self.h, l)
+
+    def thresh_layer_bits(self, l):
+        return self.L.bnnb_thresh_layer_bits(self.h, l)
+
+    def tap(self, data):
+        w = 3073 if self.is_cnv else 784
+        d = np.ascontiguousarray(data, np.uint8).reshape(-1, w)
+        acc = np.zeros((d.shape[0], self.L.bnnb_tap_acc_size(self.h)), np.int32)
+        act = np.zeros((d.shape[0], self.L.bnnb_tap_act_size(self.h)), np.int8)
+        self._ck(self.L.bnnb_tap(self.h, _p(d), d.shape[0], _p(acc), _p(act)))
+        return acc, act
+
+    # device-resident path (pointers are integers, e.g. torch.Tensor.data_ptr())
+    def infer_device(self, d_in, n, d_out, d_classes=0, number_class=10, stream=0, slot=0):
+        self._ck(self.L.bnnb_infer_device(self.h, slot, d_in, n, d_out, d_classes or None, number_class, stream or None))
+
+    def prep_device(self, d_raw, n, d_in, stream=0, slot=0):
+        self._ck(self.L.bnnb_prep_device(self.h, slot, d_raw, n, d_in, stream or None))
+
+    def sync(self, slot=0):
+        self._ck(self.L.bnnb_sync(self.h, slot))
+
+    def profile_enable(self, on=True):
+        self.L.bnnb_profile_enable(self.h, 1 if on else 0)
+
+    def profile_collect(self):
+        """-> (ms[10], launches[10]): layers 0..8, class decode."""
+        ms = np.zeros(10, np.float32)
+        cnt = np.zeros(10, np.int32)
+        self.L.bnnb_profile_collect(self.h, _p(ms), _p(cnt))
+        return ms, cnt
+
+    @property
+    def last_launches(self):
+        return self.L.bnnb_last_launches(self.h)
+
+    @property
+    def in_bytes(self):
+        return self.L.bnnb_in_bytes(self.h)
+
+    @property
+    def out_bytes(self):
+        return self.L.bnnb_out_bytes(self.h)
+
+
+def microbench(which):
+    """which: 0 POPC/s, 1 int8 mma.sync MAC/s, 2 LOP3/s.  Returns (rate, implied SM clock in MHz)."""
+    clk = C.c_double(0)
+    r = lib().bnnb_microbench(which, C.byref(clk))
+    return r, clk.value
+
+
+def pinned_array(nbytes):
+    """uint8 numpy view over cudaHostAlloc'ed memory (kept alive by the returned array's base object)."""
+    L = lib()
+    p = L.bnnb_alloc_host(nbytes)
+    if not p:
+        raise MemoryError("cudaHostAlloc failed")
+    buf = (C.c_uint8 * nbytes).from_address(p)
+    arr = np.frombuffer(buf, np.uint8)
+    return arr, p
+
+
+def free_pinned(p):
+    lib().bnnb_free_host(p)

@@ -244,8 +244,11 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
       tp = tap_acc;
       tap_acc += (size_t)n * net_.L[i].ofm_dim * net_.L[i].ofm_dim * net_.L[i].N;
     }
+    ProfEv pe{nullptr, nullptr, i, ds.id};
+    if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
     if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s);
     else launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s);
+    if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
     launches++;
     cur = out;
   }
@@ -458,6 +461,20 @@ int Engine::infer_host_with_faults(const uint8_t* input, int n, int ncls, const 
   if (!net_.is_cnv)
     for (int i = 0; i < n; i++) classes[i] = lfc_class_multi(words[i], ncls);
   if (usec) *usec = last_ms * 1000.0f;
+  return 0;
+}
+
+int Engine::profile_collect(float* ms, int* launches) {
+  for (int i = 0; i < 10; i++) { ms[i] = 0; launches[i] = 0; }
+  for (auto& e : prof_) {
+    cudaSetDevice(e.dev);
+    cudaEventSynchronize(e.b);
+    float t = 0;
+    if (cudaEventElapsedTime(&t, e.a, e.b) == cudaSuccess) { ms[e.layer] += t; launches[e.layer]++; }
+    cudaEventDestroy(e.a);
+    cudaEventDestroy(e.b);
+  }
+  prof_.clear();
   return 0;
 }
 

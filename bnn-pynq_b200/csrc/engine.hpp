@@ -64,6 +64,12 @@ class Engine {
   uint64_t mem_read(unsigned tl, unsigned mem, unsigned ind, unsigned thresh);
   int mem_set(unsigned tl, unsigned mem, unsigned ind, unsigned thresh, uint64_t val);
 
+  // Per-layer device timing: while enabled, run_chunk brackets every layer kernel with CUDA events on the launching stream.
+  // profile_collect synchronises, returns per-layer total milliseconds and launch counts since the last collect (arrays of 10:
+  // layers 0..8 then the class-decode kernel) and clears the pool.
+  void profile_enable(bool on) { profile_ = on; }
+  int profile_collect(float* ms, int* launches);
+
   void* alloc_pinned(size_t bytes);
   void free_pinned(void* p);
 
@@ -83,6 +89,9 @@ class Engine {
   std::vector<int> dev_ids_;
   bool loaded_ = false;
   int last_launches_ = 0;
+  bool profile_ = false;
+  struct ProfEv { cudaEvent_t a, b; int layer, dev; };
+  std::vector<ProfEv> prof_;
   std::string err_;
 };
 

@@ -103,6 +103,16 @@ int bnnb_last_launches(bnnb_ctx* c);
 int bnnb_in_bytes(bnnb_ctx* c);    /* per image: 3072 | 104 */
 int bnnb_out_bytes(bnnb_ctx* c);   /* per image: 128 | 8 */
 
+/* Per-layer device timing (CUDA events on the launching stream around every layer kernel while enabled).
+ * collect: ms[10] / launches[10] = totals since the last collect for layers 0..8 and (index 9) the class-decode kernel. */
+int bnnb_profile_enable(bnnb_ctx* c, int on);
+int bnnb_profile_collect(bnnb_ctx* c, float* ms, int* launches);
+
+/* Integer-pipe / tensor-pipe micro-benchmarks on device slot 0 (the roofline denominators of DESIGN.md):
+ * which: 0 = POPC (returns 32-bit popcounts per second), 1 = mma.sync.m16n8k32.s8 (returns int8 MACs per second),
+ * 2 = LOP3 (returns 32-bit logic ops per second).  clock_mhz (optional): SM clock implied by clock64() over the run. */
+double bnnb_microbench(int which, double* clock_mhz);
+
 /* Pinned host memory for full-rate asynchronous copies. */
 void* bnnb_alloc_host(size_t bytes);
 void bnnb_free_host(void* p);

@@ -1,0 +1,123 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (libbnn_b200.so / python_cuda-<net>.so), against the
+CPU oracle on the same seeded inputs and against the committed golden vectors of the reference runtime.  Bit-exact."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from oracle_py import GOLDEN, NETS, Oracle, mnist_idx_bytes, params_dir, synth_cifar, synth_mnist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "bnn-pynq_b200"))
+
+pytestmark = pytest.mark.gpu
+CNV = [n for n in NETS if n.startswith("cnv")]
+LFC = [n for n in NETS if n.startswith("lfc")]
+
+
+def runtime(net, pdir=None):
+    from bnn import native
+    return native.Runtime(net, pdir or params_dir(net), devices=[0])
+
+
+def gold(net):
+    return np.load(os.path.join(GOLDEN, "ref_%s.npz" % net))
+
+
+def data_for(net, n, seed):
+    return synth_cifar(n, seed) if net.startswith("cnv") else synth_mnist(n, seed)
+
+
+@pytest.mark.parametrize("net", CNV)
+def test_cnv_scores_vs_oracle_and_golden(net):
+    rt, o, g = runtime(net), Oracle(net), gold(net)
+    deer = np.frombuffer(open(os.path.join(GOLDEN, "images", "deer.bin"), "rb").read(), np.uint8)
+    cls, sc = rt.classify_cifar(deer, 10, want_scores=True)
+    assert cls[0] == 4 and np.array_equal(sc[:, :10], g["deer_scores"])
+    rec = synth_cifar(32, 0)
+    cls, sc = rt.classify_cifar(rec, 10, want_scores=True)
+    assert np.array_equal(sc[:, :10], g["synth_scores"]) and np.array_equal(cls, g["synth_classes"])
+    rec = synth_cifar(600, 11)  # ragged vs the 4-row groups and the chunking
+    cls, sc = rt.classify_cifar(rec, 10, want_scores=True)
+    assert np.array_equal(sc, o.cnv_scores(rec))
+    assert np.array_equal(cls, o.classes(rec))
+
+
+@pytest.mark.parametrize("net", LFC)
+def test_lfc_words_vs_oracle_and_golden(net):
+    rt, o, g = runtime(net), Oracle(net), gold(net)
+    img3 = np.frombuffer(open(os.path.join(GOLDEN, "images", "3.image-idx3-ubyte"), "rb").read(), np.uint8)[16:]
+    assert rt.classify_mnist(img3)[0] == 3
+    px = synth_mnist(256, 0)
+    cls, words = rt.classify_mnist(px, 10, want_words=True)
+    assert np.array_equal(words, g["synth_words"]) and np.array_equal(cls, g["synth_classes"])
+    px = synth_mnist(5001, 12)
+    cls, words = rt.classify_mnist(px, 10, want_words=True)
+    assert np.array_equal(words, o.lfc_words(px)) and np.array_equal(cls, o.classes(px))
+    for ncls in (1, 7, 47, 64):  # mask widths of the LFC decode
+        assert np.array_equal(rt.classify_mnist(px[:300], ncls), o.classes(px[:300], ncls))
+
+
+@pytest.mark.parametrize("net", NETS)
+def test_every_layer_accumulators_and_outputs(net):
+    rt, o = runtime(net), Oracle(net)
+    data = data_for(net, 5, 21)
+    acc, act = rt.tap(data)
+    if net.startswith("cnv"):
+        _, oacc, oact = o.cnv_scores(data, taps=True)
+    else:
+        _, oacc, oact = o.lfc_words(data, taps=True)
+    for i in range(data.shape[0]):
+        for l, (a, b) in enumerate(zip(o.split_taps(acc[i], "acc"), o.split_taps(oacc[i], "acc"))):
+            assert np.array_equal(a, b), "accumulators differ: image %d layer %d" % (i, l)
+        for l, (a, b) in enumerate(zip(o.split_taps(act[i], "act"), o.split_taps(oact[i], "act"))):
+            assert np.array_equal(a, b), "layer outputs differ: image %d layer %d" % (i, l)
+
+
+@pytest.mark.parametrize("net", NETS)
+def test_edge_cases(net):
+    rt, o = runtime(net), Oracle(net)
+    assert rt.classify(data_for(net, 0, 0)).shape == (0,)          # empty batch
+    for n in (1, 2, 3, 5):                                         # ragged tails
+        d = data_for(net, n, 30 + n)
+        assert np.array_equal(rt.classify(d), o.classes(d))
+
+
+@pytest.mark.parametrize("net", NETS)
+def test_faults_vs_reference_golden_and_oracle(net):
+    rt, o, g = runtime(net), Oracle(net), gold(net)
+    for t, l, b in g["fault_list"]:
+        rt.inject_fault(int(t), int(l), int(b), 1)
+        o.inject(int(t), int(l), int(b), 1)
+    reads = []
+    for l in range(o.nlayers):
+        li = o.layer_info(l)
+        reads += [rt.mem_read(2 * l, 0, 0, 0), rt.mem_read(2 * l + 1, li["pe"] - 1, li["tmem"] - 1, 0)]
+    assert np.array_equal(np.array(reads, np.uint64), g["fault_reads"])
+    if net.startswith("cnv"):
+        n = g["fault_scores"].shape[0]
+        _, sc = rt.classify_cifar(synth_cifar(32, 0)[:n], 10, want_scores=True)
+        assert np.array_equal(sc[:, :10], g["fault_scores"])
+    else:
+        n = g["fault_classes"].shape[0]
+        assert np.array_equal(rt.classify_mnist(synth_mnist(256, 0)[:n]), g["fault_classes"])
+    d = data_for(net, 200, 5)
+    assert np.array_equal(rt.classify(d), o.classes(d))             # still equal to the (equally faulted) oracle
+    rt.load_parameters(params_dir(net))                             # a reload discards the faults
+    assert np.array_equal(rt.classify(d), Oracle(net).classes(d))
+
+
+@pytest.mark.parametrize("net", NETS)
+def test_fault_epochs_match_one_image_at_a_time(net):
+    """Scheduled faults: time i applies before image i, cumulatively (faults.h:138-146)."""
+    rt, o = runtime(net), Oracle(net)
+    n = 96
+    d = data_for(net, n, 6)
+    fl = rt.schedule_faults(n, 40, word_size=1, target=-1, seed=3)
+    fl[:3, 0] = [0, 0, n - 1]  # faults before the first image and at the last one
+    assert fl.shape[0] > 30 and set(fl[:, 1]) <= {1, 2}
+    got = rt.classify_with_fault_list(d, fl)
+    want = o.classify_with_faults(d, fl[np.argsort(fl[:, 0], kind="stable")])
+    assert np.array_equal(got, want)
+    assert np.array_equal(rt.classify(d), o.classes(d))             # faults persist after the call
