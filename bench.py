@@ -24,6 +24,8 @@ sys.path.insert(0, os.path.join(ROOT, "bnn-pynq_b200"))
 
 ALG_BYTES = {"cnv": 3072 + 128, "lfc": 104 + 8}          # what BlackBoxJam reads + writes per image
 OPS = {"cnv": 118978048, "lfc": 6029312}                  # config.h #Ops per image (2 x MAC)
+LAYER_OPS = {"cnv": [3110400, 57802752, 21233664, 29491200, 5308416, 1179648, 262144, 524288, 65536],   # cnvW1A1/hw/config.h:15..190
+             "lfc": [1703936, 2097152, 2097152, 131072]}                                                  # lfcW1A1/hw/config.h:14..71
 PARAMS = {"cnvW1A1": "cifar10/cnvW1A1", "cnvW1A2": "cifar10/cnvW1A2", "cnvW2A2": "cifar10/cnvW2A2",
           "lfcW1A1": "mnist/lfcW1A1", "lfcW1A2": "mnist/lfcW1A2"}
 
@@ -33,11 +35,13 @@ def params_dir(net):
 
 
 def peaks():
+    """(hbm GB/s, dense bf16 TFLOP/s burst, source).  int8 tensor peak is nominally 2x the bf16 figure."""
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured"
+            d = json.load(f)
+            return float(d["hbm_gbs"]), float(d["bf16_tflops"]), "measured"
     except Exception:
-        return 6650.0, "fallback"
+        return 6650.0, 1590.0, "fallback"
 
 
 class ClockSampler(threading.Thread):
@@ -67,3 +71,224 @@ class ClockSampler(threading.Thread):
         reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
                 "samples": len(self.samples)}
+
+
+def synth_records(n, seed):
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    rec = np.zeros((n, 3073), np.uint8)
+    rec[:, 1:] = rng.integers(0, 256, (n, 3072), dtype=np.uint8)
+    return rec
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the reference's own sw runtime (oracle/_ref/python_sw-<net>.so), one process per host core
+# ---------------------------------------------------------------------------------------------------------------
+def _ref_worker(args):
+    net, pdir, nimg, seed, steps = args
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 1)  # the reference prints per call
+    from ref_py import Ref
+    r = Ref(net, pdir)
+    rec = synth_records(nimg, seed).tobytes()
+    n = C.c_int(0)
+    us = C.c_float(0)
+    path = r._file(rec)
+    out = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        p = r.L.inference_multiple(path.encode(), 10, C.byref(n), C.byref(us), 0)
+        wall = time.perf_counter() - t0
+        r.L.free_results(p)
+        out.append((us.value * n.value * 1e-6, wall))  # the reference's own timed region (BlackBoxJam only), and wall
+    os.unlink(path)
+    return out
+
+
+def run_reference_cpu(net, per_proc, steps, warmup, procs=None):
+    """Returns (images/s over the timed steps, ms per step, cores, sample description)."""
+    from multiprocessing import get_context
+    so = os.path.join(ROOT, "oracle", "_ref", "python_sw-%s.so" % net)
+    if not os.path.exists(so):
+        raise RuntimeError("oracle/_ref is missing (built by oracle/build_ref.sh where /root/reference exists)")
+    procs = procs or len(os.sched_getaffinity(0))
+    with get_context("spawn").Pool(procs) as pool:
+        res = pool.map(_ref_worker, [(net, params_dir(net), per_proc, 100 + i, steps + warmup) for i in range(procs)])
+    # per step: all processes run concurrently; the step lasts as long as the slowest accelerator call
+    step_s = [max(res[p][k][0] for p in range(procs)) for k in range(warmup, warmup + steps)]
+    total = sum(step_s)
+    ips = procs * per_proc * steps / total
+    sample = "%d images per process x %d processes per step, reference BlackBoxJam region (foldedmv-offload.h:389-392)" % (per_proc, procs)
+    return ips, 1000.0 * total / steps, procs, sample
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--net", default="cnvW1A1")
+    ap.add_argument("--batch", type=int, default=65536, help="images per GPU per step")
+    ap.add_argument("--ref-images", type=int, default=8, help="reference arm: images per process per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    fam = "cnv" if a.net.startswith("cnv") else "lfc"
+    metric = "%s images/sec" % a.net.upper().replace("CNVW", "CNV-W").replace("LFCW", "LFC-W")
+    config = {"workload": "%s, shipped %s params, batch %d synthetic images per GPU per step (uniform random bytes, seed 1)" % (a.net, PARAMS[a.net], a.batch),
+              "batch_per_gpu": a.batch, "sharding": "contiguous image ranges, parameters replicated, no collective",
+              "l2": "inputs (%d MB per step) exceed the 126 MB L2; no explicit flush" % (a.batch * (3072 if fam == "cnv" else 104) >> 20)}
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        ips, ms, cores, sample = run_reference_cpu(a.net, a.ref_images, a.steps, max(a.warmup, 1))
+        print(json.dumps({"impl": "reference", "metric": metric, "value": ips, "unit": "images/s", "n_gpus": a.gpus, "steps": a.steps,
+                          "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                          "dtype": "int1/int16 (HLS C++ on CPU)", "data": "synthetic", "config": config,
+                          "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "reference", "sample": sample},
+                          "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from bnn import native
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the runtime has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    rt = native.Runtime(a.net, params_dir(a.net), devices=[local_rank])
+    B = a.batch
+    raw_w = 3073 if fam == "cnv" else 784
+    host, host_ptr = native.pinned_array(B * raw_w)
+    if fam == "cnv":
+        host[:] = synth_records(B, 1 + rank).reshape(-1)
+    else:
+        host[:] = np.random.default_rng(1 + rank).integers(0, 256, B * 784, dtype=np.uint8)
+    d_raw = torch.empty(B * raw_w, dtype=torch.uint8, device=dev)
+    d_raw.copy_(torch.from_numpy(host), non_blocking=False)
+    d_in = torch.empty(B * rt.in_bytes, dtype=torch.uint8, device=dev)
+    d_out = torch.empty(B * rt.out_bytes, dtype=torch.uint8, device=dev)
+    d_cls = torch.empty(B, dtype=torch.int32, device=dev)
+    # a real (non-default) stream: the library launches on it and the CUDA events below are recorded on it
+    tstream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
+    rt.prep_device(d_raw.data_ptr(), B, d_in.data_ptr(), stream)
+    torch.cuda.synchronize()
+
+    def step():
+        rt.infer_device(d_in.data_ptr(), B, d_out.data_ptr(), d_cls.data_ptr() if fam == "cnv" else 0, 10, stream)
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    rt.profile_enable(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(a.steps):
+        step()
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    rt.profile_enable(False)
+    launches_per_step = rt.last_launches
+    lay_ms, lay_cnt = rt.profile_collect()
+    sampler.stop_flag = True
+    sampler.join()
+    ms_step = ms_total / a.steps
+    value = world * B * a.steps / (ms_total * 1e-3)
+    dev_classes = d_cls.cpu().numpy() if fam == "cnv" else None
+
+    # ---- end to end through the C ABI with host buffers -------------------------------------------------------
+    cls_host, cls_ptr = native.pinned_array(B * 4)
+    words_host, words_ptr = native.pinned_array(B * 8)
+    L = native.lib()
+    us = C.c_float(0)
+
+    def e2e_step():
+        if fam == "cnv":
+            rc = L.bnnb_classify_cifar(rt.h, host_ptr, B, 10, cls_ptr, None, C.byref(us))
+        else:
+            rc = L.bnnb_classify_mnist(rt.h, host_ptr, B, 10, cls_ptr, words_ptr, C.byref(us))
+        if rc != 0:
+            raise RuntimeError(L.bnnb_last_error(rt.h).decode())
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = world * B * a.steps / e2e_s
+    if fam == "cnv":
+        assert np.array_equal(cls_host.view(np.int32), dev_classes), "host-buffer and device-resident paths disagree"
+
+    # ---- roofline of the dominant kernel (live CUDA-event durations over the timed region) ----------------------
+    # The path is compute-bound by three orders of magnitude (3 200 B and 119 M ops per image: HBM allows 2.05 G images/s,
+    # the integer / tensor pipes a few M): the bound is the tensor pipe where a layer runs on it, and the same TOP/s scale is
+    # used for CUDA-core (LOP3+POPC) layers so that fractions are comparable.  1 MAC = 2 ops, as config.h counts them.
+    hbm_peak, tf_peak, how = peaks()
+    k = int(np.argmax(lay_ms))
+    launches_k = max(int(lay_cnt[k]), 1)
+    units_per_launch = B * a.steps / launches_k
+    avg_ms = float(lay_ms[k]) / launches_k
+    achieved = LAYER_OPS[fam][k] * units_per_launch / (avg_ms * 1e-3) / 1e12
+    popc, _ = native.microbench(0)
+    imma, _ = native.microbench(1)
+    roofline = {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s", "frac": achieved / tf_peak, "traffic": None,
+                "kernel": "layer %d" % k, "avg_launch_ms": avg_ms, "images_per_launch": units_per_launch,
+                "ops_per_image_this_kernel": LAYER_OPS[fam][k], "peak_source": how + " dense bf16 burst (int8 nominal = 2x)",
+                "share_of_step": float(lay_ms[k] / max(lay_ms.sum(), 1e-9)),
+                "layer_ms_per_step": [float(x) / a.steps for x in lay_ms],
+                "layer_tops": [LAYER_OPS[fam][i] * B * a.steps / (float(lay_ms[i]) * 1e-3) / 1e12 if lay_ms[i] > 0 else None for i in range(len(LAYER_OPS[fam]))],
+                "step": {"tops": OPS[fam] * value / world / 1e12, "frac_of_bf16_peak": OPS[fam] * value / world / 1e12 / tf_peak,
+                         "hbm_gbs": ALG_BYTES[fam] * value / world / 1e9, "hbm_frac": ALG_BYTES[fam] * value / world / 1e9 / hbm_peak},
+                "pipes": {"popc_per_s_measured": popc, "popc_roofline_images_per_s": popc * 32 / (OPS[fam] / 2),
+                          "popc_pipe_frac_step": (OPS[fam] / 2 / 32) * (value / world) / popc,
+                          "int8_mma_sync_mac_per_s_measured": imma}}
+
+    out = {"metric": metric, "value": value, "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+           "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "int1 (xnor-popcount, int32 accumulate)" if a.net.endswith("W1A1") else "int2 bit-serial", "data": "synthetic", "config": config,
+           "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": B * raw_w, "d2h_bytes_per_step": B * (4 if fam == "cnv" else 8)},
+           "gpu_launches": int(launches_per_step) * a.steps, "roofline": roofline, "clocks": sampler.summary()}
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        try:
+            ips, _, cores, sample = run_reference_cpu(a.net, 4, 1, 1)
+            out["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": cores, "kind": "reference", "sample": sample}
+        except Exception as e:  # the checker is missing: say so, never substitute
+            out["cpu_baseline"] = {"value": None, "unit": "images/s", "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -35,9 +35,11 @@ _SIGS = {
     "bnnb_last_launches": (C.c_int, [C.c_void_p]),
     "bnnb_in_bytes": (C.c_int, [C.c_void_p]),
     "bnnb_out_bytes": (C.c_int, [C.c_void_p]),
+    "bnnb_set_core": (C.c_int, [C.c_void_p, C.c_int]),
     "bnnb_profile_enable": (C.c_int, [C.c_void_p, C.c_int]),
     "bnnb_profile_collect": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "bnnb_microbench": (C.c_double, [C.c_int, C.c_void_p]),
+    "bnnb_tc_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "bnnb_alloc_host": (C.c_void_p, [C.c_size_t]),
     "bnnb_free_host": (None, [C.c_void_p]),
 }
@@ -178,6 +180,10 @@ class Runtime:
     def sync(self, slot=0):
         self._ck(self.L.bnnb_sync(self.h, slot))
 
+    def set_core(self, core):
+        """0: LOP3+POPC everywhere; 1: tcgen05 tensor-core kernels where instantiated."""
+        self.L.bnnb_set_core(self.h, core)
+
     def profile_enable(self, on=True):
         self.L.bnnb_profile_enable(self.h, 1 if on else 0)
 
@@ -206,6 +212,18 @@ def microbench(which):
     clk = C.c_double(0)
     r = lib().bnnb_microbench(which, C.byref(clk))
     return r, clk.value
+
+
+def tc_probe(A, B, shift=0, reps=1):
+    """tcgen05 kind::i8 probe: D[m][n] = sum_k A[m+shift][k] * B[n][k] for m < 128.  Returns (D int32 [128, N], cycles)."""
+    A = np.ascontiguousarray(A, np.int8)
+    B = np.ascontiguousarray(B, np.int8)
+    D = np.zeros((128, B.shape[0]), np.int32)
+    cyc = C.c_longlong(0)
+    rc = lib().bnnb_tc_probe(_p(A), _p(B), _p(D), A.shape[0], B.shape[0], A.shape[1], shift, reps, C.byref(cyc))
+    if rc != 0:
+        raise RuntimeError("tc_probe failed: rc=%d" % rc)
+    return D, cyc.value
 
 
 def pinned_array(nbytes):

@@ -97,6 +97,7 @@ int bnnb_last_launches(bnnb_ctx* c) { GUARD(c); return c->eng->last_launches(); 
 int bnnb_in_bytes(bnnb_ctx* c) { GUARD(c); return c->eng->net().in_bytes; }
 int bnnb_out_bytes(bnnb_ctx* c) { GUARD(c); return c->eng->net().out_bytes; }
 
+int bnnb_set_core(bnnb_ctx* c, int core) { GUARD(c); c->eng->set_core(core); return 0; }
 int bnnb_profile_enable(bnnb_ctx* c, int on) { GUARD(c); c->eng->profile_enable(on != 0); return 0; }
 int bnnb_profile_collect(bnnb_ctx* c, float* ms, int* launches) { GUARD(c); return c->eng->profile_collect(ms, launches); }
 

@@ -38,6 +38,7 @@ struct DeviceState {
   DevPatch* d_patches = nullptr;
   size_t patch_cap = 0;
   bool uploaded = false;
+  int* d_status = nullptr;  // set by a kernel whose mbarrier wait timed out
   std::vector<void*> allocs;
 };
 
@@ -51,7 +52,18 @@ static size_t act_words_per_image(const NetDesc& n) {
   return m;
 }
 
-Engine::Engine(const NetDesc& net) : net_(net), pm_(new ParamMirror(net)) {}
+Engine::Engine(const NetDesc& net) : net_(net), pm_(new ParamMirror(net)) {
+  if (const char* e = std::getenv("BNN_B200_CORE")) core_ = std::strcmp(e, "popc") == 0 ? 0 : 1;
+}
+
+int Engine::check_status(int slot) {
+  DeviceState& ds = *dev_[slot];
+  int st = 0;
+  CK(cudaSetDevice(ds.id));
+  CK(cudaMemcpy(&st, ds.d_status, 4, cudaMemcpyDeviceToHost));
+  if (st != 0) { err_ = "a tensor-core kernel timed out waiting on an mbarrier"; return -1; }
+  return 0;
+}
 
 Engine::~Engine() {
   for (auto& d : dev_) {
@@ -134,6 +146,12 @@ int Engine::ensure_devices() {
       const bool l0 = net_.is_cnv && i == 0;
       D.wp = (uint32_t*)alloc(l0 ? (size_t)64 * 8 * 4 : (size_t)l.wbits * D.kwords * l.N * 4);
       D.w8 = nullptr;
+      D.thr_tc = nullptr;
+      if (l.kind == KIND_CONV && !l0) {  // operands of the tensor-core path
+        D.w8 = (int8_t*)alloc((size_t)l.N * D.kpad);
+        D.thr_tc = (int32_t*)alloc((size_t)l.N * 2 * 4);
+        if (!D.w8 || !D.thr_tc) { err_ = "cudaMalloc failed"; return -1; }
+      }
       D.thr = (int32_t*)alloc((size_t)l.N * 2 * 4);
       D.wf = d->wf[i];
       D.tf = d->tf[i];
@@ -144,6 +162,9 @@ int Engine::ensure_devices() {
       d->folded.tmem[i] = l.tmem;
       d->folded.nthr[i] = std::max(l.nthr, 1);
     }
+    d->d_status = (int*)alloc(4);
+    if (!d->d_status) { err_ = "cudaMalloc failed"; return -1; }
+    CK(cudaMemset(d->d_status, 0, 4));
     dev_.push_back(std::move(d));
   }
   return 0;
@@ -247,6 +268,7 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     ProfEv pe{nullptr, nullptr, i, ds.id};
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
     if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s);
+    else if (core_ == 1 && !tp && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
     else launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s);
     if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
     launches++;
@@ -363,6 +385,7 @@ int Engine::infer_host(const uint8_t* input, int n, int ncls, int* classes, int1
       dev_ms[g] += ms;
     }
     CK(cudaGetLastError());
+    if (check_status(g) != 0) return -1;
     worst = std::max(worst, dev_ms[g]);
   }
   if (usec) *usec = worst * 1000.0f / (float)n;

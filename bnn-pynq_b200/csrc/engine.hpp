@@ -70,6 +70,11 @@ class Engine {
   void profile_enable(bool on) { profile_ = on; }
   int profile_collect(float* ms, int* launches);
 
+  // Compute core: 0 = LOP3+POPC CUDA-core kernels everywhere, 1 = tcgen05 tensor-core kernels where instantiated (default).
+  void set_core(int c) { core_ = c; }
+  int core() const { return core_; }
+  int check_status(int slot);
+
   void* alloc_pinned(size_t bytes);
   void free_pinned(void* p);
 
@@ -90,6 +95,7 @@ class Engine {
   bool loaded_ = false;
   int last_launches_ = 0;
   bool profile_ = false;
+  int core_ = 1;
   struct ProfEv { cudaEvent_t a, b; int layer, dev; };
   std::vector<ProfEv> prof_;
   std::string err_;

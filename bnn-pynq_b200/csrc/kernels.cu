@@ -69,6 +69,7 @@ void launch_repack(const DevLayer& L, int is_cnv_layer0, cudaStream_t s) {
   else k_repack_planes<<<(L.d.wbits * L.kwords * L.d.N + 255) / 256, 256, 0, s>>>(L);
   if (L.w8) k_repack_w8<<<(L.d.N * L.kpad + 255) / 256, 256, 0, s>>>(L);
   k_repack_thr<<<(L.d.N + 255) / 256, 256, 0, s>>>(L);
+  if (L.w8 && L.thr_tc) launch_thr_tc(L, s);
 }
 
 __global__ void k_patch(DevFolded f, const DevPatch* __restrict__ p, int n) {

@@ -24,6 +24,7 @@ struct DevLayer {
   uint32_t* wp;         // popc-path planes (or layer-0 int8x4 words)
   int8_t* w8;           // mma-path int8 B operand (may be null)
   int32_t* thr;         // [N][2]
+  int32_t* thr_tc;      // [N][2] thresholds adjusted for the tensor-core path (may be null)
   int kwords;           // K/32
   int kpad;             // K padded to a multiple of 32 (mma path)
 };
@@ -43,6 +44,10 @@ void launch_prep_mnist(const uint8_t* pixels, uint32_t* bits, int n, cudaStream_
 // tap_acc (optional): int32 [img][ofm_dim^2][N] pre-threshold accumulators.
 void launch_conv0(const DevLayer& L, const int8_t* in, uint32_t* out, int n_img, int32_t* tap_acc, int num_sms, cudaStream_t s);
 void launch_layer_popc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int32_t* tap_acc, int num_sms, cudaStream_t s);
+
+// ---- layers (tcgen05 kind::i8 tensor-core path, conv_tc.cu); returns false when the layer shape has no instantiation ----
+bool launch_conv_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
+void launch_thr_tc(const DevLayer& L, cudaStream_t s);
 
 // ---- class decode for CNV (multi-image rule, foldedmv-offload.h:398-406) ----
 void launch_cnv_classes(const int16_t* scores, int n, int ncls, int* classes, cudaStream_t s);

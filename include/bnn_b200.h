@@ -103,6 +103,10 @@ int bnnb_last_launches(bnnb_ctx* c);
 int bnnb_in_bytes(bnnb_ctx* c);    /* per image: 3072 | 104 */
 int bnnb_out_bytes(bnnb_ctx* c);   /* per image: 128 | 8 */
 
+/* Compute core per layer: 0 = LOP3+POPC CUDA-core kernels everywhere; 1 (default) = tcgen05 kind::i8 tensor-core kernels for the
+ * layers that have an instantiation (conv_tc.cu), LOP3+POPC for the rest.  $BNN_B200_CORE=popc|tc sets the default. */
+int bnnb_set_core(bnnb_ctx* c, int core);
+
 /* Per-layer device timing (CUDA events on the launching stream around every layer kernel while enabled).
  * collect: ms[10] / launches[10] = totals since the last collect for layers 0..8 and (index 9) the class-decode kernel. */
 int bnnb_profile_enable(bnnb_ctx* c, int on);

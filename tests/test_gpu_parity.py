@@ -121,3 +121,15 @@ def test_fault_epochs_match_one_image_at_a_time(net):
     want = o.classify_with_faults(d, fl[np.argsort(fl[:, 0], kind="stable")])
     assert np.array_equal(got, want)
     assert np.array_equal(rt.classify(d), o.classes(d))             # faults persist after the call
+
+
+@pytest.mark.parametrize("net", CNV)
+def test_tensor_core_and_popc_cores_agree(net):
+    """Per-layer core selection (tcgen05 kind::i8 vs LOP3+POPC) must not change a single bit."""
+    rt, o = runtime(net), Oracle(net)
+    rec = synth_cifar(777, 41)
+    want = o.cnv_scores(rec)
+    for core in (1, 0, 1):
+        rt.set_core(core)
+        cls, sc = rt.classify_cifar(rec, 10, want_scores=True)
+        assert np.array_equal(sc, want), "core %d" % core

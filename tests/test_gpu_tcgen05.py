@@ -1,0 +1,40 @@
+"""tcgen05 kind::i8 descriptor probe (bnnb_tc_probe): the operand layout and the shifted-start implicit im2col that the
+tensor-core conv kernels rely on, checked against numpy int32 matmul.  Bit-exact."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "bnn-pynq_b200"))
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("N,K,shift", [(64, 32, 0), (64, 64, 0), (64, 576, 0), (128, 128, 0), (256, 64, 0), (64, 64, 1), (64, 64, 31), (128, 96, 62), (32, 32, 3)])
+def test_probe_matches_numpy(N, K, shift):
+    from bnn import native
+    rng = np.random.default_rng(N * 1000 + K + shift)
+    rows = 128 + ((shift + 7) // 8) * 8
+    A = rng.integers(-128, 128, (rows, K), dtype=np.int8)
+    B = rng.integers(-2, 2, (N, K), dtype=np.int8)
+    D, _ = native.tc_probe(A, B, shift)
+    want = A[shift:shift + 128].astype(np.int32) @ B.astype(np.int32).T
+    assert np.array_equal(D, want)
+
+
+def test_probe_rate_report():
+    from bnn import native
+    rng = np.random.default_rng(0)
+    out = {}
+    for N in (64, 128, 256):
+        K = 256
+        A = rng.integers(-1, 2, (128, K), dtype=np.int8)
+        B = rng.integers(-1, 2, (N, K), dtype=np.int8)
+        reps = 512
+        _, c1 = native.tc_probe(A, B, 0, 1)
+        D, c = native.tc_probe(A, B, 0, reps)
+        mmas = reps * K // 32
+        out[N] = (c - c1) / (mmas - K // 32)
+        assert np.array_equal(D, reps * (A.astype(np.int32) @ B.astype(np.int32).T))
+    print("tcgen05 kind::i8 M=128 K=32 cycles per MMA by N:", out, "MAC/clk/SM:", {n: 128 * n * 32 / v for n, v in out.items()})
