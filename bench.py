@@ -254,19 +254,24 @@ def main():
     # the integer / tensor pipes a few M): the bound is the tensor pipe where a layer runs on it, and the same TOP/s scale is
     # used for CUDA-core (LOP3+POPC) layers so that fractions are comparable.  1 MAC = 2 ops, as config.h counts them.
     hbm_peak, tf_peak, how = peaks()
+    lops = list(LAYER_OPS[fam])
+    fused = []
+    for i in range(len(lops) - 1):   # a layer without its own launch was fused into the next kernel: move its ops there
+        if lay_cnt[i] == 0 and lops[i] and lay_cnt[i + 1] > 0:
+            lops[i + 1] += lops[i]; lops[i] = 0; fused.append(i)
     k = int(np.argmax(lay_ms))
     launches_k = max(int(lay_cnt[k]), 1)
     units_per_launch = B * a.steps / launches_k
     avg_ms = float(lay_ms[k]) / launches_k
-    achieved = LAYER_OPS[fam][k] * units_per_launch / (avg_ms * 1e-3) / 1e12
+    achieved = lops[k] * units_per_launch / (avg_ms * 1e-3) / 1e12
     popc, _ = native.microbench(0)
     imma, _ = native.microbench(1)
     roofline = {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s", "frac": achieved / tf_peak, "traffic": None,
-                "kernel": "layer %d" % k, "avg_launch_ms": avg_ms, "images_per_launch": units_per_launch,
-                "ops_per_image_this_kernel": LAYER_OPS[fam][k], "peak_source": how + " dense bf16 burst (int8 nominal = 2x)",
+                "kernel": "layer %d%s" % (k, " (fused with layer %d)" % (k - 1) if (k - 1) in fused else ""), "avg_launch_ms": avg_ms, "images_per_launch": units_per_launch,
+                "ops_per_image_this_kernel": lops[k], "peak_source": how + " dense bf16 burst (int8 nominal = 2x)",
                 "share_of_step": float(lay_ms[k] / max(lay_ms.sum(), 1e-9)),
                 "layer_ms_per_step": [float(x) / a.steps for x in lay_ms],
-                "layer_tops": [LAYER_OPS[fam][i] * B * a.steps / (float(lay_ms[i]) * 1e-3) / 1e12 if lay_ms[i] > 0 else None for i in range(len(LAYER_OPS[fam]))],
+                "layer_tops": [lops[i] * B * a.steps / (float(lay_ms[i]) * 1e-3) / 1e12 if lay_ms[i] > 0 else None for i in range(len(lops))],
                 "step": {"tops": OPS[fam] * value / world / 1e12, "frac_of_bf16_peak": OPS[fam] * value / world / 1e12 / tf_peak,
                          "hbm_gbs": ALG_BYTES[fam] * value / world / 1e9, "hbm_frac": ALG_BYTES[fam] * value / world / 1e9 / hbm_peak},
                 "pipes": {"popc_per_s_measured": popc, "popc_roofline_images_per_s": popc * 32 / (OPS[fam] / 2),

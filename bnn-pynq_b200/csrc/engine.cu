@@ -54,6 +54,7 @@ static size_t act_words_per_image(const NetDesc& n) {
 
 Engine::Engine(const NetDesc& net) : net_(net), pm_(new ParamMirror(net)) {
   if (const char* e = std::getenv("BNN_B200_CORE")) core_ = std::strcmp(e, "popc") == 0 ? 0 : 1;
+  if (const char* e = std::getenv("BNN_B200_FUSE01")) fuse01_ = std::atoi(e) != 0;
 }
 
 int Engine::check_status(int slot) {
@@ -257,7 +258,18 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
   const void* cur = d_in;
   int launches = 0;
   const bool per_layer = tap_acc != nullptr;  // when tapping, every layer writes its own buffer; else two ping-pong buffers
-  for (int i = 0; i < net_.nlayers; i++) {
+  int first_layer = 0;
+  if (core_ == 1 && net_.is_cnv && !per_layer && fuse01_) {  // layers 0+1 in one tensor-core kernel
+    ProfEv pe{nullptr, nullptr, 1, ds.id};
+    if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
+    if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, ds.d_status, s)) {
+      if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
+      launches++;
+      cur = bufs[1];
+      first_layer = 2;
+    } else if (profile_) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
+  }
+  for (int i = first_layer; i < net_.nlayers; i++) {
     const bool last = i == net_.nlayers - 1;
     uint32_t* out = last ? (uint32_t*)d_out : bufs[per_layer ? i : (i & 1)];
     int32_t* tp = nullptr;

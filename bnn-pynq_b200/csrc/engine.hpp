@@ -96,6 +96,7 @@ class Engine {
   int last_launches_ = 0;
   bool profile_ = false;
   int core_ = 1;
+  bool fuse01_ = true;
   struct ProfEv { cudaEvent_t a, b; int layer, dev; };
   std::vector<ProfEv> prof_;
   std::string err_;
