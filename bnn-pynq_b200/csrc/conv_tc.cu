@@ -30,6 +30,11 @@ __global__ void k_thr_tc(DevLayer L) {
     int neg = 0;
     if (d.in_mode == IN_XNOR)
       for (int k = 0; k < d.K; k++) neg += L.w8[(size_t)n * L.kpad + k] < 0;
+    if (d.out_mode == OUT_SCORE) {  // no threshold: the epilogue adds this offset to S to get the reference accumulator
+      L.thr_tc[2 * n] = neg;
+      L.thr_tc[2 * n + 1] = 0;
+      continue;
+    }
     for (int k = 0; k < 2; k++) {
       const int t = L.thr[2 * n + k];
       L.thr_tc[2 * n + k] = t == INT_MAX ? INT_MAX : t - neg;

@@ -82,7 +82,10 @@ Engine::~Engine() {
 int Engine::chunk_images() const {
   if (const char* e = std::getenv("BNN_B200_CHUNK")) { int v = std::atoi(e); if (v > 0) return v; }
   if (!net_.is_cnv) return 32768;
-  return net_.L[1].out_mode == OUT_TERN ? 2048 : 4096;  // keeps the ping-pong activations inside the 126 MB L2
+  // keeps the ping-pong activations inside the 126 MB L2 (largest: layer 0's output, 7 200 / 14 400 B per image, which exists
+  // only on the LOP3+POPC path; with layers 0+1 fused the largest is 1 568 / 3 136 B per image)
+  if (core_ == 1 && fuse01_) return net_.L[1].out_mode == OUT_TERN ? 8192 : 16384;
+  return net_.L[1].out_mode == OUT_TERN ? 2048 : 4096;
 }
 
 int Engine::set_devices(const int* ids, int n) {
@@ -106,7 +109,9 @@ int Engine::ensure_devices() {
       for (int i = 0; i < count; i++) dev_ids_.push_back(i);
     }
   }
-  const int chunk = chunk_images();
+  // buffers are sized for the largest chunk either core selection may use (set_core can change between calls)
+  int chunk = 0;
+  { const int c0 = core_; core_ = 0; chunk = chunk_images(); core_ = 1; chunk = std::max(chunk, chunk_images()); core_ = c0; }
   const size_t aw = act_words_per_image(net_);
   const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
   for (int id : dev_ids_) {
@@ -148,7 +153,7 @@ int Engine::ensure_devices() {
       D.wp = (uint32_t*)alloc(l0 ? (size_t)64 * 8 * 4 : (size_t)l.wbits * D.kwords * l.N * 4);
       D.w8 = nullptr;
       D.thr_tc = nullptr;
-      if (l.kind == KIND_CONV && !l0) {  // operands of the tensor-core path
+      if (!l0) {  // operands of the tensor-core path
         D.w8 = (int8_t*)alloc((size_t)l.N * D.kpad);
         D.thr_tc = (int32_t*)alloc((size_t)l.N * 2 * 4);
         if (!D.w8 || !D.thr_tc) { err_ = "cudaMalloc failed"; return -1; }
@@ -281,6 +286,7 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
     if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s);
     else if (core_ == 1 && !tp && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
+    else if (core_ == 1 && !tp && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
     else launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s);
     if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
     launches++;

@@ -48,6 +48,8 @@ void launch_layer_popc(const DevLayer& L, const uint32_t* in, uint32_t* out, int
 // ---- layers (tcgen05 kind::i8 tensor-core path, conv_tc.cu); returns false when the layer shape has no instantiation ----
 bool launch_conv_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
 void launch_thr_tc(const DevLayer& L, cudaStream_t s);
+// K-streamed GEMM for FC / small conv layers (gemm_tc.cu)
+bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
 // fused CNV layers 0+1 (cnv01_tc.cu): int8 HWC image -> pooled, bit-packed layer-1 output
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
 

@@ -133,3 +133,14 @@ def test_tensor_core_and_popc_cores_agree(net):
         rt.set_core(core)
         cls, sc = rt.classify_cifar(rec, 10, want_scores=True)
         assert np.array_equal(sc, want), "core %d" % core
+
+
+@pytest.mark.parametrize("net", LFC)
+def test_lfc_cores_agree(net):
+    rt, o = runtime(net), Oracle(net)
+    px = synth_mnist(1000, 43)
+    want = o.lfc_words(px)
+    for core in (1, 0):
+        rt.set_core(core)
+        _, words = rt.classify_mnist(px, 10, want_words=True)
+        assert np.array_equal(words, want), "core %d" % core
