@@ -9,8 +9,8 @@
 // image (m = y*32 + x: the 3x3x3 window row ky of pixel (y,x) is the first 9 bytes of P[m + 32*ky]).  K is laid out as
 // [ky][16]: k = ky*16 + (kx*3 + c) with zero weights for the 7 trailing bytes of each ky and for the whole 4th chunk, so
 // one tile needs two K=32 MMAs whose A descriptors differ only by a start shift (LBO = 32 rows).
-// The CTA is split in two halves of four warps: half A runs layer 1 on image i (tile loop + epilogue + pool/store) while
-// half B stages image i+1 (load, build P, layer-0 MMAs, layer-0 epilogue into the other operand buffer).
+// Warp-specialised CTA (one per SM): four warps run layer 1's epilogue on image i, four warps stage image i+1 (load, build P,
+// layer-0 MMAs, layer-0 epilogue into the other operand buffer), one warp issues layer 1's MMAs up to four tiles ahead.
 #include <climits>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
@@ -37,12 +37,19 @@ template <int OUTM> struct Smem01 {
 
 __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 
+// Warp roles (288 threads): warps 0-3 = half A (layer-1 epilogue, pool, store), warps 4-7 = half B (stage the next image:
+// load, window plane, layer-0 MMAs + epilogue into the other operand buffer), warp 8 = layer-1 MMA issuer.
+// The three roles are decoupled by mbarriers only (no CTA-wide barrier in steady state):
+//   abuf_full[b]  half B -> issuer   operand buffer b holds a staged image            (128 arrivals)
+//   abuf_empty[b] issuer -> half B   all layer-1 MMAs reading buffer b have completed  (tcgen05.commit)
+//   full[s]       issuer -> half A   accumulator slot s (of 4) holds a finished tile   (tcgen05.commit)
+//   empty[s]      half A -> issuer   slot s has been read out                          (4 arrivals, one per warp)
 template <int OUTM>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
-__global__ void __launch_bounds__(256, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
+__global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
                                                       int n_img, int* __restrict__ status) {
   using S = Smem01<OUTM>;
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t bar[4];  // [0,1]: layer-1 accumulators, [2,3]: layer-0 accumulators
+  __shared__ __align__(8) uint64_t bar0[2], full[4], empty[4], abuf_full[2], abuf_empty[2];
   __shared__ uint32_t tmem_base;
   uint8_t* sB1 = smem + S::OFF_B1;
   uint8_t* sP = smem + S::OFF_P;
@@ -52,29 +59,33 @@ __global__ void __launch_bounds__(256, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   int32_t* sthr0 = reinterpret_cast<int32_t*>(smem + S::OFF_THR);  // layer 0: floor(thr/2)   [64][2]
   int32_t* sthr1 = sthr0 + 128;                                    // layer 1: adjusted       [64][2]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const bool halfB = tid >= 128;
+  const int role = warp < 4 ? 0 : (warp < 8 ? 1 : 2);              // 0: half A, 1: half B, 2: issuer
   const int ht = tid & 127, hw = warp & 3;  // thread / warp index inside the half; hw selects the TMEM lane quarter
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
-  for (int i = tid; i < 64 * 36; i += 256) {  // layer-1 weights -> chunk-major operand layout
+  for (int i = tid; i < 64 * 36; i += 288) {  // layer-1 weights -> chunk-major operand layout
     const int n = i % 64, kc = i / 64;
     *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = *reinterpret_cast<const uint4*>(L1.w8 + (size_t)n * L1.kpad + kc * 16);
   }
-  for (int i = tid; i < 64 * 64; i += 256) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
+  for (int i = tid; i < 64 * 64; i += 288) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
     sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)v;
   }
-  for (int i = tid; i < 128; i += 256) {
+  for (int i = tid; i < 128; i += 288) {
     const int t = L0.thr[i];
     sthr0[i] = t == INT_MAX ? INT_MAX : (t >> 1);  // thr < 2S  <=>  floor(thr/2) < S
     sthr1[i] = L1.thr_tc[i];
   }
-  for (int i = tid; i < 2 * L1_A / 16; i += 256) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
-  for (int i = tid; i < (P_BYTES + IMG_BYTES) / 16; i += 256) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
-  if (warp == 0) tc::tmem_alloc(&tmem_base, 256);
-  if (tid == 0) { for (int i = 0; i < 4; i++) tc::mbar_init(&bar[i], 1); tc::mbar_init_fence(); }
+  for (int i = tid; i < 2 * L1_A / 16; i += 288) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
+  for (int i = tid; i < (P_BYTES + IMG_BYTES) / 16; i += 288) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
+  if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
+  if (tid == 0) {
+    for (int i = 0; i < 2; i++) { tc::mbar_init(&bar0[i], 1); tc::mbar_init(&abuf_full[i], 128); tc::mbar_init(&abuf_empty[i], 1); }
+    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4); }
+    tc::mbar_init_fence();
+  }
   tc::fence_async_smem();
   tc::fence_before_sync();
   __syncthreads();
@@ -82,152 +93,168 @@ __global__ void __launch_bounds__(256, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   const uint32_t tmem = tmem_base;
   const uint32_t idesc = tc::make_idesc_i8(128, 64);
   const uint32_t sA_u = tc::smem_u32(smem), sB1_u = tc::smem_u32(sB1), sP_u = tc::smem_u32(sP), sB0_u = tc::smem_u32(sB0);
-  uint32_t ph[2] = {0, 0};  // parities of this half's two barriers
   bool failed = false;
-
-  // ---- half B: stage image `img` into operand buffer `buf` (layer 0) ----------------------------------------------------
-  auto stage_l0 = [&](long long img, int buf) {
-    const uint4* src = reinterpret_cast<const uint4*>(in + img * 3072);
-    for (int i = ht; i < 192; i += 128) reinterpret_cast<uint4*>(sImg)[i] = __ldg(src + i);
-    half_sync(2);
-    const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg);
-    for (int m = ht; m < 1024 + 64; m += 128) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
-      const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
-      uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
-      if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
-      *reinterpret_cast<uint4*>(sP + (size_t)m * 16) =
-          make_uint4(__funnelshift_r(x0, x1, sh), __funnelshift_r(x1, x2, sh), __funnelshift_r(x2, x3, sh), __funnelshift_r(x3, x4, sh));
-    }
-    tc::fence_async_smem();
-    half_sync(2);
-    auto issue0 = [&](int t) {  // thread 128
-      tc::fence_after_sync();
-      const uint32_t acc = tmem + 128 + (uint32_t)(t & 1) * 64;
-      const uint32_t a0 = sP_u + (uint32_t)(t * 128) * 16;
-      tc::mma_i8(acc, tc::make_desc(a0, 32 * 16, 128), tc::make_desc(sB0_u, 64 * 16, 128), idesc, 0u);                   // ky 0, 1
-      tc::mma_i8(acc, tc::make_desc(a0 + 64 * 16, 32 * 16, 128), tc::make_desc(sB0_u + 2 * 64 * 16, 64 * 16, 128), idesc, 1u);  // ky 2, zero chunk
-      tc::commit(&bar[2 + (t & 1)]);
-    };
-    uint8_t* sA = smem + (size_t)buf * L1_A;
-    if (ht == 0) issue0(0);
-    for (int t = 0; t < L0_TILES; t++) {
-      if (ht == 0 && t + 1 < L0_TILES) issue0(t + 1);
-      if (!tc::mbar_wait(&bar[2 + (t & 1)], ph[t & 1])) failed = true;
-      ph[t & 1] ^= 1;
-      tc::fence_after_sync();
-      const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
-      const bool valid = x < 30 && y < 30;
-      const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + 128 + (uint32_t)(t & 1) * 64;
-#pragma unroll
-      for (int j = 0; j < 2; j++) {
-        uint32_t r[32];
-        tc::tmem_ld32(trow + j * 32, r);
-        tc::tmem_ld_wait();
-#pragma unroll
-        for (int c16 = 0; c16 < 2; c16++) {  // one 16-channel chunk = one uint4 store
-          uint32_t v[4];
-#pragma unroll
-          for (int q = 0; q < 4; q++) {
-            uint32_t wv = 0;
-#pragma unroll
-            for (int e = 0; e < 4; e++) {
-              const int c = c16 * 16 + q * 4 + e, n = j * 32 + c;
-              const int s = (int)r[c];
-              int val = sthr0[2 * n] < s;                       // {0,1}
-              if (OUTM == OUT_TERN) val = val + (sthr0[2 * n + 1] < s) - 1;  // {-1,0,+1}
-              wv |= (uint32_t)(val & 0xff) << (8 * e);
-            }
-            v[q] = wv;
-          }
-          if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * j + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
-        }
-      }
-      tc::fence_before_sync();
-      half_sync(2);
-    }
-    tc::fence_async_smem();  // operand planes written through the generic proxy, read by layer-1 MMAs after the CTA barrier
-  };
-
-  // ---- half A: layer 1 on operand buffer `buf`, result to image `img` -----------------------------------------------------
-  auto run_l1 = [&](long long img, int buf) {
-    const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
-    auto issue1 = [&](int t) {  // thread 0
-      tc::fence_after_sync();
-      const uint32_t acc = tmem + (uint32_t)(t & 1) * 64;
-      bool first = true;
-#pragma unroll
-      for (int tap = 0; tap < 9; tap++) {
-        const uint32_t off = (uint32_t)((tap / 3) * 30 + tap % 3 + t * 128) * 16;
-#pragma unroll
-        for (int s = 0; s < 2; s++) {
-          tc::mma_i8(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * L1_PLANE + off, L1_PLANE, 128),
-                     tc::make_desc(sB1_u + (uint32_t)((tap * 4 + 2 * s) * 64) * 16, 64 * 16, 128), idesc, first ? 0u : 1u);
-          first = false;
-        }
-      }
-      tc::commit(&bar[t & 1]);
-    };
-    constexpr int WPP = 2 * S::OPL;
-    if (ht == 0) issue1(0);
-    for (int t = 0; t < L1_TILES; t++) {
-      if (ht == 0 && t + 1 < L1_TILES) issue1(t + 1);
-      if (!tc::mbar_wait(&bar[t & 1], ph[t & 1])) failed = true;
-      ph[t & 1] ^= 1;
-      tc::fence_after_sync();
-      const int m = t * 128 + hw * 32 + lane;
-      const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)(t & 1) * 64;
-#pragma unroll
-      for (int j = 0; j < 2; j++) {
-        uint32_t r[32];
-        tc::tmem_ld32(trow + j * 32, r);
-        tc::tmem_ld_wait();
-        uint32_t b0 = 0, b1 = 0;
-#pragma unroll
-        for (int c = 0; c < 32; c++) {
-          const int s = (int)r[c];
-          const int t0 = sthr1[2 * (j * 32 + c)] < s;
-          if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
-          else { const int t1 = sthr1[2 * (j * 32 + c) + 1] < s; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
-        }
-        sbits[(size_t)m * WPP + j] = b0;
-        if (OUTM == OUT_TERN) sbits[(size_t)m * WPP + 2 + j] = b1;
-      }
-      tc::fence_before_sync();
-      half_sync(1);
-    }
-    // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
-    for (int i = ht; i < 196 * 2; i += 128) {
-      const int j = i & 1, op = i >> 1, oy = op / 14, ox = op % 14;
-      const uint32_t* r00 = sbits + (size_t)((2 * oy) * 30 + 2 * ox) * WPP;
-      const uint32_t *r01 = r00 + WPP, *r10 = r00 + 30 * WPP, *r11 = r10 + WPP;
-      uint32_t* dst = out + ((size_t)img * 196 + op) * WPP;
-      if (OUTM == OUT_BIT) {
-        dst[j] = r00[j] | r01[j] | r10[j] | r11[j];
-      } else {
-        const uint32_t P = r00[2 + j] | r01[2 + j] | r10[2 + j] | r11[2 + j];
-        const uint32_t M = (r00[j] & ~r00[2 + j]) & (r01[j] & ~r01[2 + j]) & (r10[j] & ~r10[2 + j]) & (r11[j] & ~r11[2 + j]);
-        dst[j] = P | M;
-        dst[2 + j] = P;
-      }
-    }
-  };
-
-  // ---- pipeline over this CTA's images ------------------------------------------------------------------------------------
   const long long first = blockIdx.x, stride = gridDim.x;
-  if (halfB && first < n_img) stage_l0(first, 0);
-  tc::fence_before_sync();
-  __syncthreads();
-  tc::fence_after_sync();
-  int it = 0;
-  for (long long img = first; img < n_img; img += stride, it++) {
-    if (!halfB) run_l1(img, it & 1);
-    else if (img + stride < n_img) stage_l0(img + stride, (it + 1) & 1);
-    tc::fence_before_sync();
-    __syncthreads();
-    tc::fence_after_sync();
+  const int K = first < n_img ? (int)((n_img - first + stride - 1) / stride) : 0;  // images of this CTA
+  constexpr uint32_t L0_ACC = 256;  // TMEM columns: layer-1 slots 0,64,128,192; layer-0 accumulators 256,320
+
+  if (role == 1) {
+    // ================= half B: stage image k into operand buffer k&1 (layer 0) ==========================================
+    uint32_t ph0[2] = {0, 0};
+    int thrA[64];  // first thresholds in registers: the epilogue's shared-memory traffic competes with the MMA operand reads
+#pragma unroll
+    for (int n = 0; n < 64; n++) thrA[n] = sthr0[2 * n];
+    for (int k = 0; k < K; k++) {
+      const long long img = first + (long long)k * stride;
+      const int buf = k & 1;
+      const uint4* src = reinterpret_cast<const uint4*>(in + img * 3072);
+      for (int i = ht; i < 192; i += 128) reinterpret_cast<uint4*>(sImg)[i] = __ldg(src + i);
+      half_sync(2);
+      const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg);
+      for (int m = ht; m < 1024 + 64; m += 128) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
+        const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
+        uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
+        if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
+        *reinterpret_cast<uint4*>(sP + (size_t)m * 16) =
+            make_uint4(__funnelshift_r(x0, x1, sh), __funnelshift_r(x1, x2, sh), __funnelshift_r(x2, x3, sh), __funnelshift_r(x3, x4, sh));
+      }
+      tc::fence_async_smem();
+      half_sync(2);
+      auto issue0 = [&](int t) {  // thread 128
+        tc::fence_after_sync();
+        const uint32_t acc = tmem + L0_ACC + (uint32_t)(t & 1) * 64;
+        const uint32_t a0 = sP_u + (uint32_t)(t * 128) * 16;
+        tc::mma_i8(acc, tc::make_desc(a0, 32 * 16, 128), tc::make_desc(sB0_u, 64 * 16, 128), idesc, 0u);                          // ky 0, 1
+        tc::mma_i8(acc, tc::make_desc(a0 + 64 * 16, 32 * 16, 128), tc::make_desc(sB0_u + 2 * 64 * 16, 64 * 16, 128), idesc, 1u);  // ky 2, zero chunk
+        tc::commit(&bar0[t & 1]);
+      };
+      // the layer-1 MMAs that read this buffer two images ago must have completed before it is overwritten
+      if (k >= 2 && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
+      uint8_t* sA = smem + (size_t)buf * L1_A;
+      if (ht == 0) issue0(0);
+      for (int t = 0; t < L0_TILES; t++) {
+        if (ht == 0 && t + 1 < L0_TILES) issue0(t + 1);
+        if (!tc::mbar_wait(&bar0[t & 1], ph0[t & 1])) failed = true;
+        ph0[t & 1] ^= 1;
+        tc::fence_after_sync();
+        const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
+        const bool valid = x < 30 && y < 30;
+        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)(t & 1) * 64;
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          uint32_t r[32];
+          tc::tmem_ld32(trow + j * 32, r);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int c16 = 0; c16 < 2; c16++) {  // one 16-channel chunk = one uint4 store
+            uint32_t v[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              uint32_t wv = 0;
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const int c = c16 * 16 + q * 4 + e, n = j * 32 + c;
+                const int s = (int)r[c];
+                int val = thrA[n] < s;                                          // {0,1}
+                if (OUTM == OUT_TERN) val = val + (sthr0[2 * n + 1] < s) - 1;   // {-1,0,+1}
+                wv |= (uint32_t)(val & 0xff) << (8 * e);
+              }
+              v[q] = wv;
+            }
+            if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * j + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+          }
+        }
+        tc::fence_before_sync();
+        half_sync(2);  // both layer-0 accumulators are re-used two tiles later
+      }
+      tc::fence_async_smem();  // operand planes were written through the generic proxy and are read by the async proxy (MMA)
+      tc::mbar_arrive(&abuf_full[buf]);
+    }
+  } else if (role == 2) {
+    // ================= issuer: layer-1 MMAs, up to four tiles ahead of the epilogue ========================================
+    if (lane == 0) {
+      for (int k = 0; k < K; k++) {
+        const int buf = k & 1;
+        if (!tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
+        for (int t = 0; t < L1_TILES; t++) {
+          const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
+          if (u >= 1 && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          tc::fence_after_sync();
+          const uint32_t acc = tmem + (uint32_t)slot * 64;
+          bool firstmma = true;
+#pragma unroll
+          for (int tap = 0; tap < 9; tap++) {
+            const uint32_t off = (uint32_t)((tap / 3) * 30 + tap % 3 + t * 128) * 16;
+#pragma unroll
+            for (int s = 0; s < 2; s++) {
+              tc::mma_i8(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * L1_PLANE + off, L1_PLANE, 128),
+                         tc::make_desc(sB1_u + (uint32_t)((tap * 4 + 2 * s) * 64) * 16, 64 * 16, 128), idesc, firstmma ? 0u : 1u);
+              firstmma = false;
+            }
+          }
+          tc::commit(&full[slot]);
+        }
+        tc::commit(&abuf_empty[buf]);
+      }
+    }
+  } else {
+    // ================= half A: layer-1 epilogue, 2x2 max-pool, store ========================================================
+    constexpr int WPP = 2 * S::OPL;
+    int thrA[64];
+#pragma unroll
+    for (int n = 0; n < 64; n++) thrA[n] = sthr1[2 * n];
+    for (int k = 0; k < K; k++) {
+      const long long img = first + (long long)k * stride;
+      for (int t = 0; t < L1_TILES; t++) {
+        const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
+        if (!tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
+        tc::fence_after_sync();
+        const int m = t * 128 + hw * 32 + lane;
+        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64;
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          uint32_t r[32];
+          tc::tmem_ld32(trow + j * 32, r);
+          tc::tmem_ld_wait();
+          uint32_t b0 = 0, b1 = 0;
+#pragma unroll
+          for (int c = 0; c < 32; c++) {
+            const int s = (int)r[c];
+            const int t0 = thrA[j * 32 + c] < s;
+            if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
+            else { const int t1 = sthr1[2 * (j * 32 + c) + 1] < s; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
+          }
+          sbits[(size_t)m * WPP + j] = b0;
+          if (OUTM == OUT_TERN) sbits[(size_t)m * WPP + 2 + j] = b1;
+        }
+        tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read
+      }
+      half_sync(1);
+      // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
+      for (int i = ht; i < 196 * 2; i += 128) {
+        const int j = i & 1, op = i >> 1, oy = op / 14, ox = op % 14;
+        const uint32_t* r00 = sbits + (size_t)((2 * oy) * 30 + 2 * ox) * WPP;
+        const uint32_t *r01 = r00 + WPP, *r10 = r00 + 30 * WPP, *r11 = r10 + WPP;
+        uint32_t* dst = out + ((size_t)img * 196 + op) * WPP;
+        if (OUTM == OUT_BIT) {
+          dst[j] = r00[j] | r01[j] | r10[j] | r11[j];
+        } else {
+          const uint32_t P = r00[2 + j] | r01[2 + j] | r10[2 + j] | r11[2 + j];
+          const uint32_t M = (r00[j] & ~r00[2 + j]) & (r01[j] & ~r01[2 + j]) & (r10[j] & ~r10[2 + j]) & (r11[j] & ~r11[2 + j]);
+          dst[j] = P | M;
+          dst[2 + j] = P;
+        }
+      }
+      half_sync(1);  // the next image's epilogue overwrites sbits
+    }
   }
   if (failed && status) *status = 1;
-  if (warp == 0) tc::tmem_dealloc(tmem, 256);
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
 }  // namespace
@@ -237,10 +264,10 @@ bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
   const int grid = n_img < num_sms ? n_img : num_sms;
   if (L1.d.out_mode == OUT_BIT) {
     cudaFuncSetAttribute(k_cnv01_tc<OUT_BIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem01<OUT_BIT>::TOTAL);
-    k_cnv01_tc<OUT_BIT><<<grid, 256, Smem01<OUT_BIT>::TOTAL, s>>>(L0, L1, in, out, n_img, status);
+    k_cnv01_tc<OUT_BIT><<<grid, 288, Smem01<OUT_BIT>::TOTAL, s>>>(L0, L1, in, out, n_img, status);
   } else {
     cudaFuncSetAttribute(k_cnv01_tc<OUT_TERN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem01<OUT_TERN>::TOTAL);
-    k_cnv01_tc<OUT_TERN><<<grid, 256, Smem01<OUT_TERN>::TOTAL, s>>>(L0, L1, in, out, n_img, status);
+    k_cnv01_tc<OUT_TERN><<<grid, 288, Smem01<OUT_TERN>::TOTAL, s>>>(L0, L1, in, out, n_img, status);
   }
   return true;
 }

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(128) k_conv_tc(DevLayer L, const uint32_t* __r
     const int n = i % N, kc = i / N;
     *reinterpret_cast<uint4*>(sb + ((size_t)kc * N + n) * 16) = *reinterpret_cast<const uint4*>(L.w8 + (size_t)n * L.kpad + kc * 16);
   }
-  for (int i = tid; i < 2 * N; i += 128) sthr[i] = L.thr_tc[i];
+  for (int i = tid; i < 2 * N; i += 128) sthr[(i & 1) * N + (i >> 1)] = L.thr_tc[i];  // [2][N]: consecutive channels -> LDS.128
   // the pad pixels of every plane are read by the last tile's shifted windows: keep them defined
   for (int i = tid; i < Cfg::KC * (Cfg::PITCH - Cfg::ROWS); i += 128) {
     const int g = i / (Cfg::PITCH - Cfg::ROWS), p = Cfg::ROWS + i % (Cfg::PITCH - Cfg::ROWS);
@@ -170,11 +170,11 @@ __global__ void __launch_bounds__(128) k_conv_tc(DevLayer L, const uint32_t* __r
 #pragma unroll
         for (int c = 0; c < 32; c++) {
           const int S = (int)r[c];
-          const int t0 = sthr[2 * (j * 32 + c)] < S;
+          const int t0 = sthr[j * 32 + c] < S;
           if (OUTM == OUT_BIT) {
             b0 |= (uint32_t)t0 << c;
           } else {
-            const int t1 = sthr[2 * (j * 32 + c) + 1] < S;
+            const int t1 = sthr[N + j * 32 + c] < S;
             b0 |= (uint32_t)(1 ^ t0 ^ t1) << c;   // nz
             b1 |= (uint32_t)(t0 & t1) << c;       // pos
           }

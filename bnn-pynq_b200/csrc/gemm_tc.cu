@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __r
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n0 = blockIdx.y * N;
   const long long row0 = (long long)blockIdx.x * 128;
-  for (int i = tid; i < 2 * N; i += 128) sthr[i] = L.thr_tc[2 * n0 + i];
+  for (int i = tid; i < 2 * N; i += 128) sthr[(i & 1) * N + (i >> 1)] = L.thr_tc[2 * n0 + i];  // [2][N]
   if (warp == 0) tc::tmem_alloc(&tmem_base, N < 32 ? 32 : N);
   if (tid == 0) { tc::mbar_init(&bar[0], 1); tc::mbar_init(&bar[1], 1); tc::mbar_init_fence(); }
   tc::fence_before_sync();
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __r
         int16_t* o16 = reinterpret_cast<int16_t*>(out) + (size_t)r * d.N + n0 + j * 32;
 #pragma unroll
         for (int c = 0; c < 32; c += 2) {
-          const uint32_t lo = (uint32_t)((int)v[c] + sthr[2 * (j * 32 + c)]) & 0xffff, hi = (uint32_t)((int)v[c + 1] + sthr[2 * (j * 32 + c + 1)]) & 0xffff;
+          const uint32_t lo = (uint32_t)((int)v[c] + sthr[j * 32 + c]) & 0xffff, hi = (uint32_t)((int)v[c + 1] + sthr[j * 32 + c + 1]) & 0xffff;
           *reinterpret_cast<uint32_t*>(o16 + c) = lo | (hi << 16);
         }
       }
@@ -124,9 +124,9 @@ __global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __r
 #pragma unroll
       for (int c = 0; c < 32; c++) {
         const int S = (int)v[c];
-        const int t0 = sthr[2 * (j * 32 + c)] < S;
+        const int t0 = sthr[j * 32 + c] < S;
         if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
-        else { const int t1 = sthr[2 * (j * 32 + c) + 1] < S; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
+        else { const int t1 = sthr[N + j * 32 + c] < S; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
       }
       if (rvalid) {
         uint32_t* dst = out + (size_t)r * nwt * (OUTM == OUT_TERN ? 2 : 1) + n0 / 32 + j;
