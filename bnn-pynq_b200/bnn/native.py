@@ -39,6 +39,7 @@ _SIGS = {
     "bnnb_profile_enable": (C.c_int, [C.c_void_p, C.c_int]),
     "bnnb_profile_collect": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "bnnb_microbench": (C.c_double, [C.c_int, C.c_void_p]),
+    "bnnb_tc_probe_fp4": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "bnnb_tc_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "bnnb_alloc_host": (C.c_void_p, [C.c_size_t]),
     "bnnb_free_host": (None, [C.c_void_p]),
@@ -223,6 +224,30 @@ def tc_probe(A, B, shift=0, reps=1):
     rc = lib().bnnb_tc_probe(_p(A), _p(B), _p(D), A.shape[0], B.shape[0], A.shape[1], shift, reps, C.byref(cyc))
     if rc != 0:
         raise RuntimeError("tc_probe failed: rc=%d" % rc)
+    return D, cyc.value
+
+
+_E2M1 = {0: 0x0, 1: 0x2, -1: 0xA, 2: 0x4, -2: 0xC}
+
+
+def pack_fp4(M):
+    """int matrix with values in {-2,-1,0,1,2} -> e2m1 nibbles, two per byte (even k in the low nibble)."""
+    M = np.asarray(M)
+    lut = np.zeros(5, np.uint8)
+    for v, c in _E2M1.items():
+        lut[v + 2] = c
+    nib = lut[M + 2]
+    return np.ascontiguousarray(nib[:, 0::2] | (nib[:, 1::2] << 4))
+
+
+def tc_probe_fp4(A, B, shift=0, reps=1):
+    """tcgen05 kind::mxf4 (block-scaled fp4, all scales 1.0) probe: D[m][n] = sum_k A[m+shift][k] * B[n][k]."""
+    A4, B4 = pack_fp4(A), pack_fp4(B)
+    D = np.zeros((128, B.shape[0]), np.int32)
+    cyc = C.c_longlong(0)
+    rc = lib().bnnb_tc_probe_fp4(_p(A4), _p(B4), _p(D), A.shape[0], B.shape[0], A.shape[1], shift, reps, C.byref(cyc))
+    if rc != 0:
+        raise RuntimeError("tc_probe_fp4 failed: rc=%d" % rc)
     return D, cyc.value
 
 

@@ -91,3 +91,91 @@ extern "C" int bnnb_tc_probe(const int8_t* A, const int8_t* B, int32_t* D, int r
   cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(dC); cudaFree(dS);
   return e == cudaSuccess ? st : -1;
 }
+
+// ---- fp4 probe: A [rows_a][K/2] packed e2m1, B [N][K/2], D[m][n] = sum_k A[m+shift][k] * B[n][k] (fp32 -> int32) --------------
+namespace {
+__global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, int32_t* __restrict__ D,
+                                                       int rows_a, int N, int K, int shift, int reps, long long* cyc, int* status) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_base;
+  const int kch = K / 32;  // 16-byte chunks (32 fp4 each)
+  const uint32_t plane_a = (uint32_t)rows_a * 16, plane_b = (uint32_t)N * 16;
+  uint8_t* sa = smem;
+  uint8_t* sb = smem + (size_t)kch * plane_a;
+  for (int i = threadIdx.x; i < rows_a * kch; i += blockDim.x) {
+    const int r = i / kch, g = i % kch;
+    *reinterpret_cast<uint4*>(sa + (size_t)g * plane_a + r * 16) = *reinterpret_cast<const uint4*>(A + (size_t)r * (K / 2) + g * 16);
+  }
+  for (int i = threadIdx.x; i < N * kch; i += blockDim.x) {
+    const int r = i / kch, g = i % kch;
+    *reinterpret_cast<uint4*>(sb + (size_t)g * plane_b + r * 16) = *reinterpret_cast<const uint4*>(B + (size_t)r * (K / 2) + g * 16);
+  }
+  fence_async_smem();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0) tmem_alloc(&tmem_base, 512);
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init_fence(); }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = tmem_base;
+  const uint32_t sf = tmem + 256;  // 16 columns x 128 lanes of ue8m0 1.0 serve as every scale factor
+  tmem_fill16(sf + ((uint32_t)(warp * 32) << 16), 0x7f7f7f7fu);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t idesc = make_idesc_mxf4(128, N);
+  long long t0 = 0, t1 = 0;
+  if (threadIdx.x == 0) {
+    t0 = clock64();
+    for (int rep = 0; rep < reps; rep++)
+      for (int ks = 0; ks < K / 64; ks++) {
+        const uint64_t ad = make_desc(smem_u32(sa) + (uint32_t)(2 * ks) * plane_a + (uint32_t)shift * 16, plane_a, 128);
+        const uint64_t bd = make_desc(smem_u32(sb) + (uint32_t)(2 * ks) * plane_b, plane_b, 128);
+        mma_mxf4(tmem, ad, bd, idesc, sf, sf, (ks > 0 || rep > 0) ? 1u : 0u);
+      }
+    commit(&bar);
+  }
+  const bool ok = mbar_wait(&bar, 0);
+  if (threadIdx.x == 0) { t1 = clock64(); *cyc = t1 - t0; }
+  fence_after_sync();
+  if (!ok) { if (threadIdx.x == 0) *status = 1; }
+  else {
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; j++) D[(size_t)(warp * 32 + lane) * N + c0 + j] = __float2int_rn(__uint_as_float(r[j]));
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+}  // namespace
+
+extern "C" int bnnb_tc_probe_fp4(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles) {
+  if (N % 32 || N < 32 || N > 256 || K % 64 || rows_a < 128 + shift || rows_a % 8) return -1;
+  const size_t smem = (size_t)(K / 32) * (rows_a + N) * 16;
+  if (smem > 200 * 1024) return -1;
+  uint8_t *dA, *dB; int32_t* dD; long long* dC; int* dS;
+  cudaSetDevice(0);
+  if (cudaMalloc(&dA, (size_t)rows_a * K / 2) != cudaSuccess) return -1;
+  cudaMalloc(&dB, (size_t)N * K / 2); cudaMalloc(&dD, (size_t)128 * N * 4); cudaMalloc(&dC, 8); cudaMalloc(&dS, 4);
+  cudaMemcpy(dA, A, (size_t)rows_a * K / 2, cudaMemcpyHostToDevice);
+  cudaMemcpy(dB, B, (size_t)N * K / 2, cudaMemcpyHostToDevice);
+  cudaMemset(dS, 0, 4);
+  cudaMemset(dD, 0xff, (size_t)128 * N * 4);
+  cudaFuncSetAttribute(k_tc_probe_fp4, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+  k_tc_probe_fp4<<<1, 128, smem>>>(dA, dB, dD, rows_a, N, K, shift, reps, dC, dS);
+  cudaError_t e = cudaDeviceSynchronize();
+  int st = 0;
+  if (e == cudaSuccess) {
+    cudaMemcpy(D, dD, (size_t)128 * N * 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(cycles, dC, 8, cudaMemcpyDeviceToHost);
+    cudaMemcpy(&st, dS, 4, cudaMemcpyDeviceToHost);
+  }
+  cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(dC); cudaFree(dS);
+  return e == cudaSuccess ? st : -1;
+}

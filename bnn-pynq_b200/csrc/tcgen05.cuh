@@ -97,3 +97,28 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 }  // namespace tc
 }  // namespace bnnb
+
+// ---- block-scaled fp4 (kind::mxf4, e2m1 operands packed two per byte, K = 64 per instruction, fp32 accumulate) --------------
+// With every scale factor = 1.0 (ue8m0 0x7F) this is an exact small-integer MMA: e2m1 holds {0, +-1, +-2} exactly and the
+// fp32 accumulator is exact below 2^24.
+namespace bnnb { namespace tc {
+__host__ __device__ constexpr uint32_t make_idesc_mxf4(int M, int N) {
+  return (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | (1u << 23) | ((uint32_t)(M >> 4) << 24);  // a/b = e2m1, scales ue8m0, K=64
+}
+__device__ __forceinline__ void mma_mxf4(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t sfa, uint32_t sfb, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n\t"
+      "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(sfa), "r"(sfb)
+      : "memory");
+}
+// registers -> TMEM: this warp's 32 lanes, 16 consecutive columns, all set to v
+__device__ __forceinline__ void tmem_fill16(uint32_t taddr, uint32_t v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr), "r"(v)
+      : "memory");
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+}}  // namespace bnnb::tc

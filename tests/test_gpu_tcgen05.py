@@ -38,3 +38,33 @@ def test_probe_rate_report():
         out[N] = (c - c1) / (mmas - K // 32)
         assert np.array_equal(D, reps * (A.astype(np.int32) @ B.astype(np.int32).T))
     print("tcgen05 kind::i8 M=128 K=32 cycles per MMA by N:", out, "MAC/clk/SM:", {n: 128 * n * 32 / v for n, v in out.items()})
+
+
+@pytest.mark.parametrize("N,K,shift", [(64, 64, 0), (64, 576, 0), (128, 128, 5), (256, 128, 0), (64, 128, 31), (32, 64, 2)])
+def test_fp4_probe_matches_numpy(N, K, shift):
+    """kind::mxf4 with unit scales as an exact small-integer MMA ({-1,0,1} activations x {-2..1} weights)."""
+    from bnn import native
+    rng = np.random.default_rng(N * 7 + K + shift)
+    rows = 128 + ((shift + 7) // 8) * 8
+    A = rng.integers(-1, 2, (rows, K))
+    B = rng.integers(-2, 2, (N, K))
+    D, _ = native.tc_probe_fp4(A, B, shift)
+    want = A[shift:shift + 128].astype(np.int32) @ B.astype(np.int32).T
+    assert np.array_equal(D, want)
+
+
+def test_fp4_probe_rate_report():
+    from bnn import native
+    rng = np.random.default_rng(1)
+    out = {}
+    for N in (64, 128, 256):
+        K = 512
+        A = rng.integers(0, 2, (128, K))
+        B = rng.integers(-1, 2, (N, K))
+        reps = 256
+        _, c1 = native.tc_probe_fp4(A, B, 0, 1)
+        D, c = native.tc_probe_fp4(A, B, 0, reps)
+        mmas = reps * K // 64
+        out[N] = (c - c1) / (mmas - K // 64)
+        assert np.array_equal(D, reps * (A.astype(np.int32) @ B.astype(np.int32).T))
+    print("tcgen05 kind::mxf4 M=128 K=64 cycles per MMA by N:", out, "MAC/clk/SM:", {n: 128 * n * 64 / v for n, v in out.items()})
