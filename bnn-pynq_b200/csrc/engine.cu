@@ -53,7 +53,7 @@ static size_t act_words_per_image(const NetDesc& n) {
 }
 
 Engine::Engine(const NetDesc& net) : net_(net), pm_(new ParamMirror(net)) {
-  if (const char* e = std::getenv("BNN_B200_CORE")) core_ = std::strcmp(e, "popc") == 0 ? 0 : 1;
+  if (const char* e = std::getenv("BNN_B200_CORE")) core_ = std::strcmp(e, "popc") == 0 ? 0 : (std::strcmp(e, "i8") == 0 ? 1 : 2);
   if (const char* e = std::getenv("BNN_B200_FUSE01")) fuse01_ = std::atoi(e) != 0;
 }
 
@@ -84,7 +84,7 @@ int Engine::chunk_images() const {
   if (!net_.is_cnv) return 32768;
   // keeps the ping-pong activations inside the 126 MB L2 (largest: layer 0's output, 7 200 / 14 400 B per image, which exists
   // only on the LOP3+POPC path; with layers 0+1 fused the largest is 1 568 / 3 136 B per image)
-  if (core_ == 1 && fuse01_) return net_.L[1].out_mode == OUT_TERN ? 8192 : 16384;
+  if (core_ >= 1 && fuse01_) return net_.L[1].out_mode == OUT_TERN ? 8192 : 16384;
   return net_.L[1].out_mode == OUT_TERN ? 2048 : 4096;
 }
 
@@ -111,7 +111,7 @@ int Engine::ensure_devices() {
   }
   // buffers are sized for the largest chunk either core selection may use (set_core can change between calls)
   int chunk = 0;
-  { const int c0 = core_; core_ = 0; chunk = chunk_images(); core_ = 1; chunk = std::max(chunk, chunk_images()); core_ = c0; }
+  { const int c0 = core_; core_ = 0; chunk = chunk_images(); core_ = 2; chunk = std::max(chunk, chunk_images()); core_ = c0; }
   const size_t aw = act_words_per_image(net_);
   const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
   for (int id : dev_ids_) {
@@ -152,11 +152,13 @@ int Engine::ensure_devices() {
       const bool l0 = net_.is_cnv && i == 0;
       D.wp = (uint32_t*)alloc(l0 ? (size_t)64 * 8 * 4 : (size_t)l.wbits * D.kwords * l.N * 4);
       D.w8 = nullptr;
+      D.w4 = nullptr;
       D.thr_tc = nullptr;
       if (!l0) {  // operands of the tensor-core path
         D.w8 = (int8_t*)alloc((size_t)l.N * D.kpad);
+        D.w4 = (uint8_t*)alloc((size_t)l.N * D.kpad / 2);
         D.thr_tc = (int32_t*)alloc((size_t)l.N * 2 * 4);
-        if (!D.w8 || !D.thr_tc) { err_ = "cudaMalloc failed"; return -1; }
+        if (!D.w8 || !D.w4 || !D.thr_tc) { err_ = "cudaMalloc failed"; return -1; }
       }
       D.thr = (int32_t*)alloc((size_t)l.N * 2 * 4);
       D.wf = d->wf[i];
@@ -264,7 +266,7 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
   int launches = 0;
   const bool per_layer = tap_acc != nullptr;  // when tapping, every layer writes its own buffer; else two ping-pong buffers
   int first_layer = 0;
-  if (core_ == 1 && net_.is_cnv && !per_layer && fuse01_) {  // layers 0+1 in one tensor-core kernel
+  if (core_ >= 1 && net_.is_cnv && !per_layer && fuse01_) {  // layers 0+1 in one tensor-core kernel
     ProfEv pe{nullptr, nullptr, 1, ds.id};
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
     if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, ds.d_status, s)) {
@@ -285,8 +287,9 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     ProfEv pe{nullptr, nullptr, i, ds.id};
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
     if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s);
-    else if (core_ == 1 && !tp && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
-    else if (core_ == 1 && !tp && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
+    else if (core_ == 2 && !tp && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
+    else if (core_ >= 1 && !tp && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
+    else if (core_ >= 1 && !tp && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
     else launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s);
     if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
     launches++;

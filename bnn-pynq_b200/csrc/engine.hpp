@@ -70,7 +70,8 @@ class Engine {
   void profile_enable(bool on) { profile_ = on; }
   int profile_collect(float* ms, int* launches);
 
-  // Compute core: 0 = LOP3+POPC CUDA-core kernels everywhere, 1 = tcgen05 tensor-core kernels where instantiated (default).
+  // Compute core: 0 = LOP3+POPC CUDA-core kernels everywhere, 1 = tcgen05 kind::i8 where instantiated,
+  // 2 (default) = tcgen05 kind::mxf4 (exact fp4) where instantiated, else kind::i8, else LOP3+POPC.
   void set_core(int c) { core_ = c; }
   int core() const { return core_; }
   int check_status(int slot);
@@ -95,7 +96,7 @@ class Engine {
   bool loaded_ = false;
   int last_launches_ = 0;
   bool profile_ = false;
-  int core_ = 1;
+  int core_ = 2;
   bool fuse01_ = true;
   struct ProfEv { cudaEvent_t a, b; int layer, dev; };
   std::vector<ProfEv> prof_;

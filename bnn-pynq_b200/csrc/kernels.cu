@@ -55,6 +55,22 @@ __global__ void k_repack_w8(DevLayer L) {
     L.w8[i] = k < d.K ? (int8_t)weight_value(weight_field(L.wf, d, n, k), d.wbits) : (int8_t)0;
   }
 }
+// e2m1 nibbles of the same values: 0 -> 0x0, +1 -> 0x2, -1 -> 0xA, -2 -> 0xC; even k in the low nibble
+__global__ void k_repack_w4(DevLayer L) {
+  const LayerDesc& d = L.d;
+  const int total = d.N * (L.kpad / 2);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int n = i / (L.kpad / 2), kb = i % (L.kpad / 2);
+    uint32_t byte = 0;
+    for (int h = 0; h < 2; h++) {
+      const int k = 2 * kb + h;
+      const int v = k < d.K ? weight_value(weight_field(L.wf, d, n, k), d.wbits) : 0;
+      const uint32_t nib = v == 0 ? 0x0u : (v == 1 ? 0x2u : (v == -1 ? 0xAu : 0xCu));
+      byte |= nib << (4 * h);
+    }
+    L.w4[i] = (uint8_t)byte;
+  }
+}
 __global__ void k_repack_thr(DevLayer L) {
   const LayerDesc& d = L.d;
   for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < d.N; n += gridDim.x * blockDim.x) {
@@ -68,6 +84,7 @@ void launch_repack(const DevLayer& L, int is_cnv_layer0, cudaStream_t s) {
   if (is_cnv_layer0) k_repack_l0<<<2, 256, 0, s>>>(L);
   else k_repack_planes<<<(L.d.wbits * L.kwords * L.d.N + 255) / 256, 256, 0, s>>>(L);
   if (L.w8) k_repack_w8<<<(L.d.N * L.kpad + 255) / 256, 256, 0, s>>>(L);
+  if (L.w4) k_repack_w4<<<(L.d.N * (L.kpad / 2) + 255) / 256, 256, 0, s>>>(L);
   k_repack_thr<<<(L.d.N + 255) / 256, 256, 0, s>>>(L);
   if (L.w8 && L.thr_tc) launch_thr_tc(L, s);
 }

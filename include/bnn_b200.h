@@ -103,8 +103,9 @@ int bnnb_last_launches(bnnb_ctx* c);
 int bnnb_in_bytes(bnnb_ctx* c);    /* per image: 3072 | 104 */
 int bnnb_out_bytes(bnnb_ctx* c);   /* per image: 128 | 8 */
 
-/* Compute core per layer: 0 = LOP3+POPC CUDA-core kernels everywhere; 1 (default) = tcgen05 kind::i8 tensor-core kernels for the
- * layers that have an instantiation (conv_tc.cu), LOP3+POPC for the rest.  $BNN_B200_CORE=popc|tc sets the default. */
+/* Compute core per layer: 0 = LOP3+POPC CUDA-core kernels everywhere; 1 = tcgen05 kind::i8 tensor-core kernels for the layers that
+ * have an instantiation; 2 (default) = tcgen05 kind::mxf4 (e2m1 operands, unit scales: an exact integer MMA at twice the int8
+ * rate) where instantiated, else kind::i8, else LOP3+POPC.  $BNN_B200_CORE=popc|i8|f4 sets the default. */
 int bnnb_set_core(bnnb_ctx* c, int core);
 
 /* Per-layer device timing (CUDA events on the launching stream around every layer kernel while enabled).
