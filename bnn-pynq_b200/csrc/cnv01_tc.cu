@@ -12,6 +12,7 @@
 // Warp-specialised CTA (one per SM): four warps run layer 1's epilogue on image i, four warps stage image i+1 (load, build P,
 // layer-0 MMAs, layer-0 epilogue into the other operand buffer), one warp issues layer 1's MMAs up to four tiles ahead.
 #include <climits>
+#include <type_traits>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
 
@@ -20,16 +21,19 @@ namespace {
 
 constexpr int L1_PITCH = 960;                 // 7 tiles * 128 + max shift 62, rounded to 8
 constexpr int L1_PLANE = L1_PITCH * 16;       // bytes per 16-channel plane
-constexpr int L1_A = 4 * L1_PLANE;            // one operand buffer (64 channels)
-constexpr int L1_B = 36 * 64 * 16;            // weights 64 x 576
+// layer 1 runs either on kind::i8 (16 channels per 16-byte plane row, 4 planes, 18 K=32 MMAs per tile) or on kind::mxf4 with
+// unit scales (F4: 32 e2m1 channels per plane row, 2 planes, 9 K=64 MMAs per tile: half the operand bytes, twice the MAC rate)
 constexpr int P_ROWS = 1120;                  // 8 tiles * 128 + 64 (ky = 2) + 32 (dummy chunk)
 constexpr int P_BYTES = P_ROWS * 16;
 constexpr int IMG_BYTES = 3072 + 64;          // image + slack for the 16-byte windows of the last rows
 constexpr int B0_BYTES = 4 * 64 * 16;         // layer-0 weights: 4 chunks x 64 rows x 16 bytes
 constexpr int L1_TILES = 7, L0_TILES = 8;
 
-template <int OUTM> struct Smem01 {
+template <int OUTM, bool F4> struct Smem01 {
   static constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
+  static constexpr int NPL = F4 ? 2 : 4;               // operand planes per buffer
+  static constexpr int L1_A = NPL * L1_PLANE;          // one operand buffer (64 channels)
+  static constexpr int L1_B = 9 * NPL * 64 * 16;       // weights 64 x 576
   static constexpr int BITS = L1_TILES * 128 * 2 * OPL * 4;
   static constexpr int OFF_A = 0, OFF_B1 = 2 * L1_A, OFF_P = OFF_B1 + L1_B, OFF_IMG = OFF_P + P_BYTES, OFF_B0 = OFF_IMG + IMG_BYTES,
                        OFF_BITS = OFF_B0 + B0_BYTES, OFF_THR = OFF_BITS + BITS, TOTAL = OFF_THR + 2 * 64 * 2 * 4;
@@ -44,12 +48,18 @@ __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 1
 //   abuf_empty[b] issuer -> half B   all layer-1 MMAs reading buffer b have completed  (tcgen05.commit)
 //   full[s]       issuer -> half A   accumulator slot s (of 4) holds a finished tile   (tcgen05.commit)
 //   empty[s]      half A -> issuer   slot s has been read out                          (4 arrivals, one per warp)
-template <int OUTM>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
+template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
 __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
                                                       int n_img, int* __restrict__ status) {
-  using S = Smem01<OUTM>;
+  using S = Smem01<OUTM, F4>;
+  constexpr int L1_A = S::L1_A;
+  constexpr uint32_t SF_COL = 384;  // TMEM columns of the unit scale factors (F4)
+  // FOLD: the thresholds are folded into the accumulators.  Every accumulator column n is pre-loaded with -(thr[n] + 1) (int32,
+  // layer 0) / -(thr[n] + 1/2) (fp32, layer 1) and all MMAs accumulate, so the sign bit of the result is the negated decision
+  // thr < acc and the epilogue is one funnel shift per channel instead of compare + select + insert.
+  constexpr bool FOLD = F4 && OUTM == OUT_BIT;
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t bar0[2], full[4], empty[4], abuf_full[2], abuf_empty[2];
+  __shared__ __align__(8) uint64_t bar0[2], full[4], empty[4], abuf_full[2], abuf_empty[2], pre_done;
   __shared__ uint32_t tmem_base;
   uint8_t* sB1 = smem + S::OFF_B1;
   uint8_t* sP = smem + S::OFF_P;
@@ -57,15 +67,16 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   uint8_t* sB0 = smem + S::OFF_B0;
   uint32_t* sbits = reinterpret_cast<uint32_t*>(smem + S::OFF_BITS);
   int32_t* sthr0 = reinterpret_cast<int32_t*>(smem + S::OFF_THR);  // layer 0: floor(thr/2)   [64][2]
-  int32_t* sthr1 = sthr0 + 128;                                    // layer 1: adjusted       [64][2]
+  int32_t* sthr1 = sthr0 + 128;                                    // layer 1: adjusted       [64][2] (F4: as float)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int role = warp < 4 ? 0 : (warp < 8 ? 1 : 2);              // 0: half A, 1: half B, 2: issuer
   const int ht = tid & 127, hw = warp & 3;  // thread / warp index inside the half; hw selects the TMEM lane quarter
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
-  for (int i = tid; i < 64 * 36; i += 288) {  // layer-1 weights -> chunk-major operand layout
+  for (int i = tid; i < 64 * 9 * S::NPL; i += 288) {  // layer-1 weights -> chunk-major operand layout
     const int n = i % 64, kc = i / 64;
-    *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = *reinterpret_cast<const uint4*>(L1.w8 + (size_t)n * L1.kpad + kc * 16);
+    const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
+    *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = *reinterpret_cast<const uint4*>(src + kc * 16);
   }
   for (int i = tid; i < 64 * 64; i += 288) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
@@ -76,7 +87,9 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   for (int i = tid; i < 128; i += 288) {
     const int t = L0.thr[i];
     sthr0[i] = t == INT_MAX ? INT_MAX : (t >> 1);  // thr < 2S  <=>  floor(thr/2) < S
-    sthr1[i] = L1.thr_tc[i];
+    const int t1 = L1.thr_tc[i];
+    if (F4) reinterpret_cast<float*>(sthr1)[i] = t1 == INT_MAX ? 3.0e38f : (float)t1;
+    else sthr1[i] = t1;
   }
   for (int i = tid; i < 2 * L1_A / 16; i += 288) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
   for (int i = tid; i < (P_BYTES + IMG_BYTES) / 16; i += 288) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
@@ -84,6 +97,7 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   if (tid == 0) {
     for (int i = 0; i < 2; i++) { tc::mbar_init(&bar0[i], 1); tc::mbar_init(&abuf_full[i], 128); tc::mbar_init(&abuf_empty[i], 1); }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4); }
+    tc::mbar_init(&pre_done, 1);
     tc::mbar_init_fence();
   }
   tc::fence_async_smem();
@@ -91,7 +105,13 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = tmem_base;
-  const uint32_t idesc = tc::make_idesc_i8(128, 64);
+  if (F4) {
+    if (warp < 4) tc::tmem_fill16(tmem + ((uint32_t)(warp * 32) << 16) + SF_COL, 0x7f7f7f7fu);  // every scale factor = 1.0 (ue8m0)
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+  }
+  const uint32_t idesc = tc::make_idesc_i8(128, 64), idesc_f4 = tc::make_idesc_mxf4(128, 64), sf = tmem + SF_COL;
   const uint32_t sA_u = tc::smem_u32(smem), sB1_u = tc::smem_u32(sB1), sP_u = tc::smem_u32(sP), sB0_u = tc::smem_u32(sB0);
   bool failed = false;
   const long long first = blockIdx.x, stride = gridDim.x;
@@ -103,7 +123,19 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     uint32_t ph0[2] = {0, 0};
     int thrA[64];  // first thresholds in registers: the epilogue's shared-memory traffic competes with the MMA operand reads
 #pragma unroll
-    for (int n = 0; n < 64; n++) thrA[n] = sthr0[2 * n];
+    for (int n = 0; n < 64; n++) thrA[n] = FOLD ? -(min(sthr0[2 * n], 1 << 26) + 1) : sthr0[2 * n];
+    auto preload0 = [&](int slot) {  // this warp's lane quarter of layer-0 accumulator `slot`
+      const uint32_t t0 = tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64;
+      tc::tmem_st32(t0, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
+      tc::tmem_st32(t0 + 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[32]));
+      tc::tmem_st_wait();
+    };
+    if (FOLD) {
+      preload0(0);
+      preload0(1);
+      tc::fence_before_sync();
+      half_sync(2);
+    }
     for (int k = 0; k < K; k++) {
       const long long img = first + (long long)k * stride;
       const int buf = k & 1;
@@ -124,7 +156,7 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         tc::fence_after_sync();
         const uint32_t acc = tmem + L0_ACC + (uint32_t)(t & 1) * 64;
         const uint32_t a0 = sP_u + (uint32_t)(t * 128) * 16;
-        tc::mma_i8(acc, tc::make_desc(a0, 32 * 16, 128), tc::make_desc(sB0_u, 64 * 16, 128), idesc, 0u);                          // ky 0, 1
+        tc::mma_i8(acc, tc::make_desc(a0, 32 * 16, 128), tc::make_desc(sB0_u, 64 * 16, 128), idesc, FOLD ? 1u : 0u);               // ky 0, 1
         tc::mma_i8(acc, tc::make_desc(a0 + 64 * 16, 32 * 16, 128), tc::make_desc(sB0_u + 2 * 64 * 16, 64 * 16, 128), idesc, 1u);  // ky 2, zero chunk
         tc::commit(&bar0[t & 1]);
       };
@@ -145,6 +177,36 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           uint32_t r[32];
           tc::tmem_ld32(trow + j * 32, r);
           tc::tmem_ld_wait();
+          if (FOLD) {  // the top nibble of acc - thr - 1 is 0xF (decision 0) or 0x0 (decision 1): e2m1 code = ~nibble & 0x2
+            uint32_t v[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              uint32_t wv = 0;
+#pragma unroll
+              for (int e = 7; e >= 0; e--) wv = __funnelshift_l(r[q * 8 + e], wv, 4);
+              v[q] = ~wv & 0x22222222u;
+            }
+            if (valid) *reinterpret_cast<uint4*>(sA + (size_t)j * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+          } else if (F4) {  // 32 channels = 32 e2m1 nibbles = one uint4 store into plane j: 1 -> 0x2, 0 -> 0x0, -1 -> 0xA
+            uint32_t v[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              uint32_t wv = 0;
+#pragma unroll
+              for (int e = 0; e < 8; e++) {
+                const int c = q * 8 + e, n = j * 32 + c;
+                const int s = (int)r[c];
+                if (OUTM == OUT_TERN) {
+                  const int cnt = (thrA[n] < s) + (sthr0[2 * n + 1] < s);  // 0, 1, 2 -> -1, 0, +1
+                  wv |= ((0x20Au >> (4 * cnt)) & 0xFu) << (4 * e);
+                } else {
+                  if (thrA[n] < s) wv |= 0x2u << (4 * e);
+                }
+              }
+              v[q] = wv;
+            }
+            if (valid) *reinterpret_cast<uint4*>(sA + (size_t)j * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+          } else
 #pragma unroll
           for (int c16 = 0; c16 < 2; c16++) {  // one 16-channel chunk = one uint4 store
             uint32_t v[4];
@@ -164,6 +226,7 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
             if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * j + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
           }
         }
+        if (FOLD) preload0(t & 1);
         tc::fence_before_sync();
         half_sync(2);  // both layer-0 accumulators are re-used two tiles later
       }
@@ -173,6 +236,7 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   } else if (role == 2) {
     // ================= issuer: layer-1 MMAs, up to four tiles ahead of the epilogue ========================================
     if (lane == 0) {
+      if (FOLD && !tc::mbar_wait(&pre_done, 0)) failed = true;  // layer-1 accumulators hold their pre-loads
       for (int k = 0; k < K; k++) {
         const int buf = k & 1;
         if (!tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
@@ -186,11 +250,17 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
 #pragma unroll
           for (int tap = 0; tap < 9; tap++) {
             const uint32_t off = (uint32_t)((tap / 3) * 30 + tap % 3 + t * 128) * 16;
-#pragma unroll
-            for (int s = 0; s < 2; s++) {
-              tc::mma_i8(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * L1_PLANE + off, L1_PLANE, 128),
-                         tc::make_desc(sB1_u + (uint32_t)((tap * 4 + 2 * s) * 64) * 16, 64 * 16, 128), idesc, firstmma ? 0u : 1u);
+            if (F4) {
+              tc::mma_mxf4(acc, tc::make_desc(sa_u + off, L1_PLANE, 128), tc::make_desc(sB1_u + (uint32_t)(tap * 2 * 64) * 16, 64 * 16, 128),
+                           idesc_f4, sf, sf, (FOLD || !firstmma) ? 1u : 0u);
               firstmma = false;
+            } else {
+#pragma unroll
+              for (int s = 0; s < 2; s++) {
+                tc::mma_i8(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * L1_PLANE + off, L1_PLANE, 128),
+                           tc::make_desc(sB1_u + (uint32_t)((tap * 4 + 2 * s) * 64) * 16, 64 * 16, 128), idesc, firstmma ? 0u : 1u);
+                firstmma = false;
+              }
             }
           }
           tc::commit(&full[slot]);
@@ -201,9 +271,24 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   } else {
     // ================= half A: layer-1 epilogue, 2x2 max-pool, store ========================================================
     constexpr int WPP = 2 * S::OPL;
-    int thrA[64];
+    using acc_t = typename std::conditional<F4, float, int>::type;  // kind::mxf4 accumulates in fp32 (exact: |acc| <= 1152)
+    const acc_t* sthr1t = reinterpret_cast<const acc_t*>(sthr1);
+    acc_t thrA[64];
 #pragma unroll
-    for (int n = 0; n < 64; n++) thrA[n] = sthr1[2 * n];
+    for (int n = 0; n < 64; n++) thrA[n] = FOLD ? (acc_t)(-((float)sthr1t[2 * n] + 0.5f)) : sthr1t[2 * n];
+    auto preload1 = [&](int slot) {
+      const uint32_t t0 = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64;
+      tc::tmem_st32(t0, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
+      tc::tmem_st32(t0 + 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[32]));
+      tc::tmem_st_wait();
+    };
+    if (FOLD) {
+#pragma unroll
+      for (int slot = 0; slot < 4; slot++) preload1(slot);
+      tc::fence_before_sync();
+      half_sync(1);
+      if (ht == 0) tc::mbar_arrive(&pre_done);
+    }
     for (int k = 0; k < K; k++) {
       const long long img = first + (long long)k * stride;
       for (int t = 0; t < L1_TILES; t++) {
@@ -218,19 +303,25 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           tc::tmem_ld32(trow + j * 32, r);
           tc::tmem_ld_wait();
           uint32_t b0 = 0, b1 = 0;
+          if (FOLD) {
+#pragma unroll
+            for (int c = 31; c >= 0; c--) b0 = __funnelshift_l(r[c], b0, 1);  // sign bits, channel c at bit c
+            b0 = ~b0;
+          } else
 #pragma unroll
           for (int c = 0; c < 32; c++) {
-            const int s = (int)r[c];
+            const acc_t s = F4 ? (acc_t)__uint_as_float(r[c]) : (acc_t)(int)r[c];
             const int t0 = thrA[j * 32 + c] < s;
             if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
-            else { const int t1 = sthr1[2 * (j * 32 + c) + 1] < s; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
+            else { const int t1 = sthr1t[2 * (j * 32 + c) + 1] < s; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
           }
           sbits[(size_t)m * WPP + j] = b0;
           if (OUTM == OUT_TERN) sbits[(size_t)m * WPP + 2 + j] = b1;
         }
+        if (FOLD) preload1(slot);
         tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read
+        if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
       }
       half_sync(1);
       // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
@@ -259,16 +350,23 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
 
 }  // namespace
 
-bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
-  if (n_img <= 0 || !L1.w8 || !L1.thr_tc || L0.d.N != 64 || L1.d.N != 64 || L1.d.ifm_dim != 30) return false;
+template <int OUTM, bool F4>
+static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int grid, int* status, cudaStream_t s) {
+  using S = Smem01<OUTM, F4>;
+  static_assert(S::TOTAL <= 226 * 1024, "shared memory budget");
+  cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+  k_cnv01_tc<OUTM, F4><<<grid, 288, S::TOTAL, s>>>(L0, L1, in, out, n_img, status);
+}
+
+bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int* status,
+                     cudaStream_t s) {
+  if (n_img <= 0 || !L1.w8 || !L1.w4 || !L1.thr_tc || L0.d.N != 64 || L1.d.N != 64 || L1.d.ifm_dim != 30) return false;
   const int grid = n_img < num_sms ? n_img : num_sms;
-  if (L1.d.out_mode == OUT_BIT) {
-    cudaFuncSetAttribute(k_cnv01_tc<OUT_BIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem01<OUT_BIT>::TOTAL);
-    k_cnv01_tc<OUT_BIT><<<grid, 288, Smem01<OUT_BIT>::TOTAL, s>>>(L0, L1, in, out, n_img, status);
-  } else {
-    cudaFuncSetAttribute(k_cnv01_tc<OUT_TERN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem01<OUT_TERN>::TOTAL);
-    k_cnv01_tc<OUT_TERN><<<grid, 288, Smem01<OUT_TERN>::TOTAL, s>>>(L0, L1, in, out, n_img, status);
-  }
+  const bool bit = L1.d.out_mode == OUT_BIT;
+  if (bit && fp4) launch01<OUT_BIT, true>(L0, L1, in, out, n_img, grid, status, s);
+  else if (bit) launch01<OUT_BIT, false>(L0, L1, in, out, n_img, grid, status, s);
+  else if (fp4) launch01<OUT_TERN, true>(L0, L1, in, out, n_img, grid, status, s);
+  else launch01<OUT_TERN, false>(L0, L1, in, out, n_img, grid, status, s);
   return true;
 }
 

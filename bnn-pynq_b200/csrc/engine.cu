@@ -269,7 +269,7 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
   if (core_ >= 1 && net_.is_cnv && !per_layer && fuse01_) {  // layers 0+1 in one tensor-core kernel
     ProfEv pe{nullptr, nullptr, 1, ds.id};
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
-    if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, ds.d_status, s)) {
+    if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, core_ == 2, ds.d_status, s)) {
       if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
       launches++;
       cur = bufs[1];

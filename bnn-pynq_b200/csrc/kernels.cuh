@@ -54,7 +54,7 @@ bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
 // K-streamed GEMM for FC / small conv layers (gemm_tc.cu)
 bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
 // fused CNV layers 0+1 (cnv01_tc.cu): int8 HWC image -> pooled, bit-packed layer-1 output
-bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
+bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int* status, cudaStream_t s);
 
 // ---- class decode for CNV (multi-image rule, foldedmv-offload.h:398-406) ----
 void launch_cnv_classes(const int16_t* scores, int n, int ncls, int* classes, cudaStream_t s);

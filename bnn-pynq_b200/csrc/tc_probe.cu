@@ -95,7 +95,7 @@ extern "C" int bnnb_tc_probe(const int8_t* A, const int8_t* B, int32_t* D, int r
 // ---- fp4 probe: A [rows_a][K/2] packed e2m1, B [N][K/2], D[m][n] = sum_k A[m+shift][k] * B[n][k] (fp32 -> int32) --------------
 namespace {
 __global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, int32_t* __restrict__ D,
-                                                       int rows_a, int N, int K, int shift, int reps, long long* cyc, int* status) {
+                                                       int rows_a, int N, int K, int shift, int reps, long long* cyc, int* status, const float* __restrict__ bias) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_base;
@@ -124,6 +124,18 @@ __global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict_
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
+  if (bias) {  // accumulator pre-loaded with bias[n] in every row; all MMAs then accumulate; D returns raw fp32 bits
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      uint32_t r[32];
+#pragma unroll
+      for (int j = 0; j < 32; j++) r[j] = __float_as_uint(bias[c0 + j]);
+      tmem_st32(tmem + ((uint32_t)(warp * 32) << 16) + c0, r);
+    }
+    tmem_st_wait();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+  }
   const uint32_t idesc = make_idesc_mxf4(128, N);
   long long t0 = 0, t1 = 0;
   if (threadIdx.x == 0) {
@@ -132,7 +144,7 @@ __global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict_
       for (int ks = 0; ks < K / 64; ks++) {
         const uint64_t ad = make_desc(smem_u32(sa) + (uint32_t)(2 * ks) * plane_a + (uint32_t)shift * 16, plane_a, 128);
         const uint64_t bd = make_desc(smem_u32(sb) + (uint32_t)(2 * ks) * plane_b, plane_b, 128);
-        mma_mxf4(tmem, ad, bd, idesc, sf, sf, (ks > 0 || rep > 0) ? 1u : 0u);
+        mma_mxf4(tmem, ad, bd, idesc, sf, sf, (ks > 0 || rep > 0 || bias) ? 1u : 0u);
       }
     commit(&bar);
   }
@@ -146,7 +158,7 @@ __global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict_
       tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, r);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 32; j++) D[(size_t)(warp * 32 + lane) * N + c0 + j] = __float2int_rn(__uint_as_float(r[j]));
+      for (int j = 0; j < 32; j++) D[(size_t)(warp * 32 + lane) * N + c0 + j] = bias ? (int32_t)r[j] : __float2int_rn(__uint_as_float(r[j]));
     }
   }
   fence_before_sync();
@@ -155,7 +167,13 @@ __global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict_
 }
 }  // namespace
 
+extern "C" int bnnb_tc_probe_fp4_bias(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles,
+                                      const float* bias);
 extern "C" int bnnb_tc_probe_fp4(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles) {
+  return bnnb_tc_probe_fp4_bias(A, B, D, rows_a, N, K, shift, reps, cycles, nullptr);
+}
+extern "C" int bnnb_tc_probe_fp4_bias(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles,
+                                      const float* bias) {
   if (N % 32 || N < 32 || N > 256 || K % 64 || rows_a < 128 + shift || rows_a % 8) return -1;
   const size_t smem = (size_t)(K / 32) * (rows_a + N) * 16;
   if (smem > 200 * 1024) return -1;
@@ -165,10 +183,12 @@ extern "C" int bnnb_tc_probe_fp4(const uint8_t* A, const uint8_t* B, int32_t* D,
   cudaMalloc(&dB, (size_t)N * K / 2); cudaMalloc(&dD, (size_t)128 * N * 4); cudaMalloc(&dC, 8); cudaMalloc(&dS, 4);
   cudaMemcpy(dA, A, (size_t)rows_a * K / 2, cudaMemcpyHostToDevice);
   cudaMemcpy(dB, B, (size_t)N * K / 2, cudaMemcpyHostToDevice);
+  float* dBias = nullptr;
+  if (bias) { cudaMalloc(&dBias, (size_t)N * 4); cudaMemcpy(dBias, bias, (size_t)N * 4, cudaMemcpyHostToDevice); }
   cudaMemset(dS, 0, 4);
   cudaMemset(dD, 0xff, (size_t)128 * N * 4);
   cudaFuncSetAttribute(k_tc_probe_fp4, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-  k_tc_probe_fp4<<<1, 128, smem>>>(dA, dB, dD, rows_a, N, K, shift, reps, dC, dS);
+  k_tc_probe_fp4<<<1, 128, smem>>>(dA, dB, dD, rows_a, N, K, shift, reps, dC, dS, dBias);
   cudaError_t e = cudaDeviceSynchronize();
   int st = 0;
   if (e == cudaSuccess) {
@@ -176,6 +196,7 @@ extern "C" int bnnb_tc_probe_fp4(const uint8_t* A, const uint8_t* B, int32_t* D,
     cudaMemcpy(cycles, dC, 8, cudaMemcpyDeviceToHost);
     cudaMemcpy(&st, dS, 4, cudaMemcpyDeviceToHost);
   }
+  if (dBias) cudaFree(dBias);
   cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(dC); cudaFree(dS);
   return e == cudaSuccess ? st : -1;
 }

@@ -68,3 +68,26 @@ def test_fp4_probe_rate_report():
         out[N] = (c - c1) / (mmas - K // 64)
         assert np.array_equal(D, reps * (A.astype(np.int32) @ B.astype(np.int32).T))
     print("tcgen05 kind::mxf4 M=128 K=64 cycles per MMA by N:", out, "MAC/clk/SM:", {n: 128 * n * 64 / v for n, v in out.items()})
+
+
+@pytest.mark.parametrize("N,K", [(64, 576), (128, 1152), (32, 2304)])
+def test_fp4_accumulator_preload_is_exact(N, K):
+    """Threshold folding: the accumulator is pre-loaded with -(thr + 1/2) and the MMAs accumulate on top; the sign bit of the
+    result is then the (negated) threshold decision.  Checks that fp32 accumulation stays exact with pre-loads as large as a
+    16-bit threshold field (+-32768.5) and for the 3e38 'never fires' sentinel."""
+    from bnn import native
+    rng = np.random.default_rng(N + K)
+    A = rng.integers(-1, 2, (128, K))
+    B = rng.integers(-2, 2, (N, K))
+    thr = rng.integers(-600, 600, N).astype(np.float64)
+    thr[:8] = [32767, -32768, 65535, -65536, 0, -1, 1, 40000]
+    bias = (-(thr + 0.5)).astype(np.float32)
+    bias[8] = -3.0e38
+    D, _ = native.tc_probe_fp4(A, B, 0, 1, bias=bias)
+    S = (A.astype(np.int64) @ B.astype(np.int64).T).astype(np.float64)
+    want = S + bias.astype(np.float64)[None, :]
+    ok = np.ones(N, bool); ok[8] = False
+    assert np.array_equal(D[:, ok].astype(np.float64), want[:, ok])
+    assert np.all(D[:, 8] < -1e38)
+    # the decision itself
+    assert np.array_equal(~np.signbit(D[:, ok]), S[:, ok] > thr[None, ok])
