@@ -9,8 +9,9 @@
 // image (m = y*32 + x: the 3x3x3 window row ky of pixel (y,x) is the first 9 bytes of P[m + 32*ky]).  K is laid out as
 // [ky][16]: k = ky*16 + (kx*3 + c) with zero weights for the 7 trailing bytes of each ky and for the whole 4th chunk, so
 // one tile needs two K=32 MMAs whose A descriptors differ only by a start shift (LBO = 32 rows).
-// Warp-specialised CTA (one per SM): four warps run layer 1's epilogue on image i, four warps stage image i+1 (load, build P,
-// layer-0 MMAs, layer-0 epilogue into the other operand buffer), one warp issues layer 1's MMAs up to four tiles ahead.
+// Warp-specialised CTA (one per SM, 320 threads): four warps run layer 1's epilogue on image i, four warps stage image i+1
+// (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one warp issues layer 1's MMAs up to four tiles
+// ahead, one warp prefetches images by TMA bulk copy two images ahead and issues layer 0's MMAs up to three tiles ahead.
 #include <climits>
 #include <type_traits>
 #include "kernels.cuh"
@@ -35,31 +36,37 @@ template <int OUTM, bool F4> struct Smem01 {
   static constexpr int L1_A = NPL * L1_PLANE;          // one operand buffer (64 channels)
   static constexpr int L1_B = 9 * NPL * 64 * 16;       // weights 64 x 576
   static constexpr int BITS = L1_TILES * 128 * 2 * OPL * 4;
-  static constexpr int OFF_A = 0, OFF_B1 = 2 * L1_A, OFF_P = OFF_B1 + L1_B, OFF_IMG = OFF_P + P_BYTES, OFF_B0 = OFF_IMG + IMG_BYTES,
+  static constexpr int OFF_A = 0, OFF_B1 = 2 * L1_A, OFF_P = OFF_B1 + L1_B, OFF_IMG = OFF_P + 2 * P_BYTES, OFF_B0 = OFF_IMG + 2 * IMG_BYTES,
                        OFF_BITS = OFF_B0 + B0_BYTES, OFF_THR = OFF_BITS + BITS, TOTAL = OFF_THR + 2 * 64 * 2 * 4;
 };
 
 __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 
-// Warp roles (288 threads): warps 0-3 = half A (layer-1 epilogue, pool, store), warps 4-7 = half B (stage the next image:
-// load, window plane, layer-0 MMAs + epilogue into the other operand buffer), warp 8 = layer-1 MMA issuer.
-// The three roles are decoupled by mbarriers only (no CTA-wide barrier in steady state):
-//   abuf_full[b]  half B -> issuer   operand buffer b holds a staged image            (128 arrivals)
-//   abuf_empty[b] issuer -> half B   all layer-1 MMAs reading buffer b have completed  (tcgen05.commit)
-//   full[s]       issuer -> half A   accumulator slot s (of 4) holds a finished tile   (tcgen05.commit)
-//   empty[s]      half A -> issuer   slot s has been read out                          (4 arrivals, one per warp)
+// Warp roles (320 threads): warps 0-3 = half A (layer-1 epilogue, pool, store), warps 4-7 = half B (window plane, layer-0
+// epilogue into the other operand buffer), warp 8 = layer-1 MMA issuer, warp 9 = image prefetch (TMA) + layer-0 MMA issuer.
+// The roles are decoupled by mbarriers only (no CTA-wide barrier in steady state):
+//   img_full[b]   TMA    -> half B   image buffer b holds an image                      (expect_tx 3072 bytes)
+//   p_full[b]     half B -> warp 9   window plane b is built (and image buffer b free)  (128 arrivals)
+//   p_empty[b]    warp 9 -> half B   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
+//   f0[s], e0[s]  warp 9 <-> half B  layer-0 accumulator slot s (of 3) full / read out   (commit / 4 arrivals)
+//   abuf_full[b]  half B -> warp 8   layer-1 operand buffer b holds a staged image      (128 arrivals)
+//   abuf_empty[b] warp 8 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
+//   full[s], empty[s] warp 8 <-> half A  layer-1 accumulator slot s (of 4) full / read out
 template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
-__global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
+__global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
                                                       int n_img, int* __restrict__ status) {
   using S = Smem01<OUTM, F4>;
   constexpr int L1_A = S::L1_A;
-  constexpr uint32_t SF_COL = 384;  // TMEM columns of the unit scale factors (F4)
+  constexpr uint32_t SF_COL = 448;  // TMEM columns of the unit scale factors (F4)
+  constexpr uint32_t L0_ACC = 256;  // TMEM columns: layer-1 slots 0,64,128,192; layer-0 slots 256,320,384
+  constexpr int L0_SLOTS = 3;
   // FOLD: the thresholds are folded into the accumulators.  Every accumulator column n is pre-loaded with -(thr[n] + 1) (int32,
   // layer 0) / -(thr[n] + 1/2) (fp32, layer 1) and all MMAs accumulate, so the sign bit of the result is the negated decision
   // thr < acc and the epilogue is one funnel shift per channel instead of compare + select + insert.
   constexpr bool FOLD = F4 && OUTM == OUT_BIT;
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t bar0[2], full[4], empty[4], abuf_full[2], abuf_empty[2], pre_done;
+  __shared__ __align__(8) uint64_t full[4], empty[4], abuf_full[2], abuf_empty[2], f0[L0_SLOTS], e0[L0_SLOTS], p_full[2], p_empty[2], img_full[2],
+      pre_done;
   __shared__ uint32_t tmem_base;
   uint8_t* sB1 = smem + S::OFF_B1;
   uint8_t* sP = smem + S::OFF_P;
@@ -69,35 +76,39 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   int32_t* sthr0 = reinterpret_cast<int32_t*>(smem + S::OFF_THR);  // layer 0: floor(thr/2)   [64][2]
   int32_t* sthr1 = sthr0 + 128;                                    // layer 1: adjusted       [64][2] (F4: as float)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int role = warp < 4 ? 0 : (warp < 8 ? 1 : 2);              // 0: half A, 1: half B, 2: issuer
+  const int role = warp < 4 ? 0 : (warp < 8 ? 1 : warp - 6);       // 0: half A, 1: half B, 2: layer-1 issuer, 3: loader + layer-0 issuer
   const int ht = tid & 127, hw = warp & 3;  // thread / warp index inside the half; hw selects the TMEM lane quarter
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
-  for (int i = tid; i < 64 * 9 * S::NPL; i += 288) {  // layer-1 weights -> chunk-major operand layout
+  for (int i = tid; i < 64 * 9 * S::NPL; i += 320) {  // layer-1 weights -> chunk-major operand layout
     const int n = i % 64, kc = i / 64;
     const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
     *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = *reinterpret_cast<const uint4*>(src + kc * 16);
   }
-  for (int i = tid; i < 64 * 64; i += 288) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
+  for (int i = tid; i < 64 * 64; i += 320) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
     sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)v;
   }
-  for (int i = tid; i < 128; i += 288) {
+  for (int i = tid; i < 128; i += 320) {
     const int t = L0.thr[i];
     sthr0[i] = t == INT_MAX ? INT_MAX : (t >> 1);  // thr < 2S  <=>  floor(thr/2) < S
     const int t1 = L1.thr_tc[i];
     if (F4) reinterpret_cast<float*>(sthr1)[i] = t1 == INT_MAX ? 3.0e38f : (float)t1;
     else sthr1[i] = t1;
   }
-  for (int i = tid; i < 2 * L1_A / 16; i += 288) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
-  for (int i = tid; i < (P_BYTES + IMG_BYTES) / 16; i += 288) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < 2 * L1_A / 16; i += 320) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
+  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += 320) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
-    for (int i = 0; i < 2; i++) { tc::mbar_init(&bar0[i], 1); tc::mbar_init(&abuf_full[i], 128); tc::mbar_init(&abuf_empty[i], 1); }
+    for (int i = 0; i < 2; i++) {
+      tc::mbar_init(&abuf_full[i], 128); tc::mbar_init(&abuf_empty[i], 1);
+      tc::mbar_init(&p_full[i], 128); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
+    }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4); }
-    tc::mbar_init(&pre_done, 1);
+    for (int i = 0; i < L0_SLOTS; i++) { tc::mbar_init(&f0[i], 1); tc::mbar_init(&e0[i], 4); }
+    tc::mbar_init(&pre_done, 2);
     tc::mbar_init_fence();
   }
   tc::fence_async_smem();
@@ -116,11 +127,9 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   bool failed = false;
   const long long first = blockIdx.x, stride = gridDim.x;
   const int K = first < n_img ? (int)((n_img - first + stride - 1) / stride) : 0;  // images of this CTA
-  constexpr uint32_t L0_ACC = 256;  // TMEM columns: layer-1 slots 0,64,128,192; layer-0 accumulators 256,320
 
   if (role == 1) {
-    // ================= half B: stage image k into operand buffer k&1 (layer 0) ==========================================
-    uint32_t ph0[2] = {0, 0};
+    // ================= half B: window plane of image k, then layer-0 epilogue into layer-1 operand buffer k&1 =================
     int thrA[64];  // first thresholds in registers: the epilogue's shared-memory traffic competes with the MMA operand reads
 #pragma unroll
     for (int n = 0; n < 64; n++) thrA[n] = FOLD ? -(min(sthr0[2 * n], 1 << 26) + 1) : sthr0[2 * n];
@@ -131,47 +140,46 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       tc::tmem_st_wait();
     };
     if (FOLD) {
-      preload0(0);
-      preload0(1);
+#pragma unroll
+      for (int slot = 0; slot < L0_SLOTS; slot++) preload0(slot);
       tc::fence_before_sync();
       half_sync(2);
+      if (ht == 0) tc::mbar_arrive(&pre_done);
     }
-    for (int k = 0; k < K; k++) {
-      const long long img = first + (long long)k * stride;
-      const int buf = k & 1;
-      const uint4* src = reinterpret_cast<const uint4*>(in + img * 3072);
-      for (int i = ht; i < 192; i += 128) reinterpret_cast<uint4*>(sImg)[i] = __ldg(src + i);
-      half_sync(2);
-      const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg);
+    // window plane of image kk: runs one image ahead of the epilogue so that layer 0's MMAs never wait for it
+    auto build_p = [&](int kk) {
+      const int buf = kk & 1;
+      const uint32_t par = (uint32_t)(kk >> 1) & 1;
+      if (!tc::mbar_wait(&img_full[buf], par)) failed = true;
+      if (kk >= 2 && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
+      const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
+      uint8_t* sPk = sP + (size_t)buf * P_BYTES;
+#pragma unroll 3
       for (int m = ht; m < 1024 + 64; m += 128) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
         const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
         uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
         if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
-        *reinterpret_cast<uint4*>(sP + (size_t)m * 16) =
+        *reinterpret_cast<uint4*>(sPk + (size_t)m * 16) =
             make_uint4(__funnelshift_r(x0, x1, sh), __funnelshift_r(x1, x2, sh), __funnelshift_r(x2, x3, sh), __funnelshift_r(x3, x4, sh));
       }
       tc::fence_async_smem();
-      half_sync(2);
-      auto issue0 = [&](int t) {  // thread 128
-        tc::fence_after_sync();
-        const uint32_t acc = tmem + L0_ACC + (uint32_t)(t & 1) * 64;
-        const uint32_t a0 = sP_u + (uint32_t)(t * 128) * 16;
-        tc::mma_i8(acc, tc::make_desc(a0, 32 * 16, 128), tc::make_desc(sB0_u, 64 * 16, 128), idesc, FOLD ? 1u : 0u);               // ky 0, 1
-        tc::mma_i8(acc, tc::make_desc(a0 + 64 * 16, 32 * 16, 128), tc::make_desc(sB0_u + 2 * 64 * 16, 64 * 16, 128), idesc, 1u);  // ky 2, zero chunk
-        tc::commit(&bar0[t & 1]);
-      };
-      // the layer-1 MMAs that read this buffer two images ago must have completed before it is overwritten
-      if (k >= 2 && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
+      tc::mbar_arrive(&p_full[buf]);
+    };
+    if (K > 0) build_p(0);
+    for (int k = 0; k < K; k++) {
+      const int buf = k & 1;
+      const uint32_t par = (uint32_t)(k >> 1) & 1;
+      if (k + 1 < K) build_p(k + 1);
+      // the layer-1 MMAs that read this operand buffer two images ago must have completed before it is overwritten
+      if (k >= 2 && !tc::mbar_wait(&abuf_empty[buf], par ^ 1)) failed = true;
       uint8_t* sA = smem + (size_t)buf * L1_A;
-      if (ht == 0) issue0(0);
       for (int t = 0; t < L0_TILES; t++) {
-        if (ht == 0 && t + 1 < L0_TILES) issue0(t + 1);
-        if (!tc::mbar_wait(&bar0[t & 1], ph0[t & 1])) failed = true;
-        ph0[t & 1] ^= 1;
+        const int g = k * L0_TILES + t, slot = g % L0_SLOTS, u = g / L0_SLOTS;
+        if (!tc::mbar_wait(&f0[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
         const bool valid = x < 30 && y < 30;
-        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)(t & 1) * 64;
+        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64;
 #pragma unroll
         for (int j = 0; j < 2; j++) {
           uint32_t r[32];
@@ -206,37 +214,68 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
               v[q] = wv;
             }
             if (valid) *reinterpret_cast<uint4*>(sA + (size_t)j * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
-          } else
+          } else {
 #pragma unroll
-          for (int c16 = 0; c16 < 2; c16++) {  // one 16-channel chunk = one uint4 store
-            uint32_t v[4];
+            for (int c16 = 0; c16 < 2; c16++) {  // one 16-channel chunk = one uint4 store
+              uint32_t v[4];
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-              uint32_t wv = 0;
+              for (int q = 0; q < 4; q++) {
+                uint32_t wv = 0;
 #pragma unroll
-              for (int e = 0; e < 4; e++) {
-                const int c = c16 * 16 + q * 4 + e, n = j * 32 + c;
-                const int s = (int)r[c];
-                int val = thrA[n] < s;                                          // {0,1}
-                if (OUTM == OUT_TERN) val = val + (sthr0[2 * n + 1] < s) - 1;   // {-1,0,+1}
-                wv |= (uint32_t)(val & 0xff) << (8 * e);
+                for (int e = 0; e < 4; e++) {
+                  const int c = c16 * 16 + q * 4 + e, n = j * 32 + c;
+                  const int s = (int)r[c];
+                  int val = thrA[n] < s;                                          // {0,1}
+                  if (OUTM == OUT_TERN) val = val + (sthr0[2 * n + 1] < s) - 1;   // {-1,0,+1}
+                  wv |= (uint32_t)(val & 0xff) << (8 * e);
+                }
+                v[q] = wv;
               }
-              v[q] = wv;
+              if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * j + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
             }
-            if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * j + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
           }
         }
-        if (FOLD) preload0(t & 1);
+        if (FOLD) preload0(slot);
         tc::fence_before_sync();
-        half_sync(2);  // both layer-0 accumulators are re-used two tiles later
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&e0[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
       }
       tc::fence_async_smem();  // operand planes were written through the generic proxy and are read by the async proxy (MMA)
       tc::mbar_arrive(&abuf_full[buf]);
     }
+  } else if (role == 3) {
+    // ================= loader + layer-0 issuer ================================================================================
+    if (lane == 0) {
+      for (int k = 0; k < 2 && k < K; k++) {
+        tc::mbar_expect_tx(&img_full[k], 3072);
+        tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
+      }
+      if (FOLD && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
+      for (int k = 0; k < K; k++) {
+        const int buf = k & 1;
+        if (!tc::mbar_wait(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        if (k + 2 < K) {  // image buffer `buf` has been consumed: prefetch image k+2 into it
+          tc::mbar_expect_tx(&img_full[buf], 3072);
+          tc::bulk_g2s(sImg + (size_t)buf * IMG_BYTES, in + (first + (long long)(k + 2) * stride) * 3072, 3072, &img_full[buf]);
+        }
+        const uint32_t p_u = sP_u + (uint32_t)buf * P_BYTES;
+        for (int t = 0; t < L0_TILES; t++) {
+          const int g = k * L0_TILES + t, slot = g % L0_SLOTS, u = g / L0_SLOTS;
+          if (u >= 1 && !tc::mbar_wait(&e0[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          tc::fence_after_sync();
+          const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
+          const uint32_t a0 = p_u + (uint32_t)(t * 128) * 16;
+          tc::mma_i8(acc, tc::make_desc(a0, 32 * 16, 128), tc::make_desc(sB0_u, 64 * 16, 128), idesc, FOLD ? 1u : 0u);               // ky 0, 1
+          tc::mma_i8(acc, tc::make_desc(a0 + 64 * 16, 32 * 16, 128), tc::make_desc(sB0_u + 2 * 64 * 16, 64 * 16, 128), idesc, 1u);  // ky 2, zero chunk
+          tc::commit(&f0[slot]);
+        }
+        tc::commit(&p_empty[buf]);
+      }
+    }
   } else if (role == 2) {
     // ================= issuer: layer-1 MMAs, up to four tiles ahead of the epilogue ========================================
     if (lane == 0) {
-      if (FOLD && !tc::mbar_wait(&pre_done, 0)) failed = true;  // layer-1 accumulators hold their pre-loads
+      if (FOLD && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
       for (int k = 0; k < K; k++) {
         const int buf = k & 1;
         if (!tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
@@ -307,13 +346,14 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
 #pragma unroll
             for (int c = 31; c >= 0; c--) b0 = __funnelshift_l(r[c], b0, 1);  // sign bits, channel c at bit c
             b0 = ~b0;
-          } else
+          } else {
 #pragma unroll
-          for (int c = 0; c < 32; c++) {
-            const acc_t s = F4 ? (acc_t)__uint_as_float(r[c]) : (acc_t)(int)r[c];
-            const int t0 = thrA[j * 32 + c] < s;
-            if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
-            else { const int t1 = sthr1t[2 * (j * 32 + c) + 1] < s; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
+            for (int c = 0; c < 32; c++) {
+              const acc_t s = F4 ? (acc_t)__uint_as_float(r[c]) : (acc_t)(int)r[c];
+              const int t0 = thrA[j * 32 + c] < s;
+              if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
+              else { const int t1 = sthr1t[2 * (j * 32 + c) + 1] < s; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
+            }
           }
           sbits[(size_t)m * WPP + j] = b0;
           if (OUTM == OUT_TERN) sbits[(size_t)m * WPP + 2 + j] = b1;
@@ -355,7 +395,7 @@ static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
   using S = Smem01<OUTM, F4>;
   static_assert(S::TOTAL <= 226 * 1024, "shared memory budget");
   cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-  k_cnv01_tc<OUTM, F4><<<grid, 288, S::TOTAL, s>>>(L0, L1, in, out, n_img, status);
+  k_cnv01_tc<OUTM, F4><<<grid, 320, S::TOTAL, s>>>(L0, L1, in, out, n_img, status);
 }
 
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int* status,
