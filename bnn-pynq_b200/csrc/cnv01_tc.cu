@@ -150,8 +150,8 @@ __global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     auto build_p = [&](int kk) {
       const int buf = kk & 1;
       const uint32_t par = (uint32_t)(kk >> 1) & 1;
-      if (!tc::mbar_wait(&img_full[buf], par)) failed = true;
-      if (kk >= 2 && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
+      if (!failed && !tc::mbar_wait(&img_full[buf], par)) failed = true;
+      if (kk >= 2 && !failed && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
       const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
       uint8_t* sPk = sP + (size_t)buf * P_BYTES;
 #pragma unroll 3
@@ -171,11 +171,11 @@ __global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       const uint32_t par = (uint32_t)(k >> 1) & 1;
       if (k + 1 < K) build_p(k + 1);
       // the layer-1 MMAs that read this operand buffer two images ago must have completed before it is overwritten
-      if (k >= 2 && !tc::mbar_wait(&abuf_empty[buf], par ^ 1)) failed = true;
+      if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], par ^ 1)) failed = true;
       uint8_t* sA = smem + (size_t)buf * L1_A;
       for (int t = 0; t < L0_TILES; t++) {
         const int g = k * L0_TILES + t, slot = g % L0_SLOTS, u = g / L0_SLOTS;
-        if (!tc::mbar_wait(&f0[slot], (uint32_t)u & 1)) failed = true;
+        if (!failed && !tc::mbar_wait(&f0[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
         const bool valid = x < 30 && y < 30;
@@ -250,10 +250,10 @@ __global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         tc::mbar_expect_tx(&img_full[k], 3072);
         tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
       }
-      if (FOLD && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
+      if (FOLD && !failed && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
       for (int k = 0; k < K; k++) {
         const int buf = k & 1;
-        if (!tc::mbar_wait(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        if (!failed && !tc::mbar_wait(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
         if (k + 2 < K) {  // image buffer `buf` has been consumed: prefetch image k+2 into it
           tc::mbar_expect_tx(&img_full[buf], 3072);
           tc::bulk_g2s(sImg + (size_t)buf * IMG_BYTES, in + (first + (long long)(k + 2) * stride) * 3072, 3072, &img_full[buf]);
@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         const uint32_t p_u = sP_u + (uint32_t)buf * P_BYTES;
         for (int t = 0; t < L0_TILES; t++) {
           const int g = k * L0_TILES + t, slot = g % L0_SLOTS, u = g / L0_SLOTS;
-          if (u >= 1 && !tc::mbar_wait(&e0[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          if (u >= 1 && !failed && !tc::mbar_wait(&e0[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
           const uint32_t a0 = p_u + (uint32_t)(t * 128) * 16;
@@ -275,14 +275,14 @@ __global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   } else if (role == 2) {
     // ================= issuer: layer-1 MMAs, up to four tiles ahead of the epilogue ========================================
     if (lane == 0) {
-      if (FOLD && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
+      if (FOLD && !failed && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
       for (int k = 0; k < K; k++) {
         const int buf = k & 1;
-        if (!tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
         const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
         for (int t = 0; t < L1_TILES; t++) {
           const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-          if (u >= 1 && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * 64;
           bool firstmma = true;
@@ -332,7 +332,7 @@ __global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       const long long img = first + (long long)k * stride;
       for (int t = 0; t < L1_TILES; t++) {
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-        if (!tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
+        if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64;

@@ -4,10 +4,10 @@
 // integer MVAU (mvau.hpp:86-172, activations.hpp:139-147).  Evidence: tests/test_gpu_tcgen05.py::test_fp4_probe_*.
 //
 // Same implicit GEMM as conv_tc.cu (operand planes of 16 bytes = 32 channels per pixel, tap (ky,kx) = descriptor start shifted by
-// (ky*IDIM+kx) pixels), now one K=64 MMA per 64 input channels per tap, and a warp-specialised CTA (one per SM):
-//   warps 0-3  epilogue: TMEM -> threshold -> bit rows in smem -> (pool) -> global
-//   warps 4-7  expander: bit-packed activations of group g+1 (global, L2) -> fp4 operand planes, other buffer
-//   warp  8    MMA issuer, up to three tiles ahead (three TMEM accumulator slots)
+// (ky*IDIM+kx) pixels), now one K=64 MMA per 64 input channels per tap, and a warp-specialised CTA (one per SM, 384 threads):
+//   warps 0-3, 4-7  two epilogue groups, one per half of the output channels: TMEM -> decision bits -> global (pooled: via smem)
+//   warps 8-10      expander: bit-packed activations of group g+1 (global, L2) -> fp4 operand planes, other buffer
+//   warp  11        MMA issuer, up to three tiles ahead (three TMEM accumulator slots)
 // decoupled by mbarriers only: abuf_full / abuf_empty per operand buffer, full / empty per accumulator slot.
 #include <climits>
 #include "kernels.cuh"
@@ -23,7 +23,7 @@ struct F4Cfg {
   static constexpr int KC = C / 32;  // 16-byte chunks (32 fp4 channels) per tap
   static constexpr int PLANE = PITCH * 16, A_BYTES = KC * PLANE, B_BYTES = 9 * KC * N * 16;
   static constexpr int IPL = INM == IN_TERN ? 2 : 1, OPL = OUTM == OUT_TERN ? 2 : 1, NW = N / 32, WPP = NW * OPL;
-  static constexpr int BITS_BYTES = TILES * 128 * WPP * 4;
+  static constexpr int BITS_BYTES = POOL ? TILES * 128 * WPP * 4 : 0;  // staging rows (pooled layers only)
   static constexpr int OFF_B = 2 * A_BYTES, OFF_BITS = OFF_B + B_BYTES, OFF_THR = OFF_BITS + BITS_BYTES, SMEM = OFF_THR + 2 * N * 4;
   static constexpr int SLOTS = 384 / N > 4 ? 4 : 384 / N;  // accumulator slots below the scale-factor columns
   static constexpr int SF_COL = 384, PD = POOL ? OD / 2 : OD;
@@ -56,32 +56,38 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
 }
 
 template <int C, int N, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
-__global__ void __launch_bounds__(288, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
+__global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                      int* __restrict__ status) {
   using Cfg = F4Cfg<C, N, IDIM, OD, POOL, G, INM, OUTM>;
+  static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t full[4], empty[4], abuf_full[2], abuf_empty[2];
   __shared__ uint32_t tmem_base;
   uint8_t* sb = smem + Cfg::OFF_B;
-  uint32_t* sbits = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BITS);
   float* sthr = reinterpret_cast<float*>(smem + Cfg::OFF_THR);  // [2][N]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int role = warp < 4 ? 0 : (warp < 8 ? 1 : 2), ht = tid & 127, hw = warp & 3;
+  const int role = warp < 8 ? 0 : (warp < 11 ? 1 : 2), ht = tid & 127, hw = warp & 3;
+  const int eg = (warp >> 2) & 1;  // epilogue group (role 0): output channels [eg*N/2, (eg+1)*N/2)
+  constexpr int NWG = Cfg::NW / 2;  // 32-channel words per epilogue group
   constexpr int KCT = 9 * Cfg::KC;
+  // FOLD (1-bit outputs): accumulators are pre-loaded with -(thr + 1/2) and every MMA accumulates; the sign bit of the result is
+  // the negated decision, harvested with one funnel shift per channel (see cnv01_tc.cu)
+  constexpr bool FOLD = OUTM == OUT_BIT;
 
-  for (int i = tid; i < N * KCT; i += 288) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
+  for (int i = tid; i < N * KCT; i += 384) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
     const int n = i % N, kc = i / N;
     *reinterpret_cast<uint4*>(sb + ((size_t)kc * N + n) * 16) = *reinterpret_cast<const uint4*>(L.w4 + (size_t)n * (L.kpad / 2) + kc * 16);
   }
-  for (int i = tid; i < 2 * N; i += 288) {
+  for (int i = tid; i < 2 * N; i += 384) {
     const int t = L.thr_tc[i];
-    sthr[(i & 1) * N + (i >> 1)] = t == INT_MAX ? 3.0e38f : (float)t;
+    const float tf = t == INT_MAX ? 3.0e38f : (float)t;
+    sthr[(i & 1) * N + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
   }
-  for (int i = tid; i < 2 * Cfg::A_BYTES / 16; i += 288) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // pad pixels stay 0
+  for (int i = tid; i < 2 * Cfg::A_BYTES / 16; i += 384) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // pad pixels stay 0
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
-    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], 128); tc::mbar_init(&abuf_empty[i], 1); }
-    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4); }
+    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], 96); tc::mbar_init(&abuf_empty[i], 1); }
+    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
     tc::mbar_init_fence();
   }
   tc::fence_async_smem();
@@ -90,6 +96,26 @@ __global__ void __launch_bounds__(288, 1) k_conv_f4(DevLayer L, const uint32_t* 
   tc::fence_after_sync();
   const uint32_t tmem = tmem_base;
   if (warp < 4) tc::tmem_fill16(tmem + ((uint32_t)(warp * 32) << 16) + Cfg::SF_COL, 0x7f7f7f7fu);  // every scale factor = 1.0 (ue8m0)
+  const uint32_t sthr_u = tc::smem_u32(sthr);
+  auto preload = [&](int slot) {  // this warp's lane quarter and channel half of accumulator `slot` <- -(thr + 1/2), from shared memory
+    const uint32_t t0 = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N;
+#pragma unroll
+    for (int jj = 0; jj < NWG; jj++) {
+      const int j = eg * NWG + jj;
+      uint32_t v[32];
+#pragma unroll
+      for (int q = 0; q < 8; q++) {
+        // volatile: keeps the 128 loop-invariant values out of registers
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v[4 * q]), "=r"(v[4 * q + 1]), "=r"(v[4 * q + 2]), "=r"(v[4 * q + 3])
+                     : "r"(sthr_u + (uint32_t)(j * 32 + q * 4) * 4));
+      }
+      tc::tmem_st32(t0 + j * 32, v);
+    }
+    tc::tmem_st_wait();
+  };
+  if (FOLD && warp < 8)
+    for (int slot = 0; slot < Cfg::SLOTS; slot++) preload(slot);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -104,9 +130,10 @@ __global__ void __launch_bounds__(288, 1) k_conv_f4(DevLayer L, const uint32_t* 
     constexpr int CW = C / 32;
     for (int k = 0; k < K; k++) {
       const int img0 = ((int)blockIdx.x + k * (int)gridDim.x) * G, buf = k & 1;
-      if (k >= 2 && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
+      if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
       uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
-      for (int i = ht; i < Cfg::ROWS * CW; i += 128) {
+#pragma unroll 4
+      for (int i = tid - 256; i < Cfg::ROWS * CW; i += 96) {
         const int j = i % CW, m = i / CW, gi = m / Cfg::PXI;
         uint32_t w0 = 0, w1 = 0;
         if (img0 + gi < n_img) {
@@ -124,11 +151,11 @@ __global__ void __launch_bounds__(288, 1) k_conv_f4(DevLayer L, const uint32_t* 
     if (lane == 0) {
       for (int k = 0; k < K; k++) {
         const int buf = k & 1;
-        if (!tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
         const uint32_t sa_u = sa_u0 + (uint32_t)buf * Cfg::A_BYTES;
         for (int t = 0; t < Cfg::TILES; t++) {
           const int gt = k * Cfg::TILES + t, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
-          if (u >= 1 && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * N;
           bool firstmma = true;
@@ -138,7 +165,8 @@ __global__ void __launch_bounds__(288, 1) k_conv_f4(DevLayer L, const uint32_t* 
 #pragma unroll
             for (int s = 0; s < Cfg::KC / 2; s++) {
               tc::mma_mxf4(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * Cfg::PLANE + off, Cfg::PLANE, 128),
-                           tc::make_desc(sb_u + (uint32_t)((tap * Cfg::KC + 2 * s) * N) * 16, N * 16, 128), idesc, sf, sf, firstmma ? 0u : 1u);
+                           tc::make_desc(sb_u + (uint32_t)((tap * Cfg::KC + 2 * s) * N) * 16, N * 16, 128), idesc, sf, sf,
+                           (FOLD || !firstmma) ? 1u : 0u);
               firstmma = false;
             }
           }
@@ -148,61 +176,94 @@ __global__ void __launch_bounds__(288, 1) k_conv_f4(DevLayer L, const uint32_t* 
       }
     }
   } else {
-    // ---- epilogue, pool, store ---------------------------------------------------------------------------------------------
+    // ---- epilogue groups: every tile, channels [eg*N/2, (eg+1)*N/2) --------------------------------------------------------------
+    uint32_t* sbits = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BITS);
+    constexpr int NW = Cfg::NW, WPP = Cfg::WPP;
     for (int k = 0; k < K; k++) {
       const int img0 = ((int)blockIdx.x + k * (int)gridDim.x) * G;
       for (int t = 0; t < Cfg::TILES; t++) {
         const int gt = k * Cfg::TILES + t, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
-        if (!tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
+        if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
-        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N;
+        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N + (uint32_t)eg * (N / 2);
+        uint32_t b0[NWG], b1[NWG];
+        uint32_t r[2][32];
+        tc::tmem_ld32(trow, r[0]);
 #pragma unroll
-        for (int j = 0; j < Cfg::NW; j++) {
-          uint32_t r[32];
-          tc::tmem_ld32(trow + j * 32, r);
-          tc::tmem_ld_wait();
-          uint32_t b0 = 0, b1 = 0;
+        for (int j = 0; j < NWG; j++) {
+          tc::tmem_ld_wait_dep(r[j & 1]);
+          if (j + 1 < NWG) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
+          uint32_t w0 = 0, w1 = 0;
+          if (FOLD) {
 #pragma unroll
-          for (int c = 0; c < 32; c++) {
-            const float s = __uint_as_float(r[c]);
-            const int t0 = sthr[j * 32 + c] < s;
-            if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
-            else { const int t1 = sthr[N + j * 32 + c] < s; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
+            for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
+            w0 = ~w0;
+          } else {
+            const float* th = sthr + eg * (N / 2) + j * 32;
+#pragma unroll
+            for (int c = 0; c < 32; c++) {
+              const float s = __uint_as_float(r[j & 1][c]);
+              const int t0 = th[c] < s;
+              const int t1 = th[N + c] < s;
+              w0 |= (uint32_t)(1 ^ t0 ^ t1) << c;
+              w1 |= (uint32_t)(t0 & t1) << c;
+            }
           }
-          sbits[(size_t)m * Cfg::WPP + j] = b0;
-          if (OUTM == OUT_TERN) sbits[(size_t)m * Cfg::WPP + Cfg::NW + j] = b1;
+          b0[j] = w0;
+          b1[j] = w1;
         }
+        if (FOLD) preload(slot);
         tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&empty[slot]);
-      }
-      hsync(1);
-      for (int i = ht; i < G * Cfg::PD * Cfg::PD * Cfg::NW; i += 128) {
-        const int j = i % Cfg::NW, op = (i / Cfg::NW) % (Cfg::PD * Cfg::PD), gi = i / (Cfg::NW * Cfg::PD * Cfg::PD);
-        if (img0 + gi >= n_img) continue;
-        const int oy = op / Cfg::PD, ox = op % Cfg::PD;
-        uint32_t o0, o1 = 0;
+        if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
+        uint32_t* row = nullptr;
         if (POOL) {
-          const uint32_t* r00 = sbits + (size_t)(gi * Cfg::PXI + (2 * oy) * IDIM + 2 * ox) * Cfg::WPP;
-          const uint32_t *r01 = r00 + Cfg::WPP, *r10 = r00 + (size_t)IDIM * Cfg::WPP, *r11 = r10 + Cfg::WPP;
-          if (OUTM == OUT_BIT) {
-            o0 = r00[j] | r01[j] | r10[j] | r11[j];
-          } else {
-            const uint32_t P = r00[Cfg::NW + j] | r01[Cfg::NW + j] | r10[Cfg::NW + j] | r11[Cfg::NW + j];
-            const uint32_t M = (r00[j] & ~r00[Cfg::NW + j]) & (r01[j] & ~r01[Cfg::NW + j]) & (r10[j] & ~r10[Cfg::NW + j]) & (r11[j] & ~r11[Cfg::NW + j]);
-            o0 = P | M; o1 = P;
-          }
-        } else {
-          const uint32_t* r = sbits + (size_t)(gi * Cfg::PXI + oy * IDIM + ox) * Cfg::WPP;
-          o0 = r[j];
-          if (OUTM == OUT_TERN) o1 = r[Cfg::NW + j];
+          row = sbits + (size_t)m * WPP;
+        } else {  // straight to global: one output pixel (half of its channels) per thread
+          const int gi = m / Cfg::PXI, rem = m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
+          if (m < Cfg::ROWS && y < OD && x < OD && img0 + gi < n_img) row = out + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * WPP;
         }
-        uint32_t* dst = out + ((size_t)(img0 + gi) * (Cfg::PD * Cfg::PD) + op) * Cfg::WPP;
-        dst[j] = o0;
-        if (OUTM == OUT_TERN) dst[Cfg::NW + j] = o1;
+        if (row) {
+          if (NWG == 2) {
+            *reinterpret_cast<uint2*>(row + eg * NWG) = make_uint2(b0[0], b0[1]);
+            if (OUTM == OUT_TERN) *reinterpret_cast<uint2*>(row + NW + eg * NWG) = make_uint2(b1[0], b1[1]);
+          } else {
+#pragma unroll
+            for (int q = 0; q < NWG / 4; q++) {
+              reinterpret_cast<uint4*>(row + eg * NWG)[q] = make_uint4(b0[4 * q], b0[4 * q + 1], b0[4 * q + 2], b0[4 * q + 3]);
+              if (OUTM == OUT_TERN) reinterpret_cast<uint4*>(row + NW + eg * NWG)[q] = make_uint4(b1[4 * q], b1[4 * q + 1], b1[4 * q + 2], b1[4 * q + 3]);
+            }
+          }
+        }
       }
-      hsync(1);
+      if (POOL) {
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        constexpr int PP = Cfg::PD * Cfg::PD;
+        for (int i = tid; i < G * PP; i += 256) {  // one pooled output pixel per thread
+          const int gi = i / PP, op = i - gi * PP, oy = op / Cfg::PD, ox = op - oy * Cfg::PD;
+          if (img0 + gi >= n_img) continue;
+          const uint4* r00 = reinterpret_cast<const uint4*>(sbits + (size_t)(gi * Cfg::PXI + (2 * oy) * IDIM + 2 * ox) * WPP);
+          const uint4 *r01 = r00 + WPP / 4, *r10 = r00 + (size_t)IDIM * (WPP / 4), *r11 = r10 + WPP / 4;
+          uint4* dst = reinterpret_cast<uint4*>(out + ((size_t)(img0 + gi) * PP + op) * WPP);
+          auto or4 = [](uint4 a, uint4 b) { return make_uint4(a.x | b.x, a.y | b.y, a.z | b.z, a.w | b.w); };
+          auto and4 = [](uint4 a, uint4 b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); };
+          auto andn4 = [](uint4 a, uint4 b) { return make_uint4(a.x & ~b.x, a.y & ~b.y, a.z & ~b.z, a.w & ~b.w); };
+#pragma unroll
+          for (int q = 0; q < NW / 4; q++) {
+            if (OUTM == OUT_BIT) {
+              dst[q] = or4(or4(r00[q], r01[q]), or4(r10[q], r11[q]));
+            } else {  // max over {-1,0,+1}: +1 if any +1; else -1 only if all four are -1
+              constexpr int H = NW / 4;
+              const uint4 P = or4(or4(r00[H + q], r01[H + q]), or4(r10[H + q], r11[H + q]));
+              const uint4 M = and4(and4(andn4(r00[q], r00[H + q]), andn4(r01[q], r01[H + q])), and4(andn4(r10[q], r10[H + q]), andn4(r11[q], r11[H + q])));
+              dst[q] = or4(P, M);
+              dst[H + q] = P;
+            }
+          }
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");  // the next image group overwrites the staging rows
+      }
     }
   }
   if (failed && status) *status = 1;
@@ -219,7 +280,7 @@ bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img,
   auto kern = k_conv_f4<C, N, IDIM, OD, POOL, G, INM, OUTM>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
   const int ngroups = (n_img + G - 1) / G;
-  kern<<<ngroups < num_sms ? ngroups : num_sms, 288, Cfg::SMEM, s>>>(L, in, out, n_img, status);
+  kern<<<ngroups < num_sms ? ngroups : num_sms, 384, Cfg::SMEM, s>>>(L, in, out, n_img, status);
   return true;
 }
 
@@ -235,7 +296,7 @@ bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
   }
   if (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) {
     if (a1) return launch_cfg<128, 128, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<128, 128, 12, 10, true, 5, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a2) return launch_cfg<128, 128, 12, 10, true, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
   }
   return false;
 }

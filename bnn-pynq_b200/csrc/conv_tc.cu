@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(128) k_conv_tc(DevLayer L, const uint32_t* __r
     if (tid == 0) issue_tile(0);
     for (int t = 0; t < Cfg::TILES; t++) {
       if (tid == 0 && t + 1 < Cfg::TILES) issue_tile(t + 1);
-      if (!tc::mbar_wait(&bar[t & 1], phase[t & 1])) failed = true;
+      if (!failed && !tc::mbar_wait(&bar[t & 1], phase[t & 1])) failed = true;
       phase[t & 1] ^= 1;
       tc::fence_after_sync();
       const int m = t * 128 + warp * 32 + lane;

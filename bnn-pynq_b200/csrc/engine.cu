@@ -271,6 +271,10 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
     if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, core_ == 2, ds.d_status, s)) {
       if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
+      {
+        const cudaError_t le = cudaGetLastError();
+        if (le != cudaSuccess) { err_ = std::string("fused layer 0+1 launch: ") + cudaGetErrorString(le); return -1; }
+      }
       launches++;
       cur = bufs[1];
       first_layer = 2;
@@ -292,6 +296,10 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     else if (core_ >= 1 && !tp && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
     else launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s);
     if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
+    {  // a launch that the device refuses (resources, configuration) must not pass silently
+      const cudaError_t le = cudaGetLastError();
+      if (le != cudaSuccess) { err_ = "layer " + std::to_string(i) + " launch: " + cudaGetErrorString(le); return -1; }
+    }
     launches++;
     cur = out;
   }

@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __r
     uint8_t* sa = smem + (size_t)(s & 1) * BUF;
     uint8_t* sb = sa + A_SLAB;
     if (s >= 2) {  // the MMAs that read this buffer two slabs ago must have completed
-      if (!tc::mbar_wait(&bar[s & 1], ph[s & 1])) failed = true;
+      if (!failed && !tc::mbar_wait(&bar[s & 1], ph[s & 1])) failed = true;
       ph[s & 1] ^= 1;
     }
     // weights: rows n0..n0+N, K bytes [64s, 64s+64) -> 4 chunk planes of N x 16 bytes
@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __r
   }
   // drain: the last one or two commits
   for (int s = (nslab >= 2 ? nslab - 2 : 0); s < nslab; s++) {
-    if (!tc::mbar_wait(&bar[s & 1], ph[s & 1])) failed = true;
+    if (!failed && !tc::mbar_wait(&bar[s & 1], ph[s & 1])) failed = true;
     ph[s & 1] ^= 1;
   }
   tc::fence_after_sync();
