@@ -153,12 +153,14 @@ int Engine::ensure_devices() {
       D.wp = (uint32_t*)alloc(l0 ? (size_t)64 * 8 * 4 : (size_t)l.wbits * D.kwords * l.N * 4);
       D.w8 = nullptr;
       D.w4 = nullptr;
+      D.w4s = nullptr;
       D.thr_tc = nullptr;
       if (!l0) {  // operands of the tensor-core path
         D.w8 = (int8_t*)alloc((size_t)l.N * D.kpad);
         D.w4 = (uint8_t*)alloc((size_t)l.N * D.kpad / 2);
+        D.w4s = (uint8_t*)alloc((size_t)l.N * D.kpad / 2);
         D.thr_tc = (int32_t*)alloc((size_t)l.N * 2 * 4);
-        if (!D.w8 || !D.w4 || !D.thr_tc) { err_ = "cudaMalloc failed"; return -1; }
+        if (!D.w8 || !D.w4 || !D.w4s || !D.thr_tc) { err_ = "cudaMalloc failed"; return -1; }
       }
       D.thr = (int32_t*)alloc((size_t)l.N * 2 * 4);
       D.wf = d->wf[i];
@@ -292,6 +294,7 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
     if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s);
     else if (core_ == 2 && !tp && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
+    else if (core_ == 2 && !tp && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
     else if (core_ >= 1 && !tp && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
     else if (core_ >= 1 && !tp && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
     else launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s);

@@ -1,0 +1,314 @@
+// Fully-connected layers (and the 3x3 -> 1x1 convolution, which is one) on tcgen05.mma kind::mxf4 with unit scales: the exact
+// small-integer MMA of conv_f4.cu, K-streamed.  Rows = images (tiles of 128), columns = output channels in blocks of NB.
+//
+// Warp-specialised persistent CTA (384 threads), decoupled by mbarriers only:
+//   warps 0-3  epilogue: TMEM -> decision bits / scores -> global
+//   warps 4-9  expander: bit-packed activations of tile i+1 -> e2m1 operand planes [K/32][128 rows][16 B], handed to the issuer
+//              in four K quarters so that the MMAs of a tile start while its tail is still being expanded
+//   warp  10   loader: weight slabs (NB x 64 e2m1 = NB*32 bytes, pre-arranged in operand layout by k_repack_w4s) by TMA bulk
+//              copy into a ring of R slots, running ahead of the MMAs
+//   warp  11   issuer: one K=64 MMA per slab; accumulator slots (3) let the next channel block start while one drains
+// Replaces StreamingFCLayer_Batch / ConvLayer_Batch + ThresholdsActivation / PassThroughActivation for these layers
+// (fclayer.h:83-111, convlayer.h:85-121, activations.hpp:85-148).
+#include <climits>
+#include "kernels.cuh"
+#include "tcgen05.cuh"
+
+namespace bnnb {
+namespace {
+
+constexpr int GF_RING = 8;
+
+// 8 bits -> 8 nibbles (bit i at position 4i)
+__device__ __forceinline__ uint32_t gspread8(uint32_t x) {
+  x = (x | (x << 12)) & 0x000f000fu;
+  x = (x | (x << 6)) & 0x03030303u;
+  x = (x | (x << 3)) & 0x11111111u;
+  return x;
+}
+// 32 channels -> 16 bytes of e2m1.  IN_XNOR: bit -> {0, +1}; IN_BIN: bit -> {-1, +1}; IN_TERN: (nz, pos) -> {-1, 0, +1}
+template <int INM>
+__device__ __forceinline__ uint4 gexpand(uint32_t w0, uint32_t w1) {
+  uint32_t v[4];
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const uint32_t a = gspread8((w0 >> (8 * q)) & 0xff);
+    if (INM == IN_TERN) v[q] = (a << 1) | (gspread8(((w0 & ~w1) >> (8 * q)) & 0xff) << 3);
+    else if (INM == IN_BIN) v[q] = 0xAAAAAAAAu ^ (a << 3);  // 1 -> 0x2, 0 -> 0xA
+    else v[q] = a << 1;
+  }
+  return make_uint4(v[0], v[1], v[2], v[3]);
+}
+
+struct GemmGeom {
+  int K, N, kch, ks, nblk, nbuf;  // kch = K/32 chunks, ks = K/64 slabs per channel block, nbuf = operand buffers (1 or 2)
+  int cw, ipl;                    // words per pixel and plane (C/32), input planes
+  int a_bytes, off_ring, off_thr;
+};
+
+template <int NB, int INM, int OUTM>
+__global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
+                                                     int* __restrict__ status) {
+  constexpr int SLAB = NB * 32, SLOTS = 3, SF_COL = 384, NW = NB / 32, EXP = 192, U = 4;  // EXP expander threads, U loads in flight each
+  constexpr bool FOLD = OUTM == OUT_BIT;
+  constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t full[SLOTS], empty[SLOTS], a_part[2][4], a_empty[2], ring_full[GF_RING], ring_empty[GF_RING];
+  __shared__ uint32_t tmem_base;
+  uint8_t* ring = smem + g.off_ring;
+  float* sthr = reinterpret_cast<float*>(smem + g.off_thr);  // [2][N]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int role = warp < 4 ? 0 : (warp < 10 ? 1 : warp - 8);  // 0 epilogue, 1 expander, 2 loader, 3 issuer
+  const int hw = warp & 3;
+
+  for (int i = tid; i < 2 * g.N; i += 384) {
+    const int t = L.thr_tc[i];
+    float tf = t == INT_MAX ? 3.0e38f : (float)t;
+    if (OUTM == OUT_SCORE) tf = (float)t;
+    sthr[(i & 1) * g.N + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
+  if (tid == 0) {
+    for (int i = 0; i < 2; i++) {
+      tc::mbar_init(&a_empty[i], 1);
+      for (int q = 0; q < 4; q++) tc::mbar_init(&a_part[i][q], EXP);
+    }
+    for (int i = 0; i < SLOTS; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4); }
+    for (int i = 0; i < GF_RING; i++) { tc::mbar_init(&ring_full[i], 1); tc::mbar_init(&ring_empty[i], 1); }
+    tc::mbar_init_fence();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_base;
+  if (warp < 4) tc::tmem_fill16(tmem + ((uint32_t)(warp * 32) << 16) + SF_COL, 0x7f7f7f7fu);  // every scale factor = 1.0 (ue8m0)
+  const uint32_t sthr_u = tc::smem_u32(sthr);
+  auto preload = [&](int slot, int nb) {  // this warp's lane quarter of accumulator `slot` <- -(thr + 1/2) of channel block nb
+    const uint32_t t0 = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * NB;
+#pragma unroll
+    for (int j = 0; j < NW; j++) {
+      uint32_t v[32];
+#pragma unroll
+      for (int q = 0; q < 8; q++)
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v[4 * q]), "=r"(v[4 * q + 1]), "=r"(v[4 * q + 2]), "=r"(v[4 * q + 3])
+                     : "r"(sthr_u + (uint32_t)(nb * NB + j * 32 + q * 4) * 4));
+      tc::tmem_st32(t0 + j * 32, v);
+    }
+    tc::tmem_st_wait();
+  };
+  const int ntiles = (n_img + 127) / 128;
+  const int T = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;  // tiles of this CTA
+  // FOLD: the accumulator slot of the j-th channel block overall (j = tile_local * nblk + nb) holds that block's pre-load
+  if (FOLD && warp < 4)
+    for (int j = 0; j < SLOTS && j < T * g.nblk; j++) preload(j, j % g.nblk);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t idesc = tc::make_idesc_mxf4(128, NB);
+  const uint32_t sa_u0 = tc::smem_u32(smem), ring_u = tc::smem_u32(ring), sf = tmem + SF_COL;
+  bool failed = false;
+
+  if (role == 1) {
+    // ---- expander: tile tl -> operand buffer tl % nbuf ------------------------------------------------------------------------
+    const int et = tid - 128;  // 0..191
+    const size_t img_words = (size_t)g.kch * g.ipl;
+    const int total = 128 * g.ks;  // items: (row, pair of chunks = one K=64 slab), row fastest: conflict-free 16-byte stores
+    for (int tl = 0; tl < T; tl++) {
+      const int buf = tl % g.nbuf, use = tl / g.nbuf;
+      if (use >= 1 && !failed && !tc::mbar_wait(&a_empty[buf], (uint32_t)(use - 1) & 1)) failed = true;
+      uint8_t* sa = smem + (size_t)buf * g.a_bytes;
+      const long long img0 = ((long long)blockIdx.x + (long long)tl * gridDim.x) * 128;
+      int qn = 0;
+      for (int base = et; qn < 4; base += EXP * U) {
+        uint2 w0[U], w1[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {  // U independent 8-byte loads in flight
+          const int i = base + u * EXP, row = i & 127, j = (i >> 7) * 2;
+          w0[u] = make_uint2(0, 0);
+          w1[u] = make_uint2(0, 0);
+          if (i < total && img0 + row < n_img) {
+            const int p = j / g.cw, c = j - p * g.cw;
+            const uint32_t* src = in + (size_t)(img0 + row) * img_words + (size_t)p * g.cw * g.ipl + c;
+            w0[u] = __ldg(reinterpret_cast<const uint2*>(src));
+            if (INM == IN_TERN) w1[u] = __ldg(reinterpret_cast<const uint2*>(src + g.cw));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+          const int i = base + u * EXP, row = i & 127, j = (i >> 7) * 2;
+          if (i < total) {
+            *reinterpret_cast<uint4*>(sa + (size_t)j * 2048 + row * 16) = gexpand<INM>(w0[u].x, w1[u].x);
+            *reinterpret_cast<uint4*>(sa + (size_t)(j + 1) * 2048 + row * 16) = gexpand<INM>(w0[u].y, w1[u].y);
+          }
+        }
+        // this thread's next item is base + EXP*U: every quarter that ends at or before it is complete as far as this thread goes
+        while (qn < 4 && base + EXP * U >= 128 * (((qn + 1) * g.ks) / 4)) {
+          tc::fence_async_smem();
+          tc::mbar_arrive(&a_part[buf][qn]);
+          qn++;
+        }
+      }
+    }
+  } else if (role == 2) {
+    // ---- loader: weight slabs in MMA order, R slots ahead ----------------------------------------------------------------------
+    if (lane == 0) {
+      const long long total = (long long)T * g.nblk * g.ks;
+      const int per_tile = g.nblk * g.ks;
+      for (long long gs = 0; gs < total; gs++) {
+        const int r = (int)(gs % GF_RING);
+        const long long use = gs / GF_RING;
+        if (use >= 1 && !failed && !tc::mbar_wait(&ring_empty[r], (uint32_t)(use - 1) & 1)) failed = true;
+        const int q = (int)(gs % per_tile);  // = nb * ks + slab: exactly the block order of the re-packed weights
+        tc::mbar_expect_tx(&ring_full[r], SLAB);
+        tc::bulk_g2s(ring + (size_t)r * SLAB, L.w4s + (size_t)q * SLAB, SLAB, &ring_full[r]);
+      }
+    }
+  } else if (role == 3) {
+    // ---- issuer ---------------------------------------------------------------------------------------------------------
+    if (lane == 0) {
+      long long gs = 0;
+      for (int tl = 0; tl < T; tl++) {
+        const int buf = tl % g.nbuf, use = tl / g.nbuf;
+        const uint32_t sa_u = sa_u0 + (uint32_t)buf * g.a_bytes;
+        for (int nb = 0; nb < g.nblk; nb++) {
+          const int gb = tl * g.nblk + nb, slot = gb % SLOTS, u = gb / SLOTS;
+          if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          tc::fence_after_sync();
+          const uint32_t acc = tmem + (uint32_t)slot * NB;
+          int qn = 0;
+          for (int s = 0; s < g.ks; s++, gs++) {
+            const int r = (int)(gs % GF_RING);
+            // slab s lies in quarter q with ((q+1)*ks)/4 > s: wait for the quarters up to it (first channel block of a tile only)
+            while (nb == 0 && qn < 4 && (s >= (qn * g.ks) / 4)) {
+              if (!failed && !tc::mbar_wait(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
+              tc::fence_after_sync();
+              qn++;
+            }
+            if (!failed && !tc::mbar_wait(&ring_full[r], (uint32_t)(gs / GF_RING) & 1)) failed = true;
+            tc::mma_mxf4(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * 2048, 2048, 128), tc::make_desc(ring_u + (uint32_t)r * SLAB, NB * 16, 128), idesc,
+                         sf, sf, (FOLD || s > 0) ? 1u : 0u);
+            tc::commit(&ring_empty[r]);
+          }
+          tc::commit(&full[slot]);
+        }
+        tc::commit(&a_empty[buf]);
+      }
+    }
+  } else {
+    // ---- epilogue: one image (row) per thread, every channel block ---------------------------------------------------------------
+    const int nwt = g.N / 32;
+    for (int tl = 0; tl < T; tl++) {
+      const long long img = ((long long)blockIdx.x + (long long)tl * gridDim.x) * 128 + hw * 32 + lane;
+      for (int nb = 0; nb < g.nblk; nb++) {
+        const int gb = tl * g.nblk + nb, slot = gb % SLOTS, u = gb / SLOTS;
+        if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
+        tc::fence_after_sync();
+        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * NB;
+        uint32_t b0[NW], b1[NW];
+        uint32_t r[2][32];
+        tc::tmem_ld32(trow, r[0]);
+#pragma unroll
+        for (int j = 0; j < NW; j++) {
+          tc::tmem_ld_wait_dep(r[j & 1]);
+          if (j + 1 < NW) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
+          const float* th = sthr + nb * NB + j * 32;
+          uint32_t w0 = 0, w1 = 0;
+          if (OUTM == OUT_SCORE) {  // PassThroughActivation<ap_uint<16>>: (S + offset) mod 2^16, offset = #negative weights for 1-bit inputs
+            if (img < n_img) {
+              int16_t* o16 = reinterpret_cast<int16_t*>(out) + (size_t)img * g.N + nb * NB + j * 32;
+#pragma unroll
+              for (int c = 0; c < 32; c += 8) {
+                uint32_t pk[4];
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                  const uint32_t lo = (uint32_t)(__float2int_rn(__uint_as_float(r[j & 1][c + 2 * e])) + __float2int_rn(th[c + 2 * e])) & 0xffff;
+                  const uint32_t hi = (uint32_t)(__float2int_rn(__uint_as_float(r[j & 1][c + 2 * e + 1])) + __float2int_rn(th[c + 2 * e + 1])) & 0xffff;
+                  pk[e] = lo | (hi << 16);
+                }
+                *reinterpret_cast<uint4*>(o16 + c) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              }
+            }
+          } else if (FOLD) {
+#pragma unroll
+            for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
+            w0 = ~w0;
+          } else {
+#pragma unroll
+            for (int c = 0; c < 32; c++) {
+              const float s = __uint_as_float(r[j & 1][c]);
+              const int t0 = th[c] < s;
+              const int t1 = th[g.N + c] < s;
+              w0 |= (uint32_t)(1 ^ t0 ^ t1) << c;
+              w1 |= (uint32_t)(t0 & t1) << c;
+            }
+          }
+          b0[j] = w0;
+          b1[j] = w1;
+        }
+        if (FOLD && gb + SLOTS < T * g.nblk) preload(slot, (gb + SLOTS) % g.nblk);
+        tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
+        if (OUTM != OUT_SCORE && img < n_img) {
+          uint32_t* dst = out + (size_t)img * nwt * OPL + nb * NW;
+#pragma unroll
+          for (int j = 0; j < NW; j += 2) {
+            *reinterpret_cast<uint2*>(dst + j) = make_uint2(b0[j], b0[j + 1]);
+            if (OUTM == OUT_TERN) *reinterpret_cast<uint2*>(dst + nwt + j) = make_uint2(b1[j], b1[j + 1]);
+          }
+        }
+      }
+    }
+  }
+  if (failed && status) *status = 1;
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+template <int NB, int INM, int OUTM>
+bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+  const LayerDesc& d = L.d;
+  GemmGeom g;
+  g.K = d.K; g.N = d.N; g.kch = d.K / 32; g.ks = d.K / 64; g.nblk = d.N / NB;
+  g.cw = d.ifm_ch / 32; g.ipl = INM == IN_TERN ? 2 : 1;
+  g.a_bytes = g.kch * 2048;
+  const int ring = GF_RING * NB * 32, thr = 2 * d.N * 4, budget = 224 * 1024;
+  g.nbuf = 2 * g.a_bytes + ring + thr <= budget ? 2 : 1;
+  if (g.nbuf * g.a_bytes + ring + thr > budget) return false;
+  g.off_ring = g.nbuf * g.a_bytes;
+  g.off_thr = g.off_ring + ring;
+  const int smem = g.off_thr + thr;
+  auto kern = k_gemm_f4<NB, INM, OUTM>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const int ntiles = (n_img + 127) / 128;
+  kern<<<ntiles < num_sms ? ntiles : num_sms, 384, smem, s>>>(L, g, in, out, n_img, status);
+  return true;
+}
+
+template <int NB>
+bool launch_nb(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+  const int im = L.d.in_mode, om = L.d.out_mode;
+  if (im == IN_XNOR && om == OUT_BIT) return launch_g<NB, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
+  if (im == IN_XNOR && om == OUT_SCORE) return launch_g<NB, IN_XNOR, OUT_SCORE>(L, in, out, n_img, num_sms, status, s);
+  if (im == IN_BIN && om == OUT_TERN) return launch_g<NB, IN_BIN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+  if (im == IN_TERN && om == OUT_TERN) return launch_g<NB, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+  if (im == IN_TERN && om == OUT_SCORE) return launch_g<NB, IN_TERN, OUT_SCORE>(L, in, out, n_img, num_sms, status, s);
+  if (im == IN_TERN && om == OUT_BIT) return launch_g<NB, IN_TERN, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
+  return false;
+}
+
+}  // namespace
+
+int gemm_f4_block(const LayerDesc& d) { return d.N % 128 == 0 ? 128 : 64; }
+
+// Returns false when the layer cannot run on this kernel (the caller falls back to the next core).
+bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+  const LayerDesc& d = L.d;
+  if (!L.w4s || !L.thr_tc || n_img <= 0 || d.pool || d.ofm_dim != 1 || d.K % 64 || d.ifm_ch % 64 || d.N % 64 || L.kpad != d.K) return false;
+  if (d.K != d.ifm_ch * d.ifm_dim * d.ifm_dim) return false;  // the im2col row must be the whole activation tensor of the image
+  return gemm_f4_block(d) == 128 ? launch_nb<128>(L, in, out, n_img, num_sms, status, s) : launch_nb<64>(L, in, out, n_img, num_sms, status, s);
+}
+
+}  // namespace bnnb

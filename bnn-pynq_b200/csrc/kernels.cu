@@ -71,6 +71,15 @@ __global__ void k_repack_w4(DevLayer L) {
     L.w4[i] = (uint8_t)byte;
   }
 }
+// w4 -> slabs of NB channels x 64 K in the UMMA K-major operand layout (two 16-byte chunks per row), contiguous per (block, slab)
+__global__ void k_repack_w4s(DevLayer L, int NB) {
+  const LayerDesc& d = L.d;
+  const int ks = L.kpad / 64, total = d.N * (L.kpad / 2) / 16;  // 16-byte units
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int n = i % NB, c = (i / NB) % 2, s = (i / (2 * NB)) % ks, nb = i / (2 * NB * ks);
+    reinterpret_cast<uint4*>(L.w4s)[i] = *reinterpret_cast<const uint4*>(L.w4 + (size_t)(nb * NB + n) * (L.kpad / 2) + s * 32 + c * 16);
+  }
+}
 __global__ void k_repack_thr(DevLayer L) {
   const LayerDesc& d = L.d;
   for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < d.N; n += gridDim.x * blockDim.x) {
@@ -85,6 +94,7 @@ void launch_repack(const DevLayer& L, int is_cnv_layer0, cudaStream_t s) {
   else k_repack_planes<<<(L.d.wbits * L.kwords * L.d.N + 255) / 256, 256, 0, s>>>(L);
   if (L.w8) k_repack_w8<<<(L.d.N * L.kpad + 255) / 256, 256, 0, s>>>(L);
   if (L.w4) k_repack_w4<<<(L.d.N * (L.kpad / 2) + 255) / 256, 256, 0, s>>>(L);
+  if (L.w4 && L.w4s && L.kpad % 64 == 0 && L.d.N % 64 == 0) k_repack_w4s<<<(L.d.N * (L.kpad / 32) + 255) / 256, 256, 0, s>>>(L, gemm_f4_block(L.d));
   k_repack_thr<<<(L.d.N + 255) / 256, 256, 0, s>>>(L);
   if (L.w8 && L.thr_tc) launch_thr_tc(L, s);
 }

@@ -24,6 +24,7 @@ struct DevLayer {
   uint32_t* wp;         // popc-path planes (or layer-0 int8x4 words)
   int8_t* w8;           // mma-path int8 B operand (may be null)
   uint8_t* w4;          // e2m1 (fp4) B operand, two per byte, [N][kpad/2] (may be null)
+  uint8_t* w4s;         // the same, as K=64 slabs in UMMA operand layout [N/NB][K/64][2][NB][16 B] for gemm_f4 (may be null)
   int32_t* thr;         // [N][2]
   int32_t* thr_tc;      // [N][2] thresholds adjusted for the tensor-core path (may be null)
   int kwords;           // K/32
@@ -51,6 +52,9 @@ bool launch_conv_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
 void launch_thr_tc(const DevLayer& L, cudaStream_t s);
 // conv layers on kind::mxf4 (conv_f4.cu)
 bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
+// fully-connected layers on kind::mxf4 (gemm_f4.cu); gemm_f4_block = channel block width NB of the slab layout
+int gemm_f4_block(const LayerDesc& d);
+bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
 // K-streamed GEMM for FC / small conv layers (gemm_tc.cu)
 bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
 // fused CNV layers 0+1 (cnv01_tc.cu): int8 HWC image -> pooled, bit-packed layer-1 output
