@@ -16,15 +16,16 @@
 namespace bnnb {
 namespace {
 
-template <int C, int N, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
 struct F4Cfg {
   static constexpr int PXI = IDIM * IDIM, ROWS = G * PXI, TILES = (ROWS + 127) / 128, MAXSHIFT = 2 * IDIM + 2;
   static constexpr int PITCH = (TILES * 128 + MAXSHIFT + 7) / 8 * 8;
   static constexpr int KC = C / 32;  // 16-byte chunks (32 fp4 channels) per tap
-  static constexpr int PLANE = PITCH * 16, A_BYTES = KC * PLANE, B_BYTES = 9 * KC * N * 16;
-  static constexpr int IPL = INM == IN_TERN ? 2 : 1, OPL = OUTM == OUT_TERN ? 2 : 1, NW = N / 32, WPP = NW * OPL;
+  static constexpr int NT = N * NS;  // output channels of the layer: NS blocks of N (one MMA accumulator each)
+  static constexpr int PLANE = PITCH * 16, A_BYTES = KC * PLANE, B_BYTES = 9 * KC * NT * 16;
+  static constexpr int IPL = INM == IN_TERN ? 2 : 1, OPL = OUTM == OUT_TERN ? 2 : 1, NW = N / 32, NWT = NT / 32, WPP = NWT * OPL;
   static constexpr int BITS_BYTES = POOL ? TILES * 128 * WPP * 4 : 0;  // staging rows (pooled layers only)
-  static constexpr int OFF_B = 2 * A_BYTES, OFF_BITS = OFF_B + B_BYTES, OFF_THR = OFF_BITS + BITS_BYTES, SMEM = OFF_THR + 2 * N * 4;
+  static constexpr int OFF_B = 2 * A_BYTES, OFF_BITS = OFF_B + B_BYTES, OFF_THR = OFF_BITS + BITS_BYTES, SMEM = OFF_THR + 2 * NT * 4;
   static constexpr int SLOTS = 384 / N > 4 ? 4 : 384 / N;  // accumulator slots below the scale-factor columns
   static constexpr int SF_COL = 384, PD = POOL ? OD / 2 : OD;
 };
@@ -55,10 +56,10 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
   return make_uint4(v[0], v[1], v[2], v[3]);
 }
 
-template <int C, int N, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
 __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                      int* __restrict__ status) {
-  using Cfg = F4Cfg<C, N, IDIM, OD, POOL, G, INM, OUTM>;
+  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t full[4], empty[4], abuf_full[2], abuf_empty[2];
@@ -74,14 +75,15 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
   // the negated decision, harvested with one funnel shift per channel (see cnv01_tc.cu)
   constexpr bool FOLD = OUTM == OUT_BIT;
 
-  for (int i = tid; i < N * KCT; i += 384) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
-    const int n = i % N, kc = i / N;
-    *reinterpret_cast<uint4*>(sb + ((size_t)kc * N + n) * 16) = *reinterpret_cast<const uint4*>(L.w4 + (size_t)n * (L.kpad / 2) + kc * 16);
+  constexpr int NT = Cfg::NT;
+  for (int i = tid; i < NT * KCT; i += 384) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
+    const int n = i % NT, kc = i / NT;
+    *reinterpret_cast<uint4*>(sb + ((size_t)kc * NT + n) * 16) = *reinterpret_cast<const uint4*>(L.w4 + (size_t)n * (L.kpad / 2) + kc * 16);
   }
-  for (int i = tid; i < 2 * N; i += 384) {
+  for (int i = tid; i < 2 * NT; i += 384) {
     const int t = L.thr_tc[i];
     const float tf = t == INT_MAX ? 3.0e38f : (float)t;
-    sthr[(i & 1) * N + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
+    sthr[(i & 1) * NT + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
   }
   for (int i = tid; i < 2 * Cfg::A_BYTES / 16; i += 384) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // pad pixels stay 0
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
@@ -97,7 +99,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
   const uint32_t tmem = tmem_base;
   if (warp < 4) tc::tmem_fill16(tmem + ((uint32_t)(warp * 32) << 16) + Cfg::SF_COL, 0x7f7f7f7fu);  // every scale factor = 1.0 (ue8m0)
   const uint32_t sthr_u = tc::smem_u32(sthr);
-  auto preload = [&](int slot) {  // this warp's lane quarter and channel half of accumulator `slot` <- -(thr + 1/2), from shared memory
+  auto preload = [&](int slot, int h) {  // this warp's lane quarter and channel half of accumulator `slot` <- -(thr + 1/2) of block h
     const uint32_t t0 = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N;
 #pragma unroll
     for (int jj = 0; jj < NWG; jj++) {
@@ -108,14 +110,14 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
         // volatile: keeps the 128 loop-invariant values out of registers
         asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
                      : "=r"(v[4 * q]), "=r"(v[4 * q + 1]), "=r"(v[4 * q + 2]), "=r"(v[4 * q + 3])
-                     : "r"(sthr_u + (uint32_t)(j * 32 + q * 4) * 4));
+                     : "r"(sthr_u + (uint32_t)(h * N + j * 32 + q * 4) * 4));
       }
       tc::tmem_st32(t0 + j * 32, v);
     }
     tc::tmem_st_wait();
   };
   if (FOLD && warp < 8)
-    for (int slot = 0; slot < Cfg::SLOTS; slot++) preload(slot);
+    for (int slot = 0; slot < Cfg::SLOTS; slot++) preload(slot, slot % NS);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -153,8 +155,9 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
         const int buf = k & 1;
         if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
         const uint32_t sa_u = sa_u0 + (uint32_t)buf * Cfg::A_BYTES;
-        for (int t = 0; t < Cfg::TILES; t++) {
-          const int gt = k * Cfg::TILES + t, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
+        for (int vt = 0; vt < Cfg::TILES * NS; vt++) {  // virtual tile = (row tile t, channel block h)
+          const int t = vt / NS, h = vt % NS;
+          const int gt = k * Cfg::TILES * NS + vt, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
           if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * N;
@@ -165,7 +168,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
 #pragma unroll
             for (int s = 0; s < Cfg::KC / 2; s++) {
               tc::mma_mxf4(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * Cfg::PLANE + off, Cfg::PLANE, 128),
-                           tc::make_desc(sb_u + (uint32_t)((tap * Cfg::KC + 2 * s) * N) * 16, N * 16, 128), idesc, sf, sf,
+                           tc::make_desc(sb_u + (uint32_t)((tap * Cfg::KC + 2 * s) * NT + h * N) * 16, NT * 16, 128), idesc, sf, sf,
                            (FOLD || !firstmma) ? 1u : 0u);
               firstmma = false;
             }
@@ -178,11 +181,12 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
   } else {
     // ---- epilogue groups: every tile, channels [eg*N/2, (eg+1)*N/2) --------------------------------------------------------------
     uint32_t* sbits = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BITS);
-    constexpr int NW = Cfg::NW, WPP = Cfg::WPP;
+    constexpr int NW = Cfg::NW, NWT = Cfg::NWT, WPP = Cfg::WPP;
     for (int k = 0; k < K; k++) {
       const int img0 = ((int)blockIdx.x + k * (int)gridDim.x) * G;
-      for (int t = 0; t < Cfg::TILES; t++) {
-        const int gt = k * Cfg::TILES + t, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
+      for (int vt = 0; vt < Cfg::TILES * NS; vt++) {
+        const int t = vt / NS, h = vt % NS;
+        const int gt = k * Cfg::TILES * NS + vt, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
         if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
@@ -200,12 +204,12 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
             for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
             w0 = ~w0;
           } else {
-            const float* th = sthr + eg * (N / 2) + j * 32;
+            const float* th = sthr + h * N + eg * (N / 2) + j * 32;
 #pragma unroll
             for (int c = 0; c < 32; c++) {
               const float s = __uint_as_float(r[j & 1][c]);
               const int t0 = th[c] < s;
-              const int t1 = th[N + c] < s;
+              const int t1 = th[NT + c] < s;
               w0 |= (uint32_t)(1 ^ t0 ^ t1) << c;
               w1 |= (uint32_t)(t0 & t1) << c;
             }
@@ -213,7 +217,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
           b0[j] = w0;
           b1[j] = w1;
         }
-        if (FOLD) preload(slot);
+        if (FOLD) preload(slot, (gt + Cfg::SLOTS) % NS);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
@@ -226,13 +230,13 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
         }
         if (row) {
           if (NWG == 2) {
-            *reinterpret_cast<uint2*>(row + eg * NWG) = make_uint2(b0[0], b0[1]);
-            if (OUTM == OUT_TERN) *reinterpret_cast<uint2*>(row + NW + eg * NWG) = make_uint2(b1[0], b1[1]);
+            *reinterpret_cast<uint2*>(row + h * NW + eg * NWG) = make_uint2(b0[0], b0[1]);
+            if (OUTM == OUT_TERN) *reinterpret_cast<uint2*>(row + NWT + h * NW + eg * NWG) = make_uint2(b1[0], b1[1]);
           } else {
 #pragma unroll
             for (int q = 0; q < NWG / 4; q++) {
-              reinterpret_cast<uint4*>(row + eg * NWG)[q] = make_uint4(b0[4 * q], b0[4 * q + 1], b0[4 * q + 2], b0[4 * q + 3]);
-              if (OUTM == OUT_TERN) reinterpret_cast<uint4*>(row + NW + eg * NWG)[q] = make_uint4(b1[4 * q], b1[4 * q + 1], b1[4 * q + 2], b1[4 * q + 3]);
+              reinterpret_cast<uint4*>(row + h * NW + eg * NWG)[q] = make_uint4(b0[4 * q], b0[4 * q + 1], b0[4 * q + 2], b0[4 * q + 3]);
+              if (OUTM == OUT_TERN) reinterpret_cast<uint4*>(row + NWT + h * NW + eg * NWG)[q] = make_uint4(b1[4 * q], b1[4 * q + 1], b1[4 * q + 2], b1[4 * q + 3]);
             }
           }
         }
@@ -250,11 +254,11 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
           auto and4 = [](uint4 a, uint4 b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); };
           auto andn4 = [](uint4 a, uint4 b) { return make_uint4(a.x & ~b.x, a.y & ~b.y, a.z & ~b.z, a.w & ~b.w); };
 #pragma unroll
-          for (int q = 0; q < NW / 4; q++) {
+          for (int q = 0; q < NWT / 4; q++) {
             if (OUTM == OUT_BIT) {
               dst[q] = or4(or4(r00[q], r01[q]), or4(r10[q], r11[q]));
             } else {  // max over {-1,0,+1}: +1 if any +1; else -1 only if all four are -1
-              constexpr int H = NW / 4;
+              constexpr int H = NWT / 4;
               const uint4 P = or4(or4(r00[H + q], r01[H + q]), or4(r10[H + q], r11[H + q]));
               const uint4 M = and4(and4(andn4(r00[q], r00[H + q]), andn4(r01[q], r01[H + q])), and4(andn4(r10[q], r10[H + q]), andn4(r11[q], r11[H + q])));
               dst[q] = or4(P, M);
@@ -272,12 +276,12 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
-template <int C, int N, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
 bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
-  using Cfg = F4Cfg<C, N, IDIM, OD, POOL, G, INM, OUTM>;
+  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::SMEM <= 226 * 1024, "shared memory budget");
   static_assert(Cfg::SLOTS * N <= Cfg::SF_COL, "TMEM budget");
-  auto kern = k_conv_f4<C, N, IDIM, OD, POOL, G, INM, OUTM>;
+  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
   const int ngroups = (n_img + G - 1) / G;
   kern<<<ngroups < num_sms ? ngroups : num_sms, 384, Cfg::SMEM, s>>>(L, in, out, n_img, status);
@@ -291,12 +295,16 @@ bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
   if (d.kind != KIND_CONV || !L.w4 || !L.thr_tc || n_img <= 0) return false;
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {
-    if (a1) return launch_cfg<64, 128, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<64, 128, 14, 12, false, 6, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
+    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, 6, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
   }
   if (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) {
-    if (a1) return launch_cfg<128, 128, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<128, 128, 12, 10, true, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a1) return launch_cfg<128, 128, 1, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
+    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+  }
+  if (d.ifm_ch == 128 && d.N == 256 && d.ifm_dim == 5 && !d.pool) {  // two channel blocks of 128 share the operand planes
+    if (a1) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
+    if (a2) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
   }
   return false;
 }
