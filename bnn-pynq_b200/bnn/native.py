@@ -240,13 +240,15 @@ def pack_fp4(M):
     return np.ascontiguousarray(nib[:, 0::2] | (nib[:, 1::2] << 4))
 
 
-def tc_probe_fp4(A, B, shift=0, reps=1, bias=None):
+def tc_probe_fp4(A, B, shift=0, reps=1, bias=None, mix=0):
     """tcgen05 kind::mxf4 (block-scaled fp4, all scales 1.0) probe: D[m][n] = sum_k A[m+shift][k] * B[n][k].
     With bias (float32 [N]) the accumulator is pre-loaded with bias[n] and D is returned as float32 (raw accumulator)."""
     A4, B4 = pack_fp4(A), pack_fp4(B)
     D = np.zeros((128, B.shape[0]), np.int32)
     cyc = C.c_longlong(0)
-    if bias is None:
+    if mix:
+        rc = lib().bnnb_tc_probe_fp4_mix(_p(A4), _p(B4), _p(D), A.shape[0], B.shape[0], A.shape[1], shift, reps, C.byref(cyc), None, mix)
+    elif bias is None:
         rc = lib().bnnb_tc_probe_fp4(_p(A4), _p(B4), _p(D), A.shape[0], B.shape[0], A.shape[1], shift, reps, C.byref(cyc))
     else:
         bias = np.ascontiguousarray(bias, np.float32)

@@ -9,9 +9,9 @@
 // image (m = y*32 + x: the 3x3x3 window row ky of pixel (y,x) is the first 9 bytes of P[m + 32*ky]).  K is laid out as
 // [ky][16]: k = ky*16 + (kx*3 + c) with zero weights for the 7 trailing bytes of each ky and for the whole 4th chunk, so
 // one tile needs two K=32 MMAs whose A descriptors differ only by a start shift (LBO = 32 rows).
-// Warp-specialised CTA (one per SM, 320 threads): four warps run layer 1's epilogue on image i, four warps stage image i+1
-// (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one warp issues layer 1's MMAs up to four tiles
-// ahead, one warp prefetches images by TMA bulk copy two images ahead and issues layer 0's MMAs up to three tiles ahead.
+// Warp-specialised CTA (one per SM, 288 threads): four warps run layer 1's epilogue on image i, four warps stage image i+1
+// (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one thread prefetches images by TMA bulk copy two
+// images ahead and issues all MMAs, interleaving layer 1 of image i with layer 0 of image i+1 tile by tile.
 #include <climits>
 #include <type_traits>
 #include "kernels.cuh"
@@ -42,18 +42,18 @@ template <int OUTM, bool F4> struct Smem01 {
 
 __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 
-// Warp roles (320 threads): warps 0-3 = half A (layer-1 epilogue, pool, store), warps 4-7 = half B (window plane, layer-0
-// epilogue into the other operand buffer), warp 8 = layer-1 MMA issuer, warp 9 = image prefetch (TMA) + layer-0 MMA issuer.
+// Warp roles (288 threads): warps 0-3 = half A (layer-1 epilogue, pool, store), warps 4-7 = half B (window plane, layer-0
+// epilogue into the other operand buffer), warp 8 = image prefetch (TMA) + MMA issuer for both layers.
 // The roles are decoupled by mbarriers only (no CTA-wide barrier in steady state):
 //   img_full[b]   TMA    -> half B   image buffer b holds an image                      (expect_tx 3072 bytes)
-//   p_full[b]     half B -> warp 9   window plane b is built (and image buffer b free)  (128 arrivals)
-//   p_empty[b]    warp 9 -> half B   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
-//   f0[s], e0[s]  warp 9 <-> half B  layer-0 accumulator slot s (of 3) full / read out   (commit / 4 arrivals)
+//   p_full[b]     half B -> warp 8   window plane b is built (and image buffer b free)  (128 arrivals)
+//   p_empty[b]    warp 8 -> half B   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
+//   f0[s], e0[s]  warp 8 <-> half B  layer-0 accumulator slot s (of 3) full / read out   (commit / 4 arrivals)
 //   abuf_full[b]  half B -> warp 8   layer-1 operand buffer b holds a staged image      (128 arrivals)
 //   abuf_empty[b] warp 8 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
 //   full[s], empty[s] warp 8 <-> half A  layer-1 accumulator slot s (of 4) full / read out
 template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
-__global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
+__global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
                                                       int n_img, int* __restrict__ status) {
   using S = Smem01<OUTM, F4>;
   constexpr int L1_A = S::L1_A;
@@ -76,30 +76,30 @@ __global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   int32_t* sthr0 = reinterpret_cast<int32_t*>(smem + S::OFF_THR);  // layer 0: floor(thr/2)   [64][2]
   int32_t* sthr1 = sthr0 + 128;                                    // layer 1: adjusted       [64][2] (F4: as float)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int role = warp < 4 ? 0 : (warp < 8 ? 1 : warp - 6);       // 0: half A, 1: half B, 2: layer-1 issuer, 3: loader + layer-0 issuer
+  const int role = warp < 4 ? 0 : (warp < 8 ? 1 : 2);              // 0: half A, 1: half B, 2: issuer + loader
   const int ht = tid & 127, hw = warp & 3;  // thread / warp index inside the half; hw selects the TMEM lane quarter
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
-  for (int i = tid; i < 64 * 9 * S::NPL; i += 320) {  // layer-1 weights -> chunk-major operand layout
+  for (int i = tid; i < 64 * 9 * S::NPL; i += 288) {  // layer-1 weights -> chunk-major operand layout
     const int n = i % 64, kc = i / 64;
     const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
     *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = *reinterpret_cast<const uint4*>(src + kc * 16);
   }
-  for (int i = tid; i < 64 * 64; i += 320) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
+  for (int i = tid; i < 64 * 64; i += 288) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
     sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)v;
   }
-  for (int i = tid; i < 128; i += 320) {
+  for (int i = tid; i < 128; i += 288) {
     const int t = L0.thr[i];
     sthr0[i] = t == INT_MAX ? INT_MAX : (t >> 1);  // thr < 2S  <=>  floor(thr/2) < S
     const int t1 = L1.thr_tc[i];
     if (F4) reinterpret_cast<float*>(sthr1)[i] = t1 == INT_MAX ? 3.0e38f : (float)t1;
     else sthr1[i] = t1;
   }
-  for (int i = tid; i < 2 * L1_A / 16; i += 320) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
-  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += 320) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < 2 * L1_A / 16; i += 288) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
+  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += 288) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
     for (int i = 0; i < 2; i++) {
@@ -243,69 +243,85 @@ __global__ void __launch_bounds__(320, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       tc::fence_async_smem();  // operand planes were written through the generic proxy and are read by the async proxy (MMA)
       tc::mbar_arrive(&abuf_full[buf]);
     }
-  } else if (role == 3) {
-    // ================= loader + layer-0 issuer ================================================================================
-    if (lane == 0) {
-      for (int k = 0; k < 2 && k < K; k++) {
-        tc::mbar_expect_tx(&img_full[k], 3072);
-        tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
-      }
-      if (FOLD && !failed && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
-      for (int k = 0; k < K; k++) {
-        const int buf = k & 1;
-        if (!failed && !tc::mbar_wait(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
-        if (k + 2 < K) {  // image buffer `buf` has been consumed: prefetch image k+2 into it
-          tc::mbar_expect_tx(&img_full[buf], 3072);
-          tc::bulk_g2s(sImg + (size_t)buf * IMG_BYTES, in + (first + (long long)(k + 2) * stride) * 3072, 3072, &img_full[buf]);
-        }
-        const uint32_t p_u = sP_u + (uint32_t)buf * P_BYTES;
-        for (int t = 0; t < L0_TILES; t++) {
-          const int g = k * L0_TILES + t, slot = g % L0_SLOTS, u = g / L0_SLOTS;
-          if (u >= 1 && !failed && !tc::mbar_wait(&e0[slot], (uint32_t)(u - 1) & 1)) failed = true;
-          tc::fence_after_sync();
-          const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
-          const uint32_t a0 = p_u + (uint32_t)(t * 128) * 16;
-          tc::mma_i8(acc, tc::make_desc(a0, 32 * 16, 128), tc::make_desc(sB0_u, 64 * 16, 128), idesc, FOLD ? 1u : 0u);               // ky 0, 1
-          tc::mma_i8(acc, tc::make_desc(a0 + 64 * 16, 32 * 16, 128), tc::make_desc(sB0_u + 2 * 64 * 16, 64 * 16, 128), idesc, 1u);  // ky 2, zero chunk
-          tc::commit(&f0[slot]);
-        }
-        tc::commit(&p_empty[buf]);
-      }
-    }
   } else if (role == 2) {
-    // ================= issuer: layer-1 MMAs, up to four tiles ahead of the epilogue ========================================
-    if (lane == 0) {
+    // ================= issuer + loader (one thread) =============================================================================
+    // The tensor pipe is one in-order queue, so the order of issue is the schedule.  Stage s interleaves layer 1 of image s with
+    // layer 0 of image s+1, tile by tile (L0 tile, then L1 tile): layer 0's two MMAs per tile never queue behind more than one
+    // layer-1 tile (nine MMAs), and image s+1 is staged by the time layer 1 of image s has been issued.
+    {  // the whole warp runs the schedule (uniform control flow and addresses); one elected lane issues
+      const bool leader = tc::elect_one();
+      // descriptor words: every operand here has SBO = 128; the start field (16-byte units) is the only part that moves
+      const uint32_t d_hi = tc::desc_hi(128);
+      const uint32_t p_lo[2] = {tc::desc_lo(sP_u, 32 * 16), tc::desc_lo(sP_u + P_BYTES, 32 * 16)};
+      const uint32_t a1_lo[2] = {tc::desc_lo(sA_u, L1_PLANE), tc::desc_lo(sA_u + L1_A, L1_PLANE)};
+      const uint32_t b0_lo = tc::desc_lo(sB0_u, 64 * 16), b1_lo = tc::desc_lo(sB1_u, 64 * 16);
+      for (int k = 0; k < 2 && k < K; k++)
+        if (leader) {
+          tc::mbar_expect_tx(&img_full[k], 3072);
+          tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
+        }
       if (FOLD && !failed && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
-      for (int k = 0; k < K; k++) {
+      auto issue_l0 = [&](int k, int t) {
         const int buf = k & 1;
-        if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        if (t == 0) {
+          if (!failed && !tc::mbar_wait(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+          if (k + 2 < K && leader) {  // image buffer `buf` has been consumed: prefetch image k+2 into it
+            tc::mbar_expect_tx(&img_full[buf], 3072);
+            tc::bulk_g2s(sImg + (size_t)buf * IMG_BYTES, in + (first + (long long)(k + 2) * stride) * 3072, 3072, &img_full[buf]);
+          }
+        }
+        const int g = k * L0_TILES + t, slot = g % L0_SLOTS, u = g / L0_SLOTS;
+        if (u >= 1 && !failed && !tc::mbar_wait(&e0[slot], (uint32_t)(u - 1) & 1)) failed = true;
+        tc::fence_after_sync();
+        const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
+        const uint32_t a0 = p_lo[buf] + (uint32_t)(t * 128);  // descriptor start fields are in 16-byte units: one row = 1
+        if (leader) {
+          tc::mma_i8_lh(acc, a0, d_hi, b0_lo, d_hi, idesc, FOLD ? 1u : 0u);            // ky 0, 1
+          tc::mma_i8_lh(acc, a0 + 64, d_hi, b0_lo + 2 * 64, d_hi, idesc, 1u);          // ky 2, zero chunk
+          tc::commit(&f0[slot]);
+          if (t == L0_TILES - 1) tc::commit(&p_empty[buf]);
+        }
+        __syncwarp();
+      };
+      auto issue_l1 = [&](int k, int t) {
+        const int buf = k & 1;
+        if (t == 0 && !failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
         const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
-        for (int t = 0; t < L1_TILES; t++) {
-          const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-          if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
-          tc::fence_after_sync();
-          const uint32_t acc = tmem + (uint32_t)slot * 64;
-          bool firstmma = true;
+        const uint32_t a_lo = a1_lo[buf] + (uint32_t)(t * 128);
+        const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
+        if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+        tc::fence_after_sync();
+        const uint32_t acc = tmem + (uint32_t)slot * 64;
+        bool firstmma = true;
+        if (leader) {
 #pragma unroll
-          for (int tap = 0; tap < 9; tap++) {
-            const uint32_t off = (uint32_t)((tap / 3) * 30 + tap % 3 + t * 128) * 16;
-            if (F4) {
-              tc::mma_mxf4(acc, tc::make_desc(sa_u + off, L1_PLANE, 128), tc::make_desc(sB1_u + (uint32_t)(tap * 2 * 64) * 16, 64 * 16, 128),
-                           idesc_f4, sf, sf, (FOLD || !firstmma) ? 1u : 0u);
+        for (int tap = 0; tap < 9; tap++) {
+          const uint32_t off = (uint32_t)((tap / 3) * 30 + tap % 3 + t * 128) * 16;
+          if (F4) {
+            tc::mma_mxf4_lh(acc, a_lo + (uint32_t)((tap / 3) * 30 + tap % 3), d_hi, b1_lo + (uint32_t)(tap * 2 * 64), d_hi, idesc_f4, sf, sf,
+                            (FOLD || !firstmma) ? 1u : 0u);
+            firstmma = false;
+          } else {
+#pragma unroll
+            for (int s2 = 0; s2 < 2; s2++) {
+              tc::mma_i8(acc, tc::make_desc(sa_u + (uint32_t)(2 * s2) * L1_PLANE + off, L1_PLANE, 128),
+                         tc::make_desc(sB1_u + (uint32_t)((tap * 4 + 2 * s2) * 64) * 16, 64 * 16, 128), idesc, firstmma ? 0u : 1u);
               firstmma = false;
-            } else {
-#pragma unroll
-              for (int s = 0; s < 2; s++) {
-                tc::mma_i8(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * L1_PLANE + off, L1_PLANE, 128),
-                           tc::make_desc(sB1_u + (uint32_t)((tap * 4 + 2 * s) * 64) * 16, 64 * 16, 128), idesc, firstmma ? 0u : 1u);
-                firstmma = false;
-              }
             }
           }
-          tc::commit(&full[slot]);
         }
-        tc::commit(&abuf_empty[buf]);
-      }
+        tc::commit(&full[slot]);
+        if (t == L1_TILES - 1) tc::commit(&abuf_empty[buf]);
+        }
+        __syncwarp();
+      };
+      if (K > 0)
+        for (int t = 0; t < L0_TILES; t++) issue_l0(0, t);
+      for (int k = 0; k < K; k++)
+        for (int t = 0; t < L0_TILES; t++) {
+          if (k + 1 < K) issue_l0(k + 1, t);
+          if (t < L1_TILES) issue_l1(k, t);
+        }
     }
   } else {
     // ================= half A: layer-1 epilogue, 2x2 max-pool, store ========================================================
@@ -395,7 +411,7 @@ static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
   using S = Smem01<OUTM, F4>;
   static_assert(S::TOTAL <= 226 * 1024, "shared memory budget");
   cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-  k_cnv01_tc<OUTM, F4><<<grid, 320, S::TOTAL, s>>>(L0, L1, in, out, n_img, status);
+  k_cnv01_tc<OUTM, F4><<<grid, 288, S::TOTAL, s>>>(L0, L1, in, out, n_img, status);
 }
 
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int* status,

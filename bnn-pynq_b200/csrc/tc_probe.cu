@@ -95,7 +95,7 @@ extern "C" int bnnb_tc_probe(const int8_t* A, const int8_t* B, int32_t* D, int r
 // ---- fp4 probe: A [rows_a][K/2] packed e2m1, B [N][K/2], D[m][n] = sum_k A[m+shift][k] * B[n][k] (fp32 -> int32) --------------
 namespace {
 __global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, int32_t* __restrict__ D,
-                                                       int rows_a, int N, int K, int shift, int reps, long long* cyc, int* status, const float* __restrict__ bias) {
+                                                       int rows_a, int N, int K, int shift, int reps, long long* cyc, int* status, const float* __restrict__ bias, int mix) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_base;
@@ -138,7 +138,20 @@ __global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict_
   }
   const uint32_t idesc = make_idesc_mxf4(128, N);
   long long t0 = 0, t1 = 0;
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == 0 && mix != 0) {
+    // timing experiment (results are not meaningful): `reps` groups of |mix| fp4 MMAs, each group followed by one kind::i8 MMA
+    // (mix > 0) or by one more fp4 MMA (mix < 0, the control), all on constant descriptors so that the issue loop is lean
+    const uint64_t ad = make_desc(smem_u32(sa), plane_a, 128), bd = make_desc(smem_u32(sb), plane_b, 128);
+    const uint32_t id8 = make_idesc_i8(128, 64);
+    const int grp = mix > 0 ? mix : -mix;
+    t0 = clock64();
+    for (int rep = 0; rep < reps; rep++) {
+      for (int i = 0; i < grp; i++) mma_mxf4(tmem, ad, bd, idesc, sf, sf, 1u);
+      if (mix > 0) mma_i8(tmem + 288, ad, bd, id8, 1u);
+      else mma_mxf4(tmem + 288, ad, bd, idesc, sf, sf, 1u);
+    }
+    commit(&bar);
+  } else if (threadIdx.x == 0) {
     t0 = clock64();
     for (int rep = 0; rep < reps; rep++)
       for (int ks = 0; ks < K / 64; ks++) {
@@ -167,13 +180,17 @@ __global__ void __launch_bounds__(128) k_tc_probe_fp4(const uint8_t* __restrict_
 }
 }  // namespace
 
+extern "C" int bnnb_tc_probe_fp4_mix(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles,
+                                     const float* bias, int mix);
 extern "C" int bnnb_tc_probe_fp4_bias(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles,
-                                      const float* bias);
+                                      const float* bias) {
+  return bnnb_tc_probe_fp4_mix(A, B, D, rows_a, N, K, shift, reps, cycles, bias, 0);
+}
 extern "C" int bnnb_tc_probe_fp4(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles) {
   return bnnb_tc_probe_fp4_bias(A, B, D, rows_a, N, K, shift, reps, cycles, nullptr);
 }
-extern "C" int bnnb_tc_probe_fp4_bias(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles,
-                                      const float* bias) {
+extern "C" int bnnb_tc_probe_fp4_mix(const uint8_t* A, const uint8_t* B, int32_t* D, int rows_a, int N, int K, int shift, int reps, long long* cycles,
+                                     const float* bias, int mix) {
   if (N % 32 || N < 32 || N > 256 || K % 64 || rows_a < 128 + shift || rows_a % 8) return -1;
   const size_t smem = (size_t)(K / 32) * (rows_a + N) * 16;
   if (smem > 200 * 1024) return -1;
@@ -188,7 +205,7 @@ extern "C" int bnnb_tc_probe_fp4_bias(const uint8_t* A, const uint8_t* B, int32_
   cudaMemset(dS, 0, 4);
   cudaMemset(dD, 0xff, (size_t)128 * N * 4);
   cudaFuncSetAttribute(k_tc_probe_fp4, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-  k_tc_probe_fp4<<<1, 128, smem>>>(dA, dB, dD, rows_a, N, K, shift, reps, dC, dS, dBias);
+  k_tc_probe_fp4<<<1, 128, smem>>>(dA, dB, dD, rows_a, N, K, shift, reps, dC, dS, dBias, mix);
   cudaError_t e = cudaDeviceSynchronize();
   int st = 0;
   if (e == cudaSuccess) {

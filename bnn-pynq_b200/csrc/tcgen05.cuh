@@ -160,3 +160,51 @@ __device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&r)[32]) {
                : "memory");
 }
 }}  // namespace bnnb::tc
+
+namespace bnnb { namespace tc {
+// one lane of a converged warp (the others fall through); keeps descriptor arithmetic warp-uniform for the compiler
+__device__ __forceinline__ bool elect_one() {
+  uint32_t p;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t"
+      "}\n"
+      : "=r"(p));
+  return p != 0;
+}
+}}  // namespace bnnb::tc
+
+// ---- lean issue path: descriptors as (lo, hi) words so that per-MMA address arithmetic is one 32-bit add ---------------------------
+// A single thread issues at roughly one instruction per five clocks, so the instruction count per MMA decides whether the tensor
+// pipe is kept fed (measured: tests/test_gpu_tcgen05.py::test_mma_kind_switch_cost_report, ncu source view of the issuer warp).
+namespace bnnb { namespace tc {
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) { return ((saddr >> 4) & 0x3fff) | (((lbo_bytes >> 4) & 0x3fff) << 16); }
+__device__ __forceinline__ uint32_t desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3fff) | (1u << 14); }  // version 1 at bit 46
+__device__ __forceinline__ void mma_mxf4_lh(uint32_t tmem_d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi, uint32_t idesc, uint32_t sfa,
+                                            uint32_t sfb, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b64 a, b;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 a, {%1, %2};\n\t"
+      "mov.b64 b, {%3, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %5, [%7], [%8], p;\n\t"
+      "}\n" ::"r"(tmem_d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate), "r"(sfa), "r"(sfb)
+      : "memory");
+}
+__device__ __forceinline__ void mma_i8_lh(uint32_t tmem_d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b64 a, b;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 a, {%1, %2};\n\t"
+      "mov.b64 b, {%3, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], a, b, %5, p;\n\t"
+      "}\n" ::"r"(tmem_d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+}}  // namespace bnnb::tc

@@ -91,3 +91,19 @@ def test_fp4_accumulator_preload_is_exact(N, K):
     assert np.all(D[:, 8] < -1e38)
     # the decision itself
     assert np.array_equal(~np.signbit(D[:, ok]), S[:, ok] > thr[None, ok])
+
+
+def test_mma_kind_switch_cost_report():
+    """Timing report: cost of interleaving kind::i8 MMAs among kind::mxf4 MMAs on the same tensor pipe.
+    mix = g > 0: groups of g fp4 MMAs + one int8 MMA; mix = -g: the control, g + 1 fp4 MMAs per group."""
+    from bnn import native
+    rng = np.random.default_rng(3)
+    K, N, reps = 64, 64, 512
+    A = rng.integers(0, 2, (128, K))
+    B = rng.integers(-1, 2, (N, K))
+    out = {}
+    for g in (1, 2, 4, 9):
+        _, c_mix = native.tc_probe_fp4(A, B, 0, reps, mix=g)
+        _, c_ctl = native.tc_probe_fp4(A, B, 0, reps, mix=-g)
+        out[g] = {"clk_per_group_mixed": c_mix / reps, "clk_per_group_fp4_only": c_ctl / reps}
+    print("kind switch:", out)
