@@ -149,33 +149,37 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
       tc::mbar_arrive(&abuf_full[buf]);
     }
   } else if (role == 2) {
-    // ---- issuer ---------------------------------------------------------------------------------------------------------
-    if (lane == 0) {
+    // ---- issuer: the whole warp runs the schedule (uniform control flow), one elected lane issues; descriptors as (lo, hi) words
+    // so that the address arithmetic per MMA is one add (a lone thread issues about one instruction per five clocks) ------------
+    {
+      const bool leader = tc::elect_one();
+      const uint32_t d_hi = tc::desc_hi(128);
+      const uint32_t a_lo[2] = {tc::desc_lo(sa_u0, Cfg::PLANE), tc::desc_lo(sa_u0 + Cfg::A_BYTES, Cfg::PLANE)};
+      const uint32_t b_lo = tc::desc_lo(sb_u, NT * 16);
       for (int k = 0; k < K; k++) {
         const int buf = k & 1;
         if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
-        const uint32_t sa_u = sa_u0 + (uint32_t)buf * Cfg::A_BYTES;
         for (int vt = 0; vt < Cfg::TILES * NS; vt++) {  // virtual tile = (row tile t, channel block h)
           const int t = vt / NS, h = vt % NS;
           const int gt = k * Cfg::TILES * NS + vt, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
           if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * N;
-          bool firstmma = true;
+          const uint32_t at = a_lo[buf] + (uint32_t)(t * 128), bt = b_lo + (uint32_t)(h * N);
+          if (leader) {
 #pragma unroll
-          for (int tap = 0; tap < 9; tap++) {
-            const uint32_t off = (uint32_t)((tap / 3) * IDIM + tap % 3 + t * 128) * 16;
+            for (int tap = 0; tap < 9; tap++) {
 #pragma unroll
-            for (int s = 0; s < Cfg::KC / 2; s++) {
-              tc::mma_mxf4(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * Cfg::PLANE + off, Cfg::PLANE, 128),
-                           tc::make_desc(sb_u + (uint32_t)((tap * Cfg::KC + 2 * s) * NT + h * N) * 16, NT * 16, 128), idesc, sf, sf,
-                           (FOLD || !firstmma) ? 1u : 0u);
-              firstmma = false;
+              for (int s = 0; s < Cfg::KC / 2; s++)
+                tc::mma_mxf4_lh(acc, at + (uint32_t)((tap / 3) * IDIM + tap % 3 + 2 * s * (Cfg::PLANE / 16)), d_hi,
+                                bt + (uint32_t)((tap * Cfg::KC + 2 * s) * NT), d_hi, idesc, sf, sf, (FOLD || tap + s > 0) ? 1u : 0u);
             }
+            tc::commit(&full[slot]);
           }
-          tc::commit(&full[slot]);
+          __syncwarp();
         }
-        tc::commit(&abuf_empty[buf]);
+        if (leader) tc::commit(&abuf_empty[buf]);
+        __syncwarp();
       }
     }
   } else {

@@ -165,12 +165,15 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
       }
     }
   } else if (role == 3) {
-    // ---- issuer ---------------------------------------------------------------------------------------------------------
-    if (lane == 0) {
+    // ---- issuer: converged warp, one elected lane issues; one add per descriptor -----------------------------------------------
+    {
+      const bool leader = tc::elect_one();
+      const uint32_t d_hi = tc::desc_hi(128);
+      const uint32_t b_lo = tc::desc_lo(ring_u, NB * 16);
       long long gs = 0;
       for (int tl = 0; tl < T; tl++) {
         const int buf = tl % g.nbuf, use = tl / g.nbuf;
-        const uint32_t sa_u = sa_u0 + (uint32_t)buf * g.a_bytes;
+        const uint32_t a_lo = tc::desc_lo(sa_u0 + (uint32_t)buf * g.a_bytes, 2048);
         for (int nb = 0; nb < g.nblk; nb++) {
           const int gb = tl * g.nblk + nb, slot = gb % SLOTS, u = gb / SLOTS;
           if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
@@ -186,13 +189,17 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
               qn++;
             }
             if (!failed && !tc::mbar_wait(&ring_full[r], (uint32_t)(gs / GF_RING) & 1)) failed = true;
-            tc::mma_mxf4(acc, tc::make_desc(sa_u + (uint32_t)(2 * s) * 2048, 2048, 128), tc::make_desc(ring_u + (uint32_t)r * SLAB, NB * 16, 128), idesc,
-                         sf, sf, (FOLD || s > 0) ? 1u : 0u);
-            tc::commit(&ring_empty[r]);
+            if (leader) {
+              tc::mma_mxf4_lh(acc, a_lo + (uint32_t)(2 * s) * 128, d_hi, b_lo + (uint32_t)r * (SLAB / 16), d_hi, idesc, sf, sf, (FOLD || s > 0) ? 1u : 0u);
+              tc::commit(&ring_empty[r]);
+            }
+            __syncwarp();
           }
-          tc::commit(&full[slot]);
+          if (leader) tc::commit(&full[slot]);
+          __syncwarp();
         }
-        tc::commit(&a_empty[buf]);
+        if (leader) tc::commit(&a_empty[buf]);
+        __syncwarp();
       }
     }
   } else {
