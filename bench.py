@@ -238,6 +238,18 @@ def main():
         if rc != 0:
             raise RuntimeError(L.bnnb_last_error(rt.h).decode())
 
+    # plain pinned-host -> device copy of one step's input: the floor of the end-to-end number
+    th = torch.from_numpy(host)
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    d_raw.copy_(th, non_blocking=True)
+    torch.cuda.synchronize()
+    h0.record()
+    for _ in range(3):
+        d_raw.copy_(th, non_blocking=True)
+    h1.record()
+    torch.cuda.synchronize()
+    h2d_gbs = 3 * B * raw_w / (h0.elapsed_time(h1) * 1e-3) / 1e9
+
     e2e_step()
     barrier()
     t0 = time.perf_counter()
@@ -280,8 +292,9 @@ def main():
 
     out = {"metric": metric, "value": value, "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-           "dtype": "int1 (xnor-popcount, int32 accumulate)" if a.net.endswith("W1A1") else "int2 bit-serial", "data": "synthetic", "config": config,
-           "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": B * raw_w, "d2h_bytes_per_step": B * (4 if fam == "cnv" else 8)},
+           "dtype": "int1 x int1 as e2m1 on tcgen05 kind::mxf4 with unit scales (exact; fp32 accumulate), layer 0 int8 (int32 accumulate)" if a.net.endswith("W1A1") else "int2 (ternary activations, 1/2-bit weights) as e2m1 on tcgen05 kind::mxf4 with unit scales (exact; fp32 accumulate)", "data": "synthetic", "config": config,
+           "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": B * raw_w, "d2h_bytes_per_step": B * (4 if fam == "cnv" else 8),
+                   "h2d_copy_gbs_measured": h2d_gbs, "h2d_bound_images_per_s": world * h2d_gbs * 1e9 / raw_w},
            "gpu_launches": int(launches_per_step) * a.steps, "roofline": roofline, "clocks": sampler.summary()}
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         try:
