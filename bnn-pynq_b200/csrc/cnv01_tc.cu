@@ -42,12 +42,12 @@ template <int OUTM, bool F4> struct Smem01 {
 
 __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 
-// Warp roles (288 threads): warps 0-3 = half A (layer-1 epilogue, pool, store), warps 4-7 = half B (window plane, layer-0
-// epilogue into the other operand buffer), warp 8 = image prefetch (TMA) + MMA issuer for both layers.
+// Warp roles (288 threads): warps 0-3 = half A (layer-1 epilogue, pool, store), warps 4-7 = half B (layer-0 epilogue into the
+// other operand buffer); half A also builds the window planes, warp 8 = image prefetch (TMA) + MMA issuer for both layers.
 // The roles are decoupled by mbarriers only (no CTA-wide barrier in steady state):
-//   img_full[b]   TMA    -> half B   image buffer b holds an image                      (expect_tx 3072 bytes)
-//   p_full[b]     half B -> warp 8   window plane b is built (and image buffer b free)  (128 arrivals)
-//   p_empty[b]    warp 8 -> half B   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
+//   img_full[b]   TMA    -> half A   image buffer b holds an image                      (expect_tx 3072 bytes)
+//   p_full[b]     half A -> warp 8   window plane b is built (and image buffer b free)  (128 arrivals)
+//   p_empty[b]    warp 8 -> half A   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
 //   f0[s], e0[s]  warp 8 <-> half B  layer-0 accumulator slot s (of 3) full / read out   (commit / 4 arrivals)
 //   abuf_full[b]  half B -> warp 8   layer-1 operand buffer b holds a staged image      (128 arrivals)
 //   abuf_empty[b] warp 8 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
@@ -128,6 +128,26 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   const long long first = blockIdx.x, stride = gridDim.x;
   const int K = first < n_img ? (int)((n_img - first + stride - 1) / stride) : 0;  // images of this CTA
 
+  // window plane of image kk, built by half A (which has the slack) two images ahead of its own layer-1 epilogue, so that
+  // layer 0's MMAs never wait for it
+  auto build_p = [&](int kk) {
+    const int buf = kk & 1;
+    const uint32_t par = (uint32_t)(kk >> 1) & 1;
+    if (!failed && !tc::mbar_wait(&img_full[buf], par)) failed = true;
+    if (kk >= 2 && !failed && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
+    const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
+    uint8_t* sPk = sP + (size_t)buf * P_BYTES;
+#pragma unroll 3
+    for (int m = ht; m < 1024 + 64; m += 128) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
+      const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
+      uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
+      if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
+      *reinterpret_cast<uint4*>(sPk + (size_t)m * 16) =
+          make_uint4(__funnelshift_r(x0, x1, sh), __funnelshift_r(x1, x2, sh), __funnelshift_r(x2, x3, sh), __funnelshift_r(x3, x4, sh));
+    }
+    tc::fence_async_smem();
+    tc::mbar_arrive(&p_full[buf]);
+  };
   if (role == 1) {
     // ================= half B: window plane of image k, then layer-0 epilogue into layer-1 operand buffer k&1 =================
     int thrA[64];  // first thresholds in registers: the epilogue's shared-memory traffic competes with the MMA operand reads
@@ -146,30 +166,9 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       half_sync(2);
       if (ht == 0) tc::mbar_arrive(&pre_done);
     }
-    // window plane of image kk: runs one image ahead of the epilogue so that layer 0's MMAs never wait for it
-    auto build_p = [&](int kk) {
-      const int buf = kk & 1;
-      const uint32_t par = (uint32_t)(kk >> 1) & 1;
-      if (!failed && !tc::mbar_wait(&img_full[buf], par)) failed = true;
-      if (kk >= 2 && !failed && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
-      const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
-      uint8_t* sPk = sP + (size_t)buf * P_BYTES;
-#pragma unroll 3
-      for (int m = ht; m < 1024 + 64; m += 128) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
-        const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
-        uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
-        if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
-        *reinterpret_cast<uint4*>(sPk + (size_t)m * 16) =
-            make_uint4(__funnelshift_r(x0, x1, sh), __funnelshift_r(x1, x2, sh), __funnelshift_r(x2, x3, sh), __funnelshift_r(x3, x4, sh));
-      }
-      tc::fence_async_smem();
-      tc::mbar_arrive(&p_full[buf]);
-    };
-    if (K > 0) build_p(0);
     for (int k = 0; k < K; k++) {
       const int buf = k & 1;
       const uint32_t par = (uint32_t)(k >> 1) & 1;
-      if (k + 1 < K) build_p(k + 1);
       // the layer-1 MMAs that read this operand buffer two images ago must have completed before it is overwritten
       if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], par ^ 1)) failed = true;
       uint8_t* sA = smem + (size_t)buf * L1_A;
@@ -344,8 +343,11 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       half_sync(1);
       if (ht == 0) tc::mbar_arrive(&pre_done);
     }
+    if (K > 0) build_p(0);
+    if (K > 1) build_p(1);
     for (int k = 0; k < K; k++) {
       const long long img = first + (long long)k * stride;
+      if (k + 2 < K) build_p(k + 2);  // before this image's tiles arrive: half A would be waiting anyway
       for (int t = 0; t < L1_TILES; t++) {
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
         if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
