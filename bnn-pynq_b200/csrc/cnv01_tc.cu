@@ -245,8 +245,8 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   } else if (role == 2) {
     // ================= issuer + loader (one thread) =============================================================================
     // The tensor pipe is one in-order queue, so the order of issue is the schedule.  Stage s interleaves layer 1 of image s with
-    // layer 0 of image s+1, tile by tile (L0 tile, then L1 tile): layer 0's two MMAs per tile never queue behind more than one
-    // layer-1 tile (nine MMAs), and image s+1 is staged by the time layer 1 of image s has been issued.
+    // layer 0 of image s+1 (two L0 tiles, then one L1 tile): layer 0's MMAs never queue behind more than one layer-1 tile (nine
+    // MMAs), and image s+1 is staged well before layer 1 of image s has been issued.
     {  // the whole warp runs the schedule (uniform control flow and addresses); one elected lane issues
       const bool leader = tc::elect_one();
       // descriptor words: every operand here has SBO = 128; the start field (16-byte units) is the only part that moves
@@ -316,11 +316,15 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       };
       if (K > 0)
         for (int t = 0; t < L0_TILES; t++) issue_l0(0, t);
-      for (int k = 0; k < K; k++)
-        for (int t = 0; t < L0_TILES; t++) {
-          if (k + 1 < K) issue_l0(k + 1, t);
-          if (t < L1_TILES) issue_l1(k, t);
+      // stage k: layer 0 of image k+1 is front-loaded (two tiles per layer-1 tile), so that image k+1 is completely staged about
+      // three layer-1 tiles before the stage ends and the next stage starts without a bubble
+      for (int k = 0; k < K; k++) {
+        for (int t = 0; t < L0_TILES / 2; t++) {
+          if (k + 1 < K) { issue_l0(k + 1, 2 * t); issue_l0(k + 1, 2 * t + 1); }
+          issue_l1(k, t);
         }
+        for (int t = L0_TILES / 2; t < L1_TILES; t++) issue_l1(k, t);
+      }
     }
   } else {
     // ================= half A: layer-1 epilogue, 2x2 max-pool, store ========================================================
