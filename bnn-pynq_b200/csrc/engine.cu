@@ -42,9 +42,9 @@ struct DeviceState {
   std::vector<void*> allocs;
 };
 
-static size_t act_words_per_image(const NetDesc& n) {
+static size_t act_words_per_image(const NetDesc& n, int first = 0) {  // largest inter-layer tensor written by layers >= first
   size_t m = 0;
-  for (int i = 0; i + 1 < n.nlayers; i++) {
+  for (int i = first; i + 1 < n.nlayers; i++) {
     const LayerDesc& l = n.L[i];
     const size_t w = (size_t)out_dim(l) * out_dim(l) * out_words_per_pixel(l);
     m = std::max(m, w);
@@ -79,13 +79,16 @@ Engine::~Engine() {
   }
 }
 
-int Engine::chunk_images() const {
-  if (const char* e = std::getenv("BNN_B200_CHUNK")) { int v = std::atoi(e); if (v > 0) return v; }
-  if (!net_.is_cnv) return 32768;
-  // keeps the ping-pong activations inside the 126 MB L2 (largest: layer 0's output, 7 200 / 14 400 B per image, which exists
-  // only on the LOP3+POPC path; with layers 0+1 fused the largest is 1 568 / 3 136 B per image)
-  if (core_ >= 1 && fuse01_) return net_.L[1].out_mode == OUT_TERN ? 8192 : 16384;
-  return net_.L[1].out_mode == OUT_TERN ? 2048 : 4096;
+// Images per pass through the layer chain.  host = the pipelined host-buffer path, where a chunk is also the unit of H2D/compute
+// overlap; otherwise the device-resident path, where larger chunks mean fewer launches and less tail quantisation (the path uses
+// under 1% of HBM bandwidth, so nothing is gained by keeping the inter-layer tensors L2-resident there).
+int Engine::chunk_images(bool host) const {
+  if (const char* e = std::getenv(host ? "BNN_B200_HOST_CHUNK" : "BNN_B200_CHUNK")) { int v = std::atoi(e); if (v > 0) return v; }
+  if (!net_.is_cnv) return host ? 32768 : 65536;
+  const bool tern = net_.L[1].out_mode == OUT_TERN;
+  if (core_ >= 1 && fuse01_) return host ? (tern ? 8192 : 16384) : (tern ? 32768 : 65536);
+  // LOP3+POPC path: layer 0's output (7 200 / 14 400 B per image) exists in global memory; keep it inside the 126 MB L2
+  return tern ? 2048 : 4096;
 }
 
 int Engine::set_devices(const int* ids, int n) {
@@ -110,9 +113,23 @@ int Engine::ensure_devices() {
     }
   }
   // buffers are sized for the largest chunk either core selection may use (set_core can change between calls)
-  int chunk = 0;
-  { const int c0 = core_; core_ = 0; chunk = chunk_images(); core_ = 2; chunk = std::max(chunk, chunk_images()); core_ = c0; }
-  const size_t aw = act_words_per_image(net_);
+  // lane 0 also serves the device-resident path (larger chunks); per lane: images and bytes of the ping-pong activation buffers
+  int lane_chunk[kLanes];
+  size_t lane_act[kLanes];
+  {
+    const int c0 = core_;
+    for (int k = 0; k < kLanes; k++) {
+      core_ = 0;
+      const int cp = chunk_images(true);
+      const size_t ap = (size_t)cp * act_words_per_image(net_) * 4;
+      core_ = 2;
+      const int ct = std::max(chunk_images(true), k == 0 ? chunk_images(false) : 0);
+      const size_t at = (size_t)ct * act_words_per_image(net_, net_.is_cnv && fuse01_ ? 1 : 0) * 4;
+      lane_chunk[k] = std::max(cp, ct);
+      lane_act[k] = std::max(ap, at);
+    }
+    core_ = c0;
+  }
   const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
   for (int id : dev_ids_) {
     if (id < 0 || id >= count) { err_ = "bad device id"; return -1; }
@@ -129,14 +146,16 @@ int Engine::ensure_devices() {
       d->allocs.push_back(p);
       return p;
     };
-    for (auto& ln : d->lane) {
+    for (int k = 0; k < kLanes; k++) {
+      Lane& ln = d->lane[k];
+      const int chunk = lane_chunk[k];
       CK(cudaStreamCreateWithFlags(&ln.s, cudaStreamNonBlocking));
       CK(cudaEventCreate(&ln.e0));
       CK(cudaEventCreate(&ln.e1));
       ln.d_raw = (uint8_t*)alloc((size_t)chunk * raw_bytes);
       ln.d_in = alloc((size_t)chunk * net_.in_bytes);
-      ln.buf[0] = (uint32_t*)alloc((size_t)chunk * aw * 4);
-      ln.buf[1] = (uint32_t*)alloc((size_t)chunk * aw * 4);
+      ln.buf[0] = (uint32_t*)alloc(lane_act[k]);
+      ln.buf[1] = (uint32_t*)alloc(lane_act[k]);
       ln.d_out = alloc((size_t)chunk * net_.out_bytes);
       ln.d_cls = (int*)alloc((size_t)chunk * 4);
       if (!ln.d_raw || !ln.d_in || !ln.buf[0] || !ln.buf[1] || !ln.d_out || !ln.d_cls) { err_ = "cudaMalloc failed"; return -1; }
@@ -364,7 +383,7 @@ int Engine::infer_host(const uint8_t* input, int n, int ncls, int* classes, int1
   for (auto& d : dev_) if (!d->uploaded) { if (upload_all() != 0) return -1; break; }
   if (usec) *usec = 0;
   if (n <= 0) return 0;
-  const int G = (int)dev_.size(), chunk = chunk_images();
+  const int G = (int)dev_.size(), chunk = chunk_images(true);
   const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
   std::vector<uint64_t> tmp_words;
   if (!net_.is_cnv && !words && classes) { tmp_words.resize(n); words = tmp_words.data(); }

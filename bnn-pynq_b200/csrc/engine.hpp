@@ -86,7 +86,7 @@ class Engine {
   void enqueue_patches(DeviceState& ds, const std::vector<Patch>& p, cudaStream_t s);
   int run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s,
                 int32_t* tap_acc, uint32_t** bufs);
-  int chunk_images() const;
+  int chunk_images(bool host = false) const;
   bool fail(const std::string& m) { err_ = m; return false; }
 
   NetDesc net_;
