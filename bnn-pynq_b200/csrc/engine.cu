@@ -86,7 +86,7 @@ int Engine::chunk_images(bool host) const {
   if (const char* e = std::getenv(host ? "BNN_B200_HOST_CHUNK" : "BNN_B200_CHUNK")) { int v = std::atoi(e); if (v > 0) return v; }
   if (!net_.is_cnv) return host ? 32768 : 65536;
   const bool tern = net_.L[1].out_mode == OUT_TERN;
-  if (core_ >= 1 && fuse01_) return host ? (tern ? 8192 : 16384) : (tern ? 32768 : 65536);
+  if (core_ >= 1 && fuse01_) return host ? 8192 : (tern ? 32768 : 65536);
   // LOP3+POPC path: layer 0's output (7 200 / 14 400 B per image) exists in global memory; keep it inside the 126 MB L2
   return tern ? 2048 : 4096;
 }

@@ -123,22 +123,35 @@ __device__ __forceinline__ int cifar_q(int c) {
   return (int)r;
 }
 // records [n][3073] (label, R plane, G plane, B plane) -> int8 [n][1024 px][3]   (chaninterleave + quantiseAndPack)
-__global__ void k_prep_cifar(const uint8_t* __restrict__ rec, int8_t* __restrict__ q, int n) {
+// One image per CTA iteration: the 3 073-byte record (not even 4-byte aligned) is staged in shared memory with aligned 32-bit loads,
+// then every thread emits whole output words (4 interleaved bytes through the quantisation LUT), coalesced.
+__global__ void __launch_bounds__(256) k_prep_cifar(const uint8_t* __restrict__ rec, int8_t* __restrict__ q, int n) {
   __shared__ int8_t lut[256];
+  __shared__ __align__(16) uint8_t buf[3073 + 7];
   lut[threadIdx.x & 255] = (int8_t)cifar_q(threadIdx.x & 255);
-  __syncthreads();
-  const size_t total = (size_t)n * 3072;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const size_t img = i / 3072;
-    const int o = (int)(i % 3072), px = o / 3, c = o % 3;
-    q[i] = lut[rec[img * 3073 + 1 + c * 1024 + px]];
+  for (int img = blockIdx.x; img < n; img += gridDim.x) {
+    const uint8_t* src = rec + (size_t)img * 3073;
+    const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3);
+    const uint32_t* src4 = reinterpret_cast<const uint32_t*>(src - mis);
+    __syncthreads();  // previous image's reads of buf are done (and the LUT is written)
+    for (int w = threadIdx.x; w < (3073 + 3 + 3) / 4; w += 256) reinterpret_cast<uint32_t*>(buf)[w] = __ldg(src4 + w);  // stays inside the 4-byte words the record touches
+    __syncthreads();
+    const uint8_t* p = buf + mis + 1;  // R plane; G at +1024, B at +2048
+    uint32_t* dst = reinterpret_cast<uint32_t*>(q + (size_t)img * 3072);
+    for (int w = threadIdx.x; w < 768; w += 256) {
+      uint32_t v = 0;
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        const int o = 4 * w + e, px = o / 3, c = o - 3 * px;
+        v |= (uint32_t)(uint8_t)lut[p[c * 1024 + px]] << (8 * e);
+      }
+      dst[w] = v;
+    }
   }
 }
 void launch_prep_cifar(const uint8_t* records, int8_t* q, int n, cudaStream_t s) {
   if (n <= 0) return;
-  const size_t total = (size_t)n * 3072;
-  const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-  k_prep_cifar<<<blocks, 256, 0, s>>>(records, q, n);
+  k_prep_cifar<<<n < 148 * 8 ? n : 148 * 8, 256, 0, s>>>(records, q, n);
 }
 // pixels [n][784] -> bits [n][26 words]; bit = (byte >= 128)  <=>  (c/255)*2-1 >= 0 in float (foldedmv-offload.cpp:89-92)
 __global__ void k_prep_mnist(const uint8_t* __restrict__ px, uint32_t* __restrict__ bits, int n) {
