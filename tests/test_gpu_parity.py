@@ -144,3 +144,31 @@ def test_lfc_cores_agree(net):
         rt.set_core(core)
         _, words = rt.classify_mnist(px, 10, want_words=True)
         assert np.array_equal(words, want), "core %d" % core
+
+
+def _n_gpus():
+    import ctypes
+    try:
+        n = ctypes.c_int(0)
+        rt = ctypes.CDLL("libcudart.so")
+        return n.value if rt.cudaGetDeviceCount(ctypes.byref(n)) == 0 else 0
+    except OSError:
+        import torch
+        return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("net", ["cnvW1A1", "lfcW1A1"])
+def test_two_gpu_shards_equal_one_gpu(net):
+    """contiguous shards, replicated parameters, no collective; with faults every GPU applies the whole ordered list
+    but runs only its own segments.  Needs two visible devices (skipped on a one-GPU box)."""
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    from bnn import native
+    rt1 = native.Runtime(net, params_dir(net), devices=[0])
+    rt2 = native.Runtime(net, params_dir(net), devices=[0, 1])
+    n = 3001
+    d = synth_cifar(n, 11) if net in CNV else synth_mnist(n, 11)
+    assert np.array_equal(rt2.classify(d), rt1.classify(d))
+    fl = rt1.schedule_faults(n, 30, word_size=1, target=-1, seed=5)
+    assert np.array_equal(rt2.classify_with_fault_list(d, fl), rt1.classify_with_fault_list(d, fl))
+    assert np.array_equal(rt2.classify(d), rt1.classify(d))         # the persistent faults are the same on every device
