@@ -272,3 +272,13 @@ def pinned_array(nbytes):
 
 def free_pinned(p):
     lib().bnnb_free_host(p)
+
+
+def tmem_rate(warps, store=False):
+    """TMEM read (tcgen05.ld) or write (tcgen05.st) throughput in bytes per clock per SM with `warps` warps issuing."""
+    L = lib()
+    L.bnnb_tmem_rate.restype = C.c_double
+    v = L.bnnb_tmem_rate(int(warps), int(bool(store)))
+    if v < 0:
+        raise RuntimeError("tmem_rate failed")
+    return v

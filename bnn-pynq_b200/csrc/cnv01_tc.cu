@@ -16,6 +16,7 @@
 #include <type_traits>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
+#include "f4_common.cuh"
 
 namespace bnnb {
 namespace {
@@ -54,7 +55,7 @@ __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 1
 //   full[s], empty[s] warp 8 <-> half A  layer-1 accumulator slot s (of 4) full / read out
 template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
 __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
-                                                      int n_img, int* __restrict__ status) {
+                                                      int n_img, int out_fmt, int* __restrict__ status) {
   using S = Smem01<OUTM, F4>;
   constexpr int L1_A = S::L1_A;
   constexpr uint32_t SF_COL = 448;  // TMEM columns of the unit scale factors (F4)
@@ -393,7 +394,9 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         const uint32_t *r01 = r00 + WPP, *r10 = r00 + 30 * WPP, *r11 = r10 + WPP;
         uint32_t* dst = out + ((size_t)img * 196 + op) * WPP;
         if (OUTM == OUT_BIT) {
-          dst[j] = r00[j] | r01[j] | r10[j] | r11[j];
+          const uint32_t w = r00[j] | r01[j] | r10[j] | r11[j];
+          if (out_fmt == ACT_F4P) reinterpret_cast<uint4*>(out)[((size_t)img * 2 + j) * 196 + op] = f4_from_bits(w);  // [img][plane][pixel]
+          else dst[j] = w;
         } else {
           const uint32_t P = r00[2 + j] | r01[2 + j] | r10[2 + j] | r11[2 + j];
           const uint32_t M = (r00[j] & ~r00[2 + j]) & (r01[j] & ~r01[2 + j]) & (r10[j] & ~r10[2 + j]) & (r11[j] & ~r11[2 + j]);
@@ -413,22 +416,23 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
 }  // namespace
 
 template <int OUTM, bool F4>
-static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int grid, int* status, cudaStream_t s) {
+static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int grid, int out_fmt, int* status, cudaStream_t s) {
   using S = Smem01<OUTM, F4>;
   static_assert(S::TOTAL <= 226 * 1024, "shared memory budget");
   cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-  k_cnv01_tc<OUTM, F4><<<grid, 288, S::TOTAL, s>>>(L0, L1, in, out, n_img, status);
+  k_cnv01_tc<OUTM, F4><<<grid, 288, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status);
 }
 
-bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int* status,
-                     cudaStream_t s) {
+bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt,
+                     int* status, cudaStream_t s) {
+  if (out_fmt != ACT_BITS && !(out_fmt == ACT_F4P && L1.d.out_mode == OUT_BIT)) return false;
   if (n_img <= 0 || !L1.w8 || !L1.w4 || !L1.thr_tc || L0.d.N != 64 || L1.d.N != 64 || L1.d.ifm_dim != 30) return false;
   const int grid = n_img < num_sms ? n_img : num_sms;
   const bool bit = L1.d.out_mode == OUT_BIT;
-  if (bit && fp4) launch01<OUT_BIT, true>(L0, L1, in, out, n_img, grid, status, s);
-  else if (bit) launch01<OUT_BIT, false>(L0, L1, in, out, n_img, grid, status, s);
-  else if (fp4) launch01<OUT_TERN, true>(L0, L1, in, out, n_img, grid, status, s);
-  else launch01<OUT_TERN, false>(L0, L1, in, out, n_img, grid, status, s);
+  if (bit && fp4) launch01<OUT_BIT, true>(L0, L1, in, out, n_img, grid, out_fmt, status, s);
+  else if (bit) launch01<OUT_BIT, false>(L0, L1, in, out, n_img, grid, out_fmt, status, s);
+  else if (fp4) launch01<OUT_TERN, true>(L0, L1, in, out, n_img, grid, out_fmt, status, s);
+  else launch01<OUT_TERN, false>(L0, L1, in, out, n_img, grid, out_fmt, status, s);
   return true;
 }
 

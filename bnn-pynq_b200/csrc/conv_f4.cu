@@ -12,6 +12,7 @@
 #include <climits>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
+#include "f4_common.cuh"
 
 namespace bnnb {
 namespace {
@@ -58,7 +59,7 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
 
 template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
 __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
-                                                     int* __restrict__ status) {
+                                                     int in_fmt, int out_fmt, int* __restrict__ status) {
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
   extern __shared__ __align__(128) uint8_t smem[];
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
   for (int i = tid; i < 2 * Cfg::A_BYTES / 16; i += 384) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // pad pixels stay 0
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
-    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], 96); tc::mbar_init(&abuf_empty[i], 1); }
+    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], in_fmt == ACT_F4P ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
     tc::mbar_init_fence();
   }
@@ -128,8 +129,26 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
   const int K = (int)blockIdx.x < ngroups ? (ngroups - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;  // groups of this CTA
 
   if (role == 1) {
-    // ---- expander ------------------------------------------------------------------------------------------------------
+    // ---- operand planes of group k+1: ACT_F4P input = one TMA bulk copy per (image, plane), issued by one thread; ACT_BITS input
+    // = three warps expanding bit-packed activations ------------------------------------------------------------------------
     constexpr int CW = C / 32;
+    if (in_fmt == ACT_F4P) {
+      if (tid == 256) {
+        const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
+        constexpr uint32_t IMG_PLANE = Cfg::PXI * 16;  // bytes of one plane of one image
+        for (int k = 0; k < K; k++) {
+          const int img0 = ((int)blockIdx.x + k * (int)gridDim.x) * G, buf = k & 1;
+          if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
+          uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
+          const int valid = n_img - img0 < G ? n_img - img0 : G;  // rows of missing images keep stale (finite) codes; never stored
+          tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)valid * CW * IMG_PLANE);
+          for (int gi = 0; gi < valid; gi++)
+            for (int j = 0; j < CW; j++)
+              tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE + (size_t)gi * IMG_PLANE, in4 + ((size_t)(img0 + gi) * CW + j) * IMG_PLANE, IMG_PLANE,
+                           &abuf_full[buf]);
+        }
+      }
+    } else
     for (int k = 0; k < K; k++) {
       const int img0 = ((int)blockIdx.x + k * (int)gridDim.x) * G, buf = k & 1;
       if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
@@ -196,6 +215,8 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
         const int m = t * 128 + hw * 32 + lane;
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N + (uint32_t)eg * (N / 2);
         uint32_t b0[NWG], b1[NWG];
+        uint4 c4[NWG];  // e2m1 codes instead of bits when the consumer is another fp4 kernel
+        const bool codes = FOLD && !POOL && out_fmt != ACT_BITS;
         uint32_t r[2][32];
         tc::tmem_ld32(trow, r[0]);
 #pragma unroll
@@ -203,7 +224,10 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
           tc::tmem_ld_wait_dep(r[j & 1]);
           if (j + 1 < NWG) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
           uint32_t w0 = 0, w1 = 0;
-          if (FOLD) {
+          c4[j] = make_uint4(0, 0, 0, 0);
+          if (codes) {
+            c4[j] = f4_from_signs(r[j & 1]);
+          } else if (FOLD) {
 #pragma unroll
             for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
             w0 = ~w0;
@@ -230,7 +254,19 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
           row = sbits + (size_t)m * WPP;
         } else {  // straight to global: one output pixel (half of its channels) per thread
           const int gi = m / Cfg::PXI, rem = m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
-          if (m < Cfg::ROWS && y < OD && x < OD && img0 + gi < n_img) row = out + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * WPP;
+          const bool valid = m < Cfg::ROWS && y < OD && x < OD && img0 + gi < n_img;
+          if (valid && !codes) row = out + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * WPP;
+          if (valid && codes) {
+            const size_t img = (size_t)(img0 + gi);
+            const int px = y * OD + x;
+            uint4* out4 = reinterpret_cast<uint4*>(out);
+#pragma unroll
+            for (int j = 0; j < NWG; j++) {
+              const int pj = h * NW + eg * NWG + j;  // 32-channel plane of this layer's output
+              if (out_fmt == ACT_F4P) out4[(img * NWT + pj) * (OD * OD) + px] = c4[j];
+              else out4[((img >> 7) * (OD * OD * NWT) + (size_t)(px * NWT + pj)) * 128 + (img & 127)] = c4[j];  // ACT_F4T
+            }
+          }
         }
         if (row) {
           if (NWG == 2) {
@@ -260,7 +296,13 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
 #pragma unroll
           for (int q = 0; q < NWT / 4; q++) {
             if (OUTM == OUT_BIT) {
-              dst[q] = or4(or4(r00[q], r01[q]), or4(r10[q], r11[q]));
+              const uint4 o = or4(or4(r00[q], r01[q]), or4(r10[q], r11[q]));
+              if (out_fmt == ACT_F4P) {  // [img][plane][pixel], planes 4q .. 4q+3
+                uint4* out4 = reinterpret_cast<uint4*>(out) + ((size_t)(img0 + gi) * NWT + 4 * q) * PP + op;
+                out4[0] = f4_from_bits(o.x); out4[PP] = f4_from_bits(o.y); out4[2 * PP] = f4_from_bits(o.z); out4[3 * PP] = f4_from_bits(o.w);
+              } else {
+                dst[q] = o;
+              }
             } else {  // max over {-1,0,+1}: +1 if any +1; else -1 only if all four are -1
               constexpr int H = NWT / 4;
               const uint4 P = or4(or4(r00[H + q], r01[H + q]), or4(r10[H + q], r11[H + q]));
@@ -281,34 +323,44 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
 }
 
 template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
-bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::SMEM <= 226 * 1024, "shared memory budget");
   static_assert(Cfg::SLOTS * N <= Cfg::SF_COL, "TMEM budget");
   auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
   const int ngroups = (n_img + G - 1) / G;
-  kern<<<ngroups < num_sms ? ngroups : num_sms, 384, Cfg::SMEM, s>>>(L, in, out, n_img, status);
+  kern<<<ngroups < num_sms ? ngroups : num_sms, 384, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status);
   return true;
 }
 
 }  // namespace
 
-bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+bool conv_f4_supports(const LayerDesc& d) {
+  if (d.kind != KIND_CONV) return false;
+  const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
+  if (!a1 && !a2) return false;
+  return (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) || (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) ||
+         (d.ifm_ch == 128 && d.N == 256 && d.ifm_dim == 5 && !d.pool);
+}
+
+bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
   const LayerDesc& d = L.d;
-  if (d.kind != KIND_CONV || !L.w4 || !L.thr_tc || n_img <= 0) return false;
+  if (!conv_f4_supports(d) || !L.w4 || !L.thr_tc || n_img <= 0) return false;
+  if ((in_fmt != ACT_BITS || out_fmt != ACT_BITS) && d.out_mode != OUT_BIT) return false;  // the fp4 interchange formats are for 1-bit activations
+  if (in_fmt == ACT_F4T || (d.pool && out_fmt == ACT_F4T)) return false;
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {
-    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, 6, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, 6, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
   }
   if (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) {
-    if (a1) return launch_cfg<128, 128, 1, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a1) return launch_cfg<128, 128, 1, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
   }
   if (d.ifm_ch == 128 && d.N == 256 && d.ifm_dim == 5 && !d.pool) {  // two channel blocks of 128 share the operand planes
-    if (a1) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a1) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+    if (a2) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
   }
   return false;
 }

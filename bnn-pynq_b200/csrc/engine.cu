@@ -1,4 +1,5 @@
 #include "engine.hpp"
+#include "f4_common.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -124,7 +125,11 @@ int Engine::ensure_devices() {
       const size_t ap = (size_t)cp * act_words_per_image(net_) * 4;
       core_ = 2;
       const int ct = std::max(chunk_images(true), k == 0 ? chunk_images(false) : 0);
-      const size_t at = (size_t)ct * act_words_per_image(net_, net_.is_cnv && fuse01_ ? 1 : 0) * 4;
+      size_t at = (size_t)ct * act_words_per_image(net_, net_.is_cnv && fuse01_ ? 1 : 0) * 4;
+      // between fp4 kernels of a 1-bit network activations travel as e2m1 operand planes (4 bits per value, 128-image tiles)
+      for (int i = (net_.is_cnv ? 1 : 0); i + 1 < net_.nlayers; i++)
+        if (net_.L[i].out_mode == OUT_BIT)
+          at = std::max(at, (size_t)((ct + 127) / 128 * 128) * out_dim(net_.L[i]) * out_dim(net_.L[i]) * net_.L[i].N / 2);
       lane_chunk[k] = std::max(cp, ct);
       lane_act[k] = std::max(ap, at);
     }
@@ -287,10 +292,24 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
   int launches = 0;
   const bool per_layer = tap_acc != nullptr;  // when tapping, every layer writes its own buffer; else two ping-pong buffers
   int first_layer = 0;
+  // Activation format between layers (f4_common.cuh): on the fp4 core, between two fp4 kernels of a 1-bit network, the producer
+  // writes e2m1 operand planes in the consumer's own shared-memory layout (the consumer stages them with TMA bulk copies).
+  int fam[9] = {}, ofmt[9] = {};  // kernel family of layer i on this core: 1 = conv_f4, 2 = gemm_f4, 0 = other
+  if (core_ == 2 && !per_layer)
+    for (int i = 0; i < net_.nlayers; i++) fam[i] = conv_f4_supports(net_.L[i]) ? 1 : (gemm_f4_supports(ds.L[i]) ? 2 : 0);
+  const bool fused01 = core_ >= 1 && net_.is_cnv && !per_layer && fuse01_;
+  for (int i = 0; i + 1 < net_.nlayers; i++) {
+    const LayerDesc& p = net_.L[i];
+    const LayerDesc& c = net_.L[i + 1];
+    const bool producer_f4 = fam[i] != 0 || (fused01 && i == 1 && core_ == 2);
+    if (!producer_f4 || p.out_mode != OUT_BIT || c.in_mode != IN_XNOR) continue;
+    if (fam[i + 1] == 1 && fam[i] != 2) ofmt[i] = ACT_F4P;                 // conv consumer: image planes
+    if (fam[i + 1] == 2 && !p.pool && !(fused01 && i == 1)) ofmt[i] = ACT_F4T;  // gemm consumer: 128-image tiles
+  }
   if (core_ >= 1 && net_.is_cnv && !per_layer && fuse01_) {  // layers 0+1 in one tensor-core kernel
     ProfEv pe{nullptr, nullptr, 1, ds.id};
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
-    if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, core_ == 2, ds.d_status, s)) {
+    if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, core_ == 2, ofmt[1], ds.d_status, s)) {
       if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
       {
         const cudaError_t le = cudaGetLastError();
@@ -312,10 +331,11 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     ProfEv pe{nullptr, nullptr, i, ds.id};
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
     if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s);
-    else if (core_ == 2 && !tp && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
-    else if (core_ == 2 && !tp && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
+    else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, i > 0 ? ofmt[i - 1] : ACT_BITS, ofmt[i], ds.d_status, s)) {}
+    else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, i > 0 ? ofmt[i - 1] : ACT_BITS, ofmt[i], ds.d_status, s)) {}
     else if (core_ >= 1 && !tp && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
     else if (core_ >= 1 && !tp && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
+    else if ((i > 0 && ofmt[i - 1] != ACT_BITS) || ofmt[i] != ACT_BITS) { err_ = "layer " + std::to_string(i) + ": no kernel for the planned activation format"; return -1; }
     else launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s);
     if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
     {  // a launch that the device refuses (resources, configuration) must not pass silently

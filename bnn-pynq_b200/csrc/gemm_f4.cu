@@ -13,6 +13,7 @@
 #include <climits>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
+#include "f4_common.cuh"
 
 namespace bnnb {
 namespace {
@@ -48,7 +49,7 @@ struct GemmGeom {
 
 template <int NB, int INM, int OUTM>
 __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
-                                                     int* __restrict__ status) {
+                                                     int in_fmt, int out_fmt, int* __restrict__ status) {
   constexpr int SLAB = NB * 32, SLOTS = 3, SF_COL = 384, NW = NB / 32, EXP = 192, U = 4;  // EXP expander threads, U loads in flight each
   constexpr bool FOLD = OUTM == OUT_BIT;
   constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
@@ -71,7 +72,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
   if (tid == 0) {
     for (int i = 0; i < 2; i++) {
       tc::mbar_init(&a_empty[i], 1);
-      for (int q = 0; q < 4; q++) tc::mbar_init(&a_part[i][q], EXP);
+      for (int q = 0; q < 4; q++) tc::mbar_init(&a_part[i][q], in_fmt == ACT_F4T ? 1 : EXP);
     }
     for (int i = 0; i < SLOTS; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4); }
     for (int i = 0; i < GF_RING; i++) { tc::mbar_init(&ring_full[i], 1); tc::mbar_init(&ring_empty[i], 1); }
@@ -112,6 +113,27 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
   if (role == 1) {
     // ---- expander: tile tl -> operand buffer tl % nbuf ------------------------------------------------------------------------
     const int et = tid - 128;  // 0..191
+    if (in_fmt == ACT_F4T) {
+      // the producer wrote this tile's operand planes already (ACT_F4T): four TMA bulk copies, one per K quarter
+      if (et == 0) {
+        const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
+        for (int tl = 0; tl < T; tl++) {
+          const int buf = tl % g.nbuf, use = tl / g.nbuf;
+          if (use >= 1 && !failed && !tc::mbar_wait(&a_empty[buf], (uint32_t)(use - 1) & 1)) failed = true;
+          uint8_t* sa = smem + (size_t)buf * g.a_bytes;
+          const uint8_t* src = in4 + ((size_t)blockIdx.x + (size_t)tl * gridDim.x) * g.a_bytes;
+          for (int q = 0; q < 4; q++) {
+            const int s0 = (q * g.ks) / 4, s1 = ((q + 1) * g.ks) / 4;
+            if (s1 > s0) {
+              tc::mbar_expect_tx(&a_part[buf][q], (uint32_t)(s1 - s0) * 4096);
+              tc::bulk_g2s(sa + (size_t)s0 * 4096, src + (size_t)s0 * 4096, (uint32_t)(s1 - s0) * 4096, &a_part[buf][q]);
+            } else {
+              tc::mbar_arrive(&a_part[buf][q]);
+            }
+          }
+        }
+      }
+    } else {
     const size_t img_words = (size_t)g.kch * g.ipl;
     const int total = 128 * g.ks;  // items: (row, pair of chunks = one K=64 slab), row fastest: conflict-free 16-byte stores
     for (int tl = 0; tl < T; tl++) {
@@ -149,6 +171,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
           qn++;
         }
       }
+    }
     }
   } else if (role == 2) {
     // ---- loader: weight slabs in MMA order, R slots ahead ----------------------------------------------------------------------
@@ -213,6 +236,8 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
         tc::fence_after_sync();
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * NB;
         uint32_t b0[NW], b1[NW];
+        uint4 c4[NW];  // e2m1 codes instead of bits when the consumer is another gemm_f4 launch
+        const bool codes = FOLD && out_fmt == ACT_F4T;
         uint32_t r[2][32];
         tc::tmem_ld32(trow, r[0]);
 #pragma unroll
@@ -221,6 +246,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
           if (j + 1 < NW) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
           const float* th = sthr + nb * NB + j * 32;
           uint32_t w0 = 0, w1 = 0;
+          c4[j] = make_uint4(0, 0, 0, 0);
           if (OUTM == OUT_SCORE) {  // PassThroughActivation<ap_uint<16>>: (S + offset) mod 2^16, offset = #negative weights for 1-bit inputs
             if (img < n_img) {
               int16_t* o16 = reinterpret_cast<int16_t*>(out) + (size_t)img * g.N + nb * NB + j * 32;
@@ -236,6 +262,8 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
                 *reinterpret_cast<uint4*>(o16 + c) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
               }
             }
+          } else if (codes) {
+            c4[j] = f4_from_signs(r[j & 1]);
           } else if (FOLD) {
 #pragma unroll
             for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
@@ -257,7 +285,11 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
-        if (OUTM != OUT_SCORE && img < n_img) {
+        if (codes && img < n_img) {  // ACT_F4T: [tile][chunk = channel / 32][row]
+          uint4* out4 = reinterpret_cast<uint4*>(out) + (((size_t)blockIdx.x + (size_t)tl * gridDim.x) * nwt + (size_t)nb * NW) * 128 + hw * 32 + lane;
+#pragma unroll
+          for (int j = 0; j < NW; j++) out4[(size_t)j * 128] = c4[j];
+        } else if (OUTM != OUT_SCORE && img < n_img) {
           uint32_t* dst = out + (size_t)img * nwt * OPL + nb * NW;
 #pragma unroll
           for (int j = 0; j < NW; j += 2) {
@@ -275,7 +307,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
 }
 
 template <int NB, int INM, int OUTM>
-bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
   const LayerDesc& d = L.d;
   GemmGeom g;
   g.K = d.K; g.N = d.N; g.kch = d.K / 32; g.ks = d.K / 64; g.nblk = d.N / NB;
@@ -290,19 +322,19 @@ bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, i
   auto kern = k_gemm_f4<NB, INM, OUTM>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   const int ntiles = (n_img + 127) / 128;
-  kern<<<ntiles < num_sms ? ntiles : num_sms, 384, smem, s>>>(L, g, in, out, n_img, status);
+  kern<<<ntiles < num_sms ? ntiles : num_sms, 384, smem, s>>>(L, g, in, out, n_img, in_fmt, out_fmt, status);
   return true;
 }
 
 template <int NB>
-bool launch_nb(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+bool launch_nb(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
   const int im = L.d.in_mode, om = L.d.out_mode;
-  if (im == IN_XNOR && om == OUT_BIT) return launch_g<NB, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-  if (im == IN_XNOR && om == OUT_SCORE) return launch_g<NB, IN_XNOR, OUT_SCORE>(L, in, out, n_img, num_sms, status, s);
-  if (im == IN_BIN && om == OUT_TERN) return launch_g<NB, IN_BIN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
-  if (im == IN_TERN && om == OUT_TERN) return launch_g<NB, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
-  if (im == IN_TERN && om == OUT_SCORE) return launch_g<NB, IN_TERN, OUT_SCORE>(L, in, out, n_img, num_sms, status, s);
-  if (im == IN_TERN && om == OUT_BIT) return launch_g<NB, IN_TERN, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
+  if (im == IN_XNOR && om == OUT_BIT) return launch_g<NB, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+  if (im == IN_XNOR && om == OUT_SCORE) return launch_g<NB, IN_XNOR, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+  if (im == IN_BIN && om == OUT_TERN) return launch_g<NB, IN_BIN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+  if (im == IN_TERN && om == OUT_TERN) return launch_g<NB, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+  if (im == IN_TERN && om == OUT_SCORE) return launch_g<NB, IN_TERN, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+  if (im == IN_TERN && om == OUT_BIT) return launch_g<NB, IN_TERN, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
   return false;
 }
 
@@ -311,11 +343,21 @@ bool launch_nb(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, 
 int gemm_f4_block(const LayerDesc& d) { return d.N % 128 == 0 ? 128 : 64; }
 
 // Returns false when the layer cannot run on this kernel (the caller falls back to the next core).
-bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+bool gemm_f4_supports(const DevLayer& L) {
   const LayerDesc& d = L.d;
-  if (!L.w4s || !L.thr_tc || n_img <= 0 || d.pool || d.ofm_dim != 1 || d.K % 64 || d.ifm_ch % 64 || d.N % 64 || L.kpad != d.K) return false;
+  if (!L.w4s || !L.thr_tc || d.pool || d.ofm_dim != 1 || d.K % 64 || d.ifm_ch % 64 || d.N % 64 || L.kpad != d.K) return false;
   if (d.K != d.ifm_ch * d.ifm_dim * d.ifm_dim) return false;  // the im2col row must be the whole activation tensor of the image
-  return gemm_f4_block(d) == 128 ? launch_nb<128>(L, in, out, n_img, num_sms, status, s) : launch_nb<64>(L, in, out, n_img, num_sms, status, s);
+  const int im = d.in_mode, om = d.out_mode;
+  return (im == IN_XNOR && (om == OUT_BIT || om == OUT_SCORE)) || (im == IN_BIN && om == OUT_TERN) || (im == IN_TERN);
+}
+
+bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
+  const LayerDesc& d = L.d;
+  if (!gemm_f4_supports(L) || n_img <= 0) return false;
+  if (in_fmt == ACT_F4P || out_fmt == ACT_F4P) return false;
+  if (in_fmt == ACT_F4T && d.in_mode != IN_XNOR) return false;
+  if (out_fmt == ACT_F4T && d.out_mode != OUT_BIT) return false;
+  return gemm_f4_block(d) == 128 ? launch_nb<128>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s) : launch_nb<64>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
 }
 
 }  // namespace bnnb

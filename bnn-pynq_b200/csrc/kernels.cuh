@@ -51,14 +51,18 @@ void launch_layer_popc(const DevLayer& L, const uint32_t* in, uint32_t* out, int
 bool launch_conv_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
 void launch_thr_tc(const DevLayer& L, cudaStream_t s);
 // conv layers on kind::mxf4 (conv_f4.cu)
-bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
+// in_fmt / out_fmt: ActFmt of f4_common.cuh (ACT_BITS everywhere except between fp4 kernels of a 1-bit network)
+bool conv_f4_supports(const LayerDesc& d);
+bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s);
 // fully-connected layers on kind::mxf4 (gemm_f4.cu); gemm_f4_block = channel block width NB of the slab layout
 int gemm_f4_block(const LayerDesc& d);
-bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
+bool gemm_f4_supports(const DevLayer& L);
+bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s);
 // K-streamed GEMM for FC / small conv layers (gemm_tc.cu)
 bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
 // fused CNV layers 0+1 (cnv01_tc.cu): int8 HWC image -> pooled, bit-packed layer-1 output
-bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int* status, cudaStream_t s);
+bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt, int* status,
+                     cudaStream_t s);
 
 // ---- class decode for CNV (multi-image rule, foldedmv-offload.h:398-406) ----
 void launch_cnv_classes(const int16_t* scores, int n, int ncls, int* classes, cudaStream_t s);

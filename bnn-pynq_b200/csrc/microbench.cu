@@ -94,3 +94,61 @@ extern "C" double bnnb_microbench(int which, double* clock_mhz) {
   if (which == 1) return total / 32.0 * (16.0 * 8 * 32) / (best * 1e-3);  // one mma per warp = 4096 MACs
   return total / (best * 1e-3);
 }
+
+// ---- TMEM read / write throughput: `warps` warps (1..8; warp w owns lane quarter w % 4) each issue `iters` tcgen05.ld (or .st)
+// .32x32b.x32 (4 KB per warp-instruction) back to back.  Returns bytes per clock per SM (one CTA). --------------------------------
+#include "tcgen05.cuh"
+namespace {
+__global__ void __launch_bounds__(256) k_tmem_rate(int warps, int iters, int store, long long* cyc, uint32_t* sink) {
+  __shared__ uint32_t tmem_base;
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) bnnb::tc::tmem_alloc(&tmem_base, 512);
+  bnnb::tc::fence_before_sync();
+  __syncthreads();
+  bnnb::tc::fence_after_sync();
+  const uint32_t t0 = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (warp >> 2) * 256;
+  uint32_t r[32];
+#pragma unroll
+  for (int i = 0; i < 32; i++) r[i] = threadIdx.x + i;
+  if (warp < warps) { bnnb::tc::tmem_st32(t0, r); bnnb::tc::tmem_st32(t0 + 32, r); bnnb::tc::tmem_st_wait(); }
+  __syncthreads();
+  const long long c0 = clock64();
+  uint32_t acc = 0;
+  if (warp < warps) {
+    for (int it = 0; it < iters; it++) {
+      if (store) {
+        bnnb::tc::tmem_st32(t0 + (it & 7) * 32, r);
+      } else {
+        bnnb::tc::tmem_ld32(t0 + (it & 7) * 32, r);
+      }
+    }
+    if (store) bnnb::tc::tmem_st_wait();
+    else bnnb::tc::tmem_ld_wait_dep(r);
+#pragma unroll
+    for (int i = 0; i < 32; i++) acc ^= r[i];
+  }
+  __syncthreads();
+  const long long c1 = clock64();
+  if (threadIdx.x == 0) *cyc = c1 - c0;
+  if (acc == 0x12345678u) sink[0] = acc;
+  bnnb::tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) bnnb::tc::tmem_dealloc(tmem_base, 512);
+}
+}  // namespace
+
+extern "C" double bnnb_tmem_rate(int warps, int store) {
+  long long* cyc; uint32_t* sink;
+  cudaSetDevice(0);
+  if (cudaMalloc(&cyc, 8) != cudaSuccess) return -1;
+  cudaMalloc(&sink, 4);
+  const int iters = 4096;
+  k_tmem_rate<<<1, 256>>>(warps, iters, store, cyc, sink);
+  k_tmem_rate<<<1, 256>>>(warps, iters, store, cyc, sink);
+  long long c = 0;
+  const cudaError_t e = cudaDeviceSynchronize();
+  cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
+  cudaFree(cyc); cudaFree(sink);
+  if (e != cudaSuccess || c <= 0) return -1;
+  return (double)warps * iters * 4096.0 / (double)c;
+}

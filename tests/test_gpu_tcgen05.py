@@ -107,3 +107,11 @@ def test_mma_kind_switch_cost_report():
         _, c_ctl = native.tc_probe_fp4(A, B, 0, reps, mix=-g)
         out[g] = {"clk_per_group_mixed": c_mix / reps, "clk_per_group_fp4_only": c_ctl / reps}
     print("kind switch:", out)
+
+
+def test_tmem_rate_report():
+    """Timing report: TMEM -> register (tcgen05.ld) and register -> TMEM (tcgen05.st) bytes per clock per SM by number of warps."""
+    from bnn import native
+    out = {"ld": {w: round(native.tmem_rate(w, False), 1) for w in (1, 2, 4, 8)}, "st": {w: round(native.tmem_rate(w, True), 1) for w in (1, 4, 8)}}
+    print("TMEM bytes/clk/SM:", out)
+    assert out["ld"][4] > 0
