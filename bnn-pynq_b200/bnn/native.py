@@ -282,3 +282,13 @@ def tmem_rate(warps, store=False):
     if v < 0:
         raise RuntimeError("tmem_rate failed")
     return v
+
+
+def tc_rate_fp4(N, taps=False):
+    """Clocks per tcgen05 kind::mxf4 MMA (M=128, K=64) at width N from a lean, fully unrolled issue loop."""
+    L = lib()
+    L.bnnb_tc_rate_fp4.restype = C.c_double
+    v = L.bnnb_tc_rate_fp4(int(N), int(bool(taps)))
+    if v < 0:
+        raise RuntimeError("tc_rate_fp4 failed")
+    return v

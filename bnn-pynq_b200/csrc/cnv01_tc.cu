@@ -9,7 +9,7 @@
 // image (m = y*32 + x: the 3x3x3 window row ky of pixel (y,x) is the first 9 bytes of P[m + 32*ky]).  K is laid out as
 // [ky][16]: k = ky*16 + (kx*3 + c) with zero weights for the 7 trailing bytes of each ky and for the whole 4th chunk, so
 // one tile needs two K=32 MMAs whose A descriptors differ only by a start shift (LBO = 32 rows).
-// Warp-specialised CTA (one per SM, 288 threads): four warps run layer 1's epilogue on image i, four warps stage image i+1
+// Warp-specialised CTA (one per SM, 576 threads): eight warps run layer 1's epilogue on image i, eight warps stage image i+1
 // (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one thread prefetches images by TMA bulk copy two
 // images ahead and issues all MMAs, interleaving layer 1 of image i with layer 0 of image i+1 tile by tile.
 #include <climits>
@@ -41,20 +41,21 @@ template <int OUTM, bool F4> struct Smem01 {
                        OFF_BITS = OFF_B0 + B0_BYTES, OFF_THR = OFF_BITS + BITS, TOTAL = OFF_THR + 2 * 64 * 2 * 4;
 };
 
-__device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 
-// Warp roles (288 threads): warps 0-3 = half A (layer-1 epilogue, pool, store), warps 4-7 = half B (layer-0 epilogue into the
-// other operand buffer); half A also builds the window planes, warp 8 = image prefetch (TMA) + MMA issuer for both layers.
+// Warp roles (576 threads): warps 0-7 = half A (layer-1 epilogue, pool, store), warps 8-15 = half B (layer-0 epilogue into the
+// other operand buffer), each half split into two teams of four warps by 32-channel half (the per-tile epilogue is a latency
+// chain: two teams halve it); half A also builds the window planes, warp 16 = layer-1 MMA issuer, warp 17 = image prefetch (TMA) + layer-0 MMA issuer.
 // The roles are decoupled by mbarriers only (no CTA-wide barrier in steady state):
 //   img_full[b]   TMA    -> half A   image buffer b holds an image                      (expect_tx 3072 bytes)
-//   p_full[b]     half A -> warp 8   window plane b is built (and image buffer b free)  (128 arrivals)
-//   p_empty[b]    warp 8 -> half A   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
-//   f0[s], e0[s]  warp 8 <-> half B  layer-0 accumulator slot s (of 3) full / read out   (commit / 4 arrivals)
-//   abuf_full[b]  half B -> warp 8   layer-1 operand buffer b holds a staged image      (128 arrivals)
-//   abuf_empty[b] warp 8 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
-//   full[s], empty[s] warp 8 <-> half A  layer-1 accumulator slot s (of 4) full / read out
+//   p_full[b]     half A -> warp 16   window plane b is built (and image buffer b free)  (256 arrivals)
+//   p_empty[b]    warp 16 -> half A   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
+//   f0[s], e0[s]  warp 16 <-> half B  layer-0 accumulator slot s (of 3) full / read out   (commit / 8 arrivals)
+//   abuf_full[b]  half B -> warp 16   layer-1 operand buffer b holds a staged image      (256 arrivals)
+//   abuf_empty[b] warp 16 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
+//   full[s], empty[s] warp 16 <-> half A  layer-1 accumulator slot s (of 4) full / read out
 template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
-__global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
+__global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
                                                       int n_img, int out_fmt, int* __restrict__ status) {
   using S = Smem01<OUTM, F4>;
   constexpr int L1_A = S::L1_A;
@@ -77,38 +78,38 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   int32_t* sthr0 = reinterpret_cast<int32_t*>(smem + S::OFF_THR);  // layer 0: floor(thr/2)   [64][2]
   int32_t* sthr1 = sthr0 + 128;                                    // layer 1: adjusted       [64][2] (F4: as float)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int role = warp < 4 ? 0 : (warp < 8 ? 1 : 2);              // 0: half A, 1: half B, 2: issuer + loader
-  const int ht = tid & 127, hw = warp & 3;  // thread / warp index inside the half; hw selects the TMEM lane quarter
+  const int role = warp < 8 ? 0 : (warp < 16 ? 1 : 2);             // 0: half A, 1: half B, 2: issuers (warp 16: layer 1; warp 17: layer 0 + TMA)
+  const int ht = tid & 255, hw = warp & 3, team = (warp >> 2) & 1;  // thread in the half; TMEM lane quarter; 32-channel half
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
-  for (int i = tid; i < 64 * 9 * S::NPL; i += 288) {  // layer-1 weights -> chunk-major operand layout
+  for (int i = tid; i < 64 * 9 * S::NPL; i += 576) {  // layer-1 weights -> chunk-major operand layout
     const int n = i % 64, kc = i / 64;
     const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
     *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = *reinterpret_cast<const uint4*>(src + kc * 16);
   }
-  for (int i = tid; i < 64 * 64; i += 288) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
+  for (int i = tid; i < 64 * 64; i += 576) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
     sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)v;
   }
-  for (int i = tid; i < 128; i += 288) {
+  for (int i = tid; i < 128; i += 576) {
     const int t = L0.thr[i];
     sthr0[i] = t == INT_MAX ? INT_MAX : (t >> 1);  // thr < 2S  <=>  floor(thr/2) < S
     const int t1 = L1.thr_tc[i];
     if (F4) reinterpret_cast<float*>(sthr1)[i] = t1 == INT_MAX ? 3.0e38f : (float)t1;
     else sthr1[i] = t1;
   }
-  for (int i = tid; i < 2 * L1_A / 16; i += 288) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
-  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += 288) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < 2 * L1_A / 16; i += 576) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
+  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += 576) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
     for (int i = 0; i < 2; i++) {
-      tc::mbar_init(&abuf_full[i], 128); tc::mbar_init(&abuf_empty[i], 1);
-      tc::mbar_init(&p_full[i], 128); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
+      tc::mbar_init(&abuf_full[i], 256); tc::mbar_init(&abuf_empty[i], 1);
+      tc::mbar_init(&p_full[i], 256); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
     }
-    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4); }
-    for (int i = 0; i < L0_SLOTS; i++) { tc::mbar_init(&f0[i], 1); tc::mbar_init(&e0[i], 4); }
+    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
+    for (int i = 0; i < L0_SLOTS; i++) { tc::mbar_init(&f0[i], 1); tc::mbar_init(&e0[i], 8); }
     tc::mbar_init(&pre_done, 2);
     tc::mbar_init_fence();
   }
@@ -139,7 +140,7 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
     uint8_t* sPk = sP + (size_t)buf * P_BYTES;
 #pragma unroll 3
-    for (int m = ht; m < 1024 + 64; m += 128) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
+    for (int m = ht; m < 1024 + 64; m += 256) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
       const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
       uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
       if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
@@ -150,14 +151,12 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     tc::mbar_arrive(&p_full[buf]);
   };
   if (role == 1) {
-    // ================= half B: window plane of image k, then layer-0 epilogue into layer-1 operand buffer k&1 =================
-    int thrA[64];  // first thresholds in registers: the epilogue's shared-memory traffic competes with the MMA operand reads
+    // ================= half B (8 warps): layer-0 epilogue into layer-1 operand buffer k&1; team = 32-channel half ================
+    int thrA[32];  // first thresholds in registers: the epilogue's shared-memory traffic competes with the MMA operand reads
 #pragma unroll
-    for (int n = 0; n < 64; n++) thrA[n] = FOLD ? -(min(sthr0[2 * n], 1 << 26) + 1) : sthr0[2 * n];
-    auto preload0 = [&](int slot) {  // this warp's lane quarter of layer-0 accumulator `slot`
-      const uint32_t t0 = tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64;
-      tc::tmem_st32(t0, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
-      tc::tmem_st32(t0 + 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[32]));
+    for (int c = 0; c < 32; c++) thrA[c] = FOLD ? -(min(sthr0[2 * (team * 32 + c)], 1 << 26) + 1) : sthr0[2 * (team * 32 + c)];
+    auto preload0 = [&](int slot) {  // this warp's lane quarter and channel half of layer-0 accumulator `slot`
+      tc::tmem_st32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
       tc::tmem_st_wait();
     };
     if (FOLD) {
@@ -179,66 +178,62 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
         const bool valid = x < 30 && y < 30;
-        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64;
+        uint32_t r[32];
+        tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, r);
+        tc::tmem_ld_wait_dep(r);
+        if (FOLD) {  // the top nibble of acc - thr - 1 is 0xF (decision 0) or 0x0 (decision 1): e2m1 code = ~nibble & 0x2
+          uint32_t v[4];
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
-          uint32_t r[32];
-          tc::tmem_ld32(trow + j * 32, r);
-          tc::tmem_ld_wait();
-          if (FOLD) {  // the top nibble of acc - thr - 1 is 0xF (decision 0) or 0x0 (decision 1): e2m1 code = ~nibble & 0x2
-            uint32_t v[4];
+          for (int q = 0; q < 4; q++) {
+            uint32_t wv = 0;
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-              uint32_t wv = 0;
+            for (int e = 7; e >= 0; e--) wv = __funnelshift_l(r[q * 8 + e], wv, 4);
+            v[q] = ~wv & 0x22222222u;
+          }
+          if (valid) *reinterpret_cast<uint4*>(sA + (size_t)team * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+        } else if (F4) {  // 32 channels = 32 e2m1 nibbles = one uint4 store into plane `team`: 1 -> 0x2, 0 -> 0x0, -1 -> 0xA
+          uint32_t v[4];
 #pragma unroll
-              for (int e = 7; e >= 0; e--) wv = __funnelshift_l(r[q * 8 + e], wv, 4);
-              v[q] = ~wv & 0x22222222u;
+          for (int q = 0; q < 4; q++) {
+            uint32_t wv = 0;
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+              const int c = q * 8 + e, n = team * 32 + c;
+              const int sv = (int)r[c];
+              if (OUTM == OUT_TERN) {
+                const int cnt = (thrA[c] < sv) + (sthr0[2 * n + 1] < sv);  // 0, 1, 2 -> -1, 0, +1
+                wv |= ((0x20Au >> (4 * cnt)) & 0xFu) << (4 * e);
+              } else {
+                if (thrA[c] < sv) wv |= 0x2u << (4 * e);
+              }
             }
-            if (valid) *reinterpret_cast<uint4*>(sA + (size_t)j * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
-          } else if (F4) {  // 32 channels = 32 e2m1 nibbles = one uint4 store into plane j: 1 -> 0x2, 0 -> 0x0, -1 -> 0xA
+            v[q] = wv;
+          }
+          if (valid) *reinterpret_cast<uint4*>(sA + (size_t)team * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+        } else {
+#pragma unroll
+          for (int c16 = 0; c16 < 2; c16++) {  // one 16-channel chunk = one uint4 store
             uint32_t v[4];
 #pragma unroll
             for (int q = 0; q < 4; q++) {
               uint32_t wv = 0;
 #pragma unroll
-              for (int e = 0; e < 8; e++) {
-                const int c = q * 8 + e, n = j * 32 + c;
-                const int s = (int)r[c];
-                if (OUTM == OUT_TERN) {
-                  const int cnt = (thrA[n] < s) + (sthr0[2 * n + 1] < s);  // 0, 1, 2 -> -1, 0, +1
-                  wv |= ((0x20Au >> (4 * cnt)) & 0xFu) << (4 * e);
-                } else {
-                  if (thrA[n] < s) wv |= 0x2u << (4 * e);
-                }
+              for (int e = 0; e < 4; e++) {
+                const int c = c16 * 16 + q * 4 + e, n = team * 32 + c;
+                const int sv = (int)r[c];
+                int val = thrA[c] < sv;                                           // {0,1}
+                if (OUTM == OUT_TERN) val = val + (sthr0[2 * n + 1] < sv) - 1;    // {-1,0,+1}
+                wv |= (uint32_t)(val & 0xff) << (8 * e);
               }
               v[q] = wv;
             }
-            if (valid) *reinterpret_cast<uint4*>(sA + (size_t)j * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
-          } else {
-#pragma unroll
-            for (int c16 = 0; c16 < 2; c16++) {  // one 16-channel chunk = one uint4 store
-              uint32_t v[4];
-#pragma unroll
-              for (int q = 0; q < 4; q++) {
-                uint32_t wv = 0;
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                  const int c = c16 * 16 + q * 4 + e, n = j * 32 + c;
-                  const int s = (int)r[c];
-                  int val = thrA[n] < s;                                          // {0,1}
-                  if (OUTM == OUT_TERN) val = val + (sthr0[2 * n + 1] < s) - 1;   // {-1,0,+1}
-                  wv |= (uint32_t)(val & 0xff) << (8 * e);
-                }
-                v[q] = wv;
-              }
-              if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * j + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
-            }
+            if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * team + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
           }
         }
         if (FOLD) preload0(slot);
         tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&e0[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
+        if (lane == 0) tc::mbar_arrive(&e0[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
       }
       tc::fence_async_smem();  // operand planes were written through the generic proxy and are read by the async proxy (MMA)
       tc::mbar_arrive(&abuf_full[buf]);
@@ -256,7 +251,7 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       const uint32_t a1_lo[2] = {tc::desc_lo(sA_u, L1_PLANE), tc::desc_lo(sA_u + L1_A, L1_PLANE)};
       const uint32_t b0_lo = tc::desc_lo(sB0_u, 64 * 16), b1_lo = tc::desc_lo(sB1_u, 64 * 16);
       for (int k = 0; k < 2 && k < K; k++)
-        if (leader) {
+        if (leader && warp == 17) {
           tc::mbar_expect_tx(&img_full[k], 3072);
           tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
         }
@@ -293,7 +288,11 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         tc::fence_after_sync();
         const uint32_t acc = tmem + (uint32_t)slot * 64;
         bool firstmma = true;
-        if (leader) {
+        if (leader && F4) {
+          tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, FOLD ? 1u : 0u);
+          tc::commit(&full[slot]);
+          if (t == L1_TILES - 1) tc::commit(&abuf_empty[buf]);
+        } else if (leader) {
 #pragma unroll
         for (int tap = 0; tap < 9; tap++) {
           const uint32_t off = (uint32_t)((tap / 3) * 30 + tap % 3 + t * 128) * 16;
@@ -315,30 +314,28 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         }
         __syncwarp();
       };
-      if (K > 0)
-        for (int t = 0; t < L0_TILES; t++) issue_l0(0, t);
-      // stage k: layer 0 of image k+1 is front-loaded (two tiles per layer-1 tile), so that image k+1 is completely staged about
-      // three layer-1 tiles before the stage ends and the next stage starts without a bubble
-      for (int k = 0; k < K; k++) {
-        for (int t = 0; t < L0_TILES / 2; t++) {
-          if (k + 1 < K) { issue_l0(k + 1, 2 * t); issue_l0(k + 1, 2 * t + 1); }
-          issue_l1(k, t);
-        }
-        for (int t = L0_TILES / 2; t < L1_TILES; t++) issue_l1(k, t);
+      // Two issuer warps: every tile costs the issuing thread a fixed ~250 clocks (barrier poll, fence, descriptor set-up, commit)
+      // on top of ~30 per MMA, so one thread cannot feed both layers (measured: the kernel with all MMAs and epilogues removed still
+      // took 4 240 clocks per image).  Layer 1's issue rate is below the pipe's execution rate, so the in-order MMA queue stays
+      // short and layer 0's tiles do not wait behind it.
+      if (warp == 17) {
+        for (int k = 0; k < K; k++)
+          for (int t = 0; t < L0_TILES; t++) issue_l0(k, t);
+      } else {
+        for (int k = 0; k < K; k++)
+          for (int t = 0; t < L1_TILES; t++) issue_l1(k, t);
       }
     }
   } else {
-    // ================= half A: layer-1 epilogue, 2x2 max-pool, store ========================================================
+    // ================= half A (8 warps): layer-1 epilogue, 2x2 max-pool, store; team = 32-channel half ==========================
     constexpr int WPP = 2 * S::OPL;
     using acc_t = typename std::conditional<F4, float, int>::type;  // kind::mxf4 accumulates in fp32 (exact: |acc| <= 1152)
     const acc_t* sthr1t = reinterpret_cast<const acc_t*>(sthr1);
-    acc_t thrA[64];
+    acc_t thrA[32];
 #pragma unroll
-    for (int n = 0; n < 64; n++) thrA[n] = FOLD ? (acc_t)(-((float)sthr1t[2 * n] + 0.5f)) : sthr1t[2 * n];
+    for (int c = 0; c < 32; c++) thrA[c] = FOLD ? (acc_t)(-((float)sthr1t[2 * (team * 32 + c)] + 0.5f)) : sthr1t[2 * (team * 32 + c)];
     auto preload1 = [&](int slot) {
-      const uint32_t t0 = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64;
-      tc::tmem_st32(t0, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
-      tc::tmem_st32(t0 + 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[32]));
+      tc::tmem_st32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
       tc::tmem_st_wait();
     };
     if (FOLD) {
@@ -358,37 +355,33 @@ __global__ void __launch_bounds__(288, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
-        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64;
+        uint32_t r[32];
+        tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, r);
+        tc::tmem_ld_wait_dep(r);
+        uint32_t b0 = 0, b1 = 0;
+        if (FOLD) {
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
-          uint32_t r[32];
-          tc::tmem_ld32(trow + j * 32, r);
-          tc::tmem_ld_wait();
-          uint32_t b0 = 0, b1 = 0;
-          if (FOLD) {
+          for (int c = 31; c >= 0; c--) b0 = __funnelshift_l(r[c], b0, 1);  // sign bits, channel c at bit c
+          b0 = ~b0;
+        } else {
 #pragma unroll
-            for (int c = 31; c >= 0; c--) b0 = __funnelshift_l(r[c], b0, 1);  // sign bits, channel c at bit c
-            b0 = ~b0;
-          } else {
-#pragma unroll
-            for (int c = 0; c < 32; c++) {
-              const acc_t s = F4 ? (acc_t)__uint_as_float(r[c]) : (acc_t)(int)r[c];
-              const int t0 = thrA[j * 32 + c] < s;
-              if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
-              else { const int t1 = sthr1t[2 * (j * 32 + c) + 1] < s; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
-            }
+          for (int c = 0; c < 32; c++) {
+            const acc_t sv = F4 ? (acc_t)__uint_as_float(r[c]) : (acc_t)(int)r[c];
+            const int t0 = thrA[c] < sv;
+            if (OUTM == OUT_BIT) b0 |= (uint32_t)t0 << c;
+            else { const int t1 = sthr1t[2 * (team * 32 + c) + 1] < sv; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
           }
-          sbits[(size_t)m * WPP + j] = b0;
-          if (OUTM == OUT_TERN) sbits[(size_t)m * WPP + 2 + j] = b1;
         }
+        sbits[(size_t)m * WPP + team] = b0;
+        if (OUTM == OUT_TERN) sbits[(size_t)m * WPP + 2 + team] = b1;
         if (FOLD) preload1(slot);
         tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
+        if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
       }
       half_sync(1);
       // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
-      for (int i = ht; i < 196 * 2; i += 128) {
+      for (int i = ht; i < 196 * 2; i += 256) {
         const int j = i & 1, op = i >> 1, oy = op / 14, ox = op % 14;
         const uint32_t* r00 = sbits + (size_t)((2 * oy) * 30 + 2 * ox) * WPP;
         const uint32_t *r01 = r00 + WPP, *r10 = r00 + 30 * WPP, *r11 = r10 + WPP;
@@ -420,7 +413,7 @@ static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
   using S = Smem01<OUTM, F4>;
   static_assert(S::TOTAL <= 226 * 1024, "shared memory budget");
   cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-  k_cnv01_tc<OUTM, F4><<<grid, 288, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status);
+  k_cnv01_tc<OUTM, F4><<<grid, 576, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status);
 }
 
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt,

@@ -217,3 +217,73 @@ extern "C" int bnnb_tc_probe_fp4_mix(const uint8_t* A, const uint8_t* B, int32_t
   cudaFree(dA); cudaFree(dB); cudaFree(dD); cudaFree(dC); cudaFree(dS);
   return e == cudaSuccess ? st : -1;
 }
+
+// ---- lean issue-rate probe: fully unrolled kind::mxf4 MMAs on (lo, hi) descriptor words, converged warp + elect_one, so that the
+// measured clocks per MMA are the tensor pipe's and not the issuing thread's.  taps != 0: the A start moves through the nine
+// (ky*30 + kx) row offsets of a 3x3 window (16-byte, mostly not 128-byte aligned), as in the implicit-im2col kernels. -----------------
+namespace {
+__global__ void __launch_bounds__(128) k_tc_rate_fp4(int N, int taps, int iters, long long* cyc, int* status) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_base;
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < (200 * 1024) / 16; i += 128) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0x22222222u, 0x0a0a0a0au, 0x20202020u, 0x02020202u);
+  fence_async_smem();
+  if (warp == 0) tmem_alloc(&tmem_base, 512);
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init_fence(); }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = tmem_base, sf = tmem + 384;
+  tmem_fill16(sf + ((uint32_t)(warp * 32) << 16), 0x7f7f7f7fu);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  long long t0 = 0;
+  if (warp == 0) {
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_mxf4(128, N), d_hi = desc_hi(128);
+    const uint32_t a_lo = desc_lo(smem_u32(smem), 1024 * 16), b_lo = desc_lo(smem_u32(smem) + 64 * 1024, (uint32_t)N * 16);
+    t0 = clock64();
+    for (int it = 0; it < iters; it++) {
+      if (leader) {
+#pragma unroll
+        for (int tap = 0; tap < 9; tap++) {
+          const uint32_t off = taps ? (uint32_t)((tap / 3) * 30 + tap % 3) : 0u;
+          mma_mxf4_lh(tmem + (uint32_t)(it & 1) * 128, a_lo + off, d_hi, b_lo + (uint32_t)(tap * 2 * N), d_hi, idesc, sf, sf, 1u);
+        }
+      }
+      __syncwarp();
+    }
+    if (leader) commit(&bar);
+    __syncwarp();
+  }
+  const bool ok = mbar_wait(&bar, 0);
+  if (threadIdx.x == 0) { *cyc = clock64() - t0; if (!ok) *status = 1; }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+}  // namespace
+
+// clocks per MMA (M=128, K=64, fp4) at width N with 9*iters MMAs issued back to back
+extern "C" double bnnb_tc_rate_fp4(int N, int taps) {
+  if (N % 32 || N < 32 || N > 128) return -1;
+  long long* dC; int* dS;
+  cudaSetDevice(0);
+  if (cudaMalloc(&dC, 8) != cudaSuccess) return -1;
+  cudaMalloc(&dS, 4);
+  cudaMemset(dS, 0, 4);
+  cudaFuncSetAttribute(k_tc_rate_fp4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  const int iters = 512;
+  long long c[2] = {0, 0};
+  for (int r = 0; r < 2; r++) {
+    k_tc_rate_fp4<<<1, 128, 200 * 1024>>>(N, taps, r == 0 ? 1 : iters, dC, dS);
+    if (cudaDeviceSynchronize() != cudaSuccess) { cudaFree(dC); cudaFree(dS); return -1; }
+    cudaMemcpy(&c[r], dC, 8, cudaMemcpyDeviceToHost);
+  }
+  int st = 0;
+  cudaMemcpy(&st, dS, 4, cudaMemcpyDeviceToHost);
+  cudaFree(dC); cudaFree(dS);
+  return st ? -1 : (double)(c[1] - c[0]) / (9.0 * (iters - 1));
+}

@@ -115,3 +115,29 @@ def test_tmem_rate_report():
     out = {"ld": {w: round(native.tmem_rate(w, False), 1) for w in (1, 2, 4, 8)}, "st": {w: round(native.tmem_rate(w, True), 1) for w in (1, 4, 8)}}
     print("TMEM bytes/clk/SM:", out)
     assert out["ld"][4] > 0
+
+
+def test_fp4_shifted_descriptor_rate_report():
+    """Timing report: MMA rate when the A descriptor starts at a 16-byte but not 128-byte aligned row (the implicit-im2col taps)."""
+    from bnn import native
+    rng = np.random.default_rng(5)
+    out = {}
+    for N in (64, 128):
+        K = 512
+        B = rng.integers(-1, 2, (N, K))
+        for shift in (0, 1, 2, 4, 7, 8):
+            A = rng.integers(0, 2, (136, K))
+            reps = 256
+            _, c1 = native.tc_probe_fp4(A, B, shift, 1)
+            D, c = native.tc_probe_fp4(A, B, shift, reps)
+            out[(N, shift)] = round((c - c1) / ((reps - 1) * K // 64), 1)
+            assert np.array_equal(D, reps * (A[shift:shift + 128].astype(np.int32) @ B.astype(np.int32).T))
+    print("clk per kind::mxf4 MMA (M=128, K=64) by (N, row shift):", out)
+
+
+def test_fp4_lean_issue_rate_report():
+    """Timing report: tensor-pipe clocks per MMA when the issuing thread is not the limit (unrolled, one add per descriptor)."""
+    from bnn import native
+    out = {(N, taps): round(native.tc_rate_fp4(N, taps), 1) for N in (32, 64, 128) for taps in (False, True)}
+    print("lean clk per kind::mxf4 MMA (M=128, K=64) by (N, 3x3 tap shifts):", out)
+    assert all(v > 0 for v in out.values())
