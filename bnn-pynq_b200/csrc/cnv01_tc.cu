@@ -9,7 +9,7 @@
 // image (m = y*32 + x: the 3x3x3 window row ky of pixel (y,x) is the first 9 bytes of P[m + 32*ky]).  K is laid out as
 // [ky][16]: k = ky*16 + (kx*3 + c) with zero weights for the 7 trailing bytes of each ky and for the whole 4th chunk, so
 // one tile needs two K=32 MMAs whose A descriptors differ only by a start shift (LBO = 32 rows).
-// Warp-specialised CTA (one per SM, 576 threads): eight warps run layer 1's epilogue on image i, eight warps stage image i+1
+// Warp-specialised CTA (one per SM, 608 threads): eight warps run layer 1's epilogue on image i, eight warps stage image i+1
 // (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one thread prefetches images by TMA bulk copy two
 // images ahead and issues all MMAs, interleaving layer 1 of image i with layer 0 of image i+1 tile by tile.
 #include <climits>
@@ -43,25 +43,25 @@ template <int OUTM, bool F4> struct Smem01 {
 
 __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 
-// Warp roles (576 threads): warps 0-7 = half A (layer-1 epilogue, pool, store), warps 8-15 = half B (layer-0 epilogue into the
+// Warp roles (608 threads): warps 0-7 = half A (layer-1 epilogue, pool, store), warps 8-15 = half B (layer-0 epilogue into the
 // other operand buffer), each half split into two teams of four warps by 32-channel half (the per-tile epilogue is a latency
-// chain: two teams halve it); half A also builds the window planes, warp 16 = layer-1 MMA issuer, warp 17 = image prefetch (TMA) + layer-0 MMA issuer.
+// chain: two teams halve it); half A also builds the window planes, warps 16-17 = layer-1 MMA issuers, warp 18 = image prefetch (TMA) + layer-0 MMA issuer.
 // The roles are decoupled by mbarriers only (no CTA-wide barrier in steady state):
 //   img_full[b]   TMA    -> half A   image buffer b holds an image                      (expect_tx 3072 bytes)
 //   p_full[b]     half A -> warp 16   window plane b is built (and image buffer b free)  (256 arrivals)
 //   p_empty[b]    warp 16 -> half A   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
-//   f0[s], e0[s]  warp 16 <-> half B  layer-0 accumulator slot s (of 3) full / read out   (commit / 8 arrivals)
+//   f0[s], e0[s]  warp 16 <-> half B  layer-0 accumulator slot s (of 2) full / read out   (commit / 8 arrivals)
 //   abuf_full[b]  half B -> warp 16   layer-1 operand buffer b holds a staged image      (256 arrivals)
 //   abuf_empty[b] warp 16 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
 //   full[s], empty[s] warp 16 <-> half A  layer-1 accumulator slot s (of 4) full / read out
 template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
-__global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
+__global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
                                                       int n_img, int out_fmt, int* __restrict__ status) {
   using S = Smem01<OUTM, F4>;
   constexpr int L1_A = S::L1_A;
   constexpr uint32_t SF_COL = 448;  // TMEM columns of the unit scale factors (F4)
-  constexpr uint32_t L0_ACC = 256;  // TMEM columns: layer-1 slots 0,64,128,192; layer-0 slots 256,320,384
-  constexpr int L0_SLOTS = 3;
+  constexpr uint32_t L0_ACC = 256;  // TMEM columns: layer-1 slots 0,64,128,192; layer-0 slots 256,320
+  constexpr int L0_SLOTS = 2;  // slot = tile & 1: with eight tiles per image slot and barrier parity are compile-time constants of t
   // FOLD: the thresholds are folded into the accumulators.  Every accumulator column n is pre-loaded with -(thr[n] + 1) (int32,
   // layer 0) / -(thr[n] + 1/2) (fp32, layer 1) and all MMAs accumulate, so the sign bit of the result is the negated decision
   // thr < acc and the epilogue is one funnel shift per channel instead of compare + select + insert.
@@ -78,34 +78,34 @@ __global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   int32_t* sthr0 = reinterpret_cast<int32_t*>(smem + S::OFF_THR);  // layer 0: floor(thr/2)   [64][2]
   int32_t* sthr1 = sthr0 + 128;                                    // layer 1: adjusted       [64][2] (F4: as float)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int role = warp < 8 ? 0 : (warp < 16 ? 1 : 2);             // 0: half A, 1: half B, 2: issuers (warp 16: layer 1; warp 17: layer 0 + TMA)
+  const int role = warp < 8 ? 0 : (warp < 16 ? 1 : 2);             // 0: half A, 1: half B, 2: issuers (warps 16, 17: layer 1; warp 18: layer 0 + TMA)
   const int ht = tid & 255, hw = warp & 3, team = (warp >> 2) & 1;  // thread in the half; TMEM lane quarter; 32-channel half
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
-  for (int i = tid; i < 64 * 9 * S::NPL; i += 576) {  // layer-1 weights -> chunk-major operand layout
+  for (int i = tid; i < 64 * 9 * S::NPL; i += 608) {  // layer-1 weights -> chunk-major operand layout
     const int n = i % 64, kc = i / 64;
     const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
     *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = *reinterpret_cast<const uint4*>(src + kc * 16);
   }
-  for (int i = tid; i < 64 * 64; i += 576) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
+  for (int i = tid; i < 64 * 64; i += 608) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
     sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)v;
   }
-  for (int i = tid; i < 128; i += 576) {
+  for (int i = tid; i < 128; i += 608) {
     const int t = L0.thr[i];
     sthr0[i] = t == INT_MAX ? INT_MAX : (t >> 1);  // thr < 2S  <=>  floor(thr/2) < S
     const int t1 = L1.thr_tc[i];
     if (F4) reinterpret_cast<float*>(sthr1)[i] = t1 == INT_MAX ? 3.0e38f : (float)t1;
     else sthr1[i] = t1;
   }
-  for (int i = tid; i < 2 * L1_A / 16; i += 576) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
-  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += 576) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < 2 * L1_A / 16; i += 608) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
+  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += 608) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
     for (int i = 0; i < 2; i++) {
-      tc::mbar_init(&abuf_full[i], 256); tc::mbar_init(&abuf_empty[i], 1);
+      tc::mbar_init(&abuf_full[i], 256); tc::mbar_init(&abuf_empty[i], 2);
       tc::mbar_init(&p_full[i], 256); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
     }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
@@ -172,9 +172,10 @@ __global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       // the layer-1 MMAs that read this operand buffer two images ago must have completed before it is overwritten
       if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], par ^ 1)) failed = true;
       uint8_t* sA = smem + (size_t)buf * L1_A;
+#pragma unroll
       for (int t = 0; t < L0_TILES; t++) {
-        const int g = k * L0_TILES + t, slot = g % L0_SLOTS, u = g / L0_SLOTS;
-        if (!failed && !tc::mbar_wait(&f0[slot], (uint32_t)u & 1)) failed = true;
+        const int slot = t & 1;  // u = 4k + (t >> 1): its parity does not depend on k
+        if (!failed && !tc::mbar_wait(&f0[slot], (uint32_t)(t >> 1) & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
         const bool valid = x < 30 && y < 30;
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       const uint32_t a1_lo[2] = {tc::desc_lo(sA_u, L1_PLANE), tc::desc_lo(sA_u + L1_A, L1_PLANE)};
       const uint32_t b0_lo = tc::desc_lo(sB0_u, 64 * 16), b1_lo = tc::desc_lo(sB1_u, 64 * 16);
       for (int k = 0; k < 2 && k < K; k++)
-        if (leader && warp == 17) {
+        if (leader && warp == 18) {
           tc::mbar_expect_tx(&img_full[k], 3072);
           tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
         }
@@ -265,8 +266,8 @@ __global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
             tc::bulk_g2s(sImg + (size_t)buf * IMG_BYTES, in + (first + (long long)(k + 2) * stride) * 3072, 3072, &img_full[buf]);
           }
         }
-        const int g = k * L0_TILES + t, slot = g % L0_SLOTS, u = g / L0_SLOTS;
-        if (u >= 1 && !failed && !tc::mbar_wait(&e0[slot], (uint32_t)(u - 1) & 1)) failed = true;
+        const int slot = t & 1;  // u = 4k + (t >> 1) uses of this slot so far
+        if ((k > 0 || t >= 2) && !failed && !tc::mbar_wait(&e0[slot], (uint32_t)((t >> 1) & 1) ^ 1)) failed = true;
         tc::fence_after_sync();
         const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
         const uint32_t a0 = p_lo[buf] + (uint32_t)(t * 128);  // descriptor start fields are in 16-byte units: one row = 1
@@ -280,7 +281,6 @@ __global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       };
       auto issue_l1 = [&](int k, int t) {
         const int buf = k & 1;
-        if (t == 0 && !failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
         const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
         const uint32_t a_lo = a1_lo[buf] + (uint32_t)(t * 128);
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
@@ -291,7 +291,6 @@ __global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         if (leader && F4) {
           tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, FOLD ? 1u : 0u);
           tc::commit(&full[slot]);
-          if (t == L1_TILES - 1) tc::commit(&abuf_empty[buf]);
         } else if (leader) {
 #pragma unroll
         for (int tap = 0; tap < 9; tap++) {
@@ -310,20 +309,30 @@ __global__ void __launch_bounds__(576, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           }
         }
         tc::commit(&full[slot]);
-        if (t == L1_TILES - 1) tc::commit(&abuf_empty[buf]);
         }
         __syncwarp();
       };
-      // Two issuer warps: every tile costs the issuing thread a fixed ~250 clocks (barrier poll, fence, descriptor set-up, commit)
-      // on top of ~30 per MMA, so one thread cannot feed both layers (measured: the kernel with all MMAs and epilogues removed still
-      // took 4 240 clocks per image).  Layer 1's issue rate is below the pipe's execution rate, so the in-order MMA queue stays
-      // short and layer 0's tiles do not wait behind it.
-      if (warp == 17) {
-        for (int k = 0; k < K; k++)
+      // Three issuer warps.  A lone thread retires about one instruction per 6-7 clocks, so every tile costs its issuer a fixed
+      // few hundred clocks (barrier poll, fence, descriptor set-up, commit) on top of ~30 per MMA: measured, the kernel with all MMAs
+      // and epilogues removed still took 4 240 clocks per image with one issuer and 3 470 with two.  Warps 16 and 17 issue layer 1
+      // (tiles alternate by global tile parity: each warp owns two of the four accumulator slots), warp 18 issues layer 0 and
+      // prefetches images.  Layer 1's issue rate stays below the pipe's execution rate, so the in-order MMA queue is short and
+      // layer 0's tiles do not wait behind it.
+      if (warp == 18) {
+        for (int k = 0; k < K; k++) {
+#pragma unroll
           for (int t = 0; t < L0_TILES; t++) issue_l0(k, t);
+        }
       } else {
-        for (int k = 0; k < K; k++)
-          for (int t = 0; t < L1_TILES; t++) issue_l1(k, t);
+        const int w = warp & 1;
+        for (int k = 0; k < K; k++) {
+          const int buf = k & 1;
+          if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+          for (int t = 0; t < L1_TILES; t++)
+            if (((k * L1_TILES + t) & 1) == w) issue_l1(k, t);
+          if (leader) tc::commit(&abuf_empty[buf]);  // this warp's MMAs of the image; the barrier counts both issuers
+          __syncwarp();
+        }
       }
     }
   } else {
@@ -413,7 +422,7 @@ static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
   using S = Smem01<OUTM, F4>;
   static_assert(S::TOTAL <= 226 * 1024, "shared memory budget");
   cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-  k_cnv01_tc<OUTM, F4><<<grid, 576, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status);
+  k_cnv01_tc<OUTM, F4><<<grid, 608, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status);
 }
 
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt,
