@@ -292,3 +292,10 @@ def tc_rate_fp4(N, taps=False):
     if v < 0:
         raise RuntimeError("tc_rate_fp4 failed")
     return v
+
+
+def mbar_roundtrip(mode=0):
+    """Clocks per mbarrier ping-pong round trip between two warps (mode 1: one hop is a tcgen05.commit)."""
+    L = lib()
+    L.bnnb_mbar_roundtrip.restype = C.c_double
+    return L.bnnb_mbar_roundtrip(int(mode))

@@ -51,7 +51,7 @@ __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 2
 //   p_full[b]     half A -> warp 16   window plane b is built (and image buffer b free)  (256 arrivals)
 //   p_empty[b]    warp 16 -> half A   all layer-0 MMAs reading plane b have completed    (tcgen05.commit)
 //   f0[s], e0[s]  warp 16 <-> half B  layer-0 accumulator slot s (of 2) full / read out   (commit / 8 arrivals)
-//   abuf_full[b]  half B -> warp 16   layer-1 operand buffer b holds a staged image      (256 arrivals)
+//   l0_done[b][t] half B -> warps 16-17  layer-0 tile t of the image in operand buffer b is written (256 arrivals): layer-1 tile t-1 may start
 //   abuf_empty[b] warp 16 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
 //   full[s], empty[s] warp 16 <-> half A  layer-1 accumulator slot s (of 4) full / read out
 template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   // thr < acc and the epilogue is one funnel shift per channel instead of compare + select + insert.
   constexpr bool FOLD = F4 && OUTM == OUT_BIT;
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t full[4], empty[4], abuf_full[2], abuf_empty[2], f0[L0_SLOTS], e0[L0_SLOTS], p_full[2], p_empty[2], img_full[2],
+  __shared__ __align__(8) uint64_t full[4], empty[4], l0_done[2][L0_TILES], abuf_empty[2], f0[L0_SLOTS], e0[L0_SLOTS], p_full[2], p_empty[2], img_full[2],
       pre_done;
   __shared__ uint32_t tmem_base;
   uint8_t* sB1 = smem + S::OFF_B1;
@@ -105,7 +105,8 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
     for (int i = 0; i < 2; i++) {
-      tc::mbar_init(&abuf_full[i], 256); tc::mbar_init(&abuf_empty[i], 2);
+      tc::mbar_init(&abuf_empty[i], 2);
+      for (int t = 0; t < L0_TILES; t++) tc::mbar_init(&l0_done[i][t], 256);
       tc::mbar_init(&p_full[i], 256); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
     }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
@@ -235,9 +236,11 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&e0[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
+        // rows [120t, 120t+120) of the operand planes are final: layer-1 tile t-1 (which reads rows < 128(t-1)+190) may start.
+        // (generic-proxy writes, read by the async proxy: fence first)
+        tc::fence_async_smem();
+        tc::mbar_arrive(&l0_done[buf][t]);
       }
-      tc::fence_async_smem();  // operand planes were written through the generic proxy and are read by the async proxy (MMA)
-      tc::mbar_arrive(&abuf_full[buf]);
     }
   } else if (role == 2) {
     // ================= issuer + loader (one thread) =============================================================================
@@ -327,9 +330,12 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         const int w = warp & 1;
         for (int k = 0; k < K; k++) {
           const int buf = k & 1;
-          if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
           for (int t = 0; t < L1_TILES; t++)
-            if (((k * L1_TILES + t) & 1) == w) issue_l1(k, t);
+            if (((k * L1_TILES + t) & 1) == w) {
+              // layer-1 tile t reads operand rows [128t, 128t+190): complete once layer-0 tile t+1 has been written
+              if (!failed && !tc::mbar_wait(&l0_done[buf][t + 1], (uint32_t)(k >> 1) & 1)) failed = true;
+              issue_l1(k, t);
+            }
           if (leader) tc::commit(&abuf_empty[buf]);  // this warp's MMAs of the image; the barrier counts both issuers
           __syncwarp();
         }

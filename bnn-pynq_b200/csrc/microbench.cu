@@ -152,3 +152,41 @@ extern "C" double bnnb_tmem_rate(int warps, int store) {
   if (e != cudaSuccess || c <= 0) return -1;
   return (double)warps * iters * 4096.0 / (double)c;
 }
+
+// ---- mbarrier ping-pong: warp 0 arrives on A and waits on B, warp 1 waits on A and arrives on B.  Returns clocks per round trip
+// (two hops).  mode 1: warp 0's arrival is a tcgen05.commit (no MMA outstanding) instead of a plain arrive. ---------------------------
+namespace {
+__global__ void __launch_bounds__(64) k_mbar_pingpong(int iters, int mode, long long* cyc) {
+  __shared__ __align__(8) uint64_t bar[2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) { bnnb::tc::mbar_init(&bar[0], 1); bnnb::tc::mbar_init(&bar[1], 1); bnnb::tc::mbar_init_fence(); }
+  __syncthreads();
+  const long long c0 = clock64();
+  for (int i = 0; i < iters; i++) {
+    if (warp == 0) {
+      if (lane == 0) { if (mode == 1) bnnb::tc::commit(&bar[0]); else bnnb::tc::mbar_arrive(&bar[0]); }
+      __syncwarp();
+      bnnb::tc::mbar_wait(&bar[1], i & 1);
+    } else {
+      bnnb::tc::mbar_wait(&bar[0], i & 1);
+      if (lane == 0) bnnb::tc::mbar_arrive(&bar[1]);
+      __syncwarp();
+    }
+  }
+  if (threadIdx.x == 0) *cyc = clock64() - c0;
+}
+}  // namespace
+
+extern "C" double bnnb_mbar_roundtrip(int mode) {
+  long long* cyc;
+  cudaSetDevice(0);
+  if (cudaMalloc(&cyc, 8) != cudaSuccess) return -1;
+  const int iters = 20000;
+  k_mbar_pingpong<<<1, 64>>>(iters, mode, cyc);
+  k_mbar_pingpong<<<1, 64>>>(iters, mode, cyc);
+  long long c = 0;
+  const cudaError_t e = cudaDeviceSynchronize();
+  cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
+  cudaFree(cyc);
+  return e == cudaSuccess ? (double)c / iters : -1;
+}

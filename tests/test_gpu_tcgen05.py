@@ -141,3 +141,11 @@ def test_fp4_lean_issue_rate_report():
     out = {(N, taps): round(native.tc_rate_fp4(N, taps), 1) for N in (32, 64, 128) for taps in (False, True)}
     print("lean clk per kind::mxf4 MMA (M=128, K=64) by (N, 3x3 tap shifts):", out)
     assert all(v > 0 for v in out.values())
+
+
+def test_mbarrier_roundtrip_report():
+    """Timing report: latency of the producer/consumer handshakes the warp-specialised kernels are built from."""
+    from bnn import native
+    out = {"arrive/wait round trip clk": round(native.mbar_roundtrip(0), 1), "commit/wait round trip clk": round(native.mbar_roundtrip(1), 1)}
+    print("mbarrier ping-pong:", out)
+    assert out["arrive/wait round trip clk"] > 0
