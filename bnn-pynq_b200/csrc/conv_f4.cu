@@ -185,14 +185,11 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * N;
           const uint32_t at = a_lo[buf] + (uint32_t)(t * 128), bt = b_lo + (uint32_t)(h * N);
-          if (leader) {
+          if (leader) {  // nine taps per asm block (tcgen05.cuh: mma9_mxf4), once per pair of operand planes
 #pragma unroll
-            for (int tap = 0; tap < 9; tap++) {
-#pragma unroll
-              for (int s = 0; s < Cfg::KC / 2; s++)
-                tc::mma_mxf4_lh(acc, at + (uint32_t)((tap / 3) * IDIM + tap % 3 + 2 * s * (Cfg::PLANE / 16)), d_hi,
-                                bt + (uint32_t)((tap * Cfg::KC + 2 * s) * NT), d_hi, idesc, sf, sf, (FOLD || tap + s > 0) ? 1u : 0u);
-            }
+            for (int s = 0; s < Cfg::KC / 2; s++)
+              tc::mma9_mxf4<IDIM, Cfg::KC * NT>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NT), d_hi, idesc, sf,
+                                               (FOLD || s > 0) ? 1u : 0u);
             tc::commit(&full[slot]);
           }
           __syncwarp();
