@@ -4,10 +4,12 @@
 // integer MVAU (mvau.hpp:86-172, activations.hpp:139-147).  Evidence: tests/test_gpu_tcgen05.py::test_fp4_probe_*.
 //
 // Same implicit GEMM as conv_tc.cu (operand planes of 16 bytes = 32 channels per pixel, tap (ky,kx) = descriptor start shifted by
-// (ky*IDIM+kx) pixels), now one K=64 MMA per 64 input channels per tap, and a warp-specialised CTA (one per SM, 384 threads):
-//   warps 0-3, 4-7  two epilogue groups, one per half of the output channels: TMEM -> decision bits -> global (pooled: via smem)
-//   warps 8-10      expander: bit-packed activations of group g+1 (global, L2) -> fp4 operand planes, other buffer
-//   warp  11        MMA issuer, up to three tiles ahead (three TMEM accumulator slots)
+// (ky*IDIM+kx) pixels), now one K=64 MMA per 64 input channels per tap, and a warp-specialised CTA (one per SM, 640 threads):
+//   warps 0-15      four epilogue groups of four warps, one per quarter of the channel block (a lone warp retires an instruction
+//                   every 6-7 clocks, so the per-tile epilogue is split until it is shorter than the tile's MMAs): TMEM -> decision
+//                   bits or e2m1 codes -> global (pooled layers: via smem)
+//   warps 16-18     expander: bit-packed activations of group g+1 (global, L2) -> fp4 operand planes, other buffer
+//   warp  19        MMA issuer, up to three tiles ahead (three TMEM accumulator slots)
 // decoupled by mbarriers only: abuf_full / abuf_empty per operand buffer, full / empty per accumulator slot.
 #include <climits>
 #include "kernels.cuh"
@@ -58,7 +60,7 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
 }
 
 template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
-__global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
+__global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                      int in_fmt, int out_fmt, int* __restrict__ status) {
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
@@ -68,29 +70,30 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
   uint8_t* sb = smem + Cfg::OFF_B;
   float* sthr = reinterpret_cast<float*>(smem + Cfg::OFF_THR);  // [2][N]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int role = warp < 8 ? 0 : (warp < 11 ? 1 : 2), ht = tid & 127, hw = warp & 3;
-  const int eg = (warp >> 2) & 1;  // epilogue group (role 0): output channels [eg*N/2, (eg+1)*N/2)
-  constexpr int NWG = Cfg::NW / 2;  // 32-channel words per epilogue group
+  const int role = warp < 16 ? 0 : (warp < 19 ? 1 : 2), ht = tid & 127, hw = warp & 3;
+  const int eg = (warp >> 2) & 3;  // epilogue group (role 0): output channels [eg*N/4, (eg+1)*N/4) of the block
+  constexpr int NWG = Cfg::NW / 4;  // 32-channel words per epilogue group
+  constexpr int NG = N / 4;         // channels per epilogue group
   constexpr int KCT = 9 * Cfg::KC;
   // FOLD (1-bit outputs): accumulators are pre-loaded with -(thr + 1/2) and every MMA accumulates; the sign bit of the result is
   // the negated decision, harvested with one funnel shift per channel (see cnv01_tc.cu)
   constexpr bool FOLD = OUTM == OUT_BIT;
 
   constexpr int NT = Cfg::NT;
-  for (int i = tid; i < NT * KCT; i += 384) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
+  for (int i = tid; i < NT * KCT; i += 640) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
     const int n = i % NT, kc = i / NT;
     *reinterpret_cast<uint4*>(sb + ((size_t)kc * NT + n) * 16) = *reinterpret_cast<const uint4*>(L.w4 + (size_t)n * (L.kpad / 2) + kc * 16);
   }
-  for (int i = tid; i < 2 * NT; i += 384) {
+  for (int i = tid; i < 2 * NT; i += 640) {
     const int t = L.thr_tc[i];
     const float tf = t == INT_MAX ? 3.0e38f : (float)t;
     sthr[(i & 1) * NT + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
   }
-  for (int i = tid; i < 2 * Cfg::A_BYTES / 16; i += 384) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // pad pixels stay 0
+  for (int i = tid; i < 2 * Cfg::A_BYTES / 16; i += 640) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // pad pixels stay 0
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
     for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], in_fmt == ACT_F4P ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); }
-    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
+    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 16); }
     tc::mbar_init_fence();
   }
   tc::fence_async_smem();
@@ -117,7 +120,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
     }
     tc::tmem_st_wait();
   };
-  if (FOLD && warp < 8)
+  if (FOLD && warp < 16)
     for (int slot = 0; slot < Cfg::SLOTS; slot++) preload(slot, slot % NS);
   tc::fence_before_sync();
   __syncthreads();
@@ -133,7 +136,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
     // = three warps expanding bit-packed activations ------------------------------------------------------------------------
     constexpr int CW = C / 32;
     if (in_fmt == ACT_F4P) {
-      if (tid == 256) {
+      if (tid == 512) {
         const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
         constexpr uint32_t IMG_PLANE = Cfg::PXI * 16;  // bytes of one plane of one image
         for (int k = 0; k < K; k++) {
@@ -154,7 +157,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
       if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
       uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
 #pragma unroll 4
-      for (int i = tid - 256; i < Cfg::ROWS * CW; i += 96) {
+      for (int i = tid - 512; i < Cfg::ROWS * CW; i += 96) {
         const int j = i % CW, m = i / CW, gi = m / Cfg::PXI;
         uint32_t w0 = 0, w1 = 0;
         if (img0 + gi < n_img) {
@@ -210,7 +213,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
         if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
-        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N + (uint32_t)eg * (N / 2);
+        const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N + (uint32_t)eg * NG;
         uint32_t b0[NWG], b1[NWG];
         uint4 c4[NWG];  // e2m1 codes instead of bits when the consumer is another fp4 kernel
         const bool codes = FOLD && !POOL && out_fmt != ACT_BITS;
@@ -229,7 +232,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
             for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
             w0 = ~w0;
           } else {
-            const float* th = sthr + h * N + eg * (N / 2) + j * 32;
+            const float* th = sthr + h * N + eg * NG + j * 32;
 #pragma unroll
             for (int c = 0; c < 32; c++) {
               const float s = __uint_as_float(r[j & 1][c]);
@@ -266,7 +269,10 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
           }
         }
         if (row) {
-          if (NWG == 2) {
+          if (NWG == 1) {
+            row[h * NW + eg] = b0[0];
+            if (OUTM == OUT_TERN) row[NWT + h * NW + eg] = b1[0];
+          } else if (NWG == 2) {
             *reinterpret_cast<uint2*>(row + h * NW + eg * NWG) = make_uint2(b0[0], b0[1]);
             if (OUTM == OUT_TERN) *reinterpret_cast<uint2*>(row + NWT + h * NW + eg * NWG) = make_uint2(b1[0], b1[1]);
           } else {
@@ -279,9 +285,9 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
         }
       }
       if (POOL) {
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, 512;" ::: "memory");
         constexpr int PP = Cfg::PD * Cfg::PD;
-        for (int i = tid; i < G * PP; i += 256) {  // one pooled output pixel per thread
+        for (int i = tid; i < G * PP; i += 512) {  // one pooled output pixel per thread
           const int gi = i / PP, op = i - gi * PP, oy = op / Cfg::PD, ox = op - oy * Cfg::PD;
           if (img0 + gi >= n_img) continue;
           const uint4* r00 = reinterpret_cast<const uint4*>(sbits + (size_t)(gi * Cfg::PXI + (2 * oy) * IDIM + 2 * ox) * WPP);
@@ -309,7 +315,7 @@ __global__ void __launch_bounds__(384, 1) k_conv_f4(DevLayer L, const uint32_t* 
             }
           }
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");  // the next image group overwrites the staging rows
+        asm volatile("bar.sync 1, 512;" ::: "memory");  // the next image group overwrites the staging rows
       }
     }
   }
@@ -327,7 +333,7 @@ bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img,
   auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
   const int ngroups = (n_img + G - 1) / G;
-  kern<<<ngroups < num_sms ? ngroups : num_sms, 384, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status);
+  kern<<<ngroups < num_sms ? ngroups : num_sms, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status);
   return true;
 }
 
