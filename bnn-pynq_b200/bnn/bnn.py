@@ -6,6 +6,7 @@ next to RUNTIME_HW / RUNTIME_SW.  The library is found as "{runtime}-{network}.s
 board name, bnn/bnn.py:108); pynq and the BOARD variable are not needed for this runtime (bnn/bnn.py:30,55-60 made that
 impossible).  cffi dlopen + the same cdef as bnn/bnn.py:69-76.
 """
+import io
 import os
 import tempfile
 
@@ -35,6 +36,11 @@ int* inference_multiple(const char* path, int number_class, int *image_number, f
 int* inference_multiple_with_faults(const char* path, int number_class, int *image_number, float *usecPerImage, unsigned int flip_count, int word_size, int target, int* target_layers, unsigned int num_targets);
 void free_results(int * result);
 void deinit();
+""")
+# in-memory twins exported by this runtime's libraries only (include/bnn_b200.h); bound lazily so the cdef above stays the reference's
+_ffi.cdef("""
+int* inference_buffer(const unsigned char* images, int image_count, int number_class, float *usecPerImage, int enable_detail);
+int* inference_buffer_with_faults(const unsigned char* images, int image_count, int number_class, float *usecPerImage, unsigned int flip_count, int word_size, int target, int* target_layers, unsigned int num_targets);
 """)
 
 _libraries = {}
@@ -137,18 +143,55 @@ class PynqBNN:
         return out
 
     def inference_multiple_with_faults(self, path, num_faults, word_size, target_type, target_layers=[]):
-        if len(target_layers) == 0:
-            targets = _ffi.cast("int *", 0)
-        else:
-            # the reference passes np.int (int64) through an int*, reading [0,1,2] as [0,0,1]: int32 here
-            self._targets = np.ascontiguousarray(target_layers, dtype=np.int32)
-            targets = _ffi.cast("int *", _ffi.from_buffer(self._targets))
+        # the reference passes np.int (int64) through an int*, reading [0,1,2] as [0,0,1]: int32 here
+        targets = self._targets_ptr(target_layers)
         size_ptr = _ffi.new("int *")
         usecperimage = _ffi.new("float *")
         result_ptr = self.interface.inference_multiple_with_faults(
             path.encode(), len(self.classes), size_ptr, usecperimage, num_faults, word_size, target_type, targets, len(target_layers))
         out = self._take(result_ptr, size_ptr[0])
         self._rate(usecperimage[0], size_ptr[0])
+        return out
+
+    def _targets_ptr(self, target_layers):
+        if len(target_layers) == 0:
+            return _ffi.cast("int *", 0)
+        self._targets = np.ascontiguousarray(target_layers, dtype=np.int32)
+        return _ffi.cast("int *", _ffi.from_buffer(self._targets))
+
+    def _as_images(self, images):
+        """uint8 array -> (contiguous array, count).  Rows are 3073-byte CIFAR records or 3072 planar RGB bytes (a zero label byte is
+        prepended) for CNV libraries, 784 pixels for LFC ones; the library checks nothing beyond the count."""
+        a = np.ascontiguousarray(images, dtype=np.uint8)
+        if a.ndim == 1:
+            a = a.reshape(-1, 3073) if a.size and a.size % 3073 == 0 else a.reshape(1, -1)
+        if a.shape[0] == 0:
+            return a.reshape(0, 0), 0
+        a = a.reshape(a.shape[0], -1)
+        if a.shape[1] == 3072:
+            a = np.concatenate([np.zeros((a.shape[0], 1), np.uint8), a], axis=1)
+        if a.shape[1] not in (3073, 784):
+            raise ValueError("expected rows of 3073 / 3072 bytes (CNV) or 784 bytes (LFC), got %d" % a.shape[1])
+        return a, a.shape[0]
+
+    def inference_buffer(self, images, detail=False):
+        """inference_multiple / inference_multiple_detail on images already in memory (no file)."""
+        a, n = self._as_images(images)
+        usecperimage = _ffi.new("float *")
+        ptr = _ffi.cast("const unsigned char *", _ffi.from_buffer(a)) if n else _ffi.NULL
+        result_ptr = self.interface.inference_buffer(ptr, n, len(self.classes), usecperimage, 1 if detail else 0)
+        out = self._take(result_ptr, n * len(self.classes) if detail else n)
+        self._rate(usecperimage[0], n)
+        return out
+
+    def inference_buffer_with_faults(self, images, num_faults, word_size, target_type, target_layers=[]):
+        a, n = self._as_images(images)
+        usecperimage = _ffi.new("float *")
+        ptr = _ffi.cast("const unsigned char *", _ffi.from_buffer(a)) if n else _ffi.NULL
+        result_ptr = self.interface.inference_buffer_with_faults(
+            ptr, n, len(self.classes), usecperimage, num_faults, word_size, target_type, self._targets_ptr(target_layers), len(target_layers))
+        out = self._take(result_ptr, n)
+        self._rate(usecperimage[0], n)
         return out
 
     def inference_multiple_detail(self, path):
@@ -205,6 +248,21 @@ class CnvClassifier(_Classifier):
             tmp.flush()
             return self._done(fn(tmp.name, *args))
 
+    def images_to_records(self, imgs):
+        """PIL images -> uint8 [n][3073] CIFAR records through image_to_cifar, in memory (the reference writes a temp file,
+        bnn/bnn.py:280-287)."""
+        fp = io.BytesIO()
+        for img in imgs:
+            self.image_to_cifar(img, fp)
+        return np.frombuffer(fp.getvalue(), np.uint8).reshape(-1, 3073)
+
+    def classify_records(self, records, details=False):
+        """uint8 [n][3073] records (or [n][3072] planar RGB) already in memory -> class ids, or [n*classes] scores."""
+        return self._done(self.bnn.inference_buffer(records, details))
+
+    def classify_records_with_faults(self, records, num_faults, word_size, target_type, target_layers=[]):
+        return self._done(self.bnn.inference_buffer_with_faults(records, num_faults, word_size, target_type, target_layers))
+
     def classify_image(self, img):
         return self._with_tmp([img], self.bnn.inference)
 
@@ -222,10 +280,10 @@ class CnvClassifier(_Classifier):
         return self.classify_image(Image.open(path))
 
     def classify_images(self, imgs):
-        return self._with_tmp(imgs, self.bnn.inference_multiple)
+        return self.classify_records(self.images_to_records(imgs))
 
     def classify_images_with_faults(self, imgs, num_faults, word_size, target_type, target_layers=[]):
-        return self._with_tmp(imgs, self.bnn.inference_multiple_with_faults, num_faults, word_size, target_type, target_layers)
+        return self.classify_records_with_faults(self.images_to_records(imgs), num_faults, word_size, target_type, target_layers)
 
     def classify_cifars(self, path):
         return self._done(self.bnn.inference_multiple(path))
@@ -234,7 +292,7 @@ class CnvClassifier(_Classifier):
         return self._done(self.bnn.inference_multiple_with_faults(path, num_faults, word_size, target_type, target_layers))
 
     def classify_images_details(self, imgs):
-        return self._with_tmp(imgs, self.bnn.inference_multiple_detail)
+        return self.classify_records(self.images_to_records(imgs), details=True)
 
     def classify_cifars_details(self, path):
         return self._done(self.bnn.inference_multiple_detail(path))
@@ -255,3 +313,10 @@ class LfcClassifier(_Classifier):
 
     def classify_mnists_with_faults(self, mnist_format_file, num_faults, flip_word, target_type, target_layers=[]):
         return self._done(self.bnn.inference_multiple_with_faults(mnist_format_file, num_faults, flip_word, target_type, target_layers))
+
+    def classify_pixels(self, pixels):
+        """uint8 [n][784] (or [n][28][28]) images already in memory -> class ids (no idx3 file)."""
+        return self._done(self.bnn.inference_buffer(pixels))
+
+    def classify_pixels_with_faults(self, pixels, num_faults, flip_word, target_type, target_layers=[]):
+        return self._done(self.bnn.inference_buffer_with_faults(pixels, num_faults, flip_word, target_type, target_layers))

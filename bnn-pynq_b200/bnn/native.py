@@ -78,6 +78,7 @@ class Runtime:
         self.h = self.L.bnnb_open(network.encode())
         if not self.h:
             raise ValueError("unknown network %r" % network)
+        self._devices = None if devices is None else [int(d) for d in devices]
         if devices is not None:
             ids = np.ascontiguousarray(devices, np.int32)
             self._ck(self.L.bnnb_set_devices(self.h, _p(ids), len(ids)))
@@ -180,6 +181,51 @@ class Runtime:
 
     def sync(self, slot=0):
         self._ck(self.L.bnnb_sync(self.h, slot))
+
+    def classify_tensor(self, images, number_class=10, want_scores=False):
+        """Device-resident entry point: `images` is a CUDA uint8 tensor (or any DLPack exporter on a CUDA device) of CIFAR records
+        [n, 3073] (CNV) or pixels [n, 784] (LFC).  Runs the quantise/pack kernel and the network on the tensor's device, ordered
+        after torch's current stream, and returns an int32 class tensor on that device (CNV with want_scores: also int16 scores [n, 64]; LFC with
+        want_scores: also the raw 64-bit output words as int64).  Nothing crosses PCIe."""
+        import torch
+        t = images if isinstance(images, torch.Tensor) else torch.from_dlpack(images)
+        if not t.is_cuda or t.dtype != torch.uint8:
+            raise ValueError("classify_tensor needs a CUDA uint8 tensor (host arrays go through classify_cifar / classify_mnist)")
+        w = 3073 if self.is_cnv else 784
+        t = t.contiguous().reshape(-1, w)
+        n = t.shape[0]
+        dev = t.device
+        slot = dev.index if self._devices is None else self._devices.index(dev.index)
+        with torch.cuda.device(dev):
+            # torch's default stream is the NULL handle, which the C ABI reads as "the engine's own stream": run on a side stream that
+            # is ordered after the caller's current stream, and make the current stream wait for it before returning
+            cur = torch.cuda.current_stream()
+            if not hasattr(self, "_side"):
+                self._side = {}
+            side = self._side.setdefault(dev.index, torch.cuda.Stream(dev))
+            stream = side.cuda_stream
+            d_in = torch.empty(max(n, 1) * self.in_bytes, dtype=torch.uint8, device=dev)
+            d_out = torch.empty(max(n, 1) * self.out_bytes, dtype=torch.uint8, device=dev)
+            cls = torch.zeros(n, dtype=torch.int32, device=dev)
+            if n == 0:
+                return (cls, d_out[:0].view(torch.int16).reshape(0, 64) if self.is_cnv else d_out[:0].view(torch.int64)) if want_scores else cls
+            side.wait_stream(cur)                        # after the allocations / zero-fill above, which run on `cur`
+            self.prep_device(t.data_ptr(), n, d_in.data_ptr(), stream, slot)
+            self.infer_device(d_in.data_ptr(), n, d_out.data_ptr(), cls.data_ptr() if self.is_cnv else 0, number_class, stream, slot)
+            cur.wait_stream(side)
+            if self.is_cnv:
+                return (cls, d_out.view(torch.int16).reshape(n, 64)) if want_scores else cls
+            # LFC multi-image rule (foldedmv-offload.cpp:202-220): (unsigned) log2((double)(word & mask)), 0 when no bit is set
+            words = d_out.view(torch.int64)
+            nc = max(0, min(64, number_class))
+            mask = -1 if nc == 64 else (1 << nc) - 1
+            m = words & mask
+            as_double = ((m >> 32) & 0xFFFFFFFF).to(torch.float64) * 4294967296.0 + (m & 0xFFFFFFFF).to(torch.float64)
+            # floor(log2) as the binary exponent of the rounded double: equal to glibc's log2 for every word whose top 48 bits below
+            # the leading one are not all ones (log2 of such a word rounds up to the next integer on the host); padded LFC rows carry
+            # threshold 32767 and never fire, so those words need more than 48 real classes
+            cls = torch.where(m != 0, torch.frexp(as_double)[1] - 1, torch.zeros_like(m, dtype=torch.int32)).to(torch.int32)
+            return (cls, words) if want_scores else cls
 
     def set_core(self, core):
         """0: LOP3+POPC everywhere; 1: tcgen05 tensor-core kernels where instantiated."""

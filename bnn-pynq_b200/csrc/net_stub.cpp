@@ -101,17 +101,14 @@ int inference(const char* path, int results[64], int number_class, float* usecPe
   return best;
 }
 
-int* inference_multiple(const char* path, int number_class, int* image_number, float* usecPerImage, int enable_detail) {
-  if (!ctx()) return nullptr;
-  std::vector<uint8_t> buf;
-  int n = 0;
-  if (!read_images(path, &buf, &n)) return nullptr;
+// Shared by the path-based and the in-memory entry points: images already parsed (CNV: n 3073-byte records; LFC: n x 784 pixels).
+static int* run_multiple(const uint8_t* data, int n, int number_class, float* usecPerImage, int enable_detail, const char* where) {
   float usec = 0;
   int* result = nullptr;
   if (g_is_cnv) {
     std::vector<int> cls(n);
     std::vector<int16_t> sc(enable_detail ? (size_t)n * 64 : 0);
-    if (bnnb_classify_cifar(g_ctx, buf.data(), n, number_class, cls.data(), enable_detail ? sc.data() : nullptr, &usec) != 0) { report("inference_multiple"); return nullptr; }
+    if (bnnb_classify_cifar(g_ctx, data, n, number_class, cls.data(), enable_detail ? sc.data() : nullptr, &usec) != 0) { report(where); return nullptr; }
     if (enable_detail) {  // image-major scores (cnvW1A1/sw/main_python.cpp:161-163)
       result = new (std::nothrow) int[(size_t)n * number_class + 1];
       if (result) for (int i = 0; i < n; i++) for (int j = 0; j < number_class; j++) result[(size_t)i * number_class + j] = j < 64 ? sc[(size_t)i * 64 + j] : 0;
@@ -121,11 +118,34 @@ int* inference_multiple(const char* path, int number_class, int* image_number, f
     }
   } else {  // LFC ignores enable_detail (lfcW1A1/sw/main_python.cpp:135-156)
     result = new (std::nothrow) int[n + 1];
-    if (result && bnnb_classify_mnist(g_ctx, buf.data(), n, number_class, result, nullptr, &usec) != 0) { report("inference_multiple"); delete[] result; return nullptr; }
+    if (result && bnnb_classify_mnist(g_ctx, data, n, number_class, result, nullptr, &usec) != 0) { report(where); delete[] result; return nullptr; }
   }
-  if (image_number) *image_number = n;
   if (usecPerImage) *usecPerImage = usec;
   print_rate(usec);
+  return result;
+}
+
+static int* run_multiple_with_faults(const uint8_t* data, int n, int number_class, float* usecPerImage, unsigned int flip_count, int word_size,
+                                     int target, int* target_layers, unsigned int num_targets, const char* where) {
+  long long seed = -1;  // std::random_device like the reference, unless pinned for reproducible campaigns
+  if (const char* s = std::getenv("BNN_B200_FAULT_SEED")) seed = std::atoll(s);
+  std::vector<uint32_t> fl((size_t)flip_count * 5 + 5);
+  const int nf = n > 0 ? bnnb_schedule_faults(g_ctx, (unsigned)n, flip_count, word_size, target, target_layers, target_layers ? num_targets : 0, seed, fl.data(), (int)flip_count) : 0;
+  if (nf < 0) { report(where); return nullptr; }
+  int* result = new (std::nothrow) int[n + 1];
+  float usec = 0;
+  if (result && bnnb_classify_with_fault_list(g_ctx, data, n, number_class, fl.data(), nf, result, &usec) != 0) { report(where); delete[] result; return nullptr; }
+  if (usecPerImage) *usecPerImage = usec;  // time of the last image's segment (SURVEY App. C.8)
+  return result;
+}
+
+int* inference_multiple(const char* path, int number_class, int* image_number, float* usecPerImage, int enable_detail) {
+  if (!ctx()) return nullptr;
+  std::vector<uint8_t> buf;
+  int n = 0;
+  if (!read_images(path, &buf, &n)) return nullptr;
+  int* result = run_multiple(buf.data(), n, number_class, usecPerImage, enable_detail, "inference_multiple");
+  if (result && image_number) *image_number = n;
   return result;
 }
 
@@ -135,17 +155,26 @@ int* inference_multiple_with_faults(const char* path, int number_class, int* ima
   std::vector<uint8_t> buf;
   int n = 0;
   if (!read_images(path, &buf, &n)) return nullptr;
-  long long seed = -1;  // std::random_device like the reference, unless pinned for reproducible campaigns
-  if (const char* s = std::getenv("BNN_B200_FAULT_SEED")) seed = std::atoll(s);
-  std::vector<uint32_t> fl((size_t)flip_count * 5 + 5);
-  const int nf = n > 0 ? bnnb_schedule_faults(g_ctx, (unsigned)n, flip_count, word_size, target, target_layers, target_layers ? num_targets : 0, seed, fl.data(), (int)flip_count) : 0;
-  if (nf < 0) { report("inference_multiple_with_faults"); return nullptr; }
-  int* result = new (std::nothrow) int[n + 1];
-  float usec = 0;
-  if (result && bnnb_classify_with_fault_list(g_ctx, buf.data(), n, number_class, fl.data(), nf, result, &usec) != 0) { report("inference_multiple_with_faults"); delete[] result; return nullptr; }
-  if (image_number) *image_number = n;
-  if (usecPerImage) *usecPerImage = usec;  // time of the last image's segment (SURVEY App. C.8)
+  int* result = run_multiple_with_faults(buf.data(), n, number_class, usecPerImage, flip_count, word_size, target, target_layers, num_targets,
+                                         "inference_multiple_with_faults");
+  if (result && image_number) *image_number = n;
   return result;
+}
+
+// In-memory twins of the two calls above: the caller hands over what the file would have held after parsing, so that
+// classify_images (bnn/bnn.py:280-287) needs no temp file.  Not part of the reference's cdef; bnn.py binds them when present.
+int* inference_buffer(const unsigned char* images, int image_count, int number_class, float* usecPerImage, int enable_detail) {
+  if (!ctx()) return nullptr;
+  if (image_count < 0 || (image_count > 0 && !images)) { std::fprintf(stderr, "[bnn_b200 %s] inference_buffer: bad arguments\n", BNNB_NET); return nullptr; }
+  return run_multiple(images, image_count, number_class, usecPerImage, enable_detail, "inference_buffer");
+}
+
+int* inference_buffer_with_faults(const unsigned char* images, int image_count, int number_class, float* usecPerImage, unsigned int flip_count,
+                                  int word_size, int target, int* target_layers, unsigned int num_targets) {
+  if (!ctx()) return nullptr;
+  if (image_count < 0 || (image_count > 0 && !images)) { std::fprintf(stderr, "[bnn_b200 %s] inference_buffer_with_faults: bad arguments\n", BNNB_NET); return nullptr; }
+  return run_multiple_with_faults(images, image_count, number_class, usecPerImage, flip_count, word_size, target, target_layers, num_targets,
+                                  "inference_buffer_with_faults");
 }
 
 void free_results(int* result) { delete[] result; }

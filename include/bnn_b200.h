@@ -42,6 +42,14 @@ int* inference_multiple(const char* path, int number_class, int* image_number, f
 int* inference_multiple_with_faults(const char* path, int number_class, int* image_number, float* usecPerImage,
                                     unsigned int flip_count, int word_size, int target, int* target_layers,
                                     unsigned int num_targets);
+/* In-memory twins of the two calls above (extension; bnn.py binds them when the library exports them).  They take what the
+ * file would hold after parsing -- CNV: image_count 3073-byte CIFAR records (label byte ignored); LFC: image_count x 784
+ * pixels, no idx3 header -- so that classify_images / image_to_cifar (bnn/bnn.py:226-242,280-287) need no temp file.
+ * Same results, same result ownership (free_results), same fault scheduling as the path-based calls. */
+int* inference_buffer(const unsigned char* images, int image_count, int number_class, float* usecPerImage, int enable_detail);
+int* inference_buffer_with_faults(const unsigned char* images, int image_count, int number_class, float* usecPerImage,
+                                  unsigned int flip_count, int word_size, int target, int* target_layers,
+                                  unsigned int num_targets);
 /* :225 */
 void free_results(int* result);
 /* :229 -- releases nothing the next call cannot rebuild: every entry point re-initialises on demand (FoldedMVInit). */

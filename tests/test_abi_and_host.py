@@ -15,6 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "bnn-pynq_b200")
 sys.path.insert(0, PKG)
 SIX = ["load_parameters", "inference", "inference_multiple", "inference_multiple_with_faults", "free_results", "deinit"]
+BUFFER_TWINS = ["inference_buffer", "inference_buffer_with_faults"]   # in-memory extension (include/bnn_b200.h section 1)
 
 
 @pytest.fixture(scope="session", autouse=True)
@@ -40,7 +41,11 @@ def test_core_library_exports_every_declared_symbol():
 @pytest.mark.parametrize("net", NETS)
 def test_per_network_library_exports_the_six_bnn_py_symbols(net):
     lib = C.CDLL(os.path.join(PKG, "lib", "python_cuda-%s.so" % net))
-    for n in SIX:
+    src = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "bnn_b200.h")).read(), flags=re.S)
+    section1 = src[:src.index("typedef struct bnnb_ctx")]
+    names = sorted(set(re.findall(r"\b(\w+)\s*\(", section1)))
+    assert names == sorted(SIX + BUFFER_TWINS)                          # the header declares exactly these for the per-network objects
+    for n in names:
         assert hasattr(lib, n), n
 
 
