@@ -13,6 +13,7 @@
 // (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one thread prefetches images by TMA bulk copy two
 // images ahead and issues all MMAs, interleaving layer 1 of image i with layer 0 of image i+1 tile by tile.
 #include <climits>
+#include <cstdio>
 #include <type_traits>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
@@ -30,6 +31,10 @@ constexpr int P_BYTES = P_ROWS * 16;
 constexpr int IMG_BYTES = 3072 + 64;          // image + slack for the 16-byte windows of the last rows
 constexpr int B0_BYTES = 4 * 64 * 16;         // layer-0 weights: 4 chunks x 64 rows x 16 bytes
 constexpr int L1_TILES = 7, L0_TILES = 8;
+#ifndef BNNB_PSPLIT
+#define BNNB_PSPLIT 1088
+#endif
+constexpr int P_SPLIT = BNNB_PSPLIT;        // window-plane rows [0, P_SPLIT) are built by half A, the rest (if any) by half B
 
 template <int OUTM, bool F4> struct Smem01 {
   static constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
@@ -37,10 +42,25 @@ template <int OUTM, bool F4> struct Smem01 {
   static constexpr int L1_A = NPL * L1_PLANE;          // one operand buffer (64 channels)
   static constexpr int L1_B = 9 * NPL * 64 * 16;       // weights 64 x 576
   static constexpr int BITS = L1_TILES * 128 * 2 * OPL * 4;
+  static constexpr int NBITS = F4 ? 2 : 1;             // bit-row buffers (the int8 variant has no room for a second one)
   static constexpr int OFF_A = 0, OFF_B1 = 2 * L1_A, OFF_P = OFF_B1 + L1_B, OFF_IMG = OFF_P + 2 * P_BYTES, OFF_B0 = OFF_IMG + 2 * IMG_BYTES,
-                       OFF_BITS = OFF_B0 + B0_BYTES, OFF_THR = OFF_BITS + BITS, TOTAL = OFF_THR + 2 * 64 * 2 * 4;
+                       OFF_BITS = OFF_B0 + B0_BYTES, OFF_THR = OFF_BITS + NBITS * BITS, TOTAL = OFF_THR + 2 * 64 * 2 * 4;
 };
 
+// FOLD epilogue of layer 0 (below): operand nibble 2k of every 8-channel word holds channel k, nibble 2k+1 channel 4+k; layer 1's
+// weights are put in the same order
+__device__ __forceinline__ uint32_t fold_nibble_order(uint32_t w) {
+  uint32_t o = 0;
+#pragma unroll
+  for (int n = 0; n < 8; n++) o |= ((w >> (4 * ((n >> 1) + 4 * (n & 1)))) & 0xFu) << (4 * n);
+  return o;
+}
+// bytes 1 and 3 of a and of b, each replaced by its sign bit replicated (0x00 / 0xFF): four 16-bit signs -> four byte masks
+__device__ __forceinline__ uint32_t sign_bytes(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, 0xFDB9;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
 __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 
 // Warp roles (608 threads): warps 0-7 = half A (layer-1 epilogue, pool, store), warps 8-15 = half B (layer-0 epilogue into the
@@ -62,9 +82,13 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   constexpr uint32_t SF_COL = 448;  // TMEM columns of the unit scale factors (F4)
   constexpr uint32_t L0_ACC = 256;  // TMEM columns: layer-1 slots 0,64,128,192; layer-0 slots 256,320
   constexpr int L0_SLOTS = 2;  // slot = tile & 1: with eight tiles per image slot and barrier parity are compile-time constants of t
-  // FOLD: the thresholds are folded into the accumulators.  Every accumulator column n is pre-loaded with -(thr[n] + 1) (int32,
-  // layer 0) / -(thr[n] + 1/2) (fp32, layer 1) and all MMAs accumulate, so the sign bit of the result is the negated decision
-  // thr < acc and the epilogue is one funnel shift per channel instead of compare + select + insert.
+  // FOLD: the thresholds are folded into the accumulators, arranged so that the SIGN BIT of the result is the decision thr < acc.
+  // Layer 0: column n is pre-loaded with thr[n] (clamped to the reachable range, so the result fits 16 bits) and the MMAs run on
+  // negated weights: thr - S < 0 <=> decision 1.  The epilogue reads the accumulators with .pack::16b (two channels per
+  // register), turns four signs into four 0x00 / 0xFF bytes with one PRMT and merges two such words into eight operand nibbles
+  // with one LOP3: three ALU instructions per eight channels.  A set decision is therefore the e2m1 code 0xF = -6.0, not 1.0:
+  // layer 1 accumulates -6 * (its true sum) onto a pre-load of 6 * thr + 3 (exact in fp32), negative <=> thr < sum, and its
+  // epilogue is one funnel shift per channel instead of compare + select + insert.
   constexpr bool FOLD = F4 && OUTM == OUT_BIT;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t full[4], empty[4], l0_done[2][L0_TILES], abuf_empty[2], f0[L0_SLOTS], e0[L0_SLOTS], p_full[2], p_empty[2], img_full[2],
@@ -85,13 +109,15 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   for (int i = tid; i < 64 * 9 * S::NPL; i += 608) {  // layer-1 weights -> chunk-major operand layout
     const int n = i % 64, kc = i / 64;
     const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
-    *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = *reinterpret_cast<const uint4*>(src + kc * 16);
+    uint4 wv = *reinterpret_cast<const uint4*>(src + kc * 16);
+    if (FOLD) { wv.x = fold_nibble_order(wv.x); wv.y = fold_nibble_order(wv.y); wv.z = fold_nibble_order(wv.z); wv.w = fold_nibble_order(wv.w); }
+    *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = wv;
   }
   for (int i = tid; i < 64 * 64; i += 608) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
-    sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)v;
+    sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)(FOLD ? -v : v);  // FOLD: the MMAs subtract (see below)
   }
   for (int i = tid; i < 128; i += 608) {
     const int t = L0.thr[i];
@@ -107,7 +133,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     for (int i = 0; i < 2; i++) {
       tc::mbar_init(&abuf_empty[i], 2);
       for (int t = 0; t < L0_TILES; t++) tc::mbar_init(&l0_done[i][t], 256);
-      tc::mbar_init(&p_full[i], 256); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
+      tc::mbar_init(&p_full[i], P_SPLIT < 1088 ? 512 : 256); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
     }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
     for (int i = 0; i < L0_SLOTS; i++) { tc::mbar_init(&f0[i], 1); tc::mbar_init(&e0[i], 8); }
@@ -128,34 +154,53 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   const uint32_t idesc = tc::make_idesc_i8(128, 64), idesc_f4 = tc::make_idesc_mxf4(128, 64), sf = tmem + SF_COL;
   const uint32_t sA_u = tc::smem_u32(smem), sB1_u = tc::smem_u32(sB1), sP_u = tc::smem_u32(sP), sB0_u = tc::smem_u32(sB0);
   bool failed = false;
+#ifdef BNNB_PROF01
+  long long pw[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tl_ = 0;
+#define PT0() tl_ = clock64()
+#define PT(i) { const long long n_ = clock64(); pw[i] += n_ - tl_; tl_ = n_; }
+  const long long pt0 = clock64();
+#define PWAIT(bar, par, idx) ([&] { const long long t_ = clock64(); const bool ok_ = tc::mbar_wait(bar, par); pw[idx] += clock64() - t_; return ok_; }())
+#else
+#define PWAIT(bar, par, idx) tc::mbar_wait(bar, par)
+#define PT0()
+#define PT(i)
+#endif
   const long long first = blockIdx.x, stride = gridDim.x;
   const int K = first < n_img ? (int)((n_img - first + stride - 1) / stride) : 0;  // images of this CTA
 
   // window plane of image kk, built by half A (which has the slack) two images ahead of its own layer-1 epilogue, so that
   // layer 0's MMAs never wait for it
-  auto build_p = [&](int kk) {
+  // Both halves build it (rows [0, P_SPLIT) by half A, the rest by half B): half A for image k+2 while it waits for image k's
+  // first layer-1 tile, half B for image k+1 before it starts on image k's layer-0 tiles (the plane's previous user, image k-1,
+  // has been drained by then).
+
+  auto build_p = [&](int kk, int m_lo, int m_hi) {
     const int buf = kk & 1;
     const uint32_t par = (uint32_t)(kk >> 1) & 1;
-    if (!failed && !tc::mbar_wait(&img_full[buf], par)) failed = true;
-    if (kk >= 2 && !failed && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
+    if (!failed && !PWAIT(&img_full[buf], par, 0)) failed = true;
+    if (kk >= 2 && !failed && !PWAIT(&p_empty[buf], par ^ 1, 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
+    PT0();
     const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
     uint8_t* sPk = sP + (size_t)buf * P_BYTES;
 #pragma unroll 3
-    for (int m = ht; m < 1024 + 64; m += 256) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
+    for (int m = m_lo + ht; m < m_hi; m += 256) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
       const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
       uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
       if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
       *reinterpret_cast<uint4*>(sPk + (size_t)m * 16) =
           make_uint4(__funnelshift_r(x0, x1, sh), __funnelshift_r(x1, x2, sh), __funnelshift_r(x2, x3, sh), __funnelshift_r(x3, x4, sh));
     }
+    PT(9);
     tc::fence_async_smem();
     tc::mbar_arrive(&p_full[buf]);
+    PT(10);
   };
   if (role == 1) {
     // ================= half B (8 warps): layer-0 epilogue into layer-1 operand buffer k&1; team = 32-channel half ================
     int thrA[32];  // first thresholds in registers: the epilogue's shared-memory traffic competes with the MMA operand reads
 #pragma unroll
-    for (int c = 0; c < 32; c++) thrA[c] = FOLD ? -(min(sthr0[2 * (team * 32 + c)], 1 << 26) + 1) : sthr0[2 * (team * 32 + c)];
+    for (int c = 0; c < 32; c++)  // |S| <= 27 * 128: thresholds outside [-3457, 3456] decide like the nearest bound
+      thrA[c] = FOLD ? max(min(sthr0[2 * (team * 32 + c)], 3456), -3457) : sthr0[2 * (team * 32 + c)];
     auto preload0 = [&](int slot) {  // this warp's lane quarter and channel half of layer-0 accumulator `slot`
       tc::tmem_st32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
       tc::tmem_st_wait();
@@ -167,32 +212,47 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       half_sync(2);
       if (ht == 0) tc::mbar_arrive(&pre_done);
     }
+    if (K > 0 && P_SPLIT < 1088) build_p(0, P_SPLIT, 1024 + 64);
     for (int k = 0; k < K; k++) {
       const int buf = k & 1;
       const uint32_t par = (uint32_t)(k >> 1) & 1;
+#ifdef BNNB_PROF01
+      const long long tb_ = clock64();
+#endif
+      if (k + 1 < K && P_SPLIT < 1088) build_p(k + 1, P_SPLIT, 1024 + 64);
+#ifdef BNNB_PROF01
+      pw[3] += clock64() - tb_;
+#endif
       // the layer-1 MMAs that read this operand buffer two images ago must have completed before it is overwritten
-      if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], par ^ 1)) failed = true;
+      if (k >= 2 && !failed && !PWAIT(&abuf_empty[buf], par ^ 1, 0)) failed = true;
       uint8_t* sA = smem + (size_t)buf * L1_A;
 #pragma unroll
       for (int t = 0; t < L0_TILES; t++) {
         const int slot = t & 1;  // u = 4k + (t >> 1): its parity does not depend on k
-        if (!failed && !tc::mbar_wait(&f0[slot], (uint32_t)(t >> 1) & 1)) failed = true;
+        if (!failed && !PWAIT(&f0[slot], (uint32_t)(t >> 1) & 1, 1)) failed = true;
         tc::fence_after_sync();
+        PT0();
         const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
         const bool valid = x < 30 && y < 30;
         uint32_t r[32];
-        tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, r);
-        tc::tmem_ld_wait_dep(r);
-        if (FOLD) {  // the top nibble of acc - thr - 1 is 0xF (decision 0) or 0x0 (decision 1): e2m1 code = ~nibble & 0x2
+        if (FOLD) {
+          uint32_t h[16];  // h[j]: low 16 bits of channels 2j (low half) and 2j+1 (high half)
+          tc::tmem_ld32_pack16(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, h);
+          tc::tmem_ld_wait_dep16(h);
+          PT(5);
           uint32_t v[4];
 #pragma unroll
           for (int q = 0; q < 4; q++) {
-            uint32_t wv = 0;
-#pragma unroll
-            for (int e = 7; e >= 0; e--) wv = __funnelshift_l(r[q * 8 + e], wv, 4);
-            v[q] = ~wv & 0x22222222u;
+            const uint32_t lo = sign_bytes(h[4 * q], h[4 * q + 1]), hi = sign_bytes(h[4 * q + 2], h[4 * q + 3]);  // channels 8q+0..3, 8q+4..7
+            v[q] = (lo & 0x0F0F0F0Fu) | (hi & 0xF0F0F0F0u);
           }
           if (valid) *reinterpret_cast<uint4*>(sA + (size_t)team * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+        } else {
+        tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, r);
+        tc::tmem_ld_wait_dep(r);
+        PT(5);
+        }
+        if (FOLD) {
         } else if (F4) {  // 32 channels = 32 e2m1 nibbles = one uint4 store into plane `team`: 1 -> 0x2, 0 -> 0x0, -1 -> 0xA
           uint32_t v[4];
 #pragma unroll
@@ -232,7 +292,9 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
             if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * team + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
           }
         }
+        PT(6);
         if (FOLD) preload0(slot);
+        PT(7);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&e0[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
@@ -240,6 +302,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         // (generic-proxy writes, read by the async proxy: fence first)
         tc::fence_async_smem();
         tc::mbar_arrive(&l0_done[buf][t]);
+        PT(8);
       }
     }
   } else if (role == 2) {
@@ -263,14 +326,14 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       auto issue_l0 = [&](int k, int t) {
         const int buf = k & 1;
         if (t == 0) {
-          if (!failed && !tc::mbar_wait(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+          if (!failed && !PWAIT(&p_full[buf], (uint32_t)(k >> 1) & 1, 0)) failed = true;
           if (k + 2 < K && leader) {  // image buffer `buf` has been consumed: prefetch image k+2 into it
             tc::mbar_expect_tx(&img_full[buf], 3072);
             tc::bulk_g2s(sImg + (size_t)buf * IMG_BYTES, in + (first + (long long)(k + 2) * stride) * 3072, 3072, &img_full[buf]);
           }
         }
         const int slot = t & 1;  // u = 4k + (t >> 1) uses of this slot so far
-        if ((k > 0 || t >= 2) && !failed && !tc::mbar_wait(&e0[slot], (uint32_t)((t >> 1) & 1) ^ 1)) failed = true;
+        if ((k > 0 || t >= 2) && !failed && !PWAIT(&e0[slot], (uint32_t)((t >> 1) & 1) ^ 1, 1)) failed = true;
         tc::fence_after_sync();
         const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
         const uint32_t a0 = p_lo[buf] + (uint32_t)(t * 128);  // descriptor start fields are in 16-byte units: one row = 1
@@ -287,7 +350,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
         const uint32_t a_lo = a1_lo[buf] + (uint32_t)(t * 128);
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-        if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+        if (u >= 1 && !failed && !PWAIT(&empty[slot], (uint32_t)(u - 1) & 1, 1)) failed = true;
         tc::fence_after_sync();
         const uint32_t acc = tmem + (uint32_t)slot * 64;
         bool firstmma = true;
@@ -333,7 +396,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           for (int t = 0; t < L1_TILES; t++)
             if (((k * L1_TILES + t) & 1) == w) {
               // layer-1 tile t reads operand rows [128t, 128t+190): complete once layer-0 tile t+1 has been written
-              if (!failed && !tc::mbar_wait(&l0_done[buf][t + 1], (uint32_t)(k >> 1) & 1)) failed = true;
+              if (!failed && !PWAIT(&l0_done[buf][t + 1], (uint32_t)(k >> 1) & 1, 0)) failed = true;
               issue_l1(k, t);
             }
           if (leader) tc::commit(&abuf_empty[buf]);  // this warp's MMAs of the image; the barrier counts both issuers
@@ -348,7 +411,10 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     const acc_t* sthr1t = reinterpret_cast<const acc_t*>(sthr1);
     acc_t thrA[32];
 #pragma unroll
-    for (int c = 0; c < 32; c++) thrA[c] = FOLD ? (acc_t)(-((float)sthr1t[2 * (team * 32 + c)] + 0.5f)) : sthr1t[2 * (team * 32 + c)];
+    for (int c = 0; c < 32; c++) {
+      const acc_t t = sthr1t[2 * (team * 32 + c)];
+      thrA[c] = FOLD ? (acc_t)((float)t > 1.0e38f ? 3.0e38f : 6.0f * (float)t + 3.0f) : t;  // 6 * (thr + 1/2); the sentinel never fires
+    }
     auto preload1 = [&](int slot) {
       tc::tmem_st32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
       tc::tmem_st_wait();
@@ -360,24 +426,42 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       half_sync(1);
       if (ht == 0) tc::mbar_arrive(&pre_done);
     }
-    if (K > 0) build_p(0);
-    if (K > 1) build_p(1);
+    if (K > 0) build_p(0, 0, P_SPLIT);
+    if (K > 1) build_p(1, 0, P_SPLIT);
     for (int k = 0; k < K; k++) {
       const long long img = first + (long long)k * stride;
-      if (k + 2 < K) build_p(k + 2);  // before this image's tiles arrive: half A would be waiting anyway
+#ifdef BNNB_PROF01
+      const long long tb_ = clock64();
+#endif
+      if (k + 2 < K) build_p(k + 2, 0, P_SPLIT);  // before this image's tiles arrive: half A would be waiting anyway
+#ifdef BNNB_PROF01
+      pw[3] += clock64() - tb_;
+#endif
+      uint32_t* sbk = sbits + (size_t)(k & (S::NBITS - 1)) * (S::BITS / 4);  // two buffers: the pool of image k overlaps the tiles of image k+1
       for (int t = 0; t < L1_TILES; t++) {
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-        if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
+        if (!failed && !PWAIT(&full[slot], (uint32_t)u & 1, 2)) failed = true;
         tc::fence_after_sync();
+        PT0();
         const int m = t * 128 + hw * 32 + lane;
         uint32_t r[32];
         tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, r);
         tc::tmem_ld_wait_dep(r);
+        PT(5);
         uint32_t b0 = 0, b1 = 0;
         if (FOLD) {
 #pragma unroll
-          for (int c = 31; c >= 0; c--) b0 = __funnelshift_l(r[c], b0, 1);  // sign bits, channel c at bit c
-          b0 = ~b0;
+#ifdef BNNB_ILP
+          uint32_t q0 = 0, q1 = 0, q2 = 0, q3 = 0;  // four independent chains (a lone chain of 32 dependent shifts is pure latency)
+#pragma unroll
+          for (int c = 7; c >= 0; c--) {
+            q0 = __funnelshift_l(r[c], q0, 1); q1 = __funnelshift_l(r[8 + c], q1, 1);
+            q2 = __funnelshift_l(r[16 + c], q2, 1); q3 = __funnelshift_l(r[24 + c], q3, 1);
+          }
+          b0 = __byte_perm(q0, q1, 0x1140) | __byte_perm(q2, q3, 0x4011);
+#else
+          for (int c = 31; c >= 0; c--) b0 = __funnelshift_l(r[c], b0, 1);  // sign bits = decisions, channel c at bit c
+#endif
         } else {
 #pragma unroll
           for (int c = 0; c < 32; c++) {
@@ -387,18 +471,24 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
             else { const int t1 = sthr1t[2 * (team * 32 + c) + 1] < sv; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
           }
         }
-        sbits[(size_t)m * WPP + team] = b0;
-        if (OUTM == OUT_TERN) sbits[(size_t)m * WPP + 2 + team] = b1;
+        sbk[(size_t)m * WPP + team] = b0;
+        if (OUTM == OUT_TERN) sbk[(size_t)m * WPP + 2 + team] = b1;
+        PT(6);
         if (FOLD) preload1(slot);
+        PT(7);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
+        PT(8);
       }
+#ifdef BNNB_PROF01
+      const long long tp_ = clock64();
+#endif
       half_sync(1);
       // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
       for (int i = ht; i < 196 * 2; i += 256) {
         const int j = i & 1, op = i >> 1, oy = op / 14, ox = op % 14;
-        const uint32_t* r00 = sbits + (size_t)((2 * oy) * 30 + 2 * ox) * WPP;
+        const uint32_t* r00 = sbk + (size_t)((2 * oy) * 30 + 2 * ox) * WPP;
         const uint32_t *r01 = r00 + WPP, *r10 = r00 + 30 * WPP, *r11 = r10 + WPP;
         uint32_t* dst = out + ((size_t)img * 196 + op) * WPP;
         if (OUTM == OUT_BIT) {
@@ -412,9 +502,17 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           dst[2 + j] = P;
         }
       }
-      half_sync(1);  // the next image's epilogue overwrites sbits
+      // two buffers: no second barrier (the next image writes the other buffer, and nobody passes the next image's barrier before all have pooled)
+      if (S::NBITS == 1) half_sync(1);
+#ifdef BNNB_PROF01
+      pw[4] += clock64() - tp_;
+#endif
     }
   }
+#ifdef BNNB_PROF01
+  if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4 || warp == 8 || warp == 16 || warp == 17 || warp == 18))
+    printf("PROF01 warp %d K %d total %lld w0 %lld w1 %lld w2 %lld bp %lld pool %lld | ld %lld alu %lld pre %lld arr %lld | bploop %lld bpfence %lld\n", warp, K, clock64() - pt0, pw[0], pw[1], pw[2], pw[3], pw[4], pw[5], pw[6], pw[7], pw[8], pw[9], pw[10]);
+#endif
   if (failed && status) *status = 1;
   tc::fence_before_sync();
   __syncthreads();

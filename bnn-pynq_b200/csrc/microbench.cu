@@ -58,6 +58,27 @@ __global__ void __launch_bounds__(512) mb_imma(uint32_t* out, long long* cyc) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = (uint32_t)s;
   if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
+// generic ALU-instruction throughput probes (the epilogues of the tcgen05 kernels are one such instruction per accumulator column)
+#define BNNB_MB_KERNEL(NAME, ASM)                                                                   \
+  __global__ void __launch_bounds__(512) NAME(uint32_t* out, long long* cyc) {                      \
+    uint32_t a[kUnroll], b = threadIdx.x | 1, c = blockIdx.x * 7 + 3;                               \
+    _Pragma("unroll") for (int i = 0; i < kUnroll; i++) a[i] = threadIdx.x * 2654435761u + i;       \
+    const long long t0 = clock64();                                                                 \
+    for (int it = 0; it < kIters; it++) {                                                           \
+      _Pragma("unroll") for (int i = 0; i < kUnroll; i++) asm volatile(ASM : "+r"(a[i]) : "r"(b), "r"(c)); \
+    }                                                                                               \
+    const long long t1 = clock64();                                                                 \
+    uint32_t s = 0;                                                                                 \
+    _Pragma("unroll") for (int i = 0; i < kUnroll; i++) s += a[i];                                  \
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;                                                 \
+    if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;                                                \
+  }
+BNNB_MB_KERNEL(mb_shf, "shf.l.wrap.b32 %0, %1, %0, 1;")          // the sign-bit harvest: SHF.L.W.U32.HI
+BNNB_MB_KERNEL(mb_prmt, "prmt.b32 %0, %0, %1, 0x7351;")
+BNNB_MB_KERNEL(mb_imadhi, "mad.hi.u32 %0, %0, %1, %2;")
+BNNB_MB_KERNEL(mb_imad, "mad.lo.u32 %0, %0, %1, %2;")
+BNNB_MB_KERNEL(mb_shr, "shr.u32 %0, %0, 1;")
+BNNB_MB_KERNEL(mb_fmnmx, "min.f32 %0, %0, %1;")
 }  // namespace
 
 extern "C" double bnnb_microbench(int which, double* clock_mhz) {
@@ -75,6 +96,12 @@ extern "C" double bnnb_microbench(int which, double* clock_mhz) {
     cudaEventRecord(e0);
     if (which == 0) mb_popc<<<blocks, threads>>>(out, cyc);
     else if (which == 1) mb_imma<<<blocks, threads>>>(out, cyc);
+    else if (which == 3) mb_shf<<<blocks, threads>>>(out, cyc);
+    else if (which == 4) mb_prmt<<<blocks, threads>>>(out, cyc);
+    else if (which == 5) mb_imadhi<<<blocks, threads>>>(out, cyc);
+    else if (which == 6) mb_imad<<<blocks, threads>>>(out, cyc);
+    else if (which == 7) mb_shr<<<blocks, threads>>>(out, cyc);
+    else if (which == 8) mb_fmnmx<<<blocks, threads>>>(out, cyc);
     else mb_lop3<<<blocks, threads>>>(out, cyc);
     cudaEventRecord(e1);
     cudaEventSynchronize(e1);
@@ -189,4 +216,41 @@ extern "C" double bnnb_mbar_roundtrip(int mode) {
   cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
   cudaFree(cyc);
   return e == cudaSuccess ? (double)c / iters : -1;
+}
+
+// ---- tcgen05.ld .pack::16b probe: one warp writes in[lane][0..31] to 32 TMEM columns (tcgen05.st .x32) and reads them back with
+// .32x32b.x16.pack::16b into out[lane][0..15].  Pins which 16 bits of which column land in which half of each register. -----------
+namespace {
+__global__ void __launch_bounds__(32) k_tmem_pack_probe(const uint32_t* in, uint32_t* out) {
+  __shared__ uint32_t tmem_base;
+  bnnb::tc::tmem_alloc(&tmem_base, 32);
+  bnnb::tc::fence_before_sync();
+  __syncwarp();
+  bnnb::tc::fence_after_sync();
+  uint32_t r[32], q[16];
+#pragma unroll
+  for (int i = 0; i < 32; i++) r[i] = in[threadIdx.x * 32 + i];
+  bnnb::tc::tmem_st32(tmem_base, r);
+  bnnb::tc::tmem_st_wait();
+  bnnb::tc::tmem_ld32_pack16(tmem_base, q);
+  bnnb::tc::tmem_ld_wait_dep16(q);
+#pragma unroll
+  for (int i = 0; i < 16; i++) out[threadIdx.x * 16 + i] = q[i];
+  bnnb::tc::fence_before_sync();
+  __syncwarp();
+  bnnb::tc::tmem_dealloc(tmem_base, 32);
+}
+}  // namespace
+
+extern "C" int bnnb_tmem_pack_probe(const uint32_t* in, uint32_t* out) {
+  uint32_t *di, *dout;
+  cudaSetDevice(0);
+  if (cudaMalloc(&di, 32 * 32 * 4) != cudaSuccess) return -1;
+  cudaMalloc(&dout, 32 * 16 * 4);
+  cudaMemcpy(di, in, 32 * 32 * 4, cudaMemcpyHostToDevice);
+  k_tmem_pack_probe<<<1, 32>>>(di, dout);
+  const bool ok = cudaDeviceSynchronize() == cudaSuccess;
+  cudaMemcpy(out, dout, 32 * 16 * 4, cudaMemcpyDeviceToHost);
+  cudaFree(di); cudaFree(dout);
+  return ok ? 0 : -1;
 }
