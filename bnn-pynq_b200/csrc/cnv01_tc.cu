@@ -13,7 +13,6 @@
 // (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one thread prefetches images by TMA bulk copy two
 // images ahead and issues all MMAs, interleaving layer 1 of image i with layer 0 of image i+1 tile by tile.
 #include <climits>
-#include <cstdio>
 #include <type_traits>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
@@ -32,7 +31,7 @@ constexpr int IMG_BYTES = 3072 + 64;          // image + slack for the 16-byte w
 constexpr int B0_BYTES = 4 * 64 * 16;         // layer-0 weights: 4 chunks x 64 rows x 16 bytes
 constexpr int L1_TILES = 7, L0_TILES = 8;
 #ifndef BNNB_PSPLIT
-#define BNNB_PSPLIT 1088
+#define BNNB_PSPLIT 512
 #endif
 constexpr int P_SPLIT = BNNB_PSPLIT;        // window-plane rows [0, P_SPLIT) are built by half A, the rest (if any) by half B
 
@@ -154,17 +153,6 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   const uint32_t idesc = tc::make_idesc_i8(128, 64), idesc_f4 = tc::make_idesc_mxf4(128, 64), sf = tmem + SF_COL;
   const uint32_t sA_u = tc::smem_u32(smem), sB1_u = tc::smem_u32(sB1), sP_u = tc::smem_u32(sP), sB0_u = tc::smem_u32(sB0);
   bool failed = false;
-#ifdef BNNB_PROF01
-  long long pw[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tl_ = 0;
-#define PT0() tl_ = clock64()
-#define PT(i) { const long long n_ = clock64(); pw[i] += n_ - tl_; tl_ = n_; }
-  const long long pt0 = clock64();
-#define PWAIT(bar, par, idx) ([&] { const long long t_ = clock64(); const bool ok_ = tc::mbar_wait(bar, par); pw[idx] += clock64() - t_; return ok_; }())
-#else
-#define PWAIT(bar, par, idx) tc::mbar_wait(bar, par)
-#define PT0()
-#define PT(i)
-#endif
   const long long first = blockIdx.x, stride = gridDim.x;
   const int K = first < n_img ? (int)((n_img - first + stride - 1) / stride) : 0;  // images of this CTA
 
@@ -177,9 +165,8 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   auto build_p = [&](int kk, int m_lo, int m_hi) {
     const int buf = kk & 1;
     const uint32_t par = (uint32_t)(kk >> 1) & 1;
-    if (!failed && !PWAIT(&img_full[buf], par, 0)) failed = true;
-    if (kk >= 2 && !failed && !PWAIT(&p_empty[buf], par ^ 1, 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
-    PT0();
+    if (!failed && !tc::mbar_wait(&img_full[buf], par)) failed = true;
+    if (kk >= 2 && !failed && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
     const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
     uint8_t* sPk = sP + (size_t)buf * P_BYTES;
 #pragma unroll 3
@@ -190,10 +177,8 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       *reinterpret_cast<uint4*>(sPk + (size_t)m * 16) =
           make_uint4(__funnelshift_r(x0, x1, sh), __funnelshift_r(x1, x2, sh), __funnelshift_r(x2, x3, sh), __funnelshift_r(x3, x4, sh));
     }
-    PT(9);
     tc::fence_async_smem();
     tc::mbar_arrive(&p_full[buf]);
-    PT(10);
   };
   if (role == 1) {
     // ================= half B (8 warps): layer-0 epilogue into layer-1 operand buffer k&1; team = 32-channel half ================
@@ -216,22 +201,15 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     for (int k = 0; k < K; k++) {
       const int buf = k & 1;
       const uint32_t par = (uint32_t)(k >> 1) & 1;
-#ifdef BNNB_PROF01
-      const long long tb_ = clock64();
-#endif
       if (k + 1 < K && P_SPLIT < 1088) build_p(k + 1, P_SPLIT, 1024 + 64);
-#ifdef BNNB_PROF01
-      pw[3] += clock64() - tb_;
-#endif
       // the layer-1 MMAs that read this operand buffer two images ago must have completed before it is overwritten
-      if (k >= 2 && !failed && !PWAIT(&abuf_empty[buf], par ^ 1, 0)) failed = true;
+      if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], par ^ 1)) failed = true;
       uint8_t* sA = smem + (size_t)buf * L1_A;
 #pragma unroll
       for (int t = 0; t < L0_TILES; t++) {
         const int slot = t & 1;  // u = 4k + (t >> 1): its parity does not depend on k
-        if (!failed && !PWAIT(&f0[slot], (uint32_t)(t >> 1) & 1, 1)) failed = true;
+        if (!failed && !tc::mbar_wait(&f0[slot], (uint32_t)(t >> 1) & 1)) failed = true;
         tc::fence_after_sync();
-        PT0();
         const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
         const bool valid = x < 30 && y < 30;
         uint32_t r[32];
@@ -239,7 +217,6 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           uint32_t h[16];  // h[j]: low 16 bits of channels 2j (low half) and 2j+1 (high half)
           tc::tmem_ld32_pack16(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, h);
           tc::tmem_ld_wait_dep16(h);
-          PT(5);
           uint32_t v[4];
 #pragma unroll
           for (int q = 0; q < 4; q++) {
@@ -250,7 +227,6 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         } else {
         tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, r);
         tc::tmem_ld_wait_dep(r);
-        PT(5);
         }
         if (FOLD) {
         } else if (F4) {  // 32 channels = 32 e2m1 nibbles = one uint4 store into plane `team`: 1 -> 0x2, 0 -> 0x0, -1 -> 0xA
@@ -292,9 +268,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
             if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * team + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
           }
         }
-        PT(6);
         if (FOLD) preload0(slot);
-        PT(7);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&e0[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
@@ -302,7 +276,6 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         // (generic-proxy writes, read by the async proxy: fence first)
         tc::fence_async_smem();
         tc::mbar_arrive(&l0_done[buf][t]);
-        PT(8);
       }
     }
   } else if (role == 2) {
@@ -326,14 +299,14 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       auto issue_l0 = [&](int k, int t) {
         const int buf = k & 1;
         if (t == 0) {
-          if (!failed && !PWAIT(&p_full[buf], (uint32_t)(k >> 1) & 1, 0)) failed = true;
+          if (!failed && !tc::mbar_wait(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
           if (k + 2 < K && leader) {  // image buffer `buf` has been consumed: prefetch image k+2 into it
             tc::mbar_expect_tx(&img_full[buf], 3072);
             tc::bulk_g2s(sImg + (size_t)buf * IMG_BYTES, in + (first + (long long)(k + 2) * stride) * 3072, 3072, &img_full[buf]);
           }
         }
         const int slot = t & 1;  // u = 4k + (t >> 1) uses of this slot so far
-        if ((k > 0 || t >= 2) && !failed && !PWAIT(&e0[slot], (uint32_t)((t >> 1) & 1) ^ 1, 1)) failed = true;
+        if ((k > 0 || t >= 2) && !failed && !tc::mbar_wait(&e0[slot], (uint32_t)((t >> 1) & 1) ^ 1)) failed = true;
         tc::fence_after_sync();
         const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
         const uint32_t a0 = p_lo[buf] + (uint32_t)(t * 128);  // descriptor start fields are in 16-byte units: one row = 1
@@ -350,7 +323,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
         const uint32_t a_lo = a1_lo[buf] + (uint32_t)(t * 128);
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-        if (u >= 1 && !failed && !PWAIT(&empty[slot], (uint32_t)(u - 1) & 1, 1)) failed = true;
+        if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
         tc::fence_after_sync();
         const uint32_t acc = tmem + (uint32_t)slot * 64;
         bool firstmma = true;
@@ -396,7 +369,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           for (int t = 0; t < L1_TILES; t++)
             if (((k * L1_TILES + t) & 1) == w) {
               // layer-1 tile t reads operand rows [128t, 128t+190): complete once layer-0 tile t+1 has been written
-              if (!failed && !PWAIT(&l0_done[buf][t + 1], (uint32_t)(k >> 1) & 1, 0)) failed = true;
+              if (!failed && !tc::mbar_wait(&l0_done[buf][t + 1], (uint32_t)(k >> 1) & 1)) failed = true;
               issue_l1(k, t);
             }
           if (leader) tc::commit(&abuf_empty[buf]);  // this warp's MMAs of the image; the barrier counts both issuers
@@ -430,28 +403,19 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     if (K > 1) build_p(1, 0, P_SPLIT);
     for (int k = 0; k < K; k++) {
       const long long img = first + (long long)k * stride;
-#ifdef BNNB_PROF01
-      const long long tb_ = clock64();
-#endif
       if (k + 2 < K) build_p(k + 2, 0, P_SPLIT);  // before this image's tiles arrive: half A would be waiting anyway
-#ifdef BNNB_PROF01
-      pw[3] += clock64() - tb_;
-#endif
       uint32_t* sbk = sbits + (size_t)(k & (S::NBITS - 1)) * (S::BITS / 4);  // two buffers: the pool of image k overlaps the tiles of image k+1
       for (int t = 0; t < L1_TILES; t++) {
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-        if (!failed && !PWAIT(&full[slot], (uint32_t)u & 1, 2)) failed = true;
+        if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
-        PT0();
         const int m = t * 128 + hw * 32 + lane;
         uint32_t r[32];
         tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, r);
         tc::tmem_ld_wait_dep(r);
-        PT(5);
         uint32_t b0 = 0, b1 = 0;
         if (FOLD) {
 #pragma unroll
-#ifdef BNNB_ILP
           uint32_t q0 = 0, q1 = 0, q2 = 0, q3 = 0;  // four independent chains (a lone chain of 32 dependent shifts is pure latency)
 #pragma unroll
           for (int c = 7; c >= 0; c--) {
@@ -459,9 +423,6 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
             q2 = __funnelshift_l(r[16 + c], q2, 1); q3 = __funnelshift_l(r[24 + c], q3, 1);
           }
           b0 = __byte_perm(q0, q1, 0x1140) | __byte_perm(q2, q3, 0x4011);
-#else
-          for (int c = 31; c >= 0; c--) b0 = __funnelshift_l(r[c], b0, 1);  // sign bits = decisions, channel c at bit c
-#endif
         } else {
 #pragma unroll
           for (int c = 0; c < 32; c++) {
@@ -473,17 +434,11 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         }
         sbk[(size_t)m * WPP + team] = b0;
         if (OUTM == OUT_TERN) sbk[(size_t)m * WPP + 2 + team] = b1;
-        PT(6);
         if (FOLD) preload1(slot);
-        PT(7);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
-        PT(8);
       }
-#ifdef BNNB_PROF01
-      const long long tp_ = clock64();
-#endif
       half_sync(1);
       // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
       for (int i = ht; i < 196 * 2; i += 256) {
@@ -504,15 +459,8 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       }
       // two buffers: no second barrier (the next image writes the other buffer, and nobody passes the next image's barrier before all have pooled)
       if (S::NBITS == 1) half_sync(1);
-#ifdef BNNB_PROF01
-      pw[4] += clock64() - tp_;
-#endif
     }
   }
-#ifdef BNNB_PROF01
-  if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4 || warp == 8 || warp == 16 || warp == 17 || warp == 18))
-    printf("PROF01 warp %d K %d total %lld w0 %lld w1 %lld w2 %lld bp %lld pool %lld | ld %lld alu %lld pre %lld arr %lld | bploop %lld bpfence %lld\n", warp, K, clock64() - pt0, pw[0], pw[1], pw[2], pw[3], pw[4], pw[5], pw[6], pw[7], pw[8], pw[9], pw[10]);
-#endif
   if (failed && status) *status = 1;
   tc::fence_before_sync();
   __syncthreads();
