@@ -296,7 +296,7 @@ def main():
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = world * B * a.steps / e2e_s
-    if fam == "cnv":
+    if fam == "cnv" and not os.environ.get("BNNB_BENCH_NOCHECK"):  # (kernel-stripping experiments produce garbage on purpose)
         assert np.array_equal(cls_host.view(np.int32), dev_classes), "host-buffer and device-resident paths disagree"
 
     # ---- roofline of the dominant kernel (live CUDA-event durations over the timed region) ----------------------

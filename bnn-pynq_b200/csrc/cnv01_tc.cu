@@ -13,6 +13,7 @@
 // (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one thread prefetches images by TMA bulk copy two
 // images ahead and issues all MMAs, interleaving layer 1 of image i with layer 0 of image i+1 tile by tile.
 #include <climits>
+#include <cstdio>
 #include <type_traits>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
@@ -30,10 +31,21 @@ constexpr int P_BYTES = P_ROWS * 16;
 constexpr int IMG_BYTES = 3072 + 64;          // image + slack for the 16-byte windows of the last rows
 constexpr int B0_BYTES = 4 * 64 * 16;         // layer-0 weights: 4 chunks x 64 rows x 16 bytes
 constexpr int L1_TILES = 7, L0_TILES = 8;
-#ifndef BNNB_PSPLIT
-#define BNNB_PSPLIT 512
+#ifndef BNNB_NH
+#define BNNB_NH 4
 #endif
-constexpr int P_SPLIT = BNNB_PSPLIT;        // window-plane rows [0, P_SPLIT) are built by half A, the rest (if any) by half B
+#ifdef BNNB_NOEPI
+constexpr bool kEpi = false;  // experiment: epilogue bodies compiled out (results wrong, hand-offs kept)
+#else
+constexpr bool kEpi = true;
+#endif
+#ifdef BNNB_NOMMA
+constexpr bool kMma = false;  // experiment: MMAs compiled out (commits kept)
+#else
+constexpr bool kMma = true;
+#endif
+constexpr int NH = BNNB_NH;                   // helper warps (window planes, max-pool + store)
+constexpr int NT01 = (8 + 8 + 3 + NH) * 32;   // threads per CTA
 
 template <int OUTM, bool F4> struct Smem01 {
   static constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
@@ -74,13 +86,18 @@ __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 2
 //   abuf_empty[b] warp 16 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
 //   full[s], empty[s] warp 16 <-> half A  layer-1 accumulator slot s (of 4) full / read out
 template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
-__global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
+__global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
                                                       int n_img, int out_fmt, int* __restrict__ status) {
   using S = Smem01<OUTM, F4>;
   constexpr int L1_A = S::L1_A;
   constexpr uint32_t SF_COL = 448;  // TMEM columns of the unit scale factors (F4)
   constexpr uint32_t L0_ACC = 256;  // TMEM columns: layer-1 slots 0,64,128,192; layer-0 slots 256,320
-  constexpr int L0_SLOTS = 2;  // slot = tile & 1: with eight tiles per image slot and barrier parity are compile-time constants of t
+#ifndef BNNB_L0S
+#define BNNB_L0S 2
+#endif
+  // layer-0 accumulator slots (TMEM columns 256, 320, 384).  A tile's round trip (issue -> MMAs behind layer 1's in the in-order
+  // pipe -> epilogue -> slot free) is ~1000 clocks: the slots in flight set layer 0's tile rate, which paces the whole kernel
+  constexpr int L0_SLOTS = BNNB_L0S;
   // FOLD: the thresholds are folded into the accumulators, arranged so that the SIGN BIT of the result is the decision thr < acc.
   // Layer 0: column n is pre-loaded with thr[n] (clamped to the reachable range, so the result fits 16 bits) and the MMAs run on
   // negated weights: thr - S < 0 <=> decision 1.  The epilogue reads the accumulators with .pack::16b (two channels per
@@ -90,7 +107,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   // epilogue is one funnel shift per channel instead of compare + select + insert.
   constexpr bool FOLD = F4 && OUTM == OUT_BIT;
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t full[4], empty[4], l0_done[2][L0_TILES], abuf_empty[2], f0[L0_SLOTS], e0[L0_SLOTS], p_full[2], p_empty[2], img_full[2],
+  __shared__ __align__(8) uint64_t full[4], empty[4], l0_done[2][L0_TILES], abuf_empty[2], f0[L0_SLOTS], e0[L0_SLOTS], p_full[2], p_empty[2], img_full[2], bits_full[2], bits_empty[2],
       pre_done;
   __shared__ uint32_t tmem_base;
   uint8_t* sB1 = smem + S::OFF_B1;
@@ -101,38 +118,38 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   int32_t* sthr0 = reinterpret_cast<int32_t*>(smem + S::OFF_THR);  // layer 0: floor(thr/2)   [64][2]
   int32_t* sthr1 = sthr0 + 128;                                    // layer 1: adjusted       [64][2] (F4: as float)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int role = warp < 8 ? 0 : (warp < 16 ? 1 : 2);             // 0: half A, 1: half B, 2: issuers (warps 16, 17: layer 1; warp 18: layer 0 + TMA)
+  const int role = warp < 8 ? 0 : (warp < 16 ? 1 : (warp < 19 ? 2 : 3));             // 0: half A, 1: half B, 2: issuers (warps 16, 17: layer 1; warp 18: layer 0 + TMA)
   const int ht = tid & 255, hw = warp & 3, team = (warp >> 2) & 1;  // thread in the half; TMEM lane quarter; 32-channel half
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
-  for (int i = tid; i < 64 * 9 * S::NPL; i += 608) {  // layer-1 weights -> chunk-major operand layout
+  for (int i = tid; i < 64 * 9 * S::NPL; i += NT01) {  // layer-1 weights -> chunk-major operand layout
     const int n = i % 64, kc = i / 64;
     const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
     uint4 wv = *reinterpret_cast<const uint4*>(src + kc * 16);
     if (FOLD) { wv.x = fold_nibble_order(wv.x); wv.y = fold_nibble_order(wv.y); wv.z = fold_nibble_order(wv.z); wv.w = fold_nibble_order(wv.w); }
     *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = wv;
   }
-  for (int i = tid; i < 64 * 64; i += 608) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
+  for (int i = tid; i < 64 * 64; i += NT01) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
     sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)(FOLD ? -v : v);  // FOLD: the MMAs subtract (see below)
   }
-  for (int i = tid; i < 128; i += 608) {
+  for (int i = tid; i < 128; i += NT01) {
     const int t = L0.thr[i];
     sthr0[i] = t == INT_MAX ? INT_MAX : (t >> 1);  // thr < 2S  <=>  floor(thr/2) < S
     const int t1 = L1.thr_tc[i];
     if (F4) reinterpret_cast<float*>(sthr1)[i] = t1 == INT_MAX ? 3.0e38f : (float)t1;
     else sthr1[i] = t1;
   }
-  for (int i = tid; i < 2 * L1_A / 16; i += 608) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
-  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += 608) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < 2 * L1_A / 16; i += NT01) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
+  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += NT01) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
     for (int i = 0; i < 2; i++) {
       tc::mbar_init(&abuf_empty[i], 2);
       for (int t = 0; t < L0_TILES; t++) tc::mbar_init(&l0_done[i][t], 256);
-      tc::mbar_init(&p_full[i], P_SPLIT < 1088 ? 512 : 256); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
+      tc::mbar_init(&p_full[i], NH * 32); tc::mbar_init(&bits_full[i], 8); tc::mbar_init(&bits_empty[i], NH); tc::mbar_init(&p_empty[i], 1); tc::mbar_init(&img_full[i], 1);
     }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
     for (int i = 0; i < L0_SLOTS; i++) { tc::mbar_init(&f0[i], 1); tc::mbar_init(&e0[i], 8); }
@@ -153,24 +170,27 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
   const uint32_t idesc = tc::make_idesc_i8(128, 64), idesc_f4 = tc::make_idesc_mxf4(128, 64), sf = tmem + SF_COL;
   const uint32_t sA_u = tc::smem_u32(smem), sB1_u = tc::smem_u32(sB1), sP_u = tc::smem_u32(sP), sB0_u = tc::smem_u32(sB0);
   bool failed = false;
+#ifdef BNNB_TRACE
+  __shared__ long long tr[7][4][8];  // [event][image 8..11][tile]
+#define TR(e, k, t) if (blockIdx.x == 0 && lane == 0 && (k) >= 8 && (k) < 12) tr[e][(k) - 8][t] = clock64()
+#else
+#define TR(e, k, t)
+#endif
   const long long first = blockIdx.x, stride = gridDim.x;
   const int K = first < n_img ? (int)((n_img - first + stride - 1) / stride) : 0;  // images of this CTA
 
-  // window plane of image kk, built by half A (which has the slack) two images ahead of its own layer-1 epilogue, so that
-  // layer 0's MMAs never wait for it
-  // Both halves build it (rows [0, P_SPLIT) by half A, the rest by half B): half A for image k+2 while it waits for image k's
-  // first layer-1 tile, half B for image k+1 before it starts on image k's layer-0 tiles (the plane's previous user, image k-1,
-  // has been drained by then).
-
-  auto build_p = [&](int kk, int m_lo, int m_hi) {
+  // window plane of image kk, built by the helper warps two images ahead of layer 0's MMAs.  (Shared-memory reads wait behind the
+  // MMAs' operand stream for hundreds of clocks, so this and the pool are kept off the epilogue warps' per-tile chains.)
+  auto build_p = [&](int kk) {
+    const int hx = tid - 19 * 32;
     const int buf = kk & 1;
     const uint32_t par = (uint32_t)(kk >> 1) & 1;
     if (!failed && !tc::mbar_wait(&img_full[buf], par)) failed = true;
     if (kk >= 2 && !failed && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
     const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
     uint8_t* sPk = sP + (size_t)buf * P_BYTES;
-#pragma unroll 3
-    for (int m = m_lo + ht; m < m_hi; m += 256) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
+#pragma unroll 4
+    for (int m = hx; m < 1024 + 64; m += NH * 32) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
       const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
       uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
       if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
@@ -179,6 +199,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
     }
     tc::fence_async_smem();
     tc::mbar_arrive(&p_full[buf]);
+    if (warp == 19) { TR(6, kk, 2); }
   };
   if (role == 1) {
     // ================= half B (8 warps): layer-0 epilogue into layer-1 operand buffer k&1; team = 32-channel half ================
@@ -197,23 +218,27 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       half_sync(2);
       if (ht == 0) tc::mbar_arrive(&pre_done);
     }
-    if (K > 0 && P_SPLIT < 1088) build_p(0, P_SPLIT, 1024 + 64);
+    int s0 = 0;
+    uint32_t p0 = 0;
     for (int k = 0; k < K; k++) {
       const int buf = k & 1;
       const uint32_t par = (uint32_t)(k >> 1) & 1;
-      if (k + 1 < K && P_SPLIT < 1088) build_p(k + 1, P_SPLIT, 1024 + 64);
       // the layer-1 MMAs that read this operand buffer two images ago must have completed before it is overwritten
+      if (warp == 8) { TR(6, k, 5); }
       if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], par ^ 1)) failed = true;
+      if (warp == 8) { TR(6, k, 4); }
       uint8_t* sA = smem + (size_t)buf * L1_A;
 #pragma unroll
       for (int t = 0; t < L0_TILES; t++) {
-        const int slot = t & 1;  // u = 4k + (t >> 1): its parity does not depend on k
-        if (!failed && !tc::mbar_wait(&f0[slot], (uint32_t)(t >> 1) & 1)) failed = true;
+        const int slot = s0, spar = p0;  // tile u = 8k + t uses slot u % L0_SLOTS for the (u / L0_SLOTS)-th time
+        if (++s0 == L0_SLOTS) { s0 = 0; p0 ^= 1u; }
+        if (!failed && !tc::mbar_wait(&f0[slot], spar)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
         const bool valid = x < 30 && y < 30;
         uint32_t r[32];
-        if (FOLD) {
+        if (FOLD && !kEpi) {
+        } else if (FOLD) {
           uint32_t h[16];  // h[j]: low 16 bits of channels 2j (low half) and 2j+1 (high half)
           tc::tmem_ld32_pack16(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, h);
           tc::tmem_ld_wait_dep16(h);
@@ -268,7 +293,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
             if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * team + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
           }
         }
-        if (FOLD) preload0(slot);
+        if (FOLD && kEpi) preload0(slot);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&e0[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
@@ -276,6 +301,7 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         // (generic-proxy writes, read by the async proxy: fence first)
         tc::fence_async_smem();
         tc::mbar_arrive(&l0_done[buf][t]);
+        if (warp == 8) { TR(2, k, t); }
       }
     }
   } else if (role == 2) {
@@ -296,30 +322,39 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
         }
       if (FOLD && !failed && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
+      int s0 = 0;
+      uint32_t p0 = 0;
       auto issue_l0 = [&](int k, int t) {
         const int buf = k & 1;
         if (t == 0) {
+          TR(6, k, 0);
           if (!failed && !tc::mbar_wait(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+          TR(6, k, 1);
           if (k + 2 < K && leader) {  // image buffer `buf` has been consumed: prefetch image k+2 into it
             tc::mbar_expect_tx(&img_full[buf], 3072);
             tc::bulk_g2s(sImg + (size_t)buf * IMG_BYTES, in + (first + (long long)(k + 2) * stride) * 3072, 3072, &img_full[buf]);
           }
         }
-        const int slot = t & 1;  // u = 4k + (t >> 1) uses of this slot so far
-        if ((k > 0 || t >= 2) && !failed && !tc::mbar_wait(&e0[slot], (uint32_t)((t >> 1) & 1) ^ 1)) failed = true;
+        const int slot = s0;  // tile u = 8k + t uses slot u % L0_SLOTS for the (u / L0_SLOTS)-th time
+        const uint32_t spar = p0;
+        if (++s0 == L0_SLOTS) { s0 = 0; p0 ^= 1u; }
+        TR(0, k, t);
+        if (k * L0_TILES + t >= L0_SLOTS && !failed && !tc::mbar_wait(&e0[slot], spar ^ 1u)) failed = true;
         tc::fence_after_sync();
         const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
         const uint32_t a0 = p_lo[buf] + (uint32_t)(t * 128);  // descriptor start fields are in 16-byte units: one row = 1
         if (leader) {
-          tc::mma_i8_lh(acc, a0, d_hi, b0_lo, d_hi, idesc, FOLD ? 1u : 0u);            // ky 0, 1
-          tc::mma_i8_lh(acc, a0 + 64, d_hi, b0_lo + 2 * 64, d_hi, idesc, 1u);          // ky 2, zero chunk
+          if (kMma) tc::mma_i8_lh(acc, a0, d_hi, b0_lo, d_hi, idesc, FOLD ? 1u : 0u);            // ky 0, 1
+          if (kMma) tc::mma_i8_lh(acc, a0 + 64, d_hi, b0_lo + 2 * 64, d_hi, idesc, 1u);          // ky 2, zero chunk
           tc::commit(&f0[slot]);
+          TR(1, k, t);
           if (t == L0_TILES - 1) tc::commit(&p_empty[buf]);
         }
         __syncwarp();
       };
       auto issue_l1 = [&](int k, int t) {
         const int buf = k & 1;
+        TR(3, k, t);
         const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
         const uint32_t a_lo = a1_lo[buf] + (uint32_t)(t * 128);
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
@@ -328,8 +363,9 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         const uint32_t acc = tmem + (uint32_t)slot * 64;
         bool firstmma = true;
         if (leader && F4) {
-          tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, FOLD ? 1u : 0u);
+          if (kMma) tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, FOLD ? 1u : 0u);
           tc::commit(&full[slot]);
+          TR(4, k, t);
         } else if (leader) {
 #pragma unroll
         for (int tap = 0; tap < 9; tap++) {
@@ -377,8 +413,8 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
         }
       }
     }
-  } else {
-    // ================= half A (8 warps): layer-1 epilogue, 2x2 max-pool, store; team = 32-channel half ==========================
+  } else if (role == 0) {
+    // ================= half A (8 warps): layer-1 epilogue into bit rows; team = 32-channel half ===================================
     constexpr int WPP = 2 * S::OPL;
     using acc_t = typename std::conditional<F4, float, int>::type;  // kind::mxf4 accumulates in fp32 (exact: |acc| <= 1152)
     const acc_t* sthr1t = reinterpret_cast<const acc_t*>(sthr1);
@@ -399,23 +435,23 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
       half_sync(1);
       if (ht == 0) tc::mbar_arrive(&pre_done);
     }
-    if (K > 0) build_p(0, 0, P_SPLIT);
-    if (K > 1) build_p(1, 0, P_SPLIT);
     for (int k = 0; k < K; k++) {
-      const long long img = first + (long long)k * stride;
-      if (k + 2 < K) build_p(k + 2, 0, P_SPLIT);  // before this image's tiles arrive: half A would be waiting anyway
-      uint32_t* sbk = sbits + (size_t)(k & (S::NBITS - 1)) * (S::BITS / 4);  // two buffers: the pool of image k overlaps the tiles of image k+1
+      const int bb = k & (S::NBITS - 1);  // bit-row buffer: the helpers pool image k while this half is on image k+1
+      uint32_t* sbk = sbits + (size_t)bb * (S::BITS / 4);
+      if (k >= S::NBITS && !failed && !tc::mbar_wait(&bits_empty[bb], (uint32_t)(k / S::NBITS - 1) & 1)) failed = true;
       for (int t = 0; t < L1_TILES; t++) {
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
         if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
         uint32_t r[32];
-        tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, r);
-        tc::tmem_ld_wait_dep(r);
+        if (kEpi || !FOLD) {
+          tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, r);
+          tc::tmem_ld_wait_dep(r);
+        }
         uint32_t b0 = 0, b1 = 0;
-        if (FOLD) {
-#pragma unroll
+        if (FOLD && !kEpi) {
+        } else if (FOLD) {
           uint32_t q0 = 0, q1 = 0, q2 = 0, q3 = 0;  // four independent chains (a lone chain of 32 dependent shifts is pure latency)
 #pragma unroll
           for (int c = 7; c >= 0; c--) {
@@ -432,16 +468,32 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
             else { const int t1 = sthr1t[2 * (team * 32 + c) + 1] < sv; b0 |= (uint32_t)(1 ^ t0 ^ t1) << c; b1 |= (uint32_t)(t0 & t1) << c; }
           }
         }
-        sbk[(size_t)m * WPP + team] = b0;
+        if (kEpi || !FOLD) sbk[(size_t)m * WPP + team] = b0;
         if (OUTM == OUT_TERN) sbk[(size_t)m * WPP + 2 + team] = b1;
-        if (FOLD) preload1(slot);
+        if (FOLD && kEpi) preload1(slot);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
+        if (warp == 0) { TR(5, k, t); }
       }
-      half_sync(1);
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&bits_full[bb]);  // release: this warp's bit rows of image k are written
+    }
+  } else {
+    // ================= helpers (NH warps): window planes two images ahead; 2x2 max-pool of the bit rows and store =================
+    constexpr int WPP = 2 * S::OPL;
+    const int hx = tid - 19 * 32;
+    if (K > 0) build_p(0);
+    if (K > 1) build_p(1);
+    for (int k = 0; k < K; k++) {
+      const long long img = first + (long long)k * stride;
+      if (k + 2 < K) build_p(k + 2);
+      const int bb = k & (S::NBITS - 1);
+      const uint32_t* sbk = sbits + (size_t)bb * (S::BITS / 4);
+      if (!failed && !tc::mbar_wait(&bits_full[bb], (uint32_t)(k / S::NBITS) & 1)) failed = true;
       // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
-      for (int i = ht; i < 196 * 2; i += 256) {
+#pragma unroll 2
+      for (int i = hx; i < 196 * 2; i += NH * 32) {
         const int j = i & 1, op = i >> 1, oy = op / 14, ox = op % 14;
         const uint32_t* r00 = sbk + (size_t)((2 * oy) * 30 + 2 * ox) * WPP;
         const uint32_t *r01 = r00 + WPP, *r10 = r00 + 30 * WPP, *r11 = r10 + WPP;
@@ -457,13 +509,23 @@ __global__ void __launch_bounds__(608, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, c
           dst[2 + j] = P;
         }
       }
-      // two buffers: no second barrier (the next image writes the other buffer, and nobody passes the next image's barrier before all have pooled)
-      if (S::NBITS == 1) half_sync(1);
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&bits_empty[bb]);
+      if (warp == 19) { TR(6, k, 3); }
     }
   }
   if (failed && status) *status = 1;
   tc::fence_before_sync();
   __syncthreads();
+#ifdef BNNB_TRACE
+  if (blockIdx.x == 0 && tid == 0 && K >= 12) {
+    const long long t0 = tr[0][0][0];
+    for (int e = 0; e < 7; e++)
+      for (int k = 0; k < 4; k++)
+        printf("TRACE e%d k%d: %lld %lld %lld %lld %lld %lld %lld %lld\n", e, k + 8, tr[e][k][0] - t0, tr[e][k][1] - t0, tr[e][k][2] - t0, tr[e][k][3] - t0,
+               tr[e][k][4] - t0, tr[e][k][5] - t0, tr[e][k][6] - t0, (e < 3 || e == 6) ? tr[e][k][7] - t0 : 0);
+  }
+#endif
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
@@ -474,7 +536,7 @@ static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
   using S = Smem01<OUTM, F4>;
   static_assert(S::TOTAL <= 226 * 1024, "shared memory budget");
   cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-  k_cnv01_tc<OUTM, F4><<<grid, 608, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status);
+  k_cnv01_tc<OUTM, F4><<<grid, NT01, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status);
 }
 
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt,

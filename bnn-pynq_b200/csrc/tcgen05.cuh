@@ -65,7 +65,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n\t"
       ".reg .pred p;\n\t"
-#ifdef BNNB_WAIT_HINT
+#if defined(BNNB_TESTWAIT)
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+#elif defined(BNNB_WAIT_HINT)
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
 #else
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -80,9 +82,12 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // bounded spin: returns false after ~2^22 polls (legitimate waits are microseconds) so that a protocol bug cannot hang the GPU box
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
   // eight polls per trip: the trip counter costs two ALU-pipe instructions, and the epilogue warps share that pipe
-  for (uint32_t i = 0; i < (1u << 19); i++) {
+#ifndef BNNB_POLLU
+#define BNNB_POLLU 8
+#endif
+  for (uint32_t i = 0; i < (1u << 22) / BNNB_POLLU; i++) {
 #pragma unroll
-    for (int j = 0; j < 8; j++)
+    for (int j = 0; j < BNNB_POLLU; j++)
       if (mbar_try_wait(bar, parity)) return true;
   }
   return false;

@@ -1,0 +1,52 @@
+#!/usr/bin/env python
+"""Condense ncu exports into the tracked summaries under profiles/.
+  tools/ncu_summary.py launches <launches.csv> <out.csv>     per-kernel launch count, total device time, share of the run
+  tools/ncu_summary.py full <report.ncu-rep> <out.csv>       one row per profiled launch with the metrics DESIGN.md quotes
+"""
+import csv
+import subprocess
+import sys
+from collections import OrderedDict
+
+FULL = ["launch__grid_size", "launch__block_size", "launch__registers_per_thread", "gpu__time_duration.sum", "sm__cycles_elapsed.max",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__throughput.avg.pct_of_peak_sustained_elapsed", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active"]
+
+
+def launches(src, dst):
+    rows = [r for r in csv.reader(l for l in open(src) if not l.startswith("=="))]
+    h = rows[0]
+    ik, im, iv = h.index("Kernel Name"), h.index("Metric Name"), h.index("Metric Value")
+    agg = OrderedDict()
+    for r in rows[1:]:
+        if len(r) <= iv or r[im] != "gpu__time_duration.sum":
+            continue
+        a = agg.setdefault(r[ik][:70], [0, 0.0])
+        a[0] += 1
+        a[1] += float(r[iv].replace(",", ""))
+    tot = sum(a[1] for a in agg.values())
+    with open(dst, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["kernel", "launches", "total_ns", "share"])
+        for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            w.writerow([k, a[0], int(a[1]), "%.4f" % (a[1] / tot)])
+
+
+def full(rep, dst):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    h, u = rows[0], rows[1]
+    cols = [h.index("Kernel Name")] + [h.index(m) for m in FULL if m in h]
+    with open(dst, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow([h[c] for c in cols])
+        w.writerow([u[c] for c in cols])
+        for r in rows[2:]:
+            w.writerow([r[c][:90] if c == cols[0] else r[c] for c in cols])
+
+
+if __name__ == "__main__":
+    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
