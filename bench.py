@@ -53,7 +53,29 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag = index, [], False
 
+    def _nvml(self):
+        """Fast path: NVML in-process (a few samples per millisecond-scale step instead of one nvidia-smi fork per 100 ms)."""
+        import pynvml as N
+        N.nvmlInit()
+        h = N.nvmlDeviceGetHandleByIndex(self.index)
+        mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+        bits = [(N.nvmlClocksEventReasonHwSlowdown, 2), (N.nvmlClocksEventReasonHwThermalSlowdown, 3),
+                (N.nvmlClocksEventReasonSwThermalSlowdown, 4), (N.nvmlClocksEventReasonSwPowerCap, 5)]
+        while not self.stop_flag:
+            sm = N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)
+            r = N.nvmlDeviceGetCurrentClocksEventReasons(h)
+            row = [str(sm), str(mx), "", "", "", ""]
+            for bit, pos in bits:
+                row[pos] = "Active" if (r & bit) else "Not Active"
+            self.samples.append(row)
+            time.sleep(0.002)
+
     def run(self):
+        try:
+            self._nvml()
+            return
+        except Exception:
+            pass
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
@@ -123,9 +145,11 @@ def run_reference_cpu(net, per_proc, steps, warmup, procs=None):
     return ips, 1000.0 * total / steps, procs, sample
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, one launch (16 384 images), from the committed
-# `ncu --set full` capture (profiles/r1_ncu_full_summary.csv); None where no capture exists
-TRAFFIC = {"cnv": 50412288 + 2199296, "lfc": None}
+# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel PER IMAGE, from the committed `ncu --set full` captures
+# (profiles/r1_ncu_full_summary.csv: 202.2 MB read + 357.0 MB written by one 65 536-image launch of k_cnv01_tc; the kernel's
+# algorithmic bytes are 3 072 in + 6 272 out per image, its output being the next kernel's e2m1 operand planes); None where no
+# capture exists.  roofline.traffic = this x the images one launch processes.
+TRAFFIC_PER_IMAGE = {"cnv": (202165760 + 356975616) / 65536.0, "lfc": None}
 
 
 def main():
@@ -319,7 +343,7 @@ def main():
     # kind::mxf4 issues at 4x the bf16 rate (nominal 9 vs 2.25 PFLOP/s dense): the tensor peak this path is held against is
     # 4 x the MEASURED dense bf16 number; the fraction of the plain bf16 number is kept beside it
     f4_peak = 4.0 * tf_peak
-    roofline = {"bound": "tensor", "achieved": achieved, "peak": f4_peak, "unit": "TFLOP/s", "frac": achieved / f4_peak, "traffic": TRAFFIC.get(fam),
+    roofline = {"bound": "tensor", "achieved": achieved, "peak": f4_peak, "unit": "TFLOP/s", "frac": achieved / f4_peak, "traffic": (int(TRAFFIC_PER_IMAGE[fam] * units_per_launch) if TRAFFIC_PER_IMAGE.get(fam) else None),
                 "kernel": "layer %d%s" % (k, " (fused with layer %d)" % (k - 1) if (k - 1) in fused else ""), "avg_launch_ms": avg_ms, "images_per_launch": units_per_launch,
                 "ops_per_image_this_kernel": lops[k],
                 "peak_source": "4 x " + how + " dense bf16 (%.1f TFLOP/s): tcgen05 kind::mxf4 nominal rate; ops = 2 x MAC as config.h counts them" % tf_peak,

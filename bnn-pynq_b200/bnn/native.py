@@ -320,6 +320,23 @@ def free_pinned(p):
     lib().bnnb_free_host(p)
 
 
+def tmem_pack_probe(cols):
+    """tcgen05.ld .32x32b.x16.pack::16b probe: `cols` is uint32 [32 lanes][32 columns] written to TMEM; returns the 16 packed
+    registers per lane, uint32 [32][16]."""
+    cols = np.ascontiguousarray(cols, np.uint32)
+    assert cols.shape == (32, 32)
+    out = np.zeros((32, 16), np.uint32)
+    if lib().bnnb_tmem_pack_probe(_p(cols), _p(out)) != 0:
+        raise RuntimeError("tmem_pack_probe failed")
+    return out
+
+
+def alu_rate(which):
+    """Thread-instructions per second of one ALU / FMA-pipe instruction (bnnb_microbench): 0 popc, 2 lop3, 3 shf.l.wrap, 4 prmt,
+    5 mad.hi, 6 mad.lo, 8 min.f32."""
+    return microbench(which)[0]
+
+
 def tmem_rate(warps, store=False):
     """TMEM read (tcgen05.ld) or write (tcgen05.st) throughput in bytes per clock per SM with `warps` warps issuing."""
     L = lib()

@@ -123,7 +123,8 @@ int bnnb_profile_collect(bnnb_ctx* c, float* ms, int* launches);
 
 /* Integer-pipe / tensor-pipe micro-benchmarks on device slot 0 (the roofline denominators of DESIGN.md):
  * which: 0 = POPC (returns 32-bit popcounts per second), 1 = mma.sync.m16n8k32.s8 (returns int8 MACs per second),
- * 2 = LOP3 (returns 32-bit logic ops per second).  clock_mhz (optional): SM clock implied by clock64() over the run. */
+ * 2 = LOP3 (returns 32-bit logic ops per second); 3 shf.l.wrap, 4 prmt, 5 mad.hi, 6 mad.lo, 7 shr, 8 min.f32 (thread-instructions
+ * per second: what one epilogue instruction per accumulator column costs).  clock_mhz (optional): SM clock implied by clock64(). */
 double bnnb_microbench(int which, double* clock_mhz);
 
 /* Pinned host memory for full-rate asynchronous copies. */

@@ -109,6 +109,32 @@ def test_mma_kind_switch_cost_report():
     print("kind switch:", out)
 
 
+def test_tmem_pack16_semantics():
+    """The fused kernel's layer-0 epilogue reads its int32 accumulators with tcgen05.ld .pack::16b and takes decisions from bits 15
+    and 31 of each register: register j must hold the LOW 16 bits of column 2j (low half) and of column 2j+1 (high half)."""
+    from bnn import native
+    rng = np.random.default_rng(5)
+    cols = rng.integers(0, 2**32, (32, 32), dtype=np.uint64).astype(np.uint32)
+    cols[0, :8] = np.array([0, 1, 0xFFFF, 0x8000, 0x7FFF, 0xFFFF8000, 0x00017FFF, 0xFFFFFFFF], np.uint32)
+    got = native.tmem_pack_probe(cols)
+    lo = cols & 0xFFFF
+    assert np.array_equal(got, (lo[:, 0::2] | (lo[:, 1::2] << 16)).astype(np.uint32))
+    # a folded layer-0 accumulator (|thr - S| <= 6 913) keeps its sign in bit 15 of the low half
+    acc = rng.integers(-6913, 6914, (32, 32)).astype(np.int32)
+    got = native.tmem_pack_probe(acc.view(np.uint32))
+    assert np.array_equal((got >> 15) & 1, (acc[:, 0::2] < 0).astype(np.uint32))
+    assert np.array_equal(got >> 31, (acc[:, 1::2] < 0).astype(np.uint32))
+
+
+def test_alu_pipe_rate_report():
+    """Timing report: the epilogues are one ALU instruction per accumulator column; SHF / PRMT / LOP3 share one pipe (64 lanes per
+    clock per SM), integer multiply-add runs beside it on the FMA pipe."""
+    from bnn import native
+    per_clk = {n: round(native.alu_rate(w) / (148 * 1.965e9), 1) for w, n in ((2, "lop3"), (3, "shf.l.wrap"), (4, "prmt"), (5, "mad.hi"), (6, "mad.lo"))}
+    print("thread-instructions / clk / SM:", per_clk)
+    assert per_clk["shf.l.wrap"] > 32
+
+
 def test_tmem_rate_report():
     """Timing report: TMEM -> register (tcgen05.ld) and register -> TMEM (tcgen05.st) bytes per clock per SM by number of warps."""
     from bnn import native

@@ -27,12 +27,14 @@ def launches(src, dst):
         a = agg.setdefault(r[ik][:70], [0, 0.0])
         a[0] += 1
         a[1] += float(r[iv].replace(",", ""))
-    tot = sum(a[1] for a in agg.values())
+    # the path's own kernels (bench.py also runs pipe micro-benchmarks, an L2 flush and the load-time re-pack kernels)
+    path = lambda k: any(x in k for x in ("k_cnv01", "k_conv", "k_gemm", "k_layer_popc", "k_prep_", "k_cnv_classes"))
+    tot = sum(a[1] for k, a in agg.items() if path(k))
     with open(dst, "w", newline="") as f:
         w = csv.writer(f)
-        w.writerow(["kernel", "launches", "total_ns", "share"])
+        w.writerow(["kernel", "launches", "total_ns", "share_of_path_kernels"])
         for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-            w.writerow([k, a[0], int(a[1]), "%.4f" % (a[1] / tot)])
+            w.writerow([k, a[0], int(a[1]), "%.4f" % (a[1] / tot) if path(k) else "-"])
 
 
 def full(rep, dst):
