@@ -226,6 +226,8 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    all_cpus = os.sched_getaffinity(0)
+    numa_cpus = native.bind_host_to_device(local_rank) if not os.environ.get("BENCH_NO_BIND") else None  # before any pinned allocation
     rt = native.Runtime(a.net, params_dir(a.net), devices=[local_rank])
     if a.core != 2:
         rt.set_core(a.core)
@@ -362,9 +364,11 @@ def main():
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "int1 x int1 as e2m1 on tcgen05 kind::mxf4 with unit scales (exact; fp32 accumulate), layer 0 int8 (int32 accumulate)" if a.net.endswith("W1A1") else "int2 (ternary activations, 1/2-bit weights) as e2m1 on tcgen05 kind::mxf4 with unit scales (exact; fp32 accumulate)", "data": "synthetic", "config": config,
            "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": B * raw_w, "d2h_bytes_per_step": B * (4 if fam == "cnv" else 8),
-                   "h2d_copy_gbs_measured": h2d_gbs, "h2d_bound_images_per_s": world * h2d_gbs * 1e9 / raw_w},
+                   "h2d_copy_gbs_measured": h2d_gbs, "h2d_bound_images_per_s": world * h2d_gbs * 1e9 / raw_w,
+                   "host_cpus_bound_to_gpu_node": (len(numa_cpus) if numa_cpus else None)},
            "gpu_launches": int(launches_per_step) * a.steps, "roofline": roofline, "clocks": sampler.summary()}
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core
         try:
             ips, _, cores, sample = run_reference_cpu(a.net, 4, 1, 1)
             out["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": cores, "kind": "reference", "sample": sample}

@@ -320,6 +320,25 @@ def free_pinned(p):
     lib().bnnb_free_host(p)
 
 
+def bind_host_to_device(index):
+    """Pin the calling process to the CPUs (hence, by first touch, the memory node) NVML reports as local to GPU `index`.
+    Call it before allocating pinned buffers: with one process per GPU the host-buffer path is PCIe- and host-memory-bound, and
+    a buffer on the other socket halves its copy rate.  Returns the CPU set, or None when NVML / the affinity call is unavailable."""
+    try:
+        import pynvml as N
+        N.nvmlInit()
+        h = N.nvmlDeviceGetHandleByIndex(int(index))
+        words = N.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, v in enumerate(words) for b in range(64) if (int(v) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
+
+
 def tmem_pack_probe(cols):
     """tcgen05.ld .32x32b.x16.pack::16b probe: `cols` is uint32 [32 lanes][32 columns] written to TMEM; returns the 16 packed
     registers per lane, uint32 [32][16]."""
