@@ -18,7 +18,15 @@
 namespace bnnb {
 namespace {
 
-constexpr int GF_RING = 8;
+#ifndef BNNB_GG
+#define BNNB_GG 8
+#endif
+// Weight slabs per ring slot: one bulk copy, one full / empty hand-off and one tcgen05.commit per GROUP of slabs.  A wait + commit
+// pair costs the issuer thread ~300 clocks while an MMA of these shapes runs 48-64: with one slab per slot the kernel with its MMAs
+// and epilogue bodies compiled out took as long as the full one (lfcW1A1, 1024 x 1024 layer: 0.117 vs 0.128 ms; groups of 2 / 4 /
+// 8 slabs: 0.086 / 0.071 / 0.058 ms).  The ring takes whatever shared memory is left (bytes in flight set the rate of the stream).
+constexpr int GG = BNNB_GG;
+constexpr int GF_RING_MAX = 32;
 
 // 8 bits -> 8 nibbles (bit i at position 4i)
 __device__ __forceinline__ uint32_t gspread8(uint32_t x) {
@@ -44,7 +52,7 @@ __device__ __forceinline__ uint4 gexpand(uint32_t w0, uint32_t w1) {
 struct GemmGeom {
   int K, N, kch, ks, nblk, nbuf;  // kch = K/32 chunks, ks = K/64 slabs per channel block, nbuf = operand buffers (1 or 2)
   int cw, ipl;                    // words per pixel and plane (C/32), input planes
-  int a_bytes, off_ring, off_thr;
+  int a_bytes, off_ring, off_thr, ring;  // ring = slots of the weight ring (GG slabs each)
 };
 
 template <int NB, int INM, int OUTM>
@@ -54,7 +62,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
   constexpr bool FOLD = OUTM == OUT_BIT;
   constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t full[SLOTS], empty[SLOTS], a_part[2][4], a_empty[2], ring_full[GF_RING], ring_empty[GF_RING];
+  __shared__ __align__(8) uint64_t full[SLOTS], empty[SLOTS], a_part[2][4], a_empty[2], ring_full[GF_RING_MAX], ring_empty[GF_RING_MAX];
   __shared__ uint32_t tmem_base;
   uint8_t* ring = smem + g.off_ring;
   float* sthr = reinterpret_cast<float*>(smem + g.off_thr);  // [2][N]
@@ -75,7 +83,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
       for (int q = 0; q < 4; q++) tc::mbar_init(&a_part[i][q], in_fmt == ACT_F4T ? 1 : EXP);
     }
     for (int i = 0; i < SLOTS; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4); }
-    for (int i = 0; i < GF_RING; i++) { tc::mbar_init(&ring_full[i], 1); tc::mbar_init(&ring_empty[i], 1); }
+    for (int i = 0; i < g.ring; i++) { tc::mbar_init(&ring_full[i], 1); tc::mbar_init(&ring_empty[i], 1); }
     tc::mbar_init_fence();
   }
   tc::fence_before_sync();
@@ -175,16 +183,21 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
     }
   } else if (role == 2) {
     // ---- loader: weight slabs in MMA order, R slots ahead ----------------------------------------------------------------------
-    if (lane == 0) {
-      const long long total = (long long)T * g.nblk * g.ks;
-      const int per_tile = g.nblk * g.ks;
-      for (long long gs = 0; gs < total; gs++) {
-        const int r = (int)(gs % GF_RING);
-        const long long use = gs / GF_RING;
-        if (use >= 1 && !failed && !tc::mbar_wait(&ring_empty[r], (uint32_t)(use - 1) & 1)) failed = true;
-        const int q = (int)(gs % per_tile);  // = nb * ks + slab: exactly the block order of the re-packed weights
-        tc::mbar_expect_tx(&ring_full[r], SLAB);
-        tc::bulk_g2s(ring + (size_t)r * SLAB, L.w4s + (size_t)q * SLAB, SLAB, &ring_full[r]);
+    // One lane per ring slot (lane l owns slot l: groups l, l + ring, l + 2 ring, ...), so the copies of a whole ring are issued
+    // by one pass of the warp instead of one thread's ~40 instructions per copy
+    if (lane < g.ring) {
+      const int ngrp = (g.ks + GG - 1) / GG;      // groups per channel block (the last one may be short)
+      const int per_tile = g.nblk * ngrp;
+      const int total = T * per_tile;
+      uint32_t rpar = 1;                           // parity to wait for on ring_empty = parity of the slot's previous use
+      uint8_t* dst = ring + (size_t)lane * (GG * SLAB);
+      for (int gg = lane; gg < total; gg += g.ring) {
+        const int qg = gg % per_tile, nb = qg / ngrp, gi = qg - nb * ngrp;
+        const int s0 = gi * GG, cnt = min(GG, g.ks - s0);
+        if (gg >= g.ring && !failed && !tc::mbar_wait(&ring_empty[lane], rpar)) failed = true;
+        tc::mbar_expect_tx(&ring_full[lane], (uint32_t)cnt * SLAB);
+        tc::bulk_g2s(dst, L.w4s + (size_t)(nb * g.ks + s0) * SLAB, (uint32_t)cnt * SLAB, &ring_full[lane]);  // the slabs of a block are consecutive
+        rpar ^= 1u;
       }
     }
   } else if (role == 3) {
@@ -193,7 +206,8 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
       const bool leader = tc::elect_one();
       const uint32_t d_hi = tc::desc_hi(128);
       const uint32_t b_lo = tc::desc_lo(ring_u, NB * 16);
-      long long gs = 0;
+      int r = 0;
+      uint32_t rpar = 0;  // ring slot and the parity of its current use: counted, not divided
       for (int tl = 0; tl < T; tl++) {
         const int buf = tl % g.nbuf, use = tl / g.nbuf;
         const uint32_t a_lo = tc::desc_lo(sa_u0 + (uint32_t)buf * g.a_bytes, 2048);
@@ -203,19 +217,21 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * NB;
           int qn = 0;
-          for (int s = 0; s < g.ks; s++, gs++) {
-            const int r = (int)(gs % GF_RING);
-            // slab s lies in quarter q with ((q+1)*ks)/4 > s: wait for the quarters up to it (first channel block of a tile only)
-            while (nb == 0 && qn < 4 && (s >= (qn * g.ks) / 4)) {
-              if (!failed && !tc::mbar_wait(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
-              tc::fence_after_sync();
-              qn++;
+          for (int s0 = 0; s0 < g.ks; s0 += GG) {  // one ring slot = GG slabs (fewer at the end of the block)
+            if (!failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
+            const int s1 = min(s0 + GG, g.ks);
+            for (int s = s0; s < s1; s++) {
+              // slab s lies in quarter q with ((q+1)*ks)/4 > s: wait for the quarters up to it (first channel block of a tile only)
+              while (nb == 0 && qn < 4 && (s >= (qn * g.ks) / 4)) {
+                if (!failed && !tc::mbar_wait(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
+                tc::fence_after_sync();
+                qn++;
+              }
+              if (leader)
+                tc::mma_mxf4_lh(acc, a_lo + (uint32_t)(2 * s) * 128, d_hi, b_lo + (uint32_t)(r * GG + (s - s0)) * (SLAB / 16), d_hi, idesc, sf, sf, (FOLD || s > 0) ? 1u : 0u);
             }
-            if (!failed && !tc::mbar_wait(&ring_full[r], (uint32_t)(gs / GF_RING) & 1)) failed = true;
-            if (leader) {
-              tc::mma_mxf4_lh(acc, a_lo + (uint32_t)(2 * s) * 128, d_hi, b_lo + (uint32_t)r * (SLAB / 16), d_hi, idesc, sf, sf, (FOLD || s > 0) ? 1u : 0u);
-              tc::commit(&ring_empty[r]);
-            }
+            if (leader) tc::commit(&ring_empty[r]);
+            if (++r == g.ring) { r = 0; rpar ^= 1u; }
             __syncwarp();
           }
           if (leader) tc::commit(&full[slot]);
@@ -313,9 +329,12 @@ bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, i
   g.K = d.K; g.N = d.N; g.kch = d.K / 32; g.ks = d.K / 64; g.nblk = d.N / NB;
   g.cw = d.ifm_ch / 32; g.ipl = INM == IN_TERN ? 2 : 1;
   g.a_bytes = g.kch * 2048;
-  const int ring = GF_RING * NB * 32, thr = 2 * d.N * 4, budget = 224 * 1024;
-  g.nbuf = 2 * g.a_bytes + ring + thr <= budget ? 2 : 1;
-  if (g.nbuf * g.a_bytes + ring + thr > budget) return false;
+  const int thr = 2 * d.N * 4, budget = 224 * 1024, slot_bytes = GG * NB * 32, ring_min = 2 * slot_bytes;
+  g.nbuf = 2 * g.a_bytes + 2 * ring_min + thr <= budget ? 2 : 1;  // two operand buffers only if four ring slots remain
+  if (g.nbuf * g.a_bytes + ring_min + thr > budget) return false;
+  g.ring = (budget - g.nbuf * g.a_bytes - thr) / slot_bytes;
+  if (g.ring > GF_RING_MAX) g.ring = GF_RING_MAX;
+  const int ring = g.ring * slot_bytes;
   g.off_ring = g.nbuf * g.a_bytes;
   g.off_thr = g.off_ring + ring;
   const int smem = g.off_thr + thr;
