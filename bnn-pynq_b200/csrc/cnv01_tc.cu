@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
   }
   for (int i = tid; i < 128; i += NT01) {
     const int t = L0.thr[i];
-    sthr0[i] = t == INT_MAX ? INT_MAX : (t >> 1);  // thr < 2S  <=>  floor(thr/2) < S
+    sthr0[i] = t == INT_MAX ? (1 << 26) : min(t >> 1, 1 << 26);  // thr < 2S  <=>  floor(thr/2) < S; |S| <= 3456, and thr - S must not overflow
     const int t1 = L1.thr_tc[i];
     if (F4) reinterpret_cast<float*>(sthr1)[i] = t1 == INT_MAX ? 3.0e38f : (float)t1;
     else sthr1[i] = t1;
@@ -254,6 +254,24 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         tc::tmem_ld_wait_dep(r);
         }
         if (FOLD) {
+        } else if (F4 && OUTM == OUT_TERN) {
+          // ternary: decision t = (thr < S) is the sign of thr - S.  The top nibbles of thr0 - S and thr1 - S are shifted in (bit 3 of
+          // a nibble = t0 / t1): one subtraction and one funnel shift per channel and threshold, then per eight channels
+          // both -> 0x2 (+1), neither -> 0xA (-1), one -> 0x0.  (Was two compares + table look-up + insert: the epilogue is ALU-bound.)
+          uint32_t v[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            uint32_t n0 = 0, n1 = 0;
+#pragma unroll
+            for (int e = 7; e >= 0; e--) {
+              const int c = q * 8 + e, sv = (int)r[c];
+              n0 = __funnelshift_l((uint32_t)(thrA[c] - sv), n0, 4);
+              n1 = __funnelshift_l((uint32_t)(sthr0[2 * (team * 32 + c) + 1] - sv), n1, 4);
+            }
+            const uint32_t both = n0 & n1 & 0x88888888u, none = ~(n0 | n1) & 0x88888888u;
+            v[q] = (both >> 2) | none | (none >> 2);
+          }
+          if (valid) *reinterpret_cast<uint4*>(sA + (size_t)team * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
         } else if (F4) {  // 32 channels = 32 e2m1 nibbles = one uint4 store into plane `team`: 1 -> 0x2, 0 -> 0x0, -1 -> 0xA
           uint32_t v[4];
 #pragma unroll
@@ -459,6 +477,22 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
             q2 = __funnelshift_l(r[16 + c], q2, 1); q3 = __funnelshift_l(r[24 + c], q3, 1);
           }
           b0 = __byte_perm(q0, q1, 0x1140) | __byte_perm(q2, q3, 0x4011);
+        } else if (F4 && OUTM == OUT_TERN) {  // sign bits of thr - acc (f4_common.cuh: tern_planes), first thresholds from registers
+          uint32_t u0[4] = {0, 0, 0, 0}, u1[4] = {0, 0, 0, 0};
+          const float* th1 = reinterpret_cast<const float*>(sthr1) + 2 * (team * 32) + 1;
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+#pragma unroll
+            for (int e = 7; e >= 0; e--) {
+              const float sv = __uint_as_float(r[8 * q + e]);
+              u0[q] = __funnelshift_l(__float_as_uint((float)thrA[8 * q + e] - sv), u0[q], 1);
+              u1[q] = __funnelshift_l(__float_as_uint(th1[2 * (8 * q + e)] - sv), u1[q], 1);
+            }
+          }
+          const uint32_t t0 = __byte_perm(u0[0], u0[1], 0x1140) | __byte_perm(u0[2], u0[3], 0x4011);
+          const uint32_t t1 = __byte_perm(u1[0], u1[1], 0x1140) | __byte_perm(u1[2], u1[3], 0x4011);
+          b0 = ~(t0 ^ t1);
+          b1 = t0 & t1;
         } else {
 #pragma unroll
           for (int c = 0; c < 32; c++) {

@@ -233,14 +233,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
             w0 = ~w0;
           } else {
             const float* th = sthr + h * N + eg * NG + j * 32;
-#pragma unroll
-            for (int c = 0; c < 32; c++) {
-              const float s = __uint_as_float(r[j & 1][c]);
-              const int t0 = th[c] < s;
-              const int t1 = th[NT + c] < s;
-              w0 |= (uint32_t)(1 ^ t0 ^ t1) << c;
-              w1 |= (uint32_t)(t0 & t1) << c;
-            }
+            tern_planes(r[j & 1], th, th + NT, w0, w1);
           }
           b0[j] = w0;
           b1[j] = w1;

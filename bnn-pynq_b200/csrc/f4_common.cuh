@@ -39,4 +39,25 @@ __device__ __forceinline__ uint4 f4_from_signs(const uint32_t (&r)[32]) {
   return make_uint4(v[0], v[1], v[2], v[3]);
 }
 
+// Ternary decisions of 32 fp32 accumulators against two thresholds each: plane nz = NOT(t0 XOR t1), plane pos = t0 AND t1 with
+// t = (thr < acc).  thr - acc is negative exactly when thr < acc (x - x = +0), so each decision is a sign bit: two FADDs (FMA pipe)
+// and two funnel shifts (ALU pipe) per channel instead of two compares plus predicate-to-bit logic on the ALU pipe alone - the
+// ternary epilogues are ALU-bound.  th0 / th1: 32 consecutive floats each (shared memory).
+__device__ __forceinline__ void tern_planes(const uint32_t (&r)[32], const float* th0, const float* th1, uint32_t& nz, uint32_t& pos) {
+  uint32_t u0[4] = {0, 0, 0, 0}, u1[4] = {0, 0, 0, 0};  // four independent chains each (a lone chain is pure latency)
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+#pragma unroll
+    for (int e = 7; e >= 0; e--) {
+      const float s = __uint_as_float(r[8 * q + e]);
+      u0[q] = __funnelshift_l(__float_as_uint(th0[8 * q + e] - s), u0[q], 1);
+      u1[q] = __funnelshift_l(__float_as_uint(th1[8 * q + e] - s), u1[q], 1);
+    }
+  }
+  const uint32_t t0 = __byte_perm(u0[0], u0[1], 0x1140) | __byte_perm(u0[2], u0[3], 0x4011);
+  const uint32_t t1 = __byte_perm(u1[0], u1[1], 0x1140) | __byte_perm(u1[2], u1[3], 0x4011);
+  nz = ~(t0 ^ t1);
+  pos = t0 & t1;
+}
+
 }  // namespace bnnb

@@ -285,14 +285,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
             for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
             w0 = ~w0;
           } else {
-#pragma unroll
-            for (int c = 0; c < 32; c++) {
-              const float s = __uint_as_float(r[j & 1][c]);
-              const int t0 = th[c] < s;
-              const int t1 = th[g.N + c] < s;
-              w0 |= (uint32_t)(1 ^ t0 ^ t1) << c;
-              w1 |= (uint32_t)(t0 & t1) << c;
-            }
+            tern_planes(r[j & 1], th, th + g.N, w0, w1);
           }
           b0[j] = w0;
           b1[j] = w1;
