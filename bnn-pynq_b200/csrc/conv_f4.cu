@@ -103,8 +103,25 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   const uint32_t tmem = tmem_base;
   if (warp < 4) tc::tmem_fill16(tmem + ((uint32_t)(warp * 32) << 16) + Cfg::SF_COL, 0x7f7f7f7fu);  // every scale factor = 1.0 (ue8m0)
   const uint32_t sthr_u = tc::smem_u32(sthr);
+  // One 32-channel word per warp and one channel block: the warp's 32 pre-load values never change, so they live in registers.  (A
+  // shared-memory read waits behind the MMAs' operand stream: re-reading them per tile cost the fused kernel +50 %.)
+#ifdef BNNB_CONV_PRE_SMEM
+  constexpr bool PRE_REG = false;
+#else
+  constexpr bool PRE_REG = FOLD && NWG == 1 && NS == 1;
+#endif
+  uint32_t pre[32];
+  if (PRE_REG) {
+#pragma unroll
+    for (int c = 0; c < 32; c++) pre[c] = __float_as_uint(sthr[(warp < 16 ? eg : 0) * NG + c]);
+  }
   auto preload = [&](int slot, int h) {  // this warp's lane quarter and channel half of accumulator `slot` <- -(thr + 1/2) of block h
     const uint32_t t0 = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N;
+    if (PRE_REG) {
+      tc::tmem_st32(t0 + eg * 32, pre);
+      tc::tmem_st_wait();
+      return;
+    }
 #pragma unroll
     for (int jj = 0; jj < NWG; jj++) {
       const int j = eg * NWG + jj;
