@@ -127,3 +127,15 @@ def test_compute_fails_loudly_without_a_gpu():
     rt = native.Runtime("lfcW1A1")
     with pytest.raises(RuntimeError):
         rt.classify_mnist(np.zeros((1, 784), np.uint8))
+
+
+def test_bind_host_to_device_never_raises():
+    """native.bind_host_to_device pins a rank to its GPU's CPUs when NVML knows them and is a no-op (None) otherwise; run in a
+    child process so that this process keeps its affinity."""
+    import subprocess
+    code = ("import sys, os; sys.path.insert(0, %r); from bnn import native; before = os.sched_getaffinity(0); "
+            "r = native.bind_host_to_device(0); after = os.sched_getaffinity(0); "
+            "assert r is None or (len(r) > 0 and set(r) == set(after) and set(after) <= set(before)); "
+            "assert r is not None or after == before; print('ok')") % os.path.join(ROOT, "bnn-pynq_b200")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr
