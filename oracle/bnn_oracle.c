@@ -5,11 +5,14 @@
  * algorithm, in "logical" (unfolded) int8 arithmetic so that it shares no formula with
  * the CUDA kernels (which use bit-plane popcounts / int8 MMA on re-packed parameters).
  *
- * Parity status: PINNED.  tests/test_oracle_vs_reference.py checks this file against
+ * Parity status: PINNED.  tests/test_oracle_golden.py checks this file against
  * (a) the reference's own known-answer tests (deer.bin -> 4, 3.image-idx3-ubyte -> 3;
- * make-hw.sh:123-129, tests/test_qnn.py) and (b) outputs of the UNMODIFIED reference sources
+ * make-hw.sh:123-129, tests/test_qnn.py), (b) outputs of the UNMODIFIED reference sources
  * compiled here by oracle/build_ref.sh (oracle/_ref/python_sw-<net>.so), recorded as fixtures
- * under tests/golden/ by tests/golden/make_golden.py.
+ * under tests/golden/ref_<net>.npz by tests/golden/make_golden.py, and (c) EVERY LAYER's
+ * accumulators and outputs as the reference's own templates produce them when DoCompute's call
+ * list is replayed layer by layer (oracle/tap.cpp -> oracle/_ref/tap-<net>.so, fixtures
+ * tests/golden/taps_<net>.npz by tests/golden/make_golden_taps.py).
  *
  * Every function cites the reference file:line it follows (paths relative to
  * /root/reference/bnn/src/).

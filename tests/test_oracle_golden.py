@@ -101,3 +101,48 @@ def test_short_weight_files_load_zeros():
     assert o.mem_read(16, 0, li["wmem"] - 1, 0) == 0
     o = Oracle("lfcW1A1", params_dir("lfcW1A1", "chars_merged"))
     assert o.mem_read(6, 0, o.layer_info(3)["wmem"] - 1, 0) == 0
+
+
+def tap_inputs(net):
+    """The inputs of tests/golden/make_golden_taps.py (kept in step with it by test_oracle_taps_vs_reference_templates)."""
+    n = 8
+    if net.startswith("cnv"):
+        rec = synth_cifar(n, 77)
+        rec[6, 1:] = ((np.arange(3072, dtype=np.int64) * 7) % 256).astype(np.uint8)
+        rec[7] = deer()[:3073]
+        return rec
+    px = synth_mnist(n, 77)
+    px[6] = ((np.arange(784) * 5) % 256).astype(np.uint8)
+    px[7] = img3()[:784]
+    return px
+
+
+def tap_gold(net):
+    g = np.load(os.path.join(GOLDEN, "taps_%s.npz" % net))
+    return g["acc"].astype(np.int32), g["act"]
+
+
+def wrap_last_cnv_layer(o, acc):
+    """CNV layer 8 has no threshold: the reference's accumulator there is the ap_uint<16> score itself (PassThroughActivation<
+    ap_uint<16>>, cnvW1A1/hw/top.cpp:232-233), so that layer is compared modulo 2^16."""
+    if o.is_cnv:
+        acc = acc.copy()
+        acc[:, -64:] = acc[:, -64:].astype(np.int16)
+    return acc
+
+
+@pytest.mark.parametrize("net", NETS)
+def test_oracle_taps_vs_reference_templates(net):
+    """Every layer's accumulators and outputs of the restatement == the reference's own templates replayed layer by layer
+    (oracle/tap.cpp: DoCompute's call list with PassThroughActivation for the accumulators), 8 images per network."""
+    o = Oracle(net)
+    gacc, gact = tap_gold(net)
+    data = tap_inputs(net)
+    _, acc, act = o.cnv_scores(data, taps=True) if o.is_cnv else o.lfc_words(data, taps=True)
+    acc = wrap_last_cnv_layer(o, acc)
+    assert acc.shape == gacc.shape and act.shape == gact.shape
+    for i in range(data.shape[0]):
+        for l, (a, b) in enumerate(zip(o.split_taps(acc[i], "acc"), o.split_taps(gacc[i], "acc"))):
+            assert np.array_equal(a, b), "accumulators differ from the reference templates: image %d layer %d" % (i, l)
+        for l, (a, b) in enumerate(zip(o.split_taps(act[i], "act"), o.split_taps(gact[i], "act"))):
+            assert np.array_equal(a, b), "layer outputs differ from the reference templates: image %d layer %d" % (i, l)
