@@ -145,11 +145,48 @@ def run_reference_cpu(net, per_proc, steps, warmup, procs=None):
     return ips, 1000.0 * total / steps, procs, sample
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel PER IMAGE, from the committed `ncu --set full` captures
-# (profiles/r1_ncu_full_summary.csv: 202.2 MB read + 357.0 MB written by one 65 536-image launch of k_cnv01_tc; the kernel's
-# algorithmic bytes are 3 072 in + 6 272 out per image, its output being the next kernel's e2m1 operand planes); None where no
-# capture exists.  roofline.traffic = this x the images one launch processes.
-TRAFFIC_PER_IMAGE = {"cnv": (202165760 + 356975616) / 65536.0, "lfc": None}
+def traffic_per_image(net):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the network's dominant kernel PER IMAGE, from profiles/traffic.json, which
+    tools/ncu_summary.py writes from an `ncu --set full` capture (one entry per network: bytes of ONE launch and the images that launch
+    processed).  None where no capture exists.  roofline.traffic = this x the images one launch processes."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            e = json.load(f)[net]
+        return (e["dram_bytes_read"] + e["dram_bytes_write"]) / float(e["images_per_launch"]), e.get("source")
+    except Exception:
+        return None, None
+
+
+def fast_cpu_port(net, seconds=10.0):
+    """Second CPU figure: the multi-threaded C restatement oracle/libbnn_oracle.so - NOT reference code - on all host
+    cores, on a bounded sample of the workload.  Part of the cpu_baseline leg (the only place bench.py may execute oracle/)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle_py import Oracle
+    import numpy as np
+    o = Oracle(net, params_dir(net))
+    cnv = net.startswith("cnv")
+    n = 256 if cnv else 8192
+    rng = np.random.default_rng(7)
+    if cnv:
+        data = np.zeros((n, 3073), np.uint8)
+        data[:, 1:] = rng.integers(0, 256, (n, 3072), dtype=np.uint8)
+        run = o.cnv_scores
+    else:
+        data = rng.integers(0, 256, (n, 784), dtype=np.uint8)
+        run = o.lfc_words
+    run(data[:16])
+    t0 = time.perf_counter()
+    run(data)
+    dt = time.perf_counter() - t0
+    reps = max(1, min(64, int(seconds / max(dt, 1e-6))))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        run(data)
+    dt = time.perf_counter() - t0
+    cores = len(os.sched_getaffinity(0))
+    return {"value": reps * n / dt, "unit": "images/s", "cores": cores, "kind": "port",
+            "sample": "%d images x %d passes, OpenMP over %d cores" % (n, reps, cores),
+            "note": "oracle/bnn_oracle.c, the int8 restatement used as the parity checker: not reference code"}
 
 
 def main():
@@ -162,9 +199,17 @@ def main():
     ap.add_argument("--batch", type=int, default=65536, help="images per GPU per step")
     ap.add_argument("--ref-images", type=int, default=8, help="reference arm: images per process per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--faults", type=int, default=1024, help="config 5 side measurement: faults scheduled over 1 048 576 images (0 = skip)")
+    ap.add_argument("--fault-images", type=int, default=1 << 20, help="config 5 side measurement: images in the whole job (sharded over the ranks)")
+    ap.add_argument("--sustained-s", type=float, default=2.5, help="sustained arm: seconds of back-to-back steps (0 = skip)")
+    ap.add_argument("--latency-calls", type=int, default=1000, help="batch-1 latency: calls through the host-buffer C ABI (0 = skip)")
+    ap.add_argument("--nets", default="", help="comma list of further networks measured briefly into the `networks` side field ('all' = the other four)")
+    ap.add_argument("--lean", action="store_true", help="only the headline measurement (kernel experiments): no side fields, no CPU baselines")
     ap.add_argument("--core", type=int, default=2, choices=[0, 1, 2],
                     help="compute core: 2 = tcgen05 kind::mxf4 (default), 1 = tcgen05 kind::i8, 0 = LOP3+POPC bit-serial (BASELINE configs[3] comparison)")
     a = ap.parse_args()
+    if a.lean:
+        a.faults, a.sustained_s, a.latency_calls, a.nets, a.no_cpu_baseline = 0, 0.0, 0, "", True
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -280,6 +325,7 @@ def main():
         barrier()
         ms_total = max_over_ranks(e0.elapsed_time(e1))
     rt.profile_enable(False)
+    rt.sync()  # waits for the device and fails loudly if a kernel gave up waiting on an mbarrier during the timed region
     launches_per_step = rt.last_launches
     lay_ms, lay_cnt = rt.profile_collect()
     sampler.stop_flag = True
@@ -345,7 +391,8 @@ def main():
     # kind::mxf4 issues at 4x the bf16 rate (nominal 9 vs 2.25 PFLOP/s dense): the tensor peak this path is held against is
     # 4 x the MEASURED dense bf16 number; the fraction of the plain bf16 number is kept beside it
     f4_peak = 4.0 * tf_peak
-    roofline = {"bound": "tensor", "achieved": achieved, "peak": f4_peak, "unit": "TFLOP/s", "frac": achieved / f4_peak, "traffic": (int(TRAFFIC_PER_IMAGE[fam] * units_per_launch) if TRAFFIC_PER_IMAGE.get(fam) else None),
+    tpi, tsrc = traffic_per_image(a.net)
+    roofline = {"bound": "tensor", "achieved": achieved, "peak": f4_peak, "unit": "TFLOP/s", "frac": achieved / f4_peak, "traffic": (int(tpi * units_per_launch) if tpi else None), "traffic_source": tsrc,
                 "kernel": "layer %d%s" % (k, " (fused with layer %d)" % (k - 1) if (k - 1) in fused else ""), "avg_launch_ms": avg_ms, "images_per_launch": units_per_launch,
                 "ops_per_image_this_kernel": lops[k],
                 "peak_source": "4 x " + how + " dense bf16 (%.1f TFLOP/s): tcgen05 kind::mxf4 nominal rate; ops = 2 x MAC as config.h counts them" % tf_peak,

@@ -39,8 +39,8 @@ void deinit();
 """)
 # in-memory twins exported by this runtime's libraries only (include/bnn_b200.h); bound lazily so the cdef above stays the reference's
 _ffi.cdef("""
-int* inference_buffer(const unsigned char* images, int image_count, int number_class, float *usecPerImage, int enable_detail);
-int* inference_buffer_with_faults(const unsigned char* images, int image_count, int number_class, float *usecPerImage, unsigned int flip_count, int word_size, int target, int* target_layers, unsigned int num_targets);
+int* inference_buffer(const unsigned char* images, int image_count, long long image_bytes, int number_class, float *usecPerImage, int enable_detail);
+int* inference_buffer_with_faults(const unsigned char* images, int image_count, long long image_bytes, int number_class, float *usecPerImage, unsigned int flip_count, int word_size, int target, int* target_layers, unsigned int num_targets);
 """)
 
 _libraries = {}
@@ -85,6 +85,8 @@ class PynqBNN:
                 raise RuntimeError("%s not built: run `make -C bnn-pynq_b200` (no CPU fallback exists)" % path)
             _libraries[dllname] = _ffi.dlopen(path)
         self.interface = _libraries[dllname]
+        self.network = network
+        self.is_cnv = network.startswith("cnv")  # decides the row size every in-memory entry point accepts
         self.num_classes = 0
         self.classes = []
         self.usecPerImage = 0.0
@@ -160,26 +162,31 @@ class PynqBNN:
         return _ffi.cast("int *", _ffi.from_buffer(self._targets))
 
     def _as_images(self, images):
-        """uint8 array -> (contiguous array, count).  Rows are 3073-byte CIFAR records or 3072 planar RGB bytes (a zero label byte is
-        prepended) for CNV libraries, 784 pixels for LFC ones; the library checks nothing beyond the count."""
+        """uint8 array -> (contiguous [n, row] array, n) for THIS library's network kind: CNV rows are 3073-byte CIFAR records or
+        3072 planar RGB bytes (a zero label byte is prepended), LFC rows 784 pixels.  A flat array is split by that row size.
+        Anything else is a ValueError here; the library checks the byte count once more before it reads."""
         a = np.ascontiguousarray(images, dtype=np.uint8)
+        rows = (3073, 3072) if self.is_cnv else (784,)
         if a.ndim == 1:
-            a = a.reshape(-1, 3073) if a.size and a.size % 3073 == 0 else a.reshape(1, -1)
+            fit = [r for r in rows if a.size % r == 0]
+            if a.size and not fit:
+                raise ValueError("%s: a flat input must hold whole rows of %s bytes, got %d bytes" % (self.network, " / ".join(map(str, rows)), a.size))
+            a = a.reshape(-1, fit[0] if a.size else rows[0])
         if a.shape[0] == 0:
-            return a.reshape(0, 0), 0
+            return a.reshape(0, rows[0]), 0
         a = a.reshape(a.shape[0], -1)
+        if a.shape[1] not in rows:
+            raise ValueError("%s expects rows of %s bytes, got %d" % (self.network, " / ".join(map(str, rows)), a.shape[1]))
         if a.shape[1] == 3072:
             a = np.concatenate([np.zeros((a.shape[0], 1), np.uint8), a], axis=1)
-        if a.shape[1] not in (3073, 784):
-            raise ValueError("expected rows of 3073 / 3072 bytes (CNV) or 784 bytes (LFC), got %d" % a.shape[1])
-        return a, a.shape[0]
+        return np.ascontiguousarray(a), a.shape[0]
 
     def inference_buffer(self, images, detail=False):
         """inference_multiple / inference_multiple_detail on images already in memory (no file)."""
         a, n = self._as_images(images)
         usecperimage = _ffi.new("float *")
         ptr = _ffi.cast("const unsigned char *", _ffi.from_buffer(a)) if n else _ffi.NULL
-        result_ptr = self.interface.inference_buffer(ptr, n, len(self.classes), usecperimage, 1 if detail else 0)
+        result_ptr = self.interface.inference_buffer(ptr, n, a.size, len(self.classes), usecperimage, 1 if detail else 0)
         out = self._take(result_ptr, n * len(self.classes) if detail else n)
         self._rate(usecperimage[0], n)
         return out
@@ -189,7 +196,7 @@ class PynqBNN:
         usecperimage = _ffi.new("float *")
         ptr = _ffi.cast("const unsigned char *", _ffi.from_buffer(a)) if n else _ffi.NULL
         result_ptr = self.interface.inference_buffer_with_faults(
-            ptr, n, len(self.classes), usecperimage, num_faults, word_size, target_type, self._targets_ptr(target_layers), len(target_layers))
+            ptr, n, a.size, len(self.classes), usecperimage, num_faults, word_size, target_type, self._targets_ptr(target_layers), len(target_layers))
         out = self._take(result_ptr, n)
         self._rate(usecperimage[0], n)
         return out

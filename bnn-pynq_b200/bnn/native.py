@@ -17,6 +17,8 @@ _SIGS = {
     "bnnb_set_devices": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "bnnb_num_devices": (C.c_int, [C.c_void_p]),
     "bnnb_load_parameters": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "bnnb_release": (C.c_int, [C.c_void_p]),
+    "bnnb_device_bytes": (C.c_size_t, [C.c_void_p, C.c_int]),
     "bnnb_classify_cifar": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "bnnb_classify_mnist": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "bnnb_classify_with_fault_list": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
@@ -102,6 +104,13 @@ class Runtime:
 
     def load_parameters(self, params_dir):
         self._ck(self.L.bnnb_load_parameters(self.h, params_dir.encode()))
+
+    def release(self):
+        """Free every device allocation; parameters and faults stay in the host mirror (the next call rebuilds the device state)."""
+        self._ck(self.L.bnnb_release(self.h))
+
+    def device_bytes(self, slot=0):
+        return self.L.bnnb_device_bytes(self.h, slot)
 
     @property
     def usec_per_image(self):

@@ -44,6 +44,8 @@ static int wrap(bnnb_ctx* c, int rc) { if (rc != 0) c->err = c->eng->last_error(
 
 int bnnb_set_devices(bnnb_ctx* c, const int* ids, int n) { GUARD(c); TRY return wrap(c, c->eng->set_devices(ids, n)); CATCH(c, -1) }
 int bnnb_num_devices(bnnb_ctx* c) { GUARD(c); return c->eng->num_devices(); }
+int bnnb_release(bnnb_ctx* c) { GUARD(c); TRY return wrap(c, c->eng->release()); CATCH(c, -1) }
+size_t bnnb_device_bytes(bnnb_ctx* c, int slot) { return c && c->eng ? c->eng->device_bytes(slot) : 0; }
 int bnnb_load_parameters(bnnb_ctx* c, const char* dir) { GUARD(c); TRY return wrap(c, c->eng->load_parameters(dir ? dir : "")); CATCH(c, -1) }
 
 int bnnb_classify_cifar(bnnb_ctx* c, const uint8_t* rec, int n, int ncls, int* classes, int16_t* scores, float* usec) {

@@ -9,9 +9,11 @@
 // image (m = y*32 + x: the 3x3x3 window row ky of pixel (y,x) is the first 9 bytes of P[m + 32*ky]).  K is laid out as
 // [ky][16]: k = ky*16 + (kx*3 + c) with zero weights for the 7 trailing bytes of each ky and for the whole 4th chunk, so
 // one tile needs two K=32 MMAs whose A descriptors differ only by a start shift (LBO = 32 rows).
-// Warp-specialised CTA (one per SM, 608 threads): eight warps run layer 1's epilogue on image i, eight warps stage image i+1
-// (window plane P, layer-0 epilogue into the other layer-1 operand buffer), one thread prefetches images by TMA bulk copy two
-// images ahead and issues all MMAs, interleaving layer 1 of image i with layer 0 of image i+1 tile by tile.
+// Warp-specialised CTA (one per SM, 736 threads = 23 warps): eight warps run layer 1's epilogue on image i, eight warps run layer 0's
+// epilogue of image i+1 into the other layer-1 operand buffer, three issuer warps (two for layer 1, one for layer 0 + the TMA bulk
+// prefetch of images two ahead), four helper warps (window planes, max-pool + store).  See the role table above the kernel.
+// TAP (template flag, parity tests only): the same kernel additionally stores every layer-0 / layer-1 MMA sum and layer 0's output
+// operand rows to global memory (bnnb_tap on the tensor cores); the production instantiation carries none of that code.
 #include <climits>
 #include <cstdio>
 #include <type_traits>
@@ -74,9 +76,10 @@ __device__ __forceinline__ uint32_t sign_bytes(uint32_t a, uint32_t b) {
 }
 __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 
-// Warp roles (608 threads): warps 0-7 = half A (layer-1 epilogue, pool, store), warps 8-15 = half B (layer-0 epilogue into the
+// Warp roles (736 threads): warps 0-7 = half A (layer-1 epilogue, pool, store), warps 8-15 = half B (layer-0 epilogue into the
 // other operand buffer), each half split into two teams of four warps by 32-channel half (the per-tile epilogue is a latency
-// chain: two teams halve it); half A also builds the window planes, warps 16-17 = layer-1 MMA issuers, warp 18 = image prefetch (TMA) + layer-0 MMA issuer.
+// chain: two teams halve it); warps 16-17 = layer-1 MMA issuers, warp 18 = image prefetch (TMA) + layer-0 MMA issuer, warps 19-22 = helpers
+// (window planes two images ahead, 2x2 max-pool of the bit rows + store).
 // The roles are decoupled by mbarriers only (no CTA-wide barrier in steady state):
 //   img_full[b]   TMA    -> half A   image buffer b holds an image                      (expect_tx 3072 bytes)
 //   p_full[b]     half A -> warp 16   window plane b is built (and image buffer b free)  (256 arrivals)
@@ -85,9 +88,9 @@ __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 2
 //   l0_done[b][t] half B -> warps 16-17  layer-0 tile t of the image in operand buffer b is written (256 arrivals): layer-1 tile t-1 may start
 //   abuf_empty[b] warp 16 -> half B   all layer-1 MMAs reading buffer b have completed   (tcgen05.commit)
 //   full[s], empty[s] warp 16 <-> half A  layer-1 accumulator slot s (of 4) full / read out
-template <int OUTM, bool F4>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
+template <int OUTM, bool F4, bool TAP>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
 __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
-                                                      int n_img, int out_fmt, int* __restrict__ status) {
+                                                      int n_img, int out_fmt, int* __restrict__ status, Tap01 tp) {
   using S = Smem01<OUTM, F4>;
   constexpr int L1_A = S::L1_A;
   constexpr uint32_t SF_COL = 448;  // TMEM columns of the unit scale factors (F4)
@@ -311,6 +314,22 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
             if (valid) *reinterpret_cast<uint4*>(sA + (size_t)(2 * team + c16) * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
           }
         }
+        if (TAP) {  // parity taps: the MMA sum S = sum w*q of every valid pixel and channel, and the operand row just written
+          const long long img = first + (long long)k * stride;
+          if (FOLD) {  // the accumulator holds thr - S in 32 bits (the epilogue above read only its low halves)
+            tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, r);
+            tc::tmem_ld_wait_dep(r);
+          }
+          if (valid) {
+            int32_t* ta = tp.acc0 + ((size_t)img * 900 + (y * 30 + x)) * 64 + team * 32;
+#pragma unroll
+            for (int c = 0; c < 32; c++) ta[c] = FOLD ? thrA[c] - (int)r[c] : (int)r[c];
+            const uint8_t* row = sA + (size_t)(F4 ? team : 2 * team) * L1_PLANE + (size_t)(y * 30 + x) * 16;
+            uint4* td = tp.act0 + ((size_t)img * 900 + (y * 30 + x)) * 4 + 2 * team;
+            td[0] = *reinterpret_cast<const uint4*>(row);
+            td[1] = F4 ? make_uint4(0, 0, 0, 0) : *reinterpret_cast<const uint4*>(row + L1_PLANE);
+          }
+        }
         if (FOLD && kEpi) preload0(slot);
         tc::fence_before_sync();
         __syncwarp();
@@ -504,6 +523,17 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         }
         if (kEpi || !FOLD) sbk[(size_t)m * WPP + team] = b0;
         if (OUTM == OUT_TERN) sbk[(size_t)m * WPP + 2 + team] = b1;
+        if (TAP) {  // parity taps: the MMA sum of every valid output pixel and channel (FOLD: un-fold 6*thr + 3 - 6*S)
+          const int y = m / 30, x = m - y * 30;
+          if (y < 28 && x < 28) {
+            int32_t* ta = tp.acc1 + ((size_t)(first + (long long)k * stride) * 784 + (y * 28 + x)) * 64 + team * 32;
+#pragma unroll
+            for (int c = 0; c < 32; c++) {
+              if (FOLD) ta[c] = __float2int_rn(__fdiv_rn((float)thrA[c] - __uint_as_float(r[c]), 6.0f));
+              else ta[c] = F4 ? __float2int_rn(__uint_as_float(r[c])) : (int)r[c];
+            }
+          }
+        }
         if (FOLD && kEpi) preload1(slot);
         tc::fence_before_sync();
         __syncwarp();
@@ -566,23 +596,29 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
 }  // namespace
 
 template <int OUTM, bool F4>
-static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int grid, int out_fmt, int* status, cudaStream_t s) {
+static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int grid, int out_fmt, int* status, const Tap01& tp,
+                     cudaStream_t s) {
   using S = Smem01<OUTM, F4>;
   static_assert(S::TOTAL <= 226 * 1024, "shared memory budget");
-  cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-  k_cnv01_tc<OUTM, F4><<<grid, NT01, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status);
+  if (tp.acc0) {  // parity taps: the TAP instantiation of the same kernel
+    cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+    k_cnv01_tc<OUTM, F4, true><<<grid, NT01, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status, tp);
+    return;
+  }
+  cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+  k_cnv01_tc<OUTM, F4, false><<<grid, NT01, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status, tp);
 }
 
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt,
-                     int* status, cudaStream_t s) {
+                     int* status, const Tap01& tp, cudaStream_t s) {
   if (out_fmt != ACT_BITS && !(out_fmt == ACT_F4P && L1.d.out_mode == OUT_BIT)) return false;
   if (n_img <= 0 || !L1.w8 || !L1.w4 || !L1.thr_tc || L0.d.N != 64 || L1.d.N != 64 || L1.d.ifm_dim != 30) return false;
   const int grid = n_img < num_sms ? n_img : num_sms;
   const bool bit = L1.d.out_mode == OUT_BIT;
-  if (bit && fp4) launch01<OUT_BIT, true>(L0, L1, in, out, n_img, grid, out_fmt, status, s);
-  else if (bit) launch01<OUT_BIT, false>(L0, L1, in, out, n_img, grid, out_fmt, status, s);
-  else if (fp4) launch01<OUT_TERN, true>(L0, L1, in, out, n_img, grid, out_fmt, status, s);
-  else launch01<OUT_TERN, false>(L0, L1, in, out, n_img, grid, out_fmt, status, s);
+  if (bit && fp4) launch01<OUT_BIT, true>(L0, L1, in, out, n_img, grid, out_fmt, status, tp, s);
+  else if (bit) launch01<OUT_BIT, false>(L0, L1, in, out, n_img, grid, out_fmt, status, tp, s);
+  else if (fp4) launch01<OUT_TERN, true>(L0, L1, in, out, n_img, grid, out_fmt, status, tp, s);
+  else launch01<OUT_TERN, false>(L0, L1, in, out, n_img, grid, out_fmt, status, tp, s);
   return true;
 }
 

@@ -59,9 +59,9 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
   return make_uint4(v[0], v[1], v[2], v[3]);
 }
 
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool TAP>
 __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
-                                                     int in_fmt, int out_fmt, int* __restrict__ status) {
+                                                     int in_fmt, int out_fmt, int* __restrict__ status, int32_t* __restrict__ tap) {
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
   extern __shared__ __align__(128) uint8_t smem[];
@@ -254,6 +254,15 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           }
           b0[j] = w0;
           b1[j] = w1;
+          if (TAP) {  // parity taps (TAP instantiation only): the MMA sum of every valid output pixel and channel, pre-load un-folded
+            const int gi = m / Cfg::PXI, rem = m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
+            if (m < Cfg::ROWS && y < OD && x < OD && img0 + gi < n_img) {
+              int32_t* ta = tap + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * NT + h * N + eg * NG + j * 32;
+              const float* pv = sthr + h * N + eg * NG + j * 32;
+#pragma unroll
+              for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (FOLD ? pv[c] : 0.0f));
+            }
+          }
         }
         if (FOLD) preload(slot, (gt + Cfg::SLOTS) % NS);
         tc::fence_before_sync();
@@ -336,14 +345,22 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
 }
 
 template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
-bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
+bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+                cudaStream_t s) {
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::SMEM <= 226 * 1024, "shared memory budget");
   static_assert(Cfg::SLOTS * N <= Cfg::SF_COL, "TMEM budget");
-  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
   const int ngroups = (n_img + G - 1) / G;
-  kern<<<ngroups < num_sms ? ngroups : num_sms, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status);
+  const int grid = ngroups < num_sms ? ngroups : num_sms;
+  if (tap) {  // parity taps: the TAP instantiation of the same kernel
+    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+    kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status, tap);
+    return true;
+  }
+  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+  kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status, nullptr);
   return true;
 }
 
@@ -357,23 +374,24 @@ bool conv_f4_supports(const LayerDesc& d) {
          (d.ifm_ch == 128 && d.N == 256 && d.ifm_dim == 5 && !d.pool);
 }
 
-bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
+bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+                    cudaStream_t s) {
   const LayerDesc& d = L.d;
   if (!conv_f4_supports(d) || !L.w4 || !L.thr_tc || n_img <= 0) return false;
   if ((in_fmt != ACT_BITS || out_fmt != ACT_BITS) && d.out_mode != OUT_BIT) return false;  // the fp4 interchange formats are for 1-bit activations
   if (in_fmt == ACT_F4T || (d.pool && out_fmt == ACT_F4T)) return false;
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {
-    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
-    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, 6, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, 6, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
   }
   if (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) {
-    if (a1) return launch_cfg<128, 128, 1, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
-    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+    if (a1) return launch_cfg<128, 128, 1, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
   }
   if (d.ifm_ch == 128 && d.N == 256 && d.ifm_dim == 5 && !d.pool) {  // two channel blocks of 128 share the operand planes
-    if (a1) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
-    if (a2) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+    if (a1) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+    if (a2) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
   }
   return false;
 }

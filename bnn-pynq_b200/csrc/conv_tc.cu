@@ -68,7 +68,7 @@ __device__ __forceinline__ uint32_t spread4(uint32_t nib) { return (nib * 0x0020
 
 template <int C, int N, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
 __global__ void __launch_bounds__(128) k_conv_tc(DevLayer L, const uint32_t* __restrict__ in,
-                                                  uint32_t* __restrict__ out, int n_img, int* __restrict__ status) {
+                                                  uint32_t* __restrict__ out, int n_img, int* __restrict__ status, int32_t* __restrict__ tap) {
   using Cfg = ConvTcCfg<C, N, IDIM, OD, POOL, G, INM, OUTM>;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bar[2];
@@ -166,6 +166,13 @@ __global__ void __launch_bounds__(128) k_conv_tc(DevLayer L, const uint32_t* __r
         uint32_t r[32];
         tc::tmem_ld32(trow + j * 32, r);
         tc::tmem_ld_wait();
+        if (tap) {  // parity taps: the int32 MMA sums of every valid output pixel
+          const int gi = m / Cfg::PXI, rem = m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
+          if (m < Cfg::ROWS && y < OD && x < OD && img0 + gi < n_img) {
+#pragma unroll
+            for (int c = 0; c < 32; c++) tap[((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * N + j * 32 + c] = (int)r[c];
+          }
+        }
         uint32_t b0 = 0, b1 = 0;
 #pragma unroll
         for (int c = 0; c < 32; c++) {
@@ -222,7 +229,7 @@ __global__ void __launch_bounds__(128) k_conv_tc(DevLayer L, const uint32_t* __r
 }
 
 template <int C, int N, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
-static bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+static bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, int32_t* tap, cudaStream_t s) {
   using Cfg = ConvTcCfg<C, N, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::SMEM <= 226 * 1024, "shared memory budget");
   auto kern = k_conv_tc<C, N, IDIM, OD, POOL, G, INM, OUTM>;
@@ -233,26 +240,26 @@ static bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int
   const int ngroups = (n_img + G - 1) / G;
   int grid = num_sms * per_sm;
   if (grid > ngroups) grid = ngroups;
-  kern<<<grid, 128, Cfg::SMEM, s>>>(L, in, out, n_img, status);
+  kern<<<grid, 128, Cfg::SMEM, s>>>(L, in, out, n_img, status, tap);
   return true;
 }
 
 // Returns false if this layer shape has no tensor-core instantiation (the caller then uses the LOP3+POPC kernel).
-bool launch_conv_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+bool launch_conv_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, int32_t* tap, cudaStream_t s) {
   const LayerDesc& d = L.d;
   if (d.kind != KIND_CONV || !L.w8 || !L.thr_tc || n_img <= 0) return false;
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 64 && d.ifm_dim == 30 && d.pool) {
-    if (a1) return launch_cfg<64, 64, 30, 28, true, 1, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<64, 64, 30, 28, true, 1, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a1) return launch_cfg<64, 64, 30, 28, true, 1, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, tap, s);
+    if (a2) return launch_cfg<64, 64, 30, 28, true, 1, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, tap, s);
   }
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {
-    if (a1) return launch_cfg<64, 128, 14, 12, false, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<64, 128, 14, 12, false, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a1) return launch_cfg<64, 128, 14, 12, false, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, tap, s);
+    if (a2) return launch_cfg<64, 128, 14, 12, false, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, tap, s);
   }
   if (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) {
-    if (a1) return launch_cfg<128, 128, 12, 10, true, 2, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, s);
-    if (a2) return launch_cfg<128, 128, 12, 10, true, 2, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, s);
+    if (a1) return launch_cfg<128, 128, 12, 10, true, 2, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, status, tap, s);
+    if (a2) return launch_cfg<128, 128, 12, 10, true, 2, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, status, tap, s);
   }
   return false;
 }

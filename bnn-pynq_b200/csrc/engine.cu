@@ -5,52 +5,113 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 
 namespace bnnb {
 
-#define CK(call)                                                                                   \
+// CUDA call -> error string + return -1 (E: the std::string that receives the message)
+#define CKE(E, call)                                                                               \
   do {                                                                                             \
     cudaError_t e_ = (call);                                                                       \
     if (e_ != cudaSuccess) {                                                                       \
-      err_ = std::string(#call) + ": " + cudaGetErrorString(e_);                                   \
+      (E) = std::string(#call) + ": " + cudaGetErrorString(e_);                                    \
       return -1;                                                                                   \
     }                                                                                              \
   } while (0)
+#define CK(call) CKE(err_, call)
 
-static constexpr int kLanes = 4;  // chunk pipelines per device: H2D of chunk i+1 overlaps compute of chunk i, and the host enqueues two chunks further ahead
+// Copy lanes per device: the H2D copy of chunk i+1..i+3 overlaps the compute of chunk i.  All kernels of a device run on ONE
+// in-order compute stream (they are persistent full-GPU kernels: nothing is gained by interleaving them), so the activation
+// buffers exist once per device and a chunk's kernel time is not polluted by its neighbours'.
+static constexpr int kLanes = 4;
 
 struct Lane {
-  cudaStream_t s = nullptr;
+  cudaStream_t copy = nullptr;
   uint8_t* d_raw = nullptr;   // chunk x raw input bytes (CIFAR records / MNIST pixels)
-  void* d_in = nullptr;       // chunk x layer-0 input
-  uint32_t* buf[2] = {nullptr, nullptr};  // ping-pong activations
   void* d_out = nullptr;      // chunk x out_bytes
   int* d_cls = nullptr;
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  int cap = 0;                // images the three buffers hold
+  cudaEvent_t copied = nullptr, prep_done = nullptr, done = nullptr, d2h = nullptr;
+  bool used = false;
+  // results of the chunk in flight, copied back when the lane is next needed (a device-to-pageable copy blocks the host: issuing it
+  // right after the chunk would stop the feeder from running ahead)
+  int pend_off = -1, pend_n = 0;
 };
 
 struct DeviceState {
   int id = 0, num_sms = 148;
+  bool ready = false;         // streams, parameter buffers and the parameter upload exist
+  cudaStream_t compute = nullptr;
   Lane lane[kLanes];
+  void* d_in = nullptr;       // layer-0 input of the chunk on the compute stream
+  uint32_t* act[2] = {nullptr, nullptr};  // ping-pong activations
+  int buf_cap = 0;            // images d_in / act hold
   DevLayer L[9];
-  DevFolded folded;
-  uint64_t* wf[9] = {};
-  int32_t* tf[9] = {};
+  DevLayer* d_layers = nullptr;
   DevPatch* d_patches = nullptr;
   size_t patch_cap = 0;
-  bool uploaded = false;
-  int* d_status = nullptr;  // set by a kernel whose mbarrier wait timed out
-  std::vector<void*> allocs;
+  int* d_status = nullptr;    // set by a kernel whose mbarrier wait timed out: mapped pinned host memory (device alias of h_status)
+  int* h_status = nullptr;
+  std::vector<void*> params;  // parameter-lifetime allocations
+  std::vector<cudaEvent_t> tev;
+  size_t bytes = 0;
+
+  void* alloc(size_t n, bool param) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, n ? n : 16) != cudaSuccess) return nullptr;
+    if (param) params.push_back(p);
+    bytes += n ? n : 16;
+    return p;
+  }
+  void release(void*& p, size_t n) {
+    if (p) { cudaFree(p); bytes -= n ? n : 16; }
+    p = nullptr;
+  }
+  void destroy() {
+    if (!ready && !compute) return;
+    cudaSetDevice(id);
+    if (compute) cudaStreamSynchronize(compute);
+    for (auto& ln : lane) {
+      if (ln.copy) { cudaStreamSynchronize(ln.copy); cudaStreamDestroy(ln.copy); }
+      for (cudaEvent_t* e : {&ln.copied, &ln.prep_done, &ln.done, &ln.d2h}) if (*e) cudaEventDestroy(*e);
+      cudaFree(ln.d_raw); cudaFree(ln.d_out); cudaFree(ln.d_cls);
+      ln = Lane();
+    }
+    if (compute) cudaStreamDestroy(compute);
+    compute = nullptr;
+    cudaFree(d_in); cudaFree(act[0]); cudaFree(act[1]); cudaFree(d_patches);
+    d_in = nullptr; act[0] = act[1] = nullptr; d_patches = nullptr; patch_cap = 0; buf_cap = 0;
+    for (void* p : params) cudaFree(p);
+    params.clear();
+    for (cudaEvent_t e : tev) cudaEventDestroy(e);
+    tev.clear();
+    if (h_status) cudaFreeHost(h_status);
+    d_layers = nullptr; d_status = nullptr; h_status = nullptr;
+    bytes = 0;
+    ready = false;
+  }
+  ~DeviceState() { destroy(); }
 };
 
-static size_t act_words_per_image(const NetDesc& n, int first = 0) {  // largest inter-layer tensor written by layers >= first
-  size_t m = 0;
-  for (int i = first; i + 1 < n.nlayers; i++) {
-    const LayerDesc& l = n.L[i];
-    const size_t w = (size_t)out_dim(l) * out_dim(l) * out_words_per_pixel(l);
-    m = std::max(m, w);
-  }
-  return m;
+// What run_chunk reports / needs when a parity test taps the layers.
+struct TapCtx {
+  int32_t* acc = nullptr;   // device, layer-major over the chunk: [layer][img][ofm^2][N]
+  uint4* act0 = nullptr;    // fused CNV layers 0+1: layer 0's output as the operand rows layer 1 reads
+  bool tensor = false;      // taps from the tensor-core kernels (TAP instantiations) instead of the LOP3+POPC kernels
+  int ofmt[9] = {};         // activation format every layer wrote
+  int raw[9] = {};          // 1: acc holds the MMA sum (needs the un-folding of tap_host), 0: the reference accumulator itself
+  bool fused01 = false;
+};
+
+struct Engine::Segments {   // fault epochs of one call: patches in fault order with their times
+  std::vector<Patch> patches;
+  std::vector<uint32_t> ptime;
+};
+
+static int round_cap(int images) {  // buffer capacities grow in powers of two from 128 images
+  int c = 128;
+  while (c < images) c <<= 1;
+  return c;
 }
 
 Engine::Engine(const NetDesc& net) : net_(net), pm_(new ParamMirror(net)) {
@@ -58,26 +119,30 @@ Engine::Engine(const NetDesc& net) : net_(net), pm_(new ParamMirror(net)) {
   if (const char* e = std::getenv("BNN_B200_FUSE01")) fuse01_ = std::atoi(e) != 0;
 }
 
-int Engine::check_status(int slot) {
-  DeviceState& ds = *dev_[slot];
-  int st = 0;
-  CK(cudaSetDevice(ds.id));
-  CK(cudaMemcpy(&st, ds.d_status, 4, cudaMemcpyDeviceToHost));
-  if (st != 0) { err_ = "a tensor-core kernel timed out waiting on an mbarrier"; return -1; }
+Engine::~Engine() { dev_.clear(); }
+
+int Engine::release() {
+  for (auto& d : dev_) d->destroy();
+  {
+    std::lock_guard<std::mutex> lk(prof_mu_);
+    for (auto& e : prof_) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    prof_.clear();
+  }
   return 0;
 }
 
-Engine::~Engine() {
-  for (auto& d : dev_) {
-    cudaSetDevice(d->id);
-    for (auto& ln : d->lane) {
-      if (ln.s) cudaStreamSynchronize(ln.s);
-      if (ln.e0) cudaEventDestroy(ln.e0);
-      if (ln.e1) cudaEventDestroy(ln.e1);
-      if (ln.s) cudaStreamDestroy(ln.s);
-    }
-    for (void* p : d->allocs) cudaFree(p);
+size_t Engine::device_bytes(int slot) const { return slot >= 0 && slot < (int)dev_.size() ? dev_[slot]->bytes : 0; }
+
+int Engine::check_status(DeviceState& ds, std::string& err) {
+  // the flag lives in mapped pinned memory: after the stream synchronisation that precedes every call of this function the host
+  // reads what a kernel wrote, without a copy
+  const int st = ds.h_status ? *reinterpret_cast<volatile int*>(ds.h_status) : 0;
+  if (st != 0) {
+    *reinterpret_cast<volatile int*>(ds.h_status) = 0;  // reported once; the next call starts clean
+    err = "a tensor-core kernel gave up waiting on an mbarrier (device " + std::to_string(ds.id) + "): results of this call are invalid";
+    return -1;
   }
+  return 0;
 }
 
 // Images per pass through the layer chain.  host = the pipelined host-buffer path, where a chunk is also the unit of H2D/compute
@@ -92,12 +157,27 @@ int Engine::chunk_images(bool host) const {
   return tern ? 2048 : 4096;
 }
 
+// Bytes of ONE activation buffer for chunks of `images`: the largest inter-layer tensor in any format a core may plan for it
+// (bit planes everywhere; e2m1 operand planes, 4 bits per value and 128-image tiles, between fp4 kernels of a 1-bit network).
+size_t Engine::act_bytes(int images) const {
+  size_t per = 16;
+  for (int i = 0; i + 1 < net_.nlayers; i++) {
+    const LayerDesc& l = net_.L[i];
+    const size_t px = (size_t)out_dim(l) * out_dim(l);
+    per = std::max(per, px * out_words_per_pixel(l) * 4);
+    if (l.out_mode == OUT_BIT) per = std::max(per, px * l.N / 2);
+  }
+  return (size_t)((images + 127) / 128 * 128) * per;
+}
+
 int Engine::set_devices(const int* ids, int n) {
   if (!dev_.empty()) { err_ = "set_devices must be called before the first use"; return -1; }
   dev_ids_.assign(ids, ids + n);
   return 0;
 }
 
+// The device list.  Nothing is allocated here: a device gets its streams, parameter buffers and parameter upload the first time a
+// call runs on it (upload), its activation / staging buffers sized for the chunks it is actually given (ensure_buffers / ensure_lane).
 int Engine::ensure_devices() {
   if (!dev_.empty()) return 0;
   int count = 0;
@@ -113,110 +193,67 @@ int Engine::ensure_devices() {
       for (int i = 0; i < count; i++) dev_ids_.push_back(i);
     }
   }
-  // buffers are sized for the largest chunk either core selection may use (set_core can change between calls)
-  // lane 0 also serves the device-resident path (larger chunks); per lane: images and bytes of the ping-pong activation buffers
-  int lane_chunk[kLanes];
-  size_t lane_act[kLanes];
-  {
-    const int c0 = core_;
-    for (int k = 0; k < kLanes; k++) {
-      core_ = 0;
-      const int cp = chunk_images(true);
-      const size_t ap = (size_t)cp * act_words_per_image(net_) * 4;
-      core_ = 2;
-      const int ct = std::max(chunk_images(true), k == 0 ? chunk_images(false) : 0);
-      size_t at = (size_t)ct * act_words_per_image(net_, net_.is_cnv && fuse01_ ? 1 : 0) * 4;
-      // between fp4 kernels of a 1-bit network activations travel as e2m1 operand planes (4 bits per value, 128-image tiles)
-      for (int i = (net_.is_cnv ? 1 : 0); i + 1 < net_.nlayers; i++)
-        if (net_.L[i].out_mode == OUT_BIT)
-          at = std::max(at, (size_t)((ct + 127) / 128 * 128) * out_dim(net_.L[i]) * out_dim(net_.L[i]) * net_.L[i].N / 2);
-      lane_chunk[k] = std::max(cp, ct);
-      lane_act[k] = std::max(ap, at);
-    }
-    core_ = c0;
-  }
-  const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
+  std::vector<std::unique_ptr<DeviceState>> built;
   for (int id : dev_ids_) {
     if (id < 0 || id >= count) { err_ = "bad device id"; return -1; }
-    CK(cudaSetDevice(id));
-    std::unique_ptr<DeviceState> d(new DeviceState);
-    d->id = id;
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, id));
-    d->num_sms = prop.multiProcessorCount;
     if (prop.major < 10) { err_ = "this runtime is built for sm_100a (Blackwell) only"; return -1; }
-    auto alloc = [&](size_t bytes) -> void* {
-      void* p = nullptr;
-      if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) return nullptr;
-      d->allocs.push_back(p);
-      return p;
-    };
-    for (int k = 0; k < kLanes; k++) {
-      Lane& ln = d->lane[k];
-      const int chunk = lane_chunk[k];
-      CK(cudaStreamCreateWithFlags(&ln.s, cudaStreamNonBlocking));
-      CK(cudaEventCreate(&ln.e0));
-      CK(cudaEventCreate(&ln.e1));
-      ln.d_raw = (uint8_t*)alloc((size_t)chunk * raw_bytes);
-      ln.d_in = alloc((size_t)chunk * net_.in_bytes);
-      ln.buf[0] = (uint32_t*)alloc(lane_act[k]);
-      ln.buf[1] = (uint32_t*)alloc(lane_act[k]);
-      ln.d_out = alloc((size_t)chunk * net_.out_bytes);
-      ln.d_cls = (int*)alloc((size_t)chunk * 4);
-      if (!ln.d_raw || !ln.d_in || !ln.buf[0] || !ln.buf[1] || !ln.d_out || !ln.d_cls) { err_ = "cudaMalloc failed"; return -1; }
-    }
-    for (int i = 0; i < net_.nlayers; i++) {
-      const LayerDesc& l = net_.L[i];
-      DevLayer& D = d->L[i];
-      D.d = l;
-      D.kwords = l.K / 32;
-      D.kpad = (l.K + 31) / 32 * 32;
-      d->wf[i] = (uint64_t*)alloc((size_t)l.pe * l.wmem * 8);
-      d->tf[i] = (int32_t*)alloc((size_t)l.pe * l.tmem * std::max(l.nthr, 1) * 4);
-      const bool l0 = net_.is_cnv && i == 0;
-      D.wp = (uint32_t*)alloc(l0 ? (size_t)64 * 8 * 4 : (size_t)l.wbits * D.kwords * l.N * 4);
-      D.w8 = nullptr;
-      D.w4 = nullptr;
-      D.w4s = nullptr;
-      D.thr_tc = nullptr;
-      if (!l0) {  // operands of the tensor-core path
-        D.w8 = (int8_t*)alloc((size_t)l.N * D.kpad);
-        D.w4 = (uint8_t*)alloc((size_t)l.N * D.kpad / 2);
-        D.w4s = (uint8_t*)alloc((size_t)l.N * D.kpad / 2);
-        D.thr_tc = (int32_t*)alloc((size_t)l.N * 2 * 4);
-        if (!D.w8 || !D.w4 || !D.w4s || !D.thr_tc) { err_ = "cudaMalloc failed"; return -1; }
-      }
-      D.thr = (int32_t*)alloc((size_t)l.N * 2 * 4);
-      D.wf = d->wf[i];
-      D.tf = d->tf[i];
-      if (!d->wf[i] || !d->tf[i] || !D.wp || !D.thr) { err_ = "cudaMalloc failed"; return -1; }
-      d->folded.wf[i] = d->wf[i];
-      d->folded.tf[i] = d->tf[i];
-      d->folded.wmem[i] = l.wmem;
-      d->folded.tmem[i] = l.tmem;
-      d->folded.nthr[i] = std::max(l.nthr, 1);
-    }
-    d->d_status = (int*)alloc(4);
-    if (!d->d_status) { err_ = "cudaMalloc failed"; return -1; }
-    CK(cudaMemset(d->d_status, 0, 4));
-    dev_.push_back(std::move(d));
+    std::unique_ptr<DeviceState> d(new DeviceState);
+    d->id = id;
+    d->num_sms = prop.multiProcessorCount;
+    built.push_back(std::move(d));
   }
+  dev_.swap(built);  // only a complete list is kept
   return 0;
 }
 
-int Engine::upload_all() {
-  for (auto& d : dev_) {
-    CK(cudaSetDevice(d->id));
-    cudaStream_t s = d->lane[0].s;
-    for (int i = 0; i < net_.nlayers; i++) {
-      CK(cudaMemcpyAsync(d->wf[i], pm_->weights(i).data(), pm_->weights(i).size() * 8, cudaMemcpyHostToDevice, s));
-      CK(cudaMemcpyAsync(d->tf[i], pm_->thresholds(i).data(), pm_->thresholds(i).size() * 4, cudaMemcpyHostToDevice, s));
-      launch_repack(d->L[i], net_.is_cnv && i == 0, s);
+// First use of a device (or first use after release / load_parameters): streams, parameter buffers, upload + on-device re-pack.
+int Engine::upload(DeviceState& ds, std::string& err) {
+  CKE(err, cudaSetDevice(ds.id));
+  if (!ds.compute) {
+    CKE(err, cudaStreamCreateWithFlags(&ds.compute, cudaStreamNonBlocking));
+    for (auto& ln : ds.lane) {
+      CKE(err, cudaStreamCreateWithFlags(&ln.copy, cudaStreamNonBlocking));
+      for (cudaEvent_t* e : {&ln.copied, &ln.prep_done, &ln.done, &ln.d2h}) CKE(err, cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     }
-    CK(cudaStreamSynchronize(s));
-    CK(cudaGetLastError());
-    d->uploaded = true;
+    bool ok = true;
+    for (int i = 0; i < net_.nlayers; i++) {
+      const LayerDesc& l = net_.L[i];
+      DevLayer& D = ds.L[i];
+      D.d = l;
+      D.kwords = l.K / 32;
+      D.kpad = (l.K + 31) / 32 * 32;
+      D.wf = (uint64_t*)ds.alloc((size_t)l.pe * l.wmem * 8, true);
+      D.tf = (int32_t*)ds.alloc((size_t)l.pe * l.tmem * std::max(l.nthr, 1) * 4, true);
+      const bool l0 = net_.is_cnv && i == 0;
+      D.wp = (uint32_t*)ds.alloc(l0 ? (size_t)64 * 8 * 4 : (size_t)l.wbits * D.kwords * l.N * 4, true);
+      D.w8 = nullptr; D.w4 = nullptr; D.w4s = nullptr; D.thr_tc = nullptr;
+      if (!l0) {  // operands of the tensor-core paths
+        D.w8 = (int8_t*)ds.alloc((size_t)l.N * D.kpad, true);
+        D.w4 = (uint8_t*)ds.alloc((size_t)l.N * D.kpad / 2, true);
+        D.w4s = (uint8_t*)ds.alloc((size_t)l.N * D.kpad / 2, true);
+        D.thr_tc = (int32_t*)ds.alloc((size_t)l.N * 2 * 4, true);
+        ok = ok && D.w8 && D.w4 && D.w4s && D.thr_tc;
+      }
+      D.thr = (int32_t*)ds.alloc((size_t)l.N * 2 * 4, true);
+      ok = ok && D.wf && D.tf && D.wp && D.thr;
+    }
+    ds.d_layers = (DevLayer*)ds.alloc(sizeof(DevLayer) * 9, true);
+    if (cudaHostAlloc((void**)&ds.h_status, 4, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) ds.h_status = nullptr;
+    if (ds.h_status) { *ds.h_status = 0; if (cudaHostGetDevicePointer((void**)&ds.d_status, ds.h_status, 0) != cudaSuccess) ds.d_status = nullptr; }
+    if (!ok || !ds.d_layers || !ds.d_status) { err = "cudaMalloc failed (parameters, device " + std::to_string(ds.id) + ")"; ds.destroy(); return -1; }
+    CKE(err, cudaMemcpy(ds.d_layers, ds.L, sizeof(DevLayer) * 9, cudaMemcpyHostToDevice));
   }
+  cudaStream_t s = ds.compute;
+  for (int i = 0; i < net_.nlayers; i++) {
+    CKE(err, cudaMemcpyAsync(const_cast<uint64_t*>(ds.L[i].wf), pm_->weights(i).data(), pm_->weights(i).size() * 8, cudaMemcpyHostToDevice, s));
+    CKE(err, cudaMemcpyAsync(const_cast<int32_t*>(ds.L[i].tf), pm_->thresholds(i).data(), pm_->thresholds(i).size() * 4, cudaMemcpyHostToDevice, s));
+    launch_repack(ds.L[i], net_.is_cnv && i == 0, s);
+  }
+  CKE(err, cudaStreamSynchronize(s));
+  CKE(err, cudaGetLastError());
+  ds.ready = true;
   return 0;
 }
 
@@ -227,37 +264,85 @@ int Engine::load_parameters(const std::string& dir) {
   pm_ = std::move(pm);  // a reload discards injected faults
   loaded_ = true;
   if (ensure_devices() != 0) return -1;
-  return upload_all();
+  for (auto& d : dev_)
+    if (d->ready && upload(*d, err_) != 0) return -1;  // devices not used yet take the mirror when they are first used
+  return 0;
 }
 
-void Engine::enqueue_patches(DeviceState& ds, const std::vector<Patch>& p, cudaStream_t s) {
-  // caller has set the device; patches are small: stage through a device array, then re-pack the touched layers
-  if (p.empty()) return;
-  if (ds.patch_cap < p.size()) {
-    DevPatch* np = nullptr;
-    cudaMalloc(&np, p.size() * sizeof(DevPatch) * 2);
-    ds.allocs.push_back(np);
-    ds.d_patches = np;
-    ds.patch_cap = p.size() * 2;
+int Engine::ensure_buffers(DeviceState& ds, int images, std::string& err) {
+  if (images <= ds.buf_cap) return 0;
+  const int cap = round_cap(images);
+  CKE(err, cudaStreamSynchronize(ds.compute));
+  void* p;
+  p = ds.d_in; ds.release(p, (size_t)ds.buf_cap * net_.in_bytes); ds.d_in = nullptr;
+  for (int k = 0; k < 2; k++) { p = ds.act[k]; ds.release(p, ds.buf_cap ? act_bytes(ds.buf_cap) : 0); ds.act[k] = nullptr; }
+  ds.buf_cap = 0;
+  ds.d_in = ds.alloc((size_t)cap * net_.in_bytes, false);
+  ds.act[0] = (uint32_t*)ds.alloc(act_bytes(cap), false);
+  ds.act[1] = (uint32_t*)ds.alloc(act_bytes(cap), false);
+  if (!ds.d_in || !ds.act[0] || !ds.act[1]) {
+    cudaFree(ds.d_in); cudaFree(ds.act[0]); cudaFree(ds.act[1]);
+    ds.d_in = nullptr; ds.act[0] = ds.act[1] = nullptr;
+    err = "cudaMalloc failed (activation buffers for " + std::to_string(cap) + " images, device " + std::to_string(ds.id) + ")";
+    return -1;
   }
-  static_assert(sizeof(Patch) == sizeof(DevPatch), "Patch and DevPatch must share a layout");
-  cudaMemcpyAsync(ds.d_patches, p.data(), p.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, s);
-  launch_patch(ds.folded, ds.d_patches, (int)p.size(), s);
-  bool touched[9] = {};
-  for (const Patch& e : p) touched[e.layer] = true;
-  for (int i = 0; i < net_.nlayers; i++)
-    if (touched[i]) launch_repack(ds.L[i], net_.is_cnv && i == 0, s);
+  ds.buf_cap = cap;
+  return 0;
 }
 
+int Engine::ensure_lane(DeviceState& ds, int k, int images, std::string& err) {
+  Lane& ln = ds.lane[k];
+  if (images <= ln.cap) return 0;
+  const int cap = round_cap(images);
+  const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
+  CKE(err, cudaStreamSynchronize(ln.copy));
+  CKE(err, cudaStreamSynchronize(ds.compute));
+  void* p;
+  p = ln.d_raw; ds.release(p, (size_t)ln.cap * raw_bytes);
+  p = ln.d_out; ds.release(p, (size_t)ln.cap * net_.out_bytes);
+  p = ln.d_cls; ds.release(p, (size_t)ln.cap * 4);
+  ln.cap = 0;
+  ln.d_raw = (uint8_t*)ds.alloc((size_t)cap * raw_bytes, false);
+  ln.d_out = ds.alloc((size_t)cap * net_.out_bytes, false);
+  ln.d_cls = (int*)ds.alloc((size_t)cap * 4, false);
+  if (!ln.d_raw || !ln.d_out || !ln.d_cls) {
+    cudaFree(ln.d_raw); cudaFree(ln.d_out); cudaFree(ln.d_cls);
+    ln.d_raw = nullptr; ln.d_out = nullptr; ln.d_cls = nullptr;
+    err = "cudaMalloc failed (staging buffers, device " + std::to_string(ds.id) + ")";
+    return -1;
+  }
+  ln.cap = cap;
+  return 0;
+}
+
+int Engine::ensure_patch_cap(DeviceState& ds, size_t count, std::string& err) {
+  if (count <= ds.patch_cap) return 0;
+  CKE(err, cudaStreamSynchronize(ds.compute));
+  void* p = ds.d_patches;
+  ds.release(p, ds.patch_cap * sizeof(DevPatch));
+  ds.d_patches = nullptr;
+  ds.patch_cap = 0;
+  const size_t cap = std::max<size_t>(64, count * 2);
+  ds.d_patches = (DevPatch*)ds.alloc(cap * sizeof(DevPatch), false);
+  if (!ds.d_patches) { err = "cudaMalloc failed (fault patches, device " + std::to_string(ds.id) + ")"; return -1; }
+  ds.patch_cap = cap;
+  return 0;
+}
+
+// Faults outside an inference call (bnnb_inject_fault, bnnb_mem_set): every device that holds parameters patches its operands in
+// place; a device that is not in use yet takes the mirror (which already holds the fault) when it is first used.
 int Engine::apply_patches(const std::vector<Patch>& patches) {
   if (patches.empty()) return 0;
   if (ensure_devices() != 0) return -1;
+  static_assert(sizeof(Patch) == sizeof(DevPatch), "Patch and DevPatch must share a layout");
   for (auto& d : dev_) {
+    if (!d->ready) continue;
     CK(cudaSetDevice(d->id));
-    if (!d->uploaded) continue;
-    for (auto& ln : d->lane) CK(cudaStreamSynchronize(ln.s));
-    enqueue_patches(*d, patches, d->lane[0].s);
-    CK(cudaStreamSynchronize(d->lane[0].s));  // the host vector may die after return
+    if (ensure_patch_cap(*d, patches.size(), err_) != 0) return -1;
+    CK(cudaMemcpyAsync(d->d_patches, patches.data(), patches.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, d->compute));
+    launch_patch_apply(d->d_layers, net_.is_cnv, d->d_patches, (int)patches.size(), d->compute);
+    CK(cudaStreamSynchronize(d->compute));  // the host vector may die after return
+    CK(cudaGetLastError());
   }
   return 0;
 }
@@ -285,63 +370,91 @@ int Engine::mem_set(unsigned tl, unsigned mem, unsigned ind, unsigned thresh, ui
   return apply_patches({p});
 }
 
-// One chunk through every layer.  Returns the number of kernels launched, or -1.
-int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s,
-                      int32_t* tap_acc, uint32_t** bufs) {
-  const void* cur = d_in;
-  int launches = 0;
-  const bool per_layer = tap_acc != nullptr;  // when tapping, every layer writes its own buffer; else two ping-pong buffers
-  int first_layer = 0;
-  // Activation format between layers (f4_common.cuh): on the fp4 core, between two fp4 kernels of a 1-bit network, the producer
-  // writes e2m1 operand planes in the consumer's own shared-memory layout (the consumer stages them with TMA bulk copies).
-  int fam[9] = {}, ofmt[9] = {};  // kernel family of layer i on this core: 1 = conv_f4, 2 = gemm_f4, 0 = other
-  if (core_ == 2 && !per_layer)
+// Kernel family and activation interchange format per layer (f4_common.cuh): on the fp4 core, between two fp4 kernels of a 1-bit
+// network, the producer writes e2m1 operand planes in the consumer's own shared-memory layout (staged there by TMA bulk copies).
+// per_layer: the LOP3+POPC taps (every layer on the CUDA-core kernels, bit planes everywhere).
+void Engine::plan_formats(const DeviceState& ds, bool per_layer, bool tensor_taps, int* fam, int* ofmt, bool* fused01) const {
+  const bool popc_only = per_layer && !tensor_taps;
+  for (int i = 0; i < 9; i++) { fam[i] = 0; ofmt[i] = ACT_BITS; }
+  if (core_ == 2 && !popc_only)
     for (int i = 0; i < net_.nlayers; i++) fam[i] = conv_f4_supports(net_.L[i]) ? 1 : (gemm_f4_supports(ds.L[i]) ? 2 : 0);
-  const bool fused01 = core_ >= 1 && net_.is_cnv && !per_layer && fuse01_;
+  *fused01 = core_ >= 1 && net_.is_cnv && !popc_only && fuse01_;
   for (int i = 0; i + 1 < net_.nlayers; i++) {
     const LayerDesc& p = net_.L[i];
     const LayerDesc& c = net_.L[i + 1];
-    const bool producer_f4 = fam[i] != 0 || (fused01 && i == 1 && core_ == 2);
+    const bool producer_f4 = fam[i] != 0 || (*fused01 && i == 1 && core_ == 2);
     if (!producer_f4 || p.out_mode != OUT_BIT || c.in_mode != IN_XNOR) continue;
-    if (fam[i + 1] == 1 && fam[i] != 2) ofmt[i] = ACT_F4P;                 // conv consumer: image planes
-    if (fam[i + 1] == 2 && !p.pool && !(fused01 && i == 1)) ofmt[i] = ACT_F4T;  // gemm consumer: 128-image tiles
+    if (fam[i + 1] == 1 && fam[i] != 2) ofmt[i] = ACT_F4P;                        // conv consumer: image planes
+    if (fam[i + 1] == 2 && !p.pool && !(*fused01 && i == 1)) ofmt[i] = ACT_F4T;   // gemm consumer: 128-image tiles
   }
-  if (core_ >= 1 && net_.is_cnv && !per_layer && fuse01_) {  // layers 0+1 in one tensor-core kernel
-    ProfEv pe{nullptr, nullptr, 1, ds.id};
+}
+
+// One chunk through every layer.  Returns the number of kernels launched, or -1.
+int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s, TapCtx* tap,
+                      uint32_t** bufs, std::string& err) {
+  const void* cur = d_in;
+  int launches = 0;
+  const bool per_layer = tap != nullptr;  // when tapping, every layer writes its own buffer; else two ping-pong buffers
+  const bool popc_only = per_layer && !tap->tensor;
+  int first_layer = 0;
+  int fam[9], ofmt[9];
+  bool fused01;
+  plan_formats(ds, per_layer, per_layer && tap->tensor, fam, ofmt, &fused01);
+  int32_t* tap_acc = tap ? tap->acc : nullptr;
+  auto take_tap = [&](int i) {  // this layer's slice of the tap buffer
+    int32_t* p = tap_acc;
+    if (tap_acc) tap_acc += (size_t)n * net_.L[i].ofm_dim * net_.L[i].ofm_dim * net_.L[i].N;
+    return p;
+  };
+  auto prof_begin = [&](int layer) {
+    ProfEv pe{nullptr, nullptr, layer, ds.id};
     if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
-    if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, core_ == 2, ofmt[1], ds.d_status, s)) {
-      if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
-      {
-        const cudaError_t le = cudaGetLastError();
-        if (le != cudaSuccess) { err_ = std::string("fused layer 0+1 launch: ") + cudaGetErrorString(le); return -1; }
-      }
+    return pe;
+  };
+  auto prof_end = [&](ProfEv& pe) {
+    if (!profile_) return;
+    cudaEventRecord(pe.b, s);
+    std::lock_guard<std::mutex> lk(prof_mu_);
+    prof_.push_back(pe);
+  };
+  if (fused01) {  // layers 0+1 in one tensor-core kernel
+    Tap01 tp;
+    if (tap) { tp.acc0 = take_tap(0); tp.acc1 = take_tap(1); tp.act0 = tap->act0; }
+    ProfEv pe = prof_begin(1);
+    if (launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)d_in, bufs[1], n, ds.num_sms, core_ == 2, ofmt[1], ds.d_status, tp, s)) {
+      prof_end(pe);
+      const cudaError_t le = cudaGetLastError();
+      if (le != cudaSuccess) { err = std::string("fused layer 0+1 launch: ") + cudaGetErrorString(le); return -1; }
       launches++;
       cur = bufs[1];
       first_layer = 2;
-    } else if (profile_) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
+      if (tap) { tap->fused01 = true; tap->raw[0] = tap->raw[1] = 1; tap->ofmt[0] = ACT_BITS; tap->ofmt[1] = ofmt[1]; }
+    } else {
+      if (profile_) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
+      if (tap) { tap_acc = tap->acc; }
+      fused01 = false;
+    }
   }
   for (int i = first_layer; i < net_.nlayers; i++) {
     const bool last = i == net_.nlayers - 1;
     uint32_t* out = last ? (uint32_t*)d_out : bufs[per_layer ? i : (i & 1)];
-    int32_t* tp = nullptr;
-    if (tap_acc) {
-      tp = tap_acc;
-      tap_acc += (size_t)n * net_.L[i].ofm_dim * net_.L[i].ofm_dim * net_.L[i].N;
-    }
-    ProfEv pe{nullptr, nullptr, i, ds.id};
-    if (profile_) { cudaEventCreate(&pe.a); cudaEventCreate(&pe.b); cudaEventRecord(pe.a, s); }
-    if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s);
-    else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, i > 0 ? ofmt[i - 1] : ACT_BITS, ofmt[i], ds.d_status, s)) {}
-    else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, i > 0 ? ofmt[i - 1] : ACT_BITS, ofmt[i], ds.d_status, s)) {}
-    else if (core_ >= 1 && !tp && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
-    else if (core_ >= 1 && !tp && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, s)) {}
-    else if ((i > 0 && ofmt[i - 1] != ACT_BITS) || ofmt[i] != ACT_BITS) { err_ = "layer " + std::to_string(i) + ": no kernel for the planned activation format"; return -1; }
-    else launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s);
-    if (profile_) { cudaEventRecord(pe.b, s); prof_.push_back(pe); }
+    int32_t* tp = take_tap(i);
+    const int ifmt = i > 0 ? ofmt[i - 1] : ACT_BITS;
+    int raw = 1;
+    ProfEv pe = prof_begin(i);
+    if (net_.is_cnv && i == 0) { launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s); raw = 0; }
+    else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], ds.d_status, tp, s)) {}
+    else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], ds.d_status, tp, s)) {}
+    else if (core_ >= 1 && !popc_only && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, tp, s)) {}
+    else if (core_ >= 1 && !popc_only && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, tp, s)) {}
+    else if (ifmt != ACT_BITS || ofmt[i] != ACT_BITS) { err = "layer " + std::to_string(i) + ": no kernel for the planned activation format"; return -1; }
+    else { launch_layer_popc(ds.L[i], (const uint32_t*)cur, out, n, tp, ds.num_sms, s); raw = 0; }
+    prof_end(pe);
     {  // a launch that the device refuses (resources, configuration) must not pass silently
       const cudaError_t le = cudaGetLastError();
-      if (le != cudaSuccess) { err_ = "layer " + std::to_string(i) + " launch: " + cudaGetErrorString(le); return -1; }
+      if (le != cudaSuccess) { err = "layer " + std::to_string(i) + " launch: " + cudaGetErrorString(le); return -1; }
     }
+    if (tap) { tap->raw[i] = raw; tap->ofmt[i] = last ? ACT_BITS : ofmt[i]; }
     launches++;
     cur = out;
   }
@@ -355,13 +468,15 @@ int Engine::infer_device(int slot, const void* d_in, int n, void* d_out, int* d_
   if (slot < 0 || slot >= (int)dev_.size()) { err_ = "bad device slot"; return -1; }
   DeviceState& ds = *dev_[slot];
   CK(cudaSetDevice(ds.id));
-  cudaStream_t s = stream ? stream : ds.lane[0].s;
+  if (!ds.ready && upload(ds, err_) != 0) return -1;
+  cudaStream_t s = stream ? stream : ds.compute;
   const int chunk = chunk_images();
+  if (n > 0 && ensure_buffers(ds, std::min(chunk, n), err_) != 0) return -1;
   int launches = 0;
   for (int off = 0; off < n; off += chunk) {
     const int c = std::min(chunk, n - off);
     const int r = run_chunk(ds, (const uint8_t*)d_in + (size_t)off * net_.in_bytes, c, (uint8_t*)d_out + (size_t)off * net_.out_bytes,
-                            d_classes ? d_classes + off : nullptr, ncls, s, nullptr, ds.lane[0].buf);
+                            d_classes ? d_classes + off : nullptr, ncls, s, nullptr, ds.act, err_);
     if (r < 0) return -1;
     launches += r;
   }
@@ -375,7 +490,9 @@ int Engine::prep_device(int slot, const void* d_raw, int n, void* d_in, cudaStre
   if (slot < 0 || slot >= (int)dev_.size()) { err_ = "bad device slot"; return -1; }
   DeviceState& ds = *dev_[slot];
   CK(cudaSetDevice(ds.id));
-  cudaStream_t s = stream ? stream : ds.lane[0].s;
+  if (!ds.ready && loaded_ && upload(ds, err_) != 0) return -1;
+  cudaStream_t s = stream ? stream : ds.compute;
+  if (!s) { err_ = "load_parameters has not been called"; return -1; }
   if (net_.is_cnv) launch_prep_cifar((const uint8_t*)d_raw, (int8_t*)d_in, n, s);
   else launch_prep_mnist((const uint8_t*)d_raw, (uint32_t*)d_in, n, s);
   CK(cudaGetLastError());
@@ -384,9 +501,13 @@ int Engine::prep_device(int slot, const void* d_raw, int n, void* d_in, cudaStre
 
 int Engine::sync(int slot) {
   if (slot < 0 || slot >= (int)dev_.size()) { err_ = "bad device slot"; return -1; }
-  CK(cudaSetDevice(dev_[slot]->id));
-  for (auto& ln : dev_[slot]->lane) CK(cudaStreamSynchronize(ln.s));
-  return 0;
+  DeviceState& ds = *dev_[slot];
+  if (!ds.ready) return 0;
+  CK(cudaSetDevice(ds.id));
+  // the device-resident path may run on the caller's stream: wait for the whole device, then read the status flag
+  CK(cudaDeviceSynchronize());
+  CK(cudaGetLastError());
+  return check_status(ds, err_);
 }
 
 // LFC class decode, multi-image rule (foldedmv-offload.cpp:202-220): (unsigned) log2(word & mask), 0 when no bit is set.
@@ -400,71 +521,152 @@ static int lfc_class_multi(uint64_t w, int ncls) {
   return (int)(unsigned)std::log2((double)w);
 }
 
+// One device's shard [lo, hi): copy lanes feed the in-order compute stream; with `seg`, chunks never cross a fault time and the
+// patches of an epoch are applied (in place, k_patch_apply) on the compute stream between them.
+int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, int16_t* scores, uint64_t* words,
+                      const Segments* seg, float* dev_ms, float* last_ms, int* last_imgs, std::string& err) {
+  DeviceState& ds = *dev_[g];
+  CKE(err, cudaSetDevice(ds.id));
+  if (!ds.ready && upload(ds, err) != 0) return -1;
+  const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
+  const int chunk = chunk_images(true), cnt = hi - lo;
+  cudaStream_t cs = ds.compute;
+  if (cnt > 0 && ensure_buffers(ds, std::min(chunk, cnt), err) != 0) return -1;
+  for (auto& ln : ds.lane) { ln.used = false; ln.pend_off = -1; }
+  size_t pi = 0;
+  if (seg && !seg->patches.empty()) {
+    if (ensure_patch_cap(ds, seg->patches.size(), err) != 0) return -1;
+    CKE(err, cudaMemcpyAsync(ds.d_patches, seg->patches.data(), seg->patches.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, cs));
+  }
+  auto apply_upto = [&](uint32_t t_incl) {  // patches with time <= t_incl
+    if (!seg) return;
+    const size_t b = pi;
+    while (pi < seg->patches.size() && seg->ptime[pi] <= t_incl) pi++;
+    if (pi > b) launch_patch_apply(ds.d_layers, net_.is_cnv, ds.d_patches + b, (int)(pi - b), cs);
+  };
+  auto flush_lane = [&](Lane& ln) -> int {  // results of the lane's chunk in flight -> host
+    if (ln.pend_off < 0) return 0;
+    const int off = ln.pend_off, c = ln.pend_n;
+    CKE(err, cudaStreamWaitEvent(ln.copy, ln.done, 0));
+    if (net_.is_cnv) {
+      if (scores) CKE(err, cudaMemcpyAsync(scores + (size_t)off * 64, ln.d_out, (size_t)c * 128, cudaMemcpyDeviceToHost, ln.copy));
+      if (classes) CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.copy));
+    } else if (words) {
+      CKE(err, cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.copy));
+    }
+    CKE(err, cudaEventRecord(ln.d2h, ln.copy));
+    ln.pend_off = -1;
+    return 0;
+  };
+  // timing events: every chunk without faults (usec = kernel time of the whole call), the last chunk only with faults
+  size_t tused = 0;
+  auto timing_pair = [&](cudaEvent_t* a, cudaEvent_t* b) -> int {
+    while (ds.tev.size() < tused + 2) {
+      cudaEvent_t e;
+      CKE(err, cudaEventCreate(&e));
+      ds.tev.push_back(e);
+    }
+    *a = ds.tev[tused]; *b = ds.tev[tused + 1];
+    tused += 2;
+    return 0;
+  };
+  struct Timed { cudaEvent_t a, b; int n; };
+  std::vector<Timed> timed;
+  int cur = lo, ci = 0;
+  while (cur < hi) {
+    apply_upto((uint32_t)cur);
+    int nxt = hi;
+    if (seg && pi < seg->patches.size() && (long long)seg->ptime[pi] < (long long)hi) nxt = (int)seg->ptime[pi];
+    while (cur < nxt) {  // [cur, nxt): one parameter set
+      const int rem = nxt - cur;
+      // The copy engine is the bottleneck of this path (3 073 B per image over PCIe): only the compute of the LAST chunk is not
+      // hidden behind a copy, so the tail of a shard is cut into halves (full chunks elsewhere keep the kernels efficient).
+      int c = std::min(chunk, rem);
+      if (nxt == hi && rem <= chunk + chunk / 2 && rem > 4096) c = std::min(chunk, (rem / 2 + 1023) / 1024 * 1024);
+      Lane& ln = ds.lane[ci % kLanes];
+      if (flush_lane(ln) != 0) return -1;
+      if (ensure_lane(ds, ci % kLanes, c, err) != 0) return -1;
+      if (ln.used) CKE(err, cudaStreamWaitEvent(ln.copy, ln.prep_done, 0));  // the prep kernel of the lane's previous chunk has read d_raw
+      CKE(err, cudaMemcpyAsync(ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.copy));
+      CKE(err, cudaEventRecord(ln.copied, ln.copy));
+      CKE(err, cudaStreamWaitEvent(cs, ln.copied, 0));
+      if (ln.used) CKE(err, cudaStreamWaitEvent(cs, ln.d2h, 0));             // d_out / d_cls of the previous chunk have left
+      if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ds.d_in, c, cs);
+      else launch_prep_mnist(ln.d_raw, (uint32_t*)ds.d_in, c, cs);
+      CKE(err, cudaEventRecord(ln.prep_done, cs));
+      const bool time_it = !seg || (cur + c == hi);
+      Timed t{nullptr, nullptr, c};
+      if (time_it) { if (timing_pair(&t.a, &t.b) != 0) return -1; CKE(err, cudaEventRecord(t.a, cs)); }
+      if (run_chunk(ds, ds.d_in, c, ln.d_out, (net_.is_cnv && classes) ? ln.d_cls : nullptr, ncls, cs, nullptr, ds.act, err) < 0) return -1;
+      if (time_it) { CKE(err, cudaEventRecord(t.b, cs)); timed.push_back(t); }
+      CKE(err, cudaEventRecord(ln.done, cs));
+      ln.used = true;
+      ln.pend_off = cur; ln.pend_n = c;
+      cur += c;
+      ci++;
+    }
+  }
+  apply_upto(0xffffffffu);  // faults scheduled at or after this shard's end still persist on this device
+  for (auto& ln : ds.lane) if (flush_lane(ln) != 0) return -1;
+  for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.copy));
+  CKE(err, cudaStreamSynchronize(cs));
+  CKE(err, cudaGetLastError());
+  if (check_status(ds, err) != 0) return -1;
+  float total = 0;
+  for (size_t i = 0; i < timed.size(); i++) {
+    float ms = 0;
+    CKE(err, cudaEventElapsedTime(&ms, timed[i].a, timed[i].b));
+    total += ms;
+    if (i + 1 == timed.size()) { *last_ms = ms; *last_imgs = timed[i].n; }
+  }
+  *dev_ms = total;
+  return 0;
+}
+
+int Engine::run_sharded(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, const Segments* seg,
+                        float* dev_ms_max, float* last_ms, int* last_imgs) {
+  const int G = (int)dev_.size();
+  // contiguous shards [g*n/Gs, (g+1)*n/Gs): SURVEY 8(e); a small batch stays on as few devices as give each kMinShard images
+  const int Gs = std::max(1, std::min(G, n / kMinShard));
+  std::vector<std::string> errs(G);
+  std::vector<int> rc(G, 0);
+  std::vector<float> ms(G, 0.f), lms(G, 0.f);
+  std::vector<int> limg(G, 0);
+  auto work = [&](int g) {
+    const int lo = g < Gs ? (int)((long long)g * n / Gs) : n, hi = g < Gs ? (int)((long long)(g + 1) * n / Gs) : n;
+    rc[g] = run_shard(g, lo, hi, input, ncls, classes, scores, words, seg, &ms[g], &lms[g], &limg[g], errs[g]);
+  };
+  // devices beyond Gs hold no images; with faults they still apply the patch list if they already hold parameters (a device that
+  // is not in use yet takes the mirror, faults included, when it is first used)
+  std::vector<int> active;
+  for (int g = 0; g < G; g++)
+    if (g < Gs || (seg && !seg->patches.empty() && dev_[g]->ready)) active.push_back(g);
+  if (active.size() == 1) {
+    work(active[0]);
+  } else {  // one feeder thread per device: no device waits for the host's attention to another
+    std::vector<std::thread> th;
+    for (int g : active) th.emplace_back(work, g);
+    for (auto& t : th) t.join();
+  }
+  for (int g : active)
+    if (rc[g] != 0) { err_ = errs[g]; return -1; }
+  *dev_ms_max = 0;
+  for (int g : active) *dev_ms_max = std::max(*dev_ms_max, ms[g]);
+  *last_ms = lms[Gs - 1];
+  *last_imgs = limg[Gs - 1];
+  return 0;
+}
+
 int Engine::infer_host(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, float* usec) {
   if (!loaded_) { err_ = "load_parameters has not been called"; return -1; }
   if (ensure_devices() != 0) return -1;
-  for (auto& d : dev_) if (!d->uploaded) { if (upload_all() != 0) return -1; break; }
   if (usec) *usec = 0;
   if (n <= 0) return 0;
-  const int G = (int)dev_.size(), chunk = chunk_images(true);
-  const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
   std::vector<uint64_t> tmp_words;
   if (!net_.is_cnv && !words && classes) { tmp_words.resize(n); words = tmp_words.data(); }
-  struct Timed { int dev, lane; };
-  std::vector<float> dev_ms(G, 0.f);
-  // contiguous shards [g*n/G, (g+1)*n/G): SURVEY 8(e)
-  std::vector<int> pos(G), end(G), nchunk(G, 0);
-  for (int g = 0; g < G; g++) { pos[g] = (int)((long long)g * n / G); end[g] = (int)((long long)(g + 1) * n / G); }
-  bool more = true;
-  while (more) {  // round-robin over devices so that all of them are fed concurrently
-    more = false;
-    for (int g = 0; g < G; g++) {
-      if (pos[g] >= end[g]) continue;
-      DeviceState& ds = *dev_[g];
-      CK(cudaSetDevice(ds.id));
-      Lane& ln = ds.lane[nchunk[g] % kLanes];
-      if (nchunk[g] >= kLanes) {  // the lane's previous chunk must be finished before its events/buffers are reused
-        CK(cudaStreamSynchronize(ln.s));
-        float ms = 0;
-        CK(cudaEventElapsedTime(&ms, ln.e0, ln.e1));
-        dev_ms[g] += ms;
-      }
-      // The copy engine is the bottleneck of this path (3 073 B per image over PCIe): only the compute of the LAST chunk is not
-      // hidden behind a copy, so the tail of a shard is cut into halves (full chunks elsewhere keep the kernels efficient).
-      const int off = pos[g], rem = end[g] - off;
-      const int c = rem > chunk + chunk / 2 ? chunk : (rem > 4096 ? std::min(chunk, (rem / 2 + 1023) / 1024 * 1024) : rem);
-      CK(cudaMemcpyAsync(ln.d_raw, input + (size_t)off * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
-      if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, ln.s);
-      else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, c, ln.s);
-      CK(cudaEventRecord(ln.e0, ln.s));
-      if (run_chunk(ds, ln.d_in, c, ln.d_out, (net_.is_cnv && classes) ? ln.d_cls : nullptr, ncls, ln.s, nullptr, ln.buf) < 0) return -1;
-      CK(cudaEventRecord(ln.e1, ln.s));
-      if (net_.is_cnv) {
-        if (scores) CK(cudaMemcpyAsync(scores + (size_t)off * 64, ln.d_out, (size_t)c * 128, cudaMemcpyDeviceToHost, ln.s));
-        if (classes) CK(cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.s));
-      } else if (words) {
-        CK(cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.s));
-      }
-      pos[g] += c;
-      nchunk[g]++;
-      more = true;
-    }
-  }
-  float worst = 0;
-  for (int g = 0; g < G; g++) {
-    DeviceState& ds = *dev_[g];
-    CK(cudaSetDevice(ds.id));
-    for (int k = 0; k < std::min(nchunk[g], kLanes); k++) {
-      Lane& ln = ds.lane[k];
-      CK(cudaStreamSynchronize(ln.s));
-      float ms = 0;
-      CK(cudaEventElapsedTime(&ms, ln.e0, ln.e1));
-      dev_ms[g] += ms;
-    }
-    CK(cudaGetLastError());
-    if (check_status(g) != 0) return -1;
-    worst = std::max(worst, dev_ms[g]);
-  }
+  float worst = 0, last_ms = 0;
+  int last_imgs = 0;
+  if (run_sharded(input, n, ncls, classes, scores, words, nullptr, &worst, &last_ms, &last_imgs) != 0) return -1;
   if (usec) *usec = worst * 1000.0f / (float)n;
   if (!net_.is_cnv && classes)
     for (int i = 0; i < n; i++) classes[i] = lfc_class_multi(words[i], ncls);
@@ -475,97 +677,37 @@ int Engine::infer_host_with_faults(const uint8_t* input, int n, int ncls, const 
                                    float* usec) {
   if (!loaded_) { err_ = "load_parameters has not been called"; return -1; }
   if (ensure_devices() != 0) return -1;
-  for (auto& d : dev_) if (!d->uploaded) { if (upload_all() != 0) return -1; break; }
   if (usec) *usec = 0;
-  // 1. host: run the whole read-modify-write chain in fault order (it does not depend on inference results)
+  // Every device that will run a shard must hold the PRE-fault parameters before the mirror moves on: it replays the patch list
+  // in stream order between its segments.
+  const int G = (int)dev_.size(), Gs = std::max(1, std::min(G, n / kMinShard));
+  if (n > 0)
+    for (int g = 0; g < Gs; g++)
+      if (!dev_[g]->ready && upload(*dev_[g], err_) != 0) return -1;
+  // host: run the whole read-modify-write chain in fault order (it does not depend on inference results)
   std::vector<Fault> faults = faults_in;
   std::stable_sort(faults.begin(), faults.end(), [](const Fault& a, const Fault& b) { return a.time < b.time; });
-  std::vector<Patch> patches;      // one per effective fault, in order
-  std::vector<uint32_t> ptime;
+  Segments seg;  // one patch per effective fault, in order
   for (const Fault& f : faults) {
     Patch p;
-    if (pm_->inject(f.target, f.layer, f.bit, f.word_size, &p)) { patches.push_back(p); ptime.push_back(f.time); }
+    if (pm_->inject(f.target, f.layer, f.bit, f.word_size, &p)) { seg.patches.push_back(p); seg.ptime.push_back(f.time); }
   }
-  if (n <= 0) return apply_patches(patches);
-  const int G = (int)dev_.size();
-  const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
-  struct Shard { uint8_t* raw = nullptr; void* in = nullptr; void* out = nullptr; int* cls = nullptr; DevPatch* pt = nullptr; int lo = 0, hi = 0; };
-  std::vector<Shard> sh(G);
+  if (n <= 0) return apply_patches(seg.patches);
   std::vector<uint64_t> words;
   if (!net_.is_cnv) words.resize(n);
-  int rc = 0;
-  float last_ms = 0;
-  for (int g = 0; g < G && rc == 0; g++) {
-    DeviceState& ds = *dev_[g];
-    Shard& S = sh[g];
-    S.lo = (int)((long long)g * n / G); S.hi = (int)((long long)(g + 1) * n / G);
-    const int cnt = S.hi - S.lo;
-    CK(cudaSetDevice(ds.id));
-    cudaStream_t s = ds.lane[0].s;
-    for (auto& ln : ds.lane) CK(cudaStreamSynchronize(ln.s));
-    CK(cudaMalloc(&S.raw, std::max<size_t>(16, (size_t)cnt * raw_bytes)));
-    CK(cudaMalloc(&S.in, std::max<size_t>(16, (size_t)cnt * net_.in_bytes)));
-    CK(cudaMalloc(&S.out, std::max<size_t>(16, (size_t)cnt * net_.out_bytes)));
-    CK(cudaMalloc(&S.cls, std::max<size_t>(16, (size_t)cnt * 4)));
-    CK(cudaMalloc(&S.pt, std::max<size_t>(16, patches.size() * sizeof(DevPatch))));
-    if (!patches.empty()) CK(cudaMemcpyAsync(S.pt, patches.data(), patches.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, s));
-    if (cnt > 0) {
-      CK(cudaMemcpyAsync(S.raw, input + (size_t)S.lo * raw_bytes, (size_t)cnt * raw_bytes, cudaMemcpyHostToDevice, s));
-      if (net_.is_cnv) launch_prep_cifar(S.raw, (int8_t*)S.in, cnt, s);
-      else launch_prep_mnist(S.raw, (uint32_t*)S.in, cnt, s);
-    }
-    // 2. epochs: apply every fault with time <= image index before that image (faults.h:138-146)
-    size_t pi = 0;
-    auto apply_upto = [&](uint32_t t_incl) {  // patches with time <= t_incl
-      const size_t b = pi;
-      bool touched[9] = {};
-      while (pi < patches.size() && ptime[pi] <= t_incl) { touched[patches[pi].layer] = true; pi++; }
-      if (pi > b) {
-        launch_patch(ds.folded, S.pt + b, (int)(pi - b), s);
-        for (int i = 0; i < net_.nlayers; i++)
-          if (touched[i]) launch_repack(ds.L[i], net_.is_cnv && i == 0, s);
-      }
-    };
-    int cur = S.lo;
-    const int chunk = chunk_images();
-    while (cur < S.hi) {
-      apply_upto((uint32_t)cur);
-      int nxt = S.hi;
-      if (pi < patches.size() && (long long)ptime[pi] < (long long)S.hi) nxt = (int)ptime[pi];
-      for (int off = cur; off < nxt; off += chunk) {  // segment [cur, nxt) with a fixed parameter set
-        const int c = std::min(chunk, nxt - off);
-        const bool timed = (g == G - 1) && (off + c == S.hi);  // the reference reports the LAST image's time
-        if (timed) CK(cudaEventRecord(ds.lane[0].e0, s));
-        if (run_chunk(ds, (const uint8_t*)S.in + (size_t)(off - S.lo) * net_.in_bytes, c, (uint8_t*)S.out + (size_t)(off - S.lo) * net_.out_bytes,
-                      net_.is_cnv ? S.cls + (off - S.lo) : nullptr, ncls, s, nullptr, ds.lane[0].buf) < 0) return -1;
-        if (timed) CK(cudaEventRecord(ds.lane[0].e1, s));
-      }
-      cur = nxt;
-    }
-    apply_upto(0xffffffffu);  // faults scheduled at or after this shard's end still persist on this device
-    if (cnt > 0) {
-      if (net_.is_cnv) CK(cudaMemcpyAsync(classes + S.lo, S.cls, (size_t)cnt * 4, cudaMemcpyDeviceToHost, s));
-      else CK(cudaMemcpyAsync(words.data() + S.lo, S.out, (size_t)cnt * 8, cudaMemcpyDeviceToHost, s));
-    }
-  }
-  for (int g = 0; g < G; g++) {
-    DeviceState& ds = *dev_[g];
-    cudaSetDevice(ds.id);
-    cudaError_t e = cudaStreamSynchronize(ds.lane[0].s);
-    if (e == cudaSuccess) e = cudaGetLastError();
-    if (e != cudaSuccess) { err_ = cudaGetErrorString(e); rc = -1; }
-    if (g == G - 1 && sh[g].hi > sh[g].lo && rc == 0) cudaEventElapsedTime(&last_ms, ds.lane[0].e0, ds.lane[0].e1);
-    cudaFree(sh[g].raw); cudaFree(sh[g].in); cudaFree(sh[g].out); cudaFree(sh[g].cls); cudaFree(sh[g].pt);
-  }
-  if (rc != 0) return rc;
+  float worst = 0, last_ms = 0;
+  int last_imgs = 0;
+  if (run_sharded(input, n, ncls, classes, nullptr, net_.is_cnv ? nullptr : words.data(), &seg, &worst, &last_ms, &last_imgs) != 0) return -1;
   if (!net_.is_cnv)
     for (int i = 0; i < n; i++) classes[i] = lfc_class_multi(words[i], ncls);
-  if (usec) *usec = last_ms * 1000.0f;
+  // the reference reports the time of its LAST single-image call: device time per image of the last segment
+  if (usec) *usec = last_imgs > 0 ? last_ms * 1000.0f / (float)last_imgs : 0.f;
   return 0;
 }
 
 int Engine::profile_collect(float* ms, int* launches) {
   for (int i = 0; i < 10; i++) { ms[i] = 0; launches[i] = 0; }
+  std::lock_guard<std::mutex> lk(prof_mu_);
   for (auto& e : prof_) {
     cudaSetDevice(e.dev);
     cudaEventSynchronize(e.b);
@@ -589,75 +731,144 @@ size_t Engine::tap_act_size() const {
   return s;
 }
 
+// #(-1) weights of every logical row of a 1-bit-weight layer, from the host mirror in the reference's folded coordinates
+// (row = nf*PE + pe, tile = nf*SF + sf: mvau.hpp:115,143-152): what turns an MMA sum over {0,1} activations into the reference's
+// XNOR-popcount accumulator (interpret.hpp:57-69).
+std::vector<int> Engine::row_neg_counts(int layer) const {
+  const LayerDesc& l = net_.L[layer];
+  std::vector<int> neg(l.N, 0);
+  const int SF = l.K / l.simd;
+  const uint64_t mask = l.simd >= 64 ? ~0ull : ((1ull << l.simd) - 1);
+  for (int n = 0; n < l.N; n++) {
+    const int pe = n % l.pe, nf = n / l.pe;
+    for (int sf = 0; sf < SF; sf++) neg[n] += l.simd - __builtin_popcountll(pm_->weights(layer)[(size_t)pe * l.wmem + nf * SF + sf] & mask);
+  }
+  return neg;
+}
+
+// e2m1 code of one activation -> value.  fold: the fused kernel's layer-0 epilogue writes a set decision as 0xF (-6.0, see cnv01_tc.cu)
+static inline int8_t e2m1_act(uint32_t code, bool fold) {
+  if (fold) return code ? 1 : 0;
+  return code == 0x2 ? 1 : (code == 0xA ? -1 : 0);
+}
+
 int Engine::tap_host(const uint8_t* input, int n, int32_t* acc, int8_t* act) {
   if (!loaded_) { err_ = "load_parameters has not been called"; return -1; }
   if (ensure_devices() != 0) return -1;
   DeviceState& ds = *dev_[0];
   CK(cudaSetDevice(ds.id));
-  if (!ds.uploaded && upload_all() != 0) return -1;
-  cudaStream_t s = ds.lane[0].s;
+  if (!ds.ready && upload(ds, err_) != 0) return -1;
+  cudaStream_t s = ds.compute;
   const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
   const size_t sa = tap_acc_size(), st = tap_act_size();
-  const int step = 16;
-  uint8_t* d_raw; void* d_in; int32_t* d_acc; uint32_t* bufs[9];
-  CK(cudaMalloc(&d_raw, step * raw_bytes));
-  CK(cudaMalloc(&d_in, (size_t)step * net_.in_bytes));
-  CK(cudaMalloc(&d_acc, (size_t)step * sa * 4));
-  std::vector<size_t> words(net_.nlayers);
-  for (int i = 0; i < net_.nlayers; i++) {
+  const int step = 16, NL = net_.nlayers;
+  struct Bufs {  // freed on every path out
+    std::vector<void*> v;
+    ~Bufs() { for (void* p : v) cudaFree(p); }
+    void* get(size_t bytes) { void* p = nullptr; if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) return nullptr; v.push_back(p); return p; }
+  } B;
+  uint8_t* d_raw = (uint8_t*)B.get(step * raw_bytes);
+  void* d_in = B.get((size_t)step * net_.in_bytes);
+  int32_t* d_acc = (int32_t*)B.get((size_t)step * sa * 4);
+  uint4* d_act0 = (uint4*)B.get((size_t)step * 900 * 4 * 16);
+  uint32_t* bufs[9];
+  std::vector<size_t> bytes(NL);
+  bool ok = d_raw && d_in && d_acc && d_act0;
+  for (int i = 0; i < NL; i++) {
     const LayerDesc& l = net_.L[i];
-    words[i] = (size_t)out_dim(l) * out_dim(l) * out_words_per_pixel(l);
-    CK(cudaMalloc(&bufs[i], step * words[i] * 4));
+    const size_t px = (size_t)out_dim(l) * out_dim(l);
+    bytes[i] = 128 * std::max(px * out_words_per_pixel(l) * 4, px * l.N / 2);  // any format, one 128-image tile
+    bufs[i] = (uint32_t*)B.get(bytes[i]);
+    ok = ok && bufs[i];
   }
+  if (!ok) { err_ = "cudaMalloc failed (tap buffers)"; return -1; }
+  std::vector<std::vector<int>> neg(NL);
+  for (int i = 0; i < NL; i++)
+    if (net_.L[i].in_mode == IN_XNOR) neg[i] = row_neg_counts(i);
   std::vector<int32_t> hacc((size_t)step * sa);
-  std::vector<uint32_t> hbuf;
+  std::vector<uint8_t> hbuf;
+  std::vector<uint4> hact0((size_t)step * 900 * 4);
   for (int off = 0; off < n; off += step) {
     const int c = std::min(step, n - off);
     CK(cudaMemcpyAsync(d_raw, input + (size_t)off * raw_bytes, c * raw_bytes, cudaMemcpyHostToDevice, s));
     if (net_.is_cnv) launch_prep_cifar(d_raw, (int8_t*)d_in, c, s);
     else launch_prep_mnist(d_raw, (uint32_t*)d_in, c, s);
-    if (run_chunk(ds, d_in, c, bufs[net_.nlayers - 1], nullptr, 10, s, d_acc, bufs) < 0) return -1;
+    for (int i = 0; i < NL; i++) CK(cudaMemsetAsync(bufs[i], 0, bytes[i], s));
+    TapCtx tap;
+    tap.acc = d_acc;
+    tap.act0 = d_act0;
+    tap.tensor = core_ >= 1;
+    if (run_chunk(ds, d_in, c, bufs[NL - 1], nullptr, 10, s, &tap, bufs, err_) < 0) return -1;
     CK(cudaMemcpyAsync(hacc.data(), d_acc, (size_t)c * sa * 4, cudaMemcpyDeviceToHost, s));
+    if (tap.fused01) CK(cudaMemcpyAsync(hact0.data(), d_act0, (size_t)c * 900 * 4 * 16, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     CK(cudaGetLastError());
-    // device accumulators are layer-major over the chunk; the API is image-major
+    if (check_status(ds, err_) != 0) return -1;
+    // accumulators: device buffer is layer-major over the chunk, the API image-major.  A tensor-core kernel reports its MMA sum S:
+    // CNV layer 0: S = sum w*q, the reference accumulates 2q in ap_fixed<24,16> (top.cpp:61,214) -> 2S; 1-bit layers: S runs over
+    // {0,1} activations, the reference counts XNOR matches = S + #(-1 weights of the row); ternary / +-1 inputs: S itself.
     size_t lo = 0, io = 0;
-    for (int i = 0; i < net_.nlayers; i++) {
+    for (int i = 0; i < NL; i++) {
       const LayerDesc& l = net_.L[i];
-      const size_t per = (size_t)l.ofm_dim * l.ofm_dim * l.N;
-      for (int k = 0; k < c; k++) std::memcpy(acc + (size_t)(off + k) * sa + io, hacc.data() + lo + (size_t)k * per, per * 4);
+      const size_t rows = (size_t)l.ofm_dim * l.ofm_dim, per = rows * l.N;
+      for (int k = 0; k < c; k++) {
+        int32_t* dst = acc + (size_t)(off + k) * sa + io;
+        const int32_t* src = hacc.data() + lo + (size_t)k * per;
+        if (!tap.raw[i]) { std::memcpy(dst, src, per * 4); continue; }
+        for (size_t r = 0; r < rows; r++)
+          for (int ch = 0; ch < l.N; ch++) {
+            const int32_t S = src[r * l.N + ch];
+            dst[r * l.N + ch] = l.in_mode == IN_FIX8 ? 2 * S : (l.in_mode == IN_XNOR ? S + neg[i][ch] : S);
+          }
+      }
       lo += (size_t)c * per;
       io += per;
     }
+    // layer outputs, decoded from the format each kernel wrote
     size_t ao = 0;
-    for (int i = 0; i < net_.nlayers; i++) {
+    for (int i = 0; i < NL; i++) {
       const LayerDesc& l = net_.L[i];
-      const int px = out_dim(l) * out_dim(l), nw = l.N / 32;
-      hbuf.resize((size_t)c * words[i]);
-      CK(cudaMemcpy(hbuf.data(), bufs[i], (size_t)c * words[i] * 4, cudaMemcpyDeviceToHost));
+      const int px = out_dim(l) * out_dim(l), nw = l.N / 32, wpp = out_words_per_pixel(l);
+      const bool from_act0 = tap.fused01 && i == 0;
+      if (!from_act0) {
+        hbuf.resize(bytes[i]);
+        CK(cudaMemcpy(hbuf.data(), bufs[i], bytes[i], cudaMemcpyDeviceToHost));
+      }
+      const uint32_t* hw = reinterpret_cast<const uint32_t*>(hbuf.data());
+      const uint4* h4 = reinterpret_cast<const uint4*>(hbuf.data());
       for (int k = 0; k < c; k++)
         for (int p = 0; p < px; p++)
           for (int ch = 0; ch < l.N; ch++) {
             int8_t v;
-            const uint32_t* w = hbuf.data() + (size_t)k * words[i] + (size_t)p * out_words_per_pixel(l);
-            if (l.out_mode == OUT_SCORE) v = (int8_t)reinterpret_cast<const int16_t*>(w)[ch];
-            else if (l.out_mode == OUT_BIT) v = (w[ch >> 5] >> (ch & 31)) & 1;
-            else { const int nz = (w[ch >> 5] >> (ch & 31)) & 1, ps = (w[nw + (ch >> 5)] >> (ch & 31)) & 1; v = nz ? (ps ? 1 : -1) : 0; }
+            if (from_act0) {
+              const uint4* row = hact0.data() + ((size_t)k * 900 + p) * 4;
+              if (core_ == 2) {  // e2m1 codes, 32 channels per uint4 (entries 0 and 2); 1-bit nets: FOLD nibble order and code 0xF
+                const bool fold = l.out_mode == OUT_BIT;
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(&row[2 * (ch >> 5)]);
+                const int c32 = ch & 31, wi = c32 >> 3, e = c32 & 7;
+                const int nib = fold ? ((e & 3) * 2 + (e >> 2)) : e;  // FOLD: nibble 2k = channel k, nibble 2k+1 = channel 4+k
+                v = e2m1_act((w[wi] >> (4 * nib)) & 0xF, fold);
+              } else {           // int8 operands, 16 channels per uint4
+                v = reinterpret_cast<const int8_t*>(&row[ch >> 4])[ch & 15];
+              }
+            } else if (tap.ofmt[i] == ACT_F4P) {   // uint4 [img][plane][pixel]
+              const uint32_t* w = reinterpret_cast<const uint32_t*>(&h4[((size_t)k * nw + (ch >> 5)) * px + p]);
+              v = e2m1_act((w[(ch & 31) >> 3] >> (4 * (ch & 7))) & 0xF, false);
+            } else if (tap.ofmt[i] == ACT_F4T) {   // uint4 [img/128][chunk = pixel*C/32 + plane][img%128]
+              const uint32_t* w = reinterpret_cast<const uint32_t*>(&h4[((size_t)(k >> 7) * (px * nw) + (size_t)(p * nw + (ch >> 5))) * 128 + (k & 127)]);
+              v = e2m1_act((w[(ch & 31) >> 3] >> (4 * (ch & 7))) & 0xF, false);
+            } else {
+              const uint32_t* w = hw + ((size_t)k * px + p) * wpp;
+              if (l.out_mode == OUT_SCORE) v = (int8_t)reinterpret_cast<const int16_t*>(w)[ch];
+              else if (l.out_mode == OUT_BIT) v = (w[ch >> 5] >> (ch & 31)) & 1;
+              else { const int nz = (w[ch >> 5] >> (ch & 31)) & 1, ps = (w[nw + (ch >> 5)] >> (ch & 31)) & 1; v = nz ? (ps ? 1 : -1) : 0; }
+            }
             act[(size_t)(off + k) * st + ao + (size_t)p * l.N + ch] = v;
           }
       ao += (size_t)px * l.N;
     }
   }
-  cudaFree(d_raw); cudaFree(d_in); cudaFree(d_acc);
-  for (int i = 0; i < net_.nlayers; i++) cudaFree(bufs[i]);
   return 0;
 }
-
-void* Engine::alloc_pinned(size_t bytes) {
-  void* p = nullptr;
-  if (cudaHostAlloc(&p, bytes ? bytes : 16, cudaHostAllocPortable) != cudaSuccess) return nullptr;
-  return p;
-}
-void Engine::free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
 }  // namespace bnnb

@@ -1,5 +1,6 @@
-// The CUDA runtime behind the C ABI: per-device replicated parameters, activation buffers sized to stay L2-resident,
-// stream-ordered fault epochs, and contiguous sharding of an image batch over the visible GPUs (no collective).
+// The CUDA runtime behind the C ABI: per-device replicated parameters, one in-order compute stream and a few copy lanes per
+// device, activation buffers grown on demand, stream-ordered fault epochs with in-place operand patches, and contiguous sharding
+// of an image batch over the visible GPUs (no collective; one feeder thread per device).
 // Replaces the host library's accelerator glue: FoldedMVInit/Deinit, FoldedMVOffloadBinarized (rawhls-offload.cpp:54-94),
 // testPrebuiltCIFAR10_multiple_images / _from_image (foldedmv-offload.h:316-416),
 // testPrebinarized_nolabel(_multiple_images) (foldedmv-offload.cpp:114-224) and BlackBoxJam's dispatch (top.cpp:238-291).
@@ -7,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 #include "kernels.cuh"
@@ -16,6 +18,7 @@
 namespace bnnb {
 
 struct DeviceState;
+struct TapCtx;
 
 class Engine {
  public:
@@ -31,15 +34,23 @@ class Engine {
   int load_parameters(const std::string& dir);
   bool loaded() const { return loaded_; }
   ParamMirror& mirror() { return *pm_; }
+  // Frees every device allocation (parameters, buffers, streams).  The host mirror - parameters and injected faults - is kept, so
+  // the next call re-creates the device state on demand: what deinit() needs (FoldedMVDeinit frees buffers while the parameters
+  // survive in static memories, rawhls-offload.cpp:69-74, top.cpp:51-68; every entry point re-initialises, main_python.cpp:126).
+  int release();
+  // Bytes currently allocated on device slot `slot` (tests: footprint of small calls).
+  size_t device_bytes(int slot) const;
 
   // Host-buffer inference.  `input`: CNV n x 3073-byte CIFAR records, LFC n x 784 pixel bytes.
   // classes (n, multi-image rule) / scores (CNV: n x 64 int16) / words (LFC: n x uint64) may be null.
-  // usec_per_image: device time of the inference kernels only, max over devices (the reference's timed region,
-  // foldedmv-offload.h:389-392), measured with CUDA events on the launching streams.
+  // usec_per_image: device time of the inference kernels only (the reference's timed region, foldedmv-offload.h:389-392): per
+  // device the sum of the CUDA-event durations of its chunks on its in-order compute stream, max over devices, / n.
+  // Batches are sharded in contiguous ranges over the devices, but never thinner than kMinShard images per device.
   int infer_host(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, float* usec_per_image);
 
   // Same, with faults applied between image segments ("epochs"): every fault with time i is applied before image i,
   // cumulatively, and they persist afterwards (faults.h:115-148).  All devices apply every fault; each runs only its shard.
+  // usec_per_image: device time per image of the last segment (the reference reports its last single-image call).
   int infer_host_with_faults(const uint8_t* input, int n, int ncls, const std::vector<Fault>& faults, int* classes,
                              float* usec_per_image);
 
@@ -49,12 +60,15 @@ class Engine {
   int infer_device(int slot, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t stream);
   // raw records / pixels (device) -> layer-0 input (device)
   int prep_device(int slot, const void* d_raw, int n, void* d_in, cudaStream_t stream);
+  // Waits for the slot's streams and reports a kernel that gave up waiting on an mbarrier (device status flag) as an error.
   int sync(int slot);
   // Number of kernels the last infer_device call enqueued (per call; for bench.py's gpu_launches).
   int last_launches() const { return last_launches_; }
 
-  // Debug taps for parity tests: per image, concatenated over layers, int32 accumulators [ofm^2][N] and the layer outputs
-  // after pooling as int8 values [out_dim^2][N] (last CNV layer: low 8 bits of the score).
+  // Debug taps for parity tests, ON THE SELECTED CORE: per image, concatenated over layers, int32 accumulators [ofm^2][N] (the
+  // reference's accumulator values) and the layer outputs after pooling as int8 values [out_dim^2][N] (last CNV layer: low 8 bits
+  // of the score).  Core 0: the LOP3+POPC kernels.  Cores 1 / 2: the TAP instantiations of the tensor-core kernels that ship
+  // (same source, extra stores), run with the production activation formats; outputs are decoded from those formats.
   int tap_host(const uint8_t* input, int n, int32_t* acc, int8_t* act);
   size_t tap_acc_size() const;
   size_t tap_act_size() const;
@@ -74,20 +88,28 @@ class Engine {
   // 2 (default) = tcgen05 kind::mxf4 (exact fp4) where instantiated, else kind::i8, else LOP3+POPC.
   void set_core(int c) { core_ = c; }
   int core() const { return core_; }
-  int check_status(int slot);
 
-  void* alloc_pinned(size_t bytes);
-  void free_pinned(void* p);
+  static constexpr int kMinShard = 2048;  // images: below this a device is not worth its launch latency
 
  private:
+  struct Segments;  // fault epochs of one call
   int ensure_devices();
-  int upload_all();
-  int apply_patches(const std::vector<Patch>& patches);                 // all devices, stream-ordered
-  void enqueue_patches(DeviceState& ds, const std::vector<Patch>& p, cudaStream_t s);
-  int run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s,
-                int32_t* tap_acc, uint32_t** bufs);
+  int upload(DeviceState& ds, std::string& err);
+  int check_status(DeviceState& ds, std::string& err);
+  int apply_patches(const std::vector<Patch>& patches);                 // all uploaded devices, stream-ordered
+  int ensure_buffers(DeviceState& ds, int images, std::string& err);    // d_in + activation ping-pong for `images` per chunk
+  int ensure_lane(DeviceState& ds, int lane, int images, std::string& err);
+  int ensure_patch_cap(DeviceState& ds, size_t count, std::string& err);
+  void plan_formats(const DeviceState& ds, bool per_layer, bool tensor_taps, int* fam, int* ofmt, bool* fused01) const;
+  int run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s, TapCtx* tap,
+                uint32_t** bufs, std::string& err);
+  int run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, int16_t* scores, uint64_t* words,
+                const Segments* seg, float* dev_ms, float* last_ms, int* last_imgs, std::string& err);
+  int run_sharded(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, const Segments* seg,
+                  float* dev_ms_max, float* last_ms, int* last_imgs);
   int chunk_images(bool host = false) const;
-  bool fail(const std::string& m) { err_ = m; return false; }
+  size_t act_bytes(int images) const;
+  std::vector<int> row_neg_counts(int layer) const;  // #(-1) weights per logical row, from the host mirror (taps)
 
   NetDesc net_;
   std::unique_ptr<ParamMirror> pm_;
@@ -100,6 +122,7 @@ class Engine {
   bool fuse01_ = true;
   struct ProfEv { cudaEvent_t a, b; int layer, dev; };
   std::vector<ProfEv> prof_;
+  std::mutex prof_mu_;
   std::string err_;
 };
 

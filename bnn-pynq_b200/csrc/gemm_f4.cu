@@ -55,9 +55,9 @@ struct GemmGeom {
   int a_bytes, off_ring, off_thr, ring;  // ring = slots of the weight ring (GG slabs each)
 };
 
-template <int NB, int INM, int OUTM>
+template <int NB, int INM, int OUTM, bool TAP>
 __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
-                                                     int in_fmt, int out_fmt, int* __restrict__ status) {
+                                                     int in_fmt, int out_fmt, int* __restrict__ status, int32_t* __restrict__ tap) {
   constexpr int SLAB = NB * 32, SLOTS = 3, SF_COL = 384, NW = NB / 32, EXP = 192, U = 4;  // EXP expander threads, U loads in flight each
   constexpr bool FOLD = OUTM == OUT_BIT;
   constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
@@ -289,6 +289,11 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
           }
           b0[j] = w0;
           b1[j] = w1;
+          if (TAP && img < n_img) {  // parity taps (TAP instantiation only): the MMA sum of every channel, pre-load un-folded
+            int32_t* ta = tap + (size_t)img * g.N + nb * NB + j * 32;
+#pragma unroll
+            for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (FOLD ? th[c] : 0.0f));
+          }
         }
         if (FOLD && gb + SLOTS < T * g.nblk) preload(slot, (gb + SLOTS) % g.nblk);
         tc::fence_before_sync();
@@ -316,7 +321,8 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
 }
 
 template <int NB, int INM, int OUTM>
-bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
+bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+              cudaStream_t s) {
   const LayerDesc& d = L.d;
   GemmGeom g;
   g.K = d.K; g.N = d.N; g.kch = d.K / 32; g.ks = d.K / 64; g.nblk = d.N / NB;
@@ -331,22 +337,30 @@ bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, i
   g.off_ring = g.nbuf * g.a_bytes;
   g.off_thr = g.off_ring + ring;
   const int smem = g.off_thr + thr;
-  auto kern = k_gemm_f4<NB, INM, OUTM>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   const int ntiles = (n_img + 127) / 128;
-  kern<<<ntiles < num_sms ? ntiles : num_sms, 384, smem, s>>>(L, g, in, out, n_img, in_fmt, out_fmt, status);
+  const int grid = ntiles < num_sms ? ntiles : num_sms;
+  if (tap) {  // parity taps: the TAP instantiation of the same kernel
+    auto kern = k_gemm_f4<NB, INM, OUTM, true>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    kern<<<grid, 384, smem, s>>>(L, g, in, out, n_img, in_fmt, out_fmt, status, tap);
+    return true;
+  }
+  auto kern = k_gemm_f4<NB, INM, OUTM, false>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  kern<<<grid, 384, smem, s>>>(L, g, in, out, n_img, in_fmt, out_fmt, status, nullptr);
   return true;
 }
 
 template <int NB>
-bool launch_nb(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
+bool launch_nb(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+               cudaStream_t s) {
   const int im = L.d.in_mode, om = L.d.out_mode;
-  if (im == IN_XNOR && om == OUT_BIT) return launch_g<NB, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
-  if (im == IN_XNOR && om == OUT_SCORE) return launch_g<NB, IN_XNOR, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
-  if (im == IN_BIN && om == OUT_TERN) return launch_g<NB, IN_BIN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
-  if (im == IN_TERN && om == OUT_TERN) return launch_g<NB, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
-  if (im == IN_TERN && om == OUT_SCORE) return launch_g<NB, IN_TERN, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
-  if (im == IN_TERN && om == OUT_BIT) return launch_g<NB, IN_TERN, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+  if (im == IN_XNOR && om == OUT_BIT) return launch_g<NB, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+  if (im == IN_XNOR && om == OUT_SCORE) return launch_g<NB, IN_XNOR, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+  if (im == IN_BIN && om == OUT_TERN) return launch_g<NB, IN_BIN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+  if (im == IN_TERN && om == OUT_TERN) return launch_g<NB, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+  if (im == IN_TERN && om == OUT_SCORE) return launch_g<NB, IN_TERN, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+  if (im == IN_TERN && om == OUT_BIT) return launch_g<NB, IN_TERN, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
   return false;
 }
 
@@ -363,13 +377,14 @@ bool gemm_f4_supports(const DevLayer& L) {
   return (im == IN_XNOR && (om == OUT_BIT || om == OUT_SCORE)) || (im == IN_BIN && om == OUT_TERN) || (im == IN_TERN);
 }
 
-bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s) {
+bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+                    cudaStream_t s) {
   const LayerDesc& d = L.d;
   if (!gemm_f4_supports(L) || n_img <= 0) return false;
   if (in_fmt == ACT_F4P || out_fmt == ACT_F4P) return false;
   if (in_fmt == ACT_F4T && d.in_mode != IN_XNOR) return false;
   if (out_fmt == ACT_F4T && d.out_mode != OUT_BIT) return false;
-  return gemm_f4_block(d) == 128 ? launch_nb<128>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s) : launch_nb<64>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, s);
+  return gemm_f4_block(d) == 128 ? launch_nb<128>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s) : launch_nb<64>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
 }
 
 }  // namespace bnnb

@@ -19,7 +19,7 @@ namespace {
 __device__ __forceinline__ uint32_t spread4g(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
 
 template <int N, int INM, int OUTM>  // N: channels of this CTA's slice (64, 128 or 256)
-__global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, long long rows,
+__global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, long long rows, int32_t* __restrict__ tap,
                                                   int* __restrict__ status) {
   constexpr int A_SLAB = 4 * 128 * 16, B_SLAB = 4 * N * 16, BUF = A_SLAB + B_SLAB;
   constexpr int IPL = INM == IN_TERN ? 2 : 1;
@@ -110,6 +110,10 @@ __global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __r
     uint32_t v[32];
     tc::tmem_ld32(trow + j * 32, v);
     tc::tmem_ld_wait();
+    if (tap && rvalid) {  // parity taps: the int32 MMA sums of this row
+#pragma unroll
+      for (int c = 0; c < 32; c++) tap[(size_t)r * d.N + n0 + j * 32 + c] = (int)v[c];
+    }
     if (OUTM == OUT_SCORE) {  // PassThroughActivation<ap_uint<16>>: (S + offset) mod 2^16, offset = #negative weights for 1-bit inputs
       if (rvalid) {
         int16_t* o16 = reinterpret_cast<int16_t*>(out) + (size_t)r * d.N + n0 + j * 32;
@@ -142,21 +146,21 @@ __global__ void __launch_bounds__(128) k_gemm_tc(DevLayer L, const uint32_t* __r
 }
 
 template <int N, int INM, int OUTM>
-void launch_t(const DevLayer& L, const uint32_t* in, uint32_t* out, long long rows, int* status, cudaStream_t s) {
+void launch_t(const DevLayer& L, const uint32_t* in, uint32_t* out, long long rows, int* status, int32_t* tap, cudaStream_t s) {
   constexpr int SMEM = 2 * (4 * 128 * 16 + 4 * N * 16);
   cudaFuncSetAttribute(k_gemm_tc<N, INM, OUTM>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
   dim3 grid((unsigned)((rows + 127) / 128), (unsigned)(L.d.N / N));
-  k_gemm_tc<N, INM, OUTM><<<grid, 128, SMEM, s>>>(L, in, out, rows, status);
+  k_gemm_tc<N, INM, OUTM><<<grid, 128, SMEM, s>>>(L, in, out, rows, tap, status);
 }
 
 template <int N>
-bool launch_n(const DevLayer& L, const uint32_t* in, uint32_t* out, long long rows, int* status, cudaStream_t s) {
+bool launch_n(const DevLayer& L, const uint32_t* in, uint32_t* out, long long rows, int* status, int32_t* tap, cudaStream_t s) {
   const int im = L.d.in_mode, om = L.d.out_mode;
-  if (im == IN_XNOR && om == OUT_BIT) launch_t<N, IN_XNOR, OUT_BIT>(L, in, out, rows, status, s);
-  else if (im == IN_XNOR && om == OUT_SCORE) launch_t<N, IN_XNOR, OUT_SCORE>(L, in, out, rows, status, s);
-  else if (im == IN_TERN && om == OUT_TERN) launch_t<N, IN_TERN, OUT_TERN>(L, in, out, rows, status, s);
-  else if (im == IN_TERN && om == OUT_SCORE) launch_t<N, IN_TERN, OUT_SCORE>(L, in, out, rows, status, s);
-  else if (im == IN_TERN && om == OUT_BIT) launch_t<N, IN_TERN, OUT_BIT>(L, in, out, rows, status, s);
+  if (im == IN_XNOR && om == OUT_BIT) launch_t<N, IN_XNOR, OUT_BIT>(L, in, out, rows, status, tap, s);
+  else if (im == IN_XNOR && om == OUT_SCORE) launch_t<N, IN_XNOR, OUT_SCORE>(L, in, out, rows, status, tap, s);
+  else if (im == IN_TERN && om == OUT_TERN) launch_t<N, IN_TERN, OUT_TERN>(L, in, out, rows, status, tap, s);
+  else if (im == IN_TERN && om == OUT_SCORE) launch_t<N, IN_TERN, OUT_SCORE>(L, in, out, rows, status, tap, s);
+  else if (im == IN_TERN && om == OUT_BIT) launch_t<N, IN_TERN, OUT_BIT>(L, in, out, rows, status, tap, s);
   else return false;
   return true;
 }
@@ -164,16 +168,16 @@ bool launch_n(const DevLayer& L, const uint32_t* in, uint32_t* out, long long ro
 }  // namespace
 
 // Returns false when the layer cannot run on this kernel (the caller falls back to the LOP3+POPC kernel).
-bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s) {
+bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, int32_t* tap, cudaStream_t s) {
   const LayerDesc& d = L.d;
   if (!L.w8 || !L.thr_tc || n_img <= 0 || d.pool || d.K % 64 || d.ifm_ch % 64) return false;
   if (d.in_mode != IN_XNOR && d.in_mode != IN_TERN) return false;
   const long long rows = (long long)n_img * d.ofm_dim * d.ofm_dim;
   const long long tiles = (rows + 127) / 128;
   // widest channel slice that still gives every SM about two CTAs (wide slices re-use the expanded activation slab more)
-  if (d.N % 256 == 0 && tiles * (d.N / 256) >= 2LL * num_sms) return launch_n<256>(L, in, out, rows, status, s);
-  if (d.N % 128 == 0 && tiles * (d.N / 128) >= 2LL * num_sms) return launch_n<128>(L, in, out, rows, status, s);
-  if (d.N % 64 == 0) return launch_n<64>(L, in, out, rows, status, s);
+  if (d.N % 256 == 0 && tiles * (d.N / 256) >= 2LL * num_sms) return launch_n<256>(L, in, out, rows, status, tap, s);
+  if (d.N % 128 == 0 && tiles * (d.N / 128) >= 2LL * num_sms) return launch_n<128>(L, in, out, rows, status, tap, s);
+  if (d.N % 64 == 0) return launch_n<64>(L, in, out, rows, status, tap, s);
   return false;
 }
 

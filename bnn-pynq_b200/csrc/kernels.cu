@@ -99,17 +99,94 @@ void launch_repack(const DevLayer& L, int is_cnv_layer0, cudaStream_t s) {
   if (L.w8 && L.thr_tc) launch_thr_tc(L, s);
 }
 
-__global__ void k_patch(DevFolded f, const DevPatch* __restrict__ p, int n) {
-  // one thread, in list order: later entries for the same word win, as the sequential RMWs of the reference do
-  if (blockIdx.x == 0 && threadIdx.x == 0)
-    for (int i = 0; i < n; i++) {
-      const DevPatch& e = p[i];
-      if (e.is_thr) f.tf[e.layer][((size_t)e.pe * f.tmem[e.layer] + e.ind) * f.nthr[e.layer] + e.thresh] = (int32_t)(int64_t)e.value;
-      else f.wf[e.layer][(size_t)e.pe * f.wmem[e.layer] + e.ind] = e.value;
+// ------------------------------------------------------------------------------------------------------------
+// Fault epochs: one parameter word rewritten = the device operands derived from it rewritten in place (no re-pack of the layer).
+// The patch carries the new folded word (the host mirror ran the reference's read-modify-write, foldedmv-offload.h:146-167); one
+// warp applies the list IN ORDER (later entries for the same word win, like the reference's sequential RMWs):
+//   weight word [pe][ind] = SIMD fields of row n = nf*PE + pe, columns [sf*SIMD, (sf+1)*SIMD), ind = nf*SF + sf (mvau.hpp:115,143-152)
+//     -> popc planes (the <= 3 words per plane the columns fall into), int8 operand bytes, e2m1 operand bytes and their slab copy
+//        (the 16-byte units holding them), layer-0 int8x4 words, and thr_tc[n] +- the change in the row's count of -1 weights
+//   threshold [pe][ind][k] of row n = ind*PE + pe -> thr[n][k] and thr_tc[n][k] (same offset as before)
+// ------------------------------------------------------------------------------------------------------------
+__global__ void k_patch_apply(const DevLayer* __restrict__ Ls, int is_cnv, const DevPatch* __restrict__ p, int n) {
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  for (int i = 0; i < n; i++) {
+    const DevPatch e = p[i];
+    const DevLayer& L = Ls[e.layer];
+    const LayerDesc& d = L.d;
+    if (e.is_thr) {
+      if (lane == 0 && d.nthr > 0) {
+        const int nv = (int32_t)(int64_t)e.value;
+        const_cast<int32_t*>(L.tf)[((size_t)e.pe * d.tmem + e.ind) * d.nthr + e.thresh] = nv;
+        const int row = (int)e.ind * d.pe + (int)e.pe, k = (int)e.thresh;
+        if (k < 2 && k < d.nthr) {
+          const int old = L.thr[2 * row + k];
+          L.thr[2 * row + k] = nv;
+          if (L.thr_tc && d.out_mode != OUT_SCORE) L.thr_tc[2 * row + k] = nv - (old - L.thr_tc[2 * row + k]);  // thr_tc = thr - #neg
+        }
+      }
+      __syncwarp();
+      continue;
     }
+    const int SF = d.K / d.simd, nf = (int)e.ind / SF, sf = (int)e.ind - nf * SF;
+    const int row = nf * d.pe + (int)e.pe, k0 = sf * d.simd, k1 = k0 + d.simd;  // columns [k0, k1)
+    uint64_t* wfw = const_cast<uint64_t*>(L.wf) + (size_t)e.pe * d.wmem + e.ind;
+    const uint64_t oldw = *wfw;
+    __syncwarp();
+    if (lane == 0) *wfw = e.value;
+    __syncwarp();  // the folded word is visible to the whole warp: everything below re-derives from it
+    if (is_cnv && e.layer == 0) {  // int8x4 words [64][8], K = 27 padded to 32
+      for (int k = k0 + lane; k < k1; k += 32)
+        reinterpret_cast<int8_t*>(L.wp)[row * 32 + k] = (int8_t)weight_value(weight_field(L.wf, d, row, k), d.wbits);
+      __syncwarp();
+      continue;
+    }
+    {  // popc planes: uint32 [plane][K/32][N]
+      const int w0 = k0 >> 5, nwd = ((k1 - 1) >> 5) - w0 + 1;
+      for (int j = lane; j < nwd * d.wbits; j += 32) {
+        const int plane = j / nwd, kw = w0 + j % nwd;
+        uint32_t w = 0;
+        for (int b = 0; b < 32; b++) w |= (uint32_t)((weight_field(L.wf, d, row, kw * 32 + b) >> plane) & 1) << b;
+        L.wp[((size_t)plane * L.kwords + kw) * d.N + row] = w;
+      }
+    }
+    if (L.w8)
+      for (int k = k0 + lane; k < k1; k += 32) L.w8[(size_t)row * L.kpad + k] = (int8_t)weight_value(weight_field(L.wf, d, row, k), d.wbits);
+    if (L.w4) {
+      const int b0 = k0 >> 1, b1 = (k1 - 1) >> 1;  // bytes (two nibbles each; the neighbour nibble is re-derived, not read)
+      for (int kb = b0 + lane; kb <= b1; kb += 32) {
+        uint32_t byte = 0;
+        for (int h = 0; h < 2; h++) {
+          const int k = 2 * kb + h;
+          const int v = k < d.K ? weight_value(weight_field(L.wf, d, row, k), d.wbits) : 0;
+          byte |= (v == 0 ? 0x0u : (v == 1 ? 0x2u : (v == -1 ? 0xAu : 0xCu))) << (4 * h);
+        }
+        L.w4[(size_t)row * (L.kpad / 2) + kb] = (uint8_t)byte;
+      }
+      __syncwarp();
+      if (L.w4s && L.kpad % 64 == 0 && d.N % 64 == 0) {  // slab copy: 16-byte units [N/NB][K/64][2][NB]
+        const int NB = d.N % 128 == 0 ? 128 : 64, ks = L.kpad / 64;
+        const int u0 = b0 >> 4, u1 = b1 >> 4;
+        for (int u = u0 + lane; u <= u1; u += 32) {
+          const int s = u >> 1, c = u & 1, nb = row / NB, nl = row - nb * NB;
+          reinterpret_cast<uint4*>(L.w4s)[((size_t)(nb * ks + s) * 2 + c) * NB + nl] = *reinterpret_cast<const uint4*>(L.w4 + (size_t)row * (L.kpad / 2) + u * 16);
+        }
+      }
+    }
+    if (lane == 0 && L.thr_tc && d.in_mode == IN_XNOR) {  // 1-bit weights: #(-1) = zero bits of the field range
+      const uint64_t mask = d.simd >= 64 ? ~0ull : ((1ull << d.simd) - 1);
+      const int delta = __popcll(~e.value & mask) - __popcll(~oldw & mask);
+      if (d.out_mode == OUT_SCORE) L.thr_tc[2 * row] += delta;
+      else
+        for (int k = 0; k < 2; k++)
+          if (L.thr_tc[2 * row + k] != INT_MAX) L.thr_tc[2 * row + k] -= delta;
+    }
+    __syncwarp();
+  }
 }
-void launch_patch(const DevFolded& f, const DevPatch* patches, int n, cudaStream_t s) {
-  if (n > 0) k_patch<<<1, 32, 0, s>>>(f, patches, n);
+void launch_patch_apply(const DevLayer* d_layers, int is_cnv, const DevPatch* patches, int n, cudaStream_t s) {
+  if (n > 0) k_patch_apply<<<1, 32, 0, s>>>(d_layers, is_cnv, patches, n);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -453,6 +530,7 @@ __global__ void k_cnv_classes(const int16_t* __restrict__ sc, int n, int ncls, i
 }
 void launch_cnv_classes(const int16_t* scores, int n, int ncls, int* classes, cudaStream_t s) {
   if (n <= 0) return;
+  ncls = ncls < 0 ? 0 : (ncls > 64 ? 64 : ncls);  // BlackBoxJam writes 64 scores per image (cnvW1A1/hw/top.cpp:197)
   k_cnv_classes<<<(n + 255) / 256, 256, 0, s>>>(scores, n, ncls, classes);
 }
 

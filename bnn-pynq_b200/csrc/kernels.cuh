@@ -33,10 +33,11 @@ struct DevLayer {
 
 // ---- parameter re-pack (runs once per load_parameters and after every fault epoch for the touched layers) ----
 void launch_repack(const DevLayer& L, int is_cnv_layer0, cudaStream_t s);
-// writes patch values into the folded device mirrors: entries {layer,is_thr,pe,ind,thresh,pad,value}
+// one rewritten parameter word: {layer,is_thr,pe,ind,thresh,pad,value}
 struct DevPatch { uint32_t layer, is_thr, pe, ind, thresh, pad; uint64_t value; };
-struct DevFolded { uint64_t* wf[9]; int32_t* tf[9]; int wmem[9], tmem[9], nthr[9]; };
-void launch_patch(const DevFolded& f, const DevPatch* patches, int n, cudaStream_t s);
+// applies the list in order to the folded mirrors AND to every operand derived from the touched words (no re-pack of the layer);
+// d_layers: device copy of the network's DevLayer table
+void launch_patch_apply(const DevLayer* d_layers, int is_cnv, const DevPatch* patches, int n, cudaStream_t s);
 
 // ---- input preparation ----
 void launch_prep_cifar(const uint8_t* records, int8_t* q, int n, cudaStream_t s);   // 3073-byte records -> int8 HWC
@@ -48,21 +49,28 @@ void launch_conv0(const DevLayer& L, const int8_t* in, uint32_t* out, int n_img,
 void launch_layer_popc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int32_t* tap_acc, int num_sms, cudaStream_t s);
 
 // ---- layers (tcgen05 kind::i8 tensor-core path, conv_tc.cu); returns false when the layer shape has no instantiation ----
-bool launch_conv_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
+bool launch_conv_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, int32_t* tap, cudaStream_t s);
 void launch_thr_tc(const DevLayer& L, cudaStream_t s);
 // conv layers on kind::mxf4 (conv_f4.cu)
 // in_fmt / out_fmt: ActFmt of f4_common.cuh (ACT_BITS everywhere except between fp4 kernels of a 1-bit network)
 bool conv_f4_supports(const LayerDesc& d);
-bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s);
+// tap (parity tests; null in production): int32 MMA sums [img][ofm_dim^2][N], pre-loads un-folded
+bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+                    cudaStream_t s);
 // fully-connected layers on kind::mxf4 (gemm_f4.cu); gemm_f4_block = channel block width NB of the slab layout
 int gemm_f4_block(const LayerDesc& d);
 bool gemm_f4_supports(const DevLayer& L);
-bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, cudaStream_t s);
+bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+                    cudaStream_t s);
 // K-streamed GEMM for FC / small conv layers (gemm_tc.cu)
-bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, cudaStream_t s);
+bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, int32_t* tap, cudaStream_t s);
 // fused CNV layers 0+1 (cnv01_tc.cu): int8 HWC image -> pooled, bit-packed layer-1 output
+// Tap01 (parity tests; all null in production): acc0 / acc1 = int32 MMA sums [img][900][64] / [img][784][64] (layer 0: sum w*q;
+// layer 1: sum a*w over the operand values), act0 = the layer-1 operand rows layer 0 wrote, uint4 [img][900][4]
+// (fp4: entries 0 / 2 = channels 0-31 / 32-63 as e2m1 codes, FOLD nibble order; int8: four 16-channel chunks).
+struct Tap01 { int32_t* acc0 = nullptr; int32_t* acc1 = nullptr; uint4* act0 = nullptr; };
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt, int* status,
-                     cudaStream_t s);
+                     const Tap01& tp, cudaStream_t s);
 
 // ---- class decode for CNV (multi-image rule, foldedmv-offload.h:398-406) ----
 void launch_cnv_classes(const int16_t* scores, int n, int ncls, int* classes, cudaStream_t s);

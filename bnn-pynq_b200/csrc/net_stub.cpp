@@ -77,7 +77,7 @@ int inference(const char* path, int results[64], int number_class, float* usecPe
   if (g_is_cnv) {
     int16_t sc[64];
     if (bnnb_classify_cifar(g_ctx, buf.data(), 1, number_class, nullptr, sc, &usec) != 0) { report("inference"); return -1; }
-    const int ncls = number_class < 0 ? 0 : (number_class > 64 ? 64 : number_class);
+    const int ncls = number_class < 0 ? 0 : (number_class > 64 ? 64 : number_class);  // BlackBoxJam writes 64 scores per image
     int best = 0;  // std::max_element over the number_class scores: first maximum (cnvW1A1/sw/main_python.cpp:138)
     for (int j = 0; j < ncls; j++) { if (results) results[j] = sc[j]; if (sc[j] > sc[best]) best = j; }
     if (usecPerImage) *usecPerImage = usec;
@@ -163,16 +163,26 @@ int* inference_multiple_with_faults(const char* path, int number_class, int* ima
 
 // In-memory twins of the two calls above: the caller hands over what the file would have held after parsing, so that
 // classify_images (bnn/bnn.py:280-287) needs no temp file.  Not part of the reference's cdef; bnn.py binds them when present.
-int* inference_buffer(const unsigned char* images, int image_count, int number_class, float* usecPerImage, int enable_detail) {
+// The caller states how many bytes it hands over: anything but image_count whole rows of THIS network's size (3073 for CNV, 784
+// for LFC) is refused before a single byte is read.
+static bool buffer_ok(const unsigned char* images, int image_count, long long image_bytes, const char* where) {
+  const long long row = g_is_cnv ? 3073 : 784;
+  if (image_count >= 0 && (image_count == 0 || images) && image_bytes == row * image_count) return true;
+  std::fprintf(stderr, "[bnn_b200 %s] %s: expected %d images x %lld bytes = %lld bytes, got %lld\n", BNNB_NET, where, image_count, row,
+               row * (long long)image_count, image_bytes);
+  return false;
+}
+
+int* inference_buffer(const unsigned char* images, int image_count, long long image_bytes, int number_class, float* usecPerImage, int enable_detail) {
   if (!ctx()) return nullptr;
-  if (image_count < 0 || (image_count > 0 && !images)) { std::fprintf(stderr, "[bnn_b200 %s] inference_buffer: bad arguments\n", BNNB_NET); return nullptr; }
+  if (!buffer_ok(images, image_count, image_bytes, "inference_buffer")) return nullptr;
   return run_multiple(images, image_count, number_class, usecPerImage, enable_detail, "inference_buffer");
 }
 
-int* inference_buffer_with_faults(const unsigned char* images, int image_count, int number_class, float* usecPerImage, unsigned int flip_count,
-                                  int word_size, int target, int* target_layers, unsigned int num_targets) {
+int* inference_buffer_with_faults(const unsigned char* images, int image_count, long long image_bytes, int number_class, float* usecPerImage,
+                                  unsigned int flip_count, int word_size, int target, int* target_layers, unsigned int num_targets) {
   if (!ctx()) return nullptr;
-  if (image_count < 0 || (image_count > 0 && !images)) { std::fprintf(stderr, "[bnn_b200 %s] inference_buffer_with_faults: bad arguments\n", BNNB_NET); return nullptr; }
+  if (!buffer_ok(images, image_count, image_bytes, "inference_buffer_with_faults")) return nullptr;
   return run_multiple_with_faults(images, image_count, number_class, usecPerImage, flip_count, word_size, target, target_layers, num_targets,
                                   "inference_buffer_with_faults");
 }
@@ -180,8 +190,11 @@ int* inference_buffer_with_faults(const unsigned char* images, int image_count, 
 void free_results(int* result) { delete[] result; }
 
 void deinit(void) {
-  // FoldedMVDeinit frees the host staging buffers only; parameters (and faults) survive it in the reference because they live in
-  // static memories (top.cpp:51-68).  Nothing to do: another PynqBNN may still hold this cached library (bnn/bnn.py:79,109-115).
+  // FoldedMVDeinit (rawhls-offload.cpp:69-74) frees the accelerator buffers; the parameters (and injected faults) survive it in the
+  // reference because they live in static memories (top.cpp:51-68).  Same here: every device allocation (parameter operands,
+  // activation and staging buffers, streams) is released, the host mirror of the parameters and faults is kept, and the next call
+  // - possibly from another PynqBNN holding this cached library (bnn/bnn.py:79,109-115) - rebuilds the device state on demand.
+  if (g_ctx) bnnb_release(g_ctx);
 }
 
 }  // extern "C"

@@ -79,18 +79,33 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// bounded spin: returns false after ~2^22 polls (legitimate waits are microseconds) so that a protocol bug cannot hang the GPU box
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// bounded spin: returns false once the wait has lasted BNNB_WAIT_NS of wall time (%globaltimer; legitimate waits are microseconds,
+// also under profiler replay or time-slicing, where a poll count says nothing) so that a protocol bug cannot hang the GPU box.
+// The caller stops waiting after the first failure and raises the device status flag; the engine turns that into an error.
+#ifndef BNNB_WAIT_NS
+#define BNNB_WAIT_NS 2000000000ull
+#endif
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
   // eight polls per trip: the trip counter costs two ALU-pipe instructions, and the epilogue warps share that pipe
 #ifndef BNNB_POLLU
 #define BNNB_POLLU 8
 #endif
-  for (uint32_t i = 0; i < (1u << 22) / BNNB_POLLU; i++) {
+  uint64_t t0 = 0;
+  for (;;) {
+    for (uint32_t i = 0; i < (1u << 14) / BNNB_POLLU; i++) {
 #pragma unroll
-    for (int j = 0; j < BNNB_POLLU; j++)
-      if (mbar_try_wait(bar, parity)) return true;
+      for (int j = 0; j < BNNB_POLLU; j++)
+        if (mbar_try_wait(bar, parity)) return true;
+    }
+    const uint64_t now = global_timer_ns();  // every 2^14 polls (tens of microseconds)
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > BNNB_WAIT_NS) return false;
   }
-  return false;
 }
 
 // TMEM -> registers: this warp's 32 lanes (rows), 32 consecutive 32-bit columns starting at taddr's column

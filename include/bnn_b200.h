@@ -45,14 +45,17 @@ int* inference_multiple_with_faults(const char* path, int number_class, int* ima
 /* In-memory twins of the two calls above (extension; bnn.py binds them when the library exports them).  They take what the
  * file would hold after parsing -- CNV: image_count 3073-byte CIFAR records (label byte ignored); LFC: image_count x 784
  * pixels, no idx3 header -- so that classify_images / image_to_cifar (bnn/bnn.py:226-242,280-287) need no temp file.
- * Same results, same result ownership (free_results), same fault scheduling as the path-based calls. */
-int* inference_buffer(const unsigned char* images, int image_count, int number_class, float* usecPerImage, int enable_detail);
-int* inference_buffer_with_faults(const unsigned char* images, int image_count, int number_class, float* usecPerImage,
-                                  unsigned int flip_count, int word_size, int target, int* target_layers,
+ * image_bytes = the size of the buffer handed over; it must equal image_count rows of THIS network's size or the call is refused
+ * (NULL) before anything is read.  Same results, same result ownership (free_results), same fault scheduling as the path-based calls. */
+int* inference_buffer(const unsigned char* images, int image_count, long long image_bytes, int number_class, float* usecPerImage,
+                      int enable_detail);
+int* inference_buffer_with_faults(const unsigned char* images, int image_count, long long image_bytes, int number_class,
+                                  float* usecPerImage, unsigned int flip_count, int word_size, int target, int* target_layers,
                                   unsigned int num_targets);
 /* :225 */
 void free_results(int* result);
-/* :229 -- releases nothing the next call cannot rebuild: every entry point re-initialises on demand (FoldedMVInit). */
+/* :229 -- FoldedMVDeinit: releases every device allocation (bnnb_release).  The parameters and injected faults are kept in the host
+ * mirror, as the reference keeps them in static memories, and every entry point re-initialises on demand (FoldedMVInit). */
 void deinit(void);
 
 /* ------------------------------------------------------------------------------------------------------------------
@@ -69,6 +72,11 @@ const char* bnnb_last_error(bnnb_ctx* c);
 int bnnb_set_devices(bnnb_ctx* c, const int* device_ids, int n);
 int bnnb_num_devices(bnnb_ctx* c);
 int bnnb_load_parameters(bnnb_ctx* c, const char* dir);
+/* Frees every device allocation of the context (parameter operands, buffers, streams); parameters and faults stay in the host mirror and
+ * the next call rebuilds the device state on demand.  Device memory is otherwise taken lazily: a device is set up the first time a call
+ * runs on it, and its buffers are sized for the chunks it is given (a one-image call takes a few MB on one device). */
+int bnnb_release(bnnb_ctx* c);
+size_t bnnb_device_bytes(bnnb_ctx* c, int slot);   /* bytes currently allocated on device slot `slot` */
 
 /* Host-buffer inference.  records: n x 3073 bytes (label + planar RGB, the CIFAR-10 binary record bnn.py writes, bnn/bnn.py:226-242);
  * pixels: n x 784 bytes (idx3 payload).  Output pointers may be NULL.  scores: n x 64 int16 (what BlackBoxJam writes per image);
@@ -94,8 +102,10 @@ int bnnb_mem_set(bnnb_ctx* c, unsigned target_layer, unsigned mem, unsigned ind,
 unsigned bnnb_weight_layer_bits(bnnb_ctx* c, int layer);   /* topology.h:55-62 */
 unsigned bnnb_thresh_layer_bits(bnnb_ctx* c, int layer);   /* topology.h:63-70 */
 
-/* Per-layer taps (parity tests): per image, concatenated over layers: int32 accumulators [ofm_dim^2][N] before the threshold,
- * and int8 layer outputs [out_dim^2][N] after the layer's max-pool (values 0/1, -1/0/+1, or the low byte of the score). */
+/* Per-layer taps (parity tests) ON THE SELECTED CORE (bnnb_set_core): per image, concatenated over layers: int32 accumulators
+ * [ofm_dim^2][N] before the threshold (the reference's accumulator values, mvau.hpp:110,166-169), and int8 layer outputs
+ * [out_dim^2][N] after the layer's max-pool (values 0/1, -1/0/+1, or the low byte of the score).  Cores 1 / 2 run the TAP
+ * instantiations of the tensor-core kernels that ship (same source + extra stores) with the production activation formats. */
 size_t bnnb_tap_acc_size(bnnb_ctx* c);
 size_t bnnb_tap_act_size(bnnb_ctx* c);
 int bnnb_tap(bnnb_ctx* c, const uint8_t* input, int n, int32_t* acc, int8_t* act);
@@ -106,6 +116,7 @@ int bnnb_tap(bnnb_ctx* c, const uint8_t* input, int n, int32_t* acc, int8_t* act
  * Asynchronous: call bnnb_sync or synchronise the stream.  bnnb_last_launches: kernels enqueued by the last call. */
 int bnnb_infer_device(bnnb_ctx* c, int slot, const void* d_in, int n, void* d_out, int* d_classes, int number_class, void* stream);
 int bnnb_prep_device(bnnb_ctx* c, int slot, const void* d_raw, int n, void* d_in, void* stream);  /* records/pixels -> layer-0 input */
+/* Waits for the device and fails if a kernel gave up waiting on an mbarrier since the last check (results invalid). */
 int bnnb_sync(bnnb_ctx* c, int slot);
 int bnnb_last_launches(bnnb_ctx* c);
 int bnnb_in_bytes(bnnb_ctx* c);    /* per image: 3072 | 104 */

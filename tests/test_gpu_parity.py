@@ -59,20 +59,104 @@ def test_lfc_words_vs_oracle_and_golden(net):
         assert np.array_equal(rt.classify_mnist(px[:300], ncls), o.classes(px[:300], ncls))
 
 
-@pytest.mark.parametrize("net", NETS)
-def test_every_layer_accumulators_and_outputs(net):
-    rt, o = runtime(net), Oracle(net)
-    data = data_for(net, 5, 21)
-    acc, act = rt.tap(data)
+def structured(net, n=6):
+    """Inputs with structure instead of iid bytes: constant blocks, ramps, one saturated channel, a checkerboard."""
     if net.startswith("cnv"):
-        _, oacc, oact = o.cnv_scores(data, taps=True)
-    else:
-        _, oacc, oact = o.lfc_words(data, taps=True)
-    for i in range(data.shape[0]):
+        rec = np.zeros((n, 3073), np.uint8)
+        img = rec[:, 1:].reshape(n, 3, 32, 32)
+        img[0, :, :16, :] = 255                                         # half black, half white
+        img[1] = (np.arange(32, dtype=np.int64)[None, None, :] * 8).astype(np.uint8)      # horizontal ramp
+        img[2] = (np.arange(32, dtype=np.int64)[None, :, None] * 8 + 3).astype(np.uint8)  # vertical ramp
+        img[3, 0] = 255                                                 # red channel saturated, others zero
+        img[4] = ((np.add.outer(np.arange(32), np.arange(32)) % 2) * 255).astype(np.uint8)[None]  # checkerboard
+        img[5] = 128                                                    # mid grey: quantises to the value nearest zero
+        return rec
+    px = np.zeros((n, 784), np.uint8)
+    im = px.reshape(n, 28, 28)
+    im[0, :14] = 255
+    im[1] = (np.arange(28, dtype=np.int64)[None, :] * 9).astype(np.uint8)
+    im[2] = (np.arange(28, dtype=np.int64)[:, None] * 9 + 4).astype(np.uint8)
+    im[3, 10:18, 10:18] = 255
+    im[4] = ((np.add.outer(np.arange(28), np.arange(28)) % 2) * 255).astype(np.uint8)
+    im[5] = 128
+    return px
+
+
+def oracle_taps(o, data):
+    _, oacc, oact = o.cnv_scores(data, taps=True) if o.is_cnv else o.lfc_words(data, taps=True)
+    return oacc, oact
+
+
+def check_taps(o, acc, act, oacc, oact, what):
+    for i in range(acc.shape[0]):
         for l, (a, b) in enumerate(zip(o.split_taps(acc[i], "acc"), o.split_taps(oacc[i], "acc"))):
-            assert np.array_equal(a, b), "accumulators differ: image %d layer %d" % (i, l)
+            if o.is_cnv and l == o.nlayers - 1:   # no threshold: the reference's accumulator IS the 16-bit score (top.cpp:232-233)
+                a, b = a.astype(np.int16), b.astype(np.int16)
+            assert np.array_equal(a, b), "%s: accumulators differ: image %d layer %d" % (what, i, l)
         for l, (a, b) in enumerate(zip(o.split_taps(act[i], "act"), o.split_taps(oact[i], "act"))):
-            assert np.array_equal(a, b), "layer outputs differ: image %d layer %d" % (i, l)
+            assert np.array_equal(a, b), "%s: layer outputs differ: image %d layer %d" % (what, i, l)
+
+
+@pytest.mark.parametrize("core", [2, 1, 0])
+@pytest.mark.parametrize("net", NETS)
+def test_every_layer_accumulators_and_outputs(net, core):
+    """north_star: every layer's accumulators and threshold outputs, bit-exact, ON EVERY CORE.  Cores 1 / 2 run the TAP
+    instantiations of the tensor-core kernels that ship (the fused layer-0/1 kernel, conv_f4 / gemm_f4 or conv_tc / gemm_tc) with
+    the production activation formats; the oracle's taps are pinned to the reference's own templates (tests/golden/taps_<net>.npz)."""
+    rt, o = runtime(net), Oracle(net)
+    rt.set_core(core)
+    data = np.concatenate([data_for(net, 17, 21), structured(net)])  # 17: more than one 16-image tap step; + structured inputs
+    acc, act = rt.tap(data)
+    oacc, oact = oracle_taps(o, data)
+    check_taps(o, acc, act, oacc, oact, "core %d" % core)
+
+
+@pytest.mark.parametrize("core", [2, 0])
+@pytest.mark.parametrize("net", NETS)
+def test_every_layer_vs_reference_template_taps(net, core):
+    """The same taps against the committed per-layer tensors the reference's own templates produced (oracle/tap.cpp)."""
+    from test_oracle_golden import tap_gold, tap_inputs
+    rt, o = runtime(net), Oracle(net)
+    rt.set_core(core)
+    gacc, gact = tap_gold(net)
+    acc, act = rt.tap(tap_inputs(net))
+    check_taps(o, acc, act, gacc, gact, "core %d vs reference templates" % core)
+
+
+@pytest.mark.parametrize("core", [2, 1, 0])
+@pytest.mark.parametrize("net", NETS)
+def test_structured_inputs(net, core):
+    rt, o = runtime(net), Oracle(net)
+    rt.set_core(core)
+    d = structured(net)
+    if net.startswith("cnv"):
+        cls, sc = rt.classify_cifar(d, 10, want_scores=True)
+        assert np.array_equal(sc, o.cnv_scores(d))
+    else:
+        cls, words = rt.classify_mnist(d, 10, want_words=True)
+        assert np.array_equal(words, o.lfc_words(d))
+    assert np.array_equal(cls, o.classes(d))
+
+
+@pytest.mark.parametrize("net", ["cnvW1A1", "lfcW1A1"])
+def test_small_calls_take_little_memory_and_release_frees_it(net):
+    """A one-image call sets up ONE device with buffers for one small chunk; release() (what deinit() calls) frees every device
+    allocation and the next call rebuilds the state with the same parameters and faults (rawhls-offload.cpp:54-74)."""
+    from bnn import native
+    rt = native.Runtime(net, params_dir(net))           # every visible device is a candidate
+    o = Oracle(net)
+    d = data_for(net, 3, 8)
+    assert rt.device_bytes(0) == 0                        # load_parameters allocates nothing by itself
+    assert np.array_equal(rt.classify(d[:1]), o.classes(d[:1]))
+    assert 0 < rt.device_bytes(0) < 64 << 20, rt.device_bytes(0)
+    for slot in range(1, rt.L.bnnb_num_devices(rt.h)):
+        assert rt.device_bytes(slot) == 0                 # a small batch stays on one device
+    rt.inject_fault(1, 1, 5, 1)
+    o.inject(1, 1, 5, 1)
+    rt.release()
+    assert rt.device_bytes(0) == 0
+    assert np.array_equal(rt.classify(d), o.classes(d))   # re-initialised on demand, fault kept
+    assert rt.mem_read(2, 0, 0, 0) == o.mem_read(2, 0, 0, 0)
 
 
 @pytest.mark.parametrize("net", NETS)
