@@ -145,6 +145,42 @@ def run_reference_cpu(net, per_proc, steps, warmup, procs=None):
     return ips, 1000.0 * total / steps, procs, sample
 
 
+def _peaks_json():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+def one_process_e2e(native, L, net, ngpu, B, steps):
+    """Host-buffer images/s of ONE process sharding ngpu x B images over ngpu devices through bnnb_classify_cifar (Engine::infer_host:
+    contiguous shards, one feeder thread per device)."""
+    import numpy as np
+    rt = native.Runtime(net, params_dir(net), devices=list(range(ngpu)))
+    n = ngpu * B
+    host, host_ptr = native.pinned_array(n * 3073)
+    rng = np.random.default_rng(9)
+    for o in range(0, n, 65536):
+        m = min(65536, n - o)
+        host[o * 3073:(o + m) * 3073] = rng.integers(0, 256, m * 3073, dtype=np.uint8)
+    cls, cls_ptr = native.pinned_array(n * 4)
+    us = C.c_float(0)
+
+    def call():
+        if L.bnnb_classify_cifar(rt.h, host_ptr, n, 10, cls_ptr, None, C.byref(us)) != 0:
+            raise RuntimeError(L.bnnb_last_error(rt.h).decode())
+
+    call(); call()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        call()
+    dt = (time.perf_counter() - t0) / steps
+    native.free_pinned(host_ptr); native.free_pinned(cls_ptr)
+    rt.close()
+    return {"value": n / dt, "unit": "images/s", "images_per_call": n, "devices": ngpu, "device_kernel_usec_per_image": float(us.value)}
+
+
 def traffic_per_image(net):
     """dram__bytes_read.sum + dram__bytes_write.sum of the network's dominant kernel PER IMAGE, from profiles/traffic.json, which
     tools/ncu_summary.py writes from an `ncu --set full` capture (one entry per network: bytes of ONE launch and the images that launch
@@ -189,6 +225,164 @@ def fast_cpu_port(net, seconds=10.0):
             "note": "oracle/bnn_oracle.c, the int8 restatement used as the parity checker: not reference code"}
 
 
+def measure_sustained(step, seconds, stream_events, B, world, max_over_ranks, barrier, sampler_cls, local_rank):
+    """Back-to-back steps for `seconds` (no L2 flush, no host work between launches): the sustained arm, with its own clock samples."""
+    import torch
+    probe_a, probe_b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    probe_a.record(); step(); probe_b.record(); torch.cuda.synchronize()
+    per = max(probe_a.elapsed_time(probe_b), 1e-3)
+    steps = max(10, int(seconds * 1000.0 / per))
+    sampler = sampler_cls(local_rank)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    sampler.stop_flag = True
+    sampler.join()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    return {"seconds": ms * 1e-3, "steps": steps, "ms_per_step": ms / steps, "value": world * B * steps / (ms * 1e-3), "unit": "images/s",
+            "clocks": sampler.summary()}
+
+
+def measure_latency(L, rt, fam, host_ptr, calls):
+    """Batch-1 latency of the host-buffer call bnn.py's inference() makes (record in pinned host memory -> class on the host)."""
+    import numpy as np
+    from bnn import native
+    out, out_ptr = native.pinned_array(64)
+    us = C.c_float(0)
+    fn = L.bnnb_classify_cifar if fam == "cnv" else L.bnnb_classify_mnist
+    ts = []
+    for i in range(calls + 20):
+        t0 = time.perf_counter()
+        rc = fn(rt.h, host_ptr, 1, 10, out_ptr, None, C.byref(us))
+        ts.append(time.perf_counter() - t0)
+        if rc != 0:
+            raise RuntimeError(L.bnnb_last_error(rt.h).decode())
+    ts = np.sort(np.array(ts[20:])) * 1e6
+    native.free_pinned(out_ptr)
+    return {"calls": calls, "median_us": float(ts[len(ts) // 2]), "p10_us": float(ts[len(ts) // 10]), "p99_us": float(ts[int(len(ts) * 0.99)]),
+            "device_kernel_us": float(us.value),
+            "reference_fpga_us": {"cnvW1A1": 527, "cnvW1A2": 543, "cnvW2A2": 1622, "lfcW1A1": 8}.get(rt.network),
+            "note": "wall clock around bnnb_classify_* with n = 1 (H2D of one record, quantise, all layers, class D2H); the FPGA figure is the "
+                    "reference's notebook number for its overlay (notebooks/CNV-QNN_Cifar10.ipynb:129,217,298, LFC-BNN_MNIST_Webcam.ipynb:291)"}
+
+
+def measure_faults(native, L, net, local_rank, rank, world, total_images, nfaults, barrier, max_over_ranks):
+    """BASELINE configs[4]: `total_images` synthetic images, sharded contiguously over the ranks, classified through
+    bnnb_classify_with_fault_list with a seeded schedule of `nfaults` parameter upsets (time i = applied before image i of the WHOLE job:
+    a rank applies the faults that fall before its shard first, then runs its segments) - against the same call with no faults."""
+    import numpy as np
+    fam_cnv = net.startswith("cnv")
+    raw_w = 3073 if fam_cnv else 784
+    lo, hi = rank * total_images // world, (rank + 1) * total_images // world
+    n = hi - lo
+    rt = native.Runtime(net, params_dir(net), devices=[local_rank])
+    host, host_ptr = native.pinned_array(n * raw_w)
+    rng = np.random.default_rng(2 + rank)
+    blk = 1 << 16
+    for o in range(0, n, blk):   # generated in blocks: 3 GB of random bytes at once would double the host footprint
+        m = min(blk, n - o)
+        r = rng.integers(0, 256, (m, raw_w), dtype=np.uint8)
+        if fam_cnv:
+            r[:, 0] = 0
+        host[o * raw_w:(o + m) * raw_w] = r.reshape(-1)
+    cls, cls_ptr = native.pinned_array(n * 4)
+    fl = rt.schedule_faults(total_images, nfaults, word_size=1, target=-1, seed=3)   # the same list on every rank
+    mine = fl.copy()
+    t = mine[:, 0].astype(np.int64) - lo
+    mine[:, 0] = np.clip(t, 0, max(n - 1, 0)).astype(np.uint32)   # earlier faults: before my first image
+    late = t >= n                                                 # later faults: after my last image (they persist, nothing to classify)
+    run_list = np.ascontiguousarray(mine[~late])
+    us = C.c_float(0)
+
+    def call(flist):
+        fp = flist.ctypes.data_as(C.c_void_p) if flist.shape[0] else None
+        rc = L.bnnb_classify_with_fault_list(rt.h, host_ptr, n, 10, fp, flist.shape[0], cls_ptr, C.byref(us))
+        if rc != 0:
+            raise RuntimeError(L.bnnb_last_error(rt.h).decode())
+
+    empty = np.zeros((0, 5), np.uint32)
+    call(empty)                      # warm-up (buffers, clocks)
+    barrier()
+    t0 = time.perf_counter(); call(empty); t_clean = max_over_ranks(time.perf_counter() - t0)
+    clean = cls.view(np.int32).copy()
+    rt.load_parameters(params_dir(net))
+    barrier()
+    t0 = time.perf_counter(); call(run_list); t_fault = max_over_ranks(time.perf_counter() - t0)
+    faulted = cls.view(np.int32).copy()
+    first = int(run_list[:, 0].min()) if run_list.shape[0] else n
+    ok_prefix = bool(np.array_equal(clean[:first], faulted[:first]))
+    changed = int((clean != faulted).sum())
+    segs = int(np.unique(run_list[:, 0]).size) + 1 if run_list.shape[0] else 1
+    native.free_pinned(host_ptr); native.free_pinned(cls_ptr)
+    rt.close()
+    return {"images": total_images, "faults_scheduled": int(fl.shape[0]), "segments_rank0": segs,
+            "e2e_unfaulted_images_per_s": total_images / t_clean, "e2e_faulted_images_per_s": total_images / t_fault,
+            "ratio": t_clean / t_fault, "results_changed_rank0": changed, "prefix_before_first_fault_identical": ok_prefix,
+            "note": "bnnb_classify_with_fault_list on pinned host records, wall clock, max over ranks; bit-exactness of faulted runs is pinned by "
+                    "tests/test_gpu_full_size.py (oracle) - bench.py only checks that nothing changes before the first fault time"}
+
+
+def measure_network(native, L, net, local_rank, steps, B):
+    """One more network, briefly: device-resident images/s and host-buffer images/s (side field `networks`)."""
+    import numpy as np
+    import torch
+    rt = native.Runtime(net, params_dir(net), devices=[local_rank])
+    cnv = net.startswith("cnv")
+    raw_w = 3073 if cnv else 784
+    if cnv and not net.endswith("W1A1"):
+        B = min(B, 32768)
+    host, host_ptr = native.pinned_array(B * raw_w)
+    host[:] = np.random.default_rng(5).integers(0, 256, B * raw_w, dtype=np.uint8)
+    dev = torch.device("cuda", local_rank)
+    d_raw = torch.from_numpy(host).to(dev)
+    d_in = torch.empty(B * rt.in_bytes, dtype=torch.uint8, device=dev)
+    d_out = torch.empty(B * rt.out_bytes, dtype=torch.uint8, device=dev)
+    d_cls = torch.empty(B, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    rt.prep_device(d_raw.data_ptr(), B, d_in.data_ptr(), stream)
+
+    def step():
+        rt.infer_device(d_in.data_ptr(), B, d_out.data_ptr(), d_cls.data_ptr() if cnv else 0, 10, stream)
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    rt.sync()
+    ms = e0.elapsed_time(e1) / steps
+    cls_host, cls_ptr = native.pinned_array(B * 4)
+    words_host, words_ptr = native.pinned_array(B * 8)
+    us = C.c_float(0)
+
+    def e2e():
+        rc = (L.bnnb_classify_cifar(rt.h, host_ptr, B, 10, cls_ptr, None, C.byref(us)) if cnv
+              else L.bnnb_classify_mnist(rt.h, host_ptr, B, 10, cls_ptr, words_ptr, C.byref(us)))
+        if rc != 0:
+            raise RuntimeError(L.bnnb_last_error(rt.h).decode())
+
+    e2e()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e2e()
+    dt = (time.perf_counter() - t0) / steps
+    fam = "cnv" if cnv else "lfc"
+    for ptr in (host_ptr, cls_ptr, words_ptr):
+        native.free_pinned(ptr)
+    rt.close()
+    return {"value": B / (ms * 1e-3), "ms_per_step": ms, "batch": B, "e2e": B / dt, "unit": "images/s",
+            "tops": OPS[fam] * B / (ms * 1e-3) / 1e12}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -203,7 +397,7 @@ def main():
     ap.add_argument("--fault-images", type=int, default=1 << 20, help="config 5 side measurement: images in the whole job (sharded over the ranks)")
     ap.add_argument("--sustained-s", type=float, default=2.5, help="sustained arm: seconds of back-to-back steps (0 = skip)")
     ap.add_argument("--latency-calls", type=int, default=1000, help="batch-1 latency: calls through the host-buffer C ABI (0 = skip)")
-    ap.add_argument("--nets", default="", help="comma list of further networks measured briefly into the `networks` side field ('all' = the other four)")
+    ap.add_argument("--nets", default="all", help="comma list of further networks measured briefly into the `networks` side field ('all' = the other four)")
     ap.add_argument("--lean", action="store_true", help="only the headline measurement (kernel experiments): no side fields, no CPU baselines")
     ap.add_argument("--core", type=int, default=2, choices=[0, 1, 2],
                     help="compute core: 2 = tcgen05 kind::mxf4 (default), 1 = tcgen05 kind::i8, 0 = LOP3+POPC bit-serial (BASELINE configs[3] comparison)")
@@ -414,13 +608,59 @@ def main():
                    "h2d_copy_gbs_measured": h2d_gbs, "h2d_bound_images_per_s": world * h2d_gbs * 1e9 / raw_w,
                    "host_cpus_bound_to_gpu_node": (len(numa_cpus) if numa_cpus else None)},
            "gpu_launches": int(launches_per_step) * a.steps, "roofline": roofline, "clocks": sampler.summary()}
+    # ---- side measurements (each optional; none of them changes the headline fields above) ---------------------------
+    tf_sust = _peaks_json().get("bf16_tflops_sustained")
+    if a.sustained_s > 0:
+        sus = measure_sustained(step, a.sustained_s, None, B, world, max_over_ranks, barrier, ClockSampler, local_rank)
+        rt.sync()
+        sus["tops"] = OPS[fam] * sus["value"] / world / 1e12
+        if tf_sust:
+            sus["frac_of_4x_bf16_sustained"] = sus["tops"] / (4.0 * float(tf_sust))
+            sus["peak"] = 4.0 * float(tf_sust)
+        sus["note"] = "back-to-back device-resident steps, no L2 flush, against 4 x MEASURED_PEAKS.bf16_tflops_sustained"
+        out["sustained"] = sus
+    if a.latency_calls > 0 and rank == 0:
+        out["latency_batch1"] = measure_latency(L, rt, fam, host_ptr, a.latency_calls)
+    if world > 1:
+        barrier()
+    if a.faults > 0 and fam == "cnv":
+        for ptr in (host_ptr, cls_ptr, words_ptr):
+            native.free_pinned(ptr)
+        host_ptr = None
+        rt.release()
+        out["faults"] = measure_faults(native, L, a.net, local_rank, rank, world, a.fault_images, a.faults, barrier, max_over_ranks)
+    if a.nets and rank == 0 and world == 1:
+        others = [n for n in PARAMS if n != a.net] if a.nets == "all" else [n for n in a.nets.split(",") if n in PARAMS and n != a.net]
+        rt.release()
+        out["networks"] = {n: measure_network(native, L, n, local_rank, 5, B) for n in others}
+    if world > 1 and os.environ.get("BENCH_ONE_PROCESS", "1") != "0":
+        # the engine's own multi-device path: ONE process feeding every GPU (one feeder thread per device), measured by rank 0 while the
+        # other ranks wait at the barrier
+        rt.release()
+        barrier()
+        if rank == 0:
+            try:
+                out["e2e_one_process"] = one_process_e2e(native, L, a.net, world, B, max(a.steps // 2, 3))
+            except Exception as e:
+                out["e2e_one_process"] = {"error": str(e)}
+        barrier()
+    if rank == 0 and world > 1:
+        try:
+            topo = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
+            out["e2e"]["topology"] = [ln for ln in topo.splitlines() if ln.startswith("GPU") or ln.strip().startswith("GPU0")][: world + 1]
+        except Exception:
+            pass
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
-        os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core
+        os.sched_setaffinity(0, all_cpus)  # the CPU baselines use every host core
         try:
             ips, _, cores, sample = run_reference_cpu(a.net, 4, 1, 1)
             out["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": cores, "kind": "reference", "sample": sample}
         except Exception as e:  # the checker is missing: say so, never substitute
             out["cpu_baseline"] = {"value": None, "unit": "images/s", "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
+        try:
+            out["cpu_baseline_fast"] = fast_cpu_port(a.net)
+        except Exception as e:
+            out["cpu_baseline_fast"] = {"value": None, "kind": "port", "sample": "unavailable: %s" % e}
     if rank == 0:
         print(json.dumps(out))
     if world > 1:

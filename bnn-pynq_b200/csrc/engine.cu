@@ -20,18 +20,23 @@ namespace bnnb {
   } while (0)
 #define CK(call) CKE(err_, call)
 
-// Copy lanes per device: the H2D copy of chunk i+1..i+3 overlaps the compute of chunk i.  All kernels of a device run on ONE
-// in-order compute stream (they are persistent full-GPU kernels: nothing is gained by interleaving them), so the activation
-// buffers exist once per device and a chunk's kernel time is not polluted by its neighbours'.
+// Chunk pipelines ("lanes") per device, each an in-order stream of its own: H2D copy -> quantise/pack -> layer kernels -> results.
+// The copy of chunk i+1..i+3 overlaps the compute of chunk i, and consecutive chunks' kernels overlap their ramp-up / ramp-down
+// (every kernel here is a persistent full-GPU kernel with a prologue of several microseconds: one in-order compute stream for all
+// chunks cost the host-buffer path 17 %).  The parameter stream (`compute`) carries uploads and fault patches; lanes wait for it
+// by event.
 static constexpr int kLanes = 4;
 
 struct Lane {
-  cudaStream_t copy = nullptr;
+  cudaStream_t s = nullptr;
   uint8_t* d_raw = nullptr;   // chunk x raw input bytes (CIFAR records / MNIST pixels)
+  void* d_in = nullptr;       // chunk x layer-0 input
+  uint32_t* act[2] = {nullptr, nullptr};  // ping-pong activations
   void* d_out = nullptr;      // chunk x out_bytes
   int* d_cls = nullptr;
-  int cap = 0;                // images the three buffers hold
-  cudaEvent_t copied = nullptr, prep_done = nullptr, done = nullptr, d2h = nullptr;
+  int cap = 0;                // images the staging buffers (d_raw, d_out, d_cls) hold
+  int act_cap = 0;            // images d_in / act hold
+  cudaEvent_t done = nullptr, copied = nullptr;  // fault epochs: the chunk's kernels (parameter stream) / its input copy (lane stream)
   bool used = false;
   // results of the chunk in flight, copied back when the lane is next needed (a device-to-pageable copy blocks the host: issuing it
   // right after the chunk would stop the feeder from running ahead)
@@ -41,11 +46,8 @@ struct Lane {
 struct DeviceState {
   int id = 0, num_sms = 148;
   bool ready = false;         // streams, parameter buffers and the parameter upload exist
-  cudaStream_t compute = nullptr;
+  cudaStream_t compute = nullptr;  // parameter stream: uploads, fault patches, taps, default stream of the device-resident path
   Lane lane[kLanes];
-  void* d_in = nullptr;       // layer-0 input of the chunk on the compute stream
-  uint32_t* act[2] = {nullptr, nullptr};  // ping-pong activations
-  int buf_cap = 0;            // images d_in / act hold
   DevLayer L[9];
   DevLayer* d_layers = nullptr;
   DevPatch* d_patches = nullptr;
@@ -63,7 +65,7 @@ struct DeviceState {
     bytes += n ? n : 16;
     return p;
   }
-  void release(void*& p, size_t n) {
+  template <typename T> void release(T*& p, size_t n) {
     if (p) { cudaFree(p); bytes -= n ? n : 16; }
     p = nullptr;
   }
@@ -72,15 +74,16 @@ struct DeviceState {
     cudaSetDevice(id);
     if (compute) cudaStreamSynchronize(compute);
     for (auto& ln : lane) {
-      if (ln.copy) { cudaStreamSynchronize(ln.copy); cudaStreamDestroy(ln.copy); }
-      for (cudaEvent_t* e : {&ln.copied, &ln.prep_done, &ln.done, &ln.d2h}) if (*e) cudaEventDestroy(*e);
-      cudaFree(ln.d_raw); cudaFree(ln.d_out); cudaFree(ln.d_cls);
+      if (ln.s) { cudaStreamSynchronize(ln.s); cudaStreamDestroy(ln.s); }
+      if (ln.done) cudaEventDestroy(ln.done);
+      if (ln.copied) cudaEventDestroy(ln.copied);
+      cudaFree(ln.d_raw); cudaFree(ln.d_in); cudaFree(ln.act[0]); cudaFree(ln.act[1]); cudaFree(ln.d_out); cudaFree(ln.d_cls);
       ln = Lane();
     }
     if (compute) cudaStreamDestroy(compute);
     compute = nullptr;
-    cudaFree(d_in); cudaFree(act[0]); cudaFree(act[1]); cudaFree(d_patches);
-    d_in = nullptr; act[0] = act[1] = nullptr; d_patches = nullptr; patch_cap = 0; buf_cap = 0;
+    cudaFree(d_patches);
+    d_patches = nullptr; patch_cap = 0;
     for (void* p : params) cudaFree(p);
     params.clear();
     for (cudaEvent_t e : tev) cudaEventDestroy(e);
@@ -106,6 +109,16 @@ struct TapCtx {
 struct Engine::Segments {   // fault epochs of one call: patches in fault order with their times
   std::vector<Patch> patches;
   std::vector<uint32_t> ptime;
+};
+
+// Fault epochs of one shard, PER KERNEL: a fault on layer l changes nothing below layer l, so only the kernel that holds layer l is
+// split at that fault's time; every other kernel runs whole chunks.  group = index of the kernel's last layer (the fused layer-0/1
+// kernel is group 1).  The device patch array is ordered by group, time order kept inside a group.
+struct FaultPlan {
+  int group_of_layer[9] = {};
+  std::vector<uint32_t> gtime[9];   // patch times of the group, ascending
+  size_t goff[9] = {};              // the group's offset in the device patch array
+  size_t gcur[9] = {};              // next patch of the group to apply
 };
 
 static int round_cap(int images) {  // buffer capacities grow in powers of two from 128 images
@@ -214,8 +227,9 @@ int Engine::upload(DeviceState& ds, std::string& err) {
   if (!ds.compute) {
     CKE(err, cudaStreamCreateWithFlags(&ds.compute, cudaStreamNonBlocking));
     for (auto& ln : ds.lane) {
-      CKE(err, cudaStreamCreateWithFlags(&ln.copy, cudaStreamNonBlocking));
-      for (cudaEvent_t* e : {&ln.copied, &ln.prep_done, &ln.done, &ln.d2h}) CKE(err, cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+      CKE(err, cudaStreamCreateWithFlags(&ln.s, cudaStreamNonBlocking));
+      CKE(err, cudaEventCreateWithFlags(&ln.done, cudaEventDisableTiming));
+      CKE(err, cudaEventCreateWithFlags(&ln.copied, cudaEventDisableTiming));
     }
     bool ok = true;
     for (int i = 0; i < net_.nlayers; i++) {
@@ -269,38 +283,39 @@ int Engine::load_parameters(const std::string& dir) {
   return 0;
 }
 
-int Engine::ensure_buffers(DeviceState& ds, int images, std::string& err) {
-  if (images <= ds.buf_cap) return 0;
+// Lane k's layer-0 input and activation ping-pong for chunks of `images` (grown on demand, powers of two).
+int Engine::ensure_buffers(DeviceState& ds, int k, int images, std::string& err) {
+  Lane& ln = ds.lane[k];
+  if (images <= ln.act_cap) return 0;
   const int cap = round_cap(images);
+  CKE(err, cudaStreamSynchronize(ln.s));
   CKE(err, cudaStreamSynchronize(ds.compute));
-  void* p;
-  p = ds.d_in; ds.release(p, (size_t)ds.buf_cap * net_.in_bytes); ds.d_in = nullptr;
-  for (int k = 0; k < 2; k++) { p = ds.act[k]; ds.release(p, ds.buf_cap ? act_bytes(ds.buf_cap) : 0); ds.act[k] = nullptr; }
-  ds.buf_cap = 0;
-  ds.d_in = ds.alloc((size_t)cap * net_.in_bytes, false);
-  ds.act[0] = (uint32_t*)ds.alloc(act_bytes(cap), false);
-  ds.act[1] = (uint32_t*)ds.alloc(act_bytes(cap), false);
-  if (!ds.d_in || !ds.act[0] || !ds.act[1]) {
-    cudaFree(ds.d_in); cudaFree(ds.act[0]); cudaFree(ds.act[1]);
-    ds.d_in = nullptr; ds.act[0] = ds.act[1] = nullptr;
+  ds.release(ln.d_in, (size_t)ln.act_cap * net_.in_bytes);
+  for (int j = 0; j < 2; j++) ds.release(ln.act[j], ln.act_cap ? act_bytes(ln.act_cap) : 0);
+  ln.act_cap = 0;
+  ln.d_in = ds.alloc((size_t)cap * net_.in_bytes, false);
+  ln.act[0] = (uint32_t*)ds.alloc(act_bytes(cap), false);
+  ln.act[1] = (uint32_t*)ds.alloc(act_bytes(cap), false);
+  if (!ln.d_in || !ln.act[0] || !ln.act[1]) {
+    cudaFree(ln.d_in); cudaFree(ln.act[0]); cudaFree(ln.act[1]);
+    ln.d_in = nullptr; ln.act[0] = ln.act[1] = nullptr;
     err = "cudaMalloc failed (activation buffers for " + std::to_string(cap) + " images, device " + std::to_string(ds.id) + ")";
     return -1;
   }
-  ds.buf_cap = cap;
+  ln.act_cap = cap;
   return 0;
 }
 
+// Lane k's staging buffers (raw input, results) for chunks of `images`.
 int Engine::ensure_lane(DeviceState& ds, int k, int images, std::string& err) {
   Lane& ln = ds.lane[k];
   if (images <= ln.cap) return 0;
   const int cap = round_cap(images);
   const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
-  CKE(err, cudaStreamSynchronize(ln.copy));
-  CKE(err, cudaStreamSynchronize(ds.compute));
-  void* p;
-  p = ln.d_raw; ds.release(p, (size_t)ln.cap * raw_bytes);
-  p = ln.d_out; ds.release(p, (size_t)ln.cap * net_.out_bytes);
-  p = ln.d_cls; ds.release(p, (size_t)ln.cap * 4);
+  CKE(err, cudaStreamSynchronize(ln.s));
+  ds.release(ln.d_raw, (size_t)ln.cap * raw_bytes);
+  ds.release(ln.d_out, (size_t)ln.cap * net_.out_bytes);
+  ds.release(ln.d_cls, (size_t)ln.cap * 4);
   ln.cap = 0;
   ln.d_raw = (uint8_t*)ds.alloc((size_t)cap * raw_bytes, false);
   ln.d_out = ds.alloc((size_t)cap * net_.out_bytes, false);
@@ -318,9 +333,7 @@ int Engine::ensure_lane(DeviceState& ds, int k, int images, std::string& err) {
 int Engine::ensure_patch_cap(DeviceState& ds, size_t count, std::string& err) {
   if (count <= ds.patch_cap) return 0;
   CKE(err, cudaStreamSynchronize(ds.compute));
-  void* p = ds.d_patches;
-  ds.release(p, ds.patch_cap * sizeof(DevPatch));
-  ds.d_patches = nullptr;
+  ds.release(ds.d_patches, ds.patch_cap * sizeof(DevPatch));
   ds.patch_cap = 0;
   const size_t cap = std::max<size_t>(64, count * 2);
   ds.d_patches = (DevPatch*)ds.alloc(cap * sizeof(DevPatch), false);
@@ -338,6 +351,7 @@ int Engine::apply_patches(const std::vector<Patch>& patches) {
   for (auto& d : dev_) {
     if (!d->ready) continue;
     CK(cudaSetDevice(d->id));
+    for (auto& ln : d->lane) CK(cudaStreamSynchronize(ln.s));
     if (ensure_patch_cap(*d, patches.size(), err_) != 0) return -1;
     CK(cudaMemcpyAsync(d->d_patches, patches.data(), patches.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, d->compute));
     launch_patch_apply(d->d_layers, net_.is_cnv, d->d_patches, (int)patches.size(), d->compute);
@@ -373,7 +387,7 @@ int Engine::mem_set(unsigned tl, unsigned mem, unsigned ind, unsigned thresh, ui
 // Kernel family and activation interchange format per layer (f4_common.cuh): on the fp4 core, between two fp4 kernels of a 1-bit
 // network, the producer writes e2m1 operand planes in the consumer's own shared-memory layout (staged there by TMA bulk copies).
 // per_layer: the LOP3+POPC taps (every layer on the CUDA-core kernels, bit planes everywhere).
-void Engine::plan_formats(const DeviceState& ds, bool per_layer, bool tensor_taps, int* fam, int* ofmt, bool* fused01) const {
+void Engine::plan_formats(const DeviceState& ds, bool per_layer, bool tensor_taps, int* fam, int* ofmt, bool* fused01, bool no_tiles) const {
   const bool popc_only = per_layer && !tensor_taps;
   for (int i = 0; i < 9; i++) { fam[i] = 0; ofmt[i] = ACT_BITS; }
   if (core_ == 2 && !popc_only)
@@ -385,7 +399,7 @@ void Engine::plan_formats(const DeviceState& ds, bool per_layer, bool tensor_tap
     const bool producer_f4 = fam[i] != 0 || (*fused01 && i == 1 && core_ == 2);
     if (!producer_f4 || p.out_mode != OUT_BIT || c.in_mode != IN_XNOR) continue;
     if (fam[i + 1] == 1 && fam[i] != 2) ofmt[i] = ACT_F4P;                        // conv consumer: image planes
-    if (fam[i + 1] == 2 && !p.pool && !(*fused01 && i == 1)) ofmt[i] = ACT_F4T;   // gemm consumer: 128-image tiles
+    if (fam[i + 1] == 2 && !p.pool && !(*fused01 && i == 1) && !no_tiles) ofmt[i] = ACT_F4T;   // gemm consumer: 128-image tiles
   }
 }
 
@@ -462,6 +476,60 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
   return launches;
 }
 
+// One chunk through every layer with fault epochs (images [img0, img0 + n) of the call): each kernel is launched once per run of
+// images between two fault times OF ITS OWN LAYER(S), the patches due at the start of a run applied just before it on the same
+// stream (k_patch_apply rewrites only that layer's operands).  Activations travel as bit planes or per-image e2m1 planes (no
+// 128-image tiles), so a run is a pointer offset into the chunk's buffers.
+int Engine::run_chunk_faulted(DeviceState& ds, const void* d_in, int n, long long img0, void* d_out, int* d_classes, int ncls,
+                              cudaStream_t s, uint32_t** bufs, FaultPlan& fp, std::string& err) {
+  int fam[9], ofmt[9];
+  bool fused01;
+  plan_formats(ds, false, false, fam, ofmt, &fused01, true);
+  const int NL = net_.nlayers;
+  auto out_stride = [&](int i) -> size_t {  // bytes per image of what layer i writes
+    if (i == NL - 1) return (size_t)net_.out_bytes;
+    const LayerDesc& l = net_.L[i];
+    const size_t px = (size_t)out_dim(l) * out_dim(l);
+    return ofmt[i] == ACT_F4P ? px * l.N / 2 : px * out_words_per_pixel(l) * 4;
+  };
+  const uint8_t* cur = (const uint8_t*)d_in;
+  size_t cur_stride = (size_t)net_.in_bytes;
+  for (int i = fused01 ? 1 : 0; i < NL; i++) {
+    const bool last = i == NL - 1, fused = fused01 && i == 1;
+    uint8_t* out = last ? (uint8_t*)d_out : (uint8_t*)bufs[i & 1];
+    const size_t ostr = out_stride(i);
+    const int grp = i, ifmt = (i > 0 && !fused) ? ofmt[i - 1] : ACT_BITS;
+    const std::vector<uint32_t>& gt = fp.gtime[grp];
+    int a = 0;
+    while (a < n) {
+      const size_t b = fp.gcur[grp];
+      while (fp.gcur[grp] < gt.size() && (long long)gt[fp.gcur[grp]] <= img0 + a) fp.gcur[grp]++;
+      if (fp.gcur[grp] > b) launch_patch_apply(ds.d_layers, net_.is_cnv, ds.d_patches + fp.goff[grp] + b, (int)(fp.gcur[grp] - b), s);
+      int nxt = n;
+      if (fp.gcur[grp] < gt.size() && (long long)gt[fp.gcur[grp]] < img0 + n) nxt = (int)((long long)gt[fp.gcur[grp]] - img0);
+      const int c = nxt - a;
+      const uint8_t* in_p = cur + (size_t)a * cur_stride;
+      uint32_t* out_p = (uint32_t*)(out + (size_t)a * ostr);
+      bool ok = true;
+      if (fused) ok = launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)in_p, out_p, c, ds.num_sms, core_ == 2, ofmt[1], ds.d_status, Tap01(), s);
+      else if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)in_p, out_p, c, nullptr, ds.num_sms, s);
+      else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], ds.d_status, nullptr, s)) {}
+      else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], ds.d_status, nullptr, s)) {}
+      else if (core_ >= 1 && launch_conv_tc(ds.L[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ds.d_status, nullptr, s)) {}
+      else if (core_ >= 1 && launch_gemm_tc(ds.L[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ds.d_status, nullptr, s)) {}
+      else if (ifmt != ACT_BITS || ofmt[i] != ACT_BITS) ok = false;
+      else launch_layer_popc(ds.L[i], (const uint32_t*)in_p, out_p, c, nullptr, ds.num_sms, s);
+      const cudaError_t le = cudaGetLastError();
+      if (!ok || le != cudaSuccess) { err = "layer " + std::to_string(i) + " launch (fault epochs): " + (ok ? cudaGetErrorString(le) : "no kernel for the planned format"); return -1; }
+      a = nxt;
+    }
+    cur = out;
+    cur_stride = ostr;
+  }
+  if (net_.is_cnv && d_classes) launch_cnv_classes((const int16_t*)d_out, n, ncls, d_classes, s);
+  return 0;
+}
+
 int Engine::infer_device(int slot, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t stream) {
   if (!loaded_) { err_ = "load_parameters has not been called"; return -1; }
   if (ensure_devices() != 0) return -1;
@@ -471,12 +539,12 @@ int Engine::infer_device(int slot, const void* d_in, int n, void* d_out, int* d_
   if (!ds.ready && upload(ds, err_) != 0) return -1;
   cudaStream_t s = stream ? stream : ds.compute;
   const int chunk = chunk_images();
-  if (n > 0 && ensure_buffers(ds, std::min(chunk, n), err_) != 0) return -1;
+  if (n > 0 && ensure_buffers(ds, 0, std::min(chunk, n), err_) != 0) return -1;  // lane 0's buffers serve this path
   int launches = 0;
   for (int off = 0; off < n; off += chunk) {
     const int c = std::min(chunk, n - off);
     const int r = run_chunk(ds, (const uint8_t*)d_in + (size_t)off * net_.in_bytes, c, (uint8_t*)d_out + (size_t)off * net_.out_bytes,
-                            d_classes ? d_classes + off : nullptr, ncls, s, nullptr, ds.act, err_);
+                            d_classes ? d_classes + off : nullptr, ncls, s, nullptr, ds.lane[0].act, err_);
     if (r < 0) return -1;
     launches += r;
   }
@@ -521,44 +589,29 @@ static int lfc_class_multi(uint64_t w, int ncls) {
   return (int)(unsigned)std::log2((double)w);
 }
 
-// One device's shard [lo, hi): copy lanes feed the in-order compute stream; with `seg`, chunks never cross a fault time and the
-// patches of an epoch are applied (in place, k_patch_apply) on the compute stream between them.
+// One device's shard [lo, hi): chunks go round-robin through the lanes (with fault epochs: run_shard_faulted).
 int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, int16_t* scores, uint64_t* words,
                       const Segments* seg, float* dev_ms, float* last_ms, int* last_imgs, std::string& err) {
   DeviceState& ds = *dev_[g];
   CKE(err, cudaSetDevice(ds.id));
   if (!ds.ready && upload(ds, err) != 0) return -1;
+  if (seg) { *dev_ms = 0; return run_shard_faulted(g, lo, hi, input, ncls, classes, words, *seg, last_ms, last_imgs, err); }
   const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
-  const int chunk = chunk_images(true), cnt = hi - lo;
-  cudaStream_t cs = ds.compute;
-  if (cnt > 0 && ensure_buffers(ds, std::min(chunk, cnt), err) != 0) return -1;
+  const int chunk = chunk_images(true);
   for (auto& ln : ds.lane) { ln.used = false; ln.pend_off = -1; }
-  size_t pi = 0;
-  if (seg && !seg->patches.empty()) {
-    if (ensure_patch_cap(ds, seg->patches.size(), err) != 0) return -1;
-    CKE(err, cudaMemcpyAsync(ds.d_patches, seg->patches.data(), seg->patches.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, cs));
-  }
-  auto apply_upto = [&](uint32_t t_incl) {  // patches with time <= t_incl
-    if (!seg) return;
-    const size_t b = pi;
-    while (pi < seg->patches.size() && seg->ptime[pi] <= t_incl) pi++;
-    if (pi > b) launch_patch_apply(ds.d_layers, net_.is_cnv, ds.d_patches + b, (int)(pi - b), cs);
-  };
   auto flush_lane = [&](Lane& ln) -> int {  // results of the lane's chunk in flight -> host
     if (ln.pend_off < 0) return 0;
     const int off = ln.pend_off, c = ln.pend_n;
-    CKE(err, cudaStreamWaitEvent(ln.copy, ln.done, 0));
     if (net_.is_cnv) {
-      if (scores) CKE(err, cudaMemcpyAsync(scores + (size_t)off * 64, ln.d_out, (size_t)c * 128, cudaMemcpyDeviceToHost, ln.copy));
-      if (classes) CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.copy));
+      if (scores) CKE(err, cudaMemcpyAsync(scores + (size_t)off * 64, ln.d_out, (size_t)c * 128, cudaMemcpyDeviceToHost, ln.s));
+      if (classes) CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.s));
     } else if (words) {
-      CKE(err, cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.copy));
+      CKE(err, cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.s));
     }
-    CKE(err, cudaEventRecord(ln.d2h, ln.copy));
     ln.pend_off = -1;
     return 0;
   };
-  // timing events: every chunk without faults (usec = kernel time of the whole call), the last chunk only with faults
+  // timing events around the layer kernels of every chunk
   size_t tused = 0;
   auto timing_pair = [&](cudaEvent_t* a, cudaEvent_t* b) -> int {
     while (ds.tev.size() < tused + 2) {
@@ -573,53 +626,138 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
   struct Timed { cudaEvent_t a, b; int n; };
   std::vector<Timed> timed;
   int cur = lo, ci = 0;
-  while (cur < hi) {
-    apply_upto((uint32_t)cur);
-    int nxt = hi;
-    if (seg && pi < seg->patches.size() && (long long)seg->ptime[pi] < (long long)hi) nxt = (int)seg->ptime[pi];
-    while (cur < nxt) {  // [cur, nxt): one parameter set
-      const int rem = nxt - cur;
+  {
+    while (cur < hi) {
+      const int rem = hi - cur;
       // The copy engine is the bottleneck of this path (3 073 B per image over PCIe): only the compute of the LAST chunk is not
       // hidden behind a copy, so the tail of a shard is cut into halves (full chunks elsewhere keep the kernels efficient).
       int c = std::min(chunk, rem);
-      if (nxt == hi && rem <= chunk + chunk / 2 && rem > 4096) c = std::min(chunk, (rem / 2 + 1023) / 1024 * 1024);
-      Lane& ln = ds.lane[ci % kLanes];
+      if (rem <= chunk + chunk / 2 && rem > 4096) c = std::min(chunk, (rem / 2 + 1023) / 1024 * 1024);
+      const int k = ci % kLanes;
+      Lane& ln = ds.lane[k];
       if (flush_lane(ln) != 0) return -1;
-      if (ensure_lane(ds, ci % kLanes, c, err) != 0) return -1;
-      if (ln.used) CKE(err, cudaStreamWaitEvent(ln.copy, ln.prep_done, 0));  // the prep kernel of the lane's previous chunk has read d_raw
-      CKE(err, cudaMemcpyAsync(ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.copy));
-      CKE(err, cudaEventRecord(ln.copied, ln.copy));
-      CKE(err, cudaStreamWaitEvent(cs, ln.copied, 0));
-      if (ln.used) CKE(err, cudaStreamWaitEvent(cs, ln.d2h, 0));             // d_out / d_cls of the previous chunk have left
-      if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ds.d_in, c, cs);
-      else launch_prep_mnist(ln.d_raw, (uint32_t*)ds.d_in, c, cs);
-      CKE(err, cudaEventRecord(ln.prep_done, cs));
-      const bool time_it = !seg || (cur + c == hi);
+      if (ensure_lane(ds, k, c, err) != 0 || ensure_buffers(ds, k, c, err) != 0) return -1;
+      CKE(err, cudaMemcpyAsync(ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
+      if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, ln.s);
+      else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, c, ln.s);
+      const bool time_it = true;
       Timed t{nullptr, nullptr, c};
-      if (time_it) { if (timing_pair(&t.a, &t.b) != 0) return -1; CKE(err, cudaEventRecord(t.a, cs)); }
-      if (run_chunk(ds, ds.d_in, c, ln.d_out, (net_.is_cnv && classes) ? ln.d_cls : nullptr, ncls, cs, nullptr, ds.act, err) < 0) return -1;
-      if (time_it) { CKE(err, cudaEventRecord(t.b, cs)); timed.push_back(t); }
-      CKE(err, cudaEventRecord(ln.done, cs));
+      if (time_it) { if (timing_pair(&t.a, &t.b) != 0) return -1; CKE(err, cudaEventRecord(t.a, ln.s)); }
+      if (run_chunk(ds, ln.d_in, c, ln.d_out, (net_.is_cnv && classes) ? ln.d_cls : nullptr, ncls, ln.s, nullptr, ln.act, err) < 0) return -1;
+      if (time_it) { CKE(err, cudaEventRecord(t.b, ln.s)); timed.push_back(t); }
       ln.used = true;
       ln.pend_off = cur; ln.pend_n = c;
       cur += c;
       ci++;
     }
   }
-  apply_upto(0xffffffffu);  // faults scheduled at or after this shard's end still persist on this device
   for (auto& ln : ds.lane) if (flush_lane(ln) != 0) return -1;
-  for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.copy));
+  for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.s));
+  CKE(err, cudaStreamSynchronize(ds.compute));
+  CKE(err, cudaGetLastError());
+  if (check_status(ds, err) != 0) return -1;
+  // Device time of the call = the time during which at least one chunk's layer kernels were in flight: the union of the chunks'
+  // [start, end] intervals (lanes overlap; a plain sum would count the overlap several times, and the gaps in which every lane waits
+  // for its copy are not kernel time).
+  std::vector<std::pair<float, float>> iv;
+  for (size_t i = 0; i < timed.size(); i++) {
+    float a = 0, b = 0;
+    if (i > 0) CKE(err, cudaEventElapsedTime(&a, timed[0].a, timed[i].a));
+    CKE(err, cudaEventElapsedTime(&b, timed[0].a, timed[i].b));
+    iv.emplace_back(a, b);
+    if (i + 1 == timed.size()) { *last_ms = b - a; *last_imgs = timed[i].n; }
+  }
+  std::sort(iv.begin(), iv.end());
+  float total = 0, end = -1e30f;
+  for (auto& x : iv) {
+    if (x.first > end) { total += x.second - x.first; end = x.second; }
+    else if (x.second > end) { total += x.second - end; end = x.second; }
+  }
+  *dev_ms = total;
+  return 0;
+}
+
+// A shard with fault epochs.  Copies still run on the lanes (H2D of chunk i+1.. overlaps the compute of chunk i), but every chunk's
+// kernels and patches run on the parameter stream, in image order: the patches rewrite operands in place, so the chunks' kernels must
+// not overlap.  Chunks are NOT cut at fault times - run_chunk_faulted splits only the kernel of the faulted layer.
+int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, uint64_t* words, const Segments& seg,
+                              float* last_ms, int* last_imgs, std::string& err) {
+  DeviceState& ds = *dev_[g];
+  const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
+  const int chunk = chunk_images(true);
+  cudaStream_t cs = ds.compute;
+  for (auto& ln : ds.lane) { ln.used = false; ln.pend_off = -1; }
+  // patches by kernel (group), time order kept
+  FaultPlan fp;
+  {
+    int fam[9], ofmt[9];
+    bool fused01;
+    plan_formats(ds, false, false, fam, ofmt, &fused01, true);
+    for (int l = 0; l < 9; l++) fp.group_of_layer[l] = (fused01 && l == 0) ? 1 : l;
+    std::vector<Patch> grouped;
+    grouped.reserve(seg.patches.size());
+    for (int grp = 0; grp < 9; grp++) {
+      fp.goff[grp] = grouped.size();
+      for (size_t i = 0; i < seg.patches.size(); i++)
+        if (fp.group_of_layer[seg.patches[i].layer] == grp) { grouped.push_back(seg.patches[i]); fp.gtime[grp].push_back(seg.ptime[i]); }
+    }
+    if (!grouped.empty()) {
+      for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.s));
+      if (ensure_patch_cap(ds, grouped.size(), err) != 0) return -1;
+      CKE(err, cudaMemcpyAsync(ds.d_patches, grouped.data(), grouped.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, cs));
+      CKE(err, cudaStreamSynchronize(cs));  // `grouped` dies with this block
+    }
+  }
+  auto flush_lane = [&](Lane& ln) -> int {  // results of the lane's chunk in flight -> host, after its kernels
+    if (ln.pend_off < 0) return 0;
+    const int off = ln.pend_off, c = ln.pend_n;
+    CKE(err, cudaStreamWaitEvent(ln.s, ln.done, 0));
+    if (net_.is_cnv) CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.s));
+    else CKE(err, cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.s));
+    ln.pend_off = -1;
+    return 0;
+  };
+  while (ds.tev.size() < 2) {
+    cudaEvent_t e;
+    CKE(err, cudaEventCreate(&e));
+    ds.tev.push_back(e);
+  }
+  int cur = lo, ci = 0;
+  bool timed = false;
+  while (cur < hi) {
+    const int rem = hi - cur;
+    int c = std::min(chunk, rem);
+    if (rem <= chunk + chunk / 2 && rem > 4096) c = std::min(chunk, (rem / 2 + 1023) / 1024 * 1024);
+    const int k = ci % kLanes;
+    Lane& ln = ds.lane[k];
+    if (flush_lane(ln) != 0) return -1;  // also orders this lane's next copy after the kernels that read its buffers
+    if (ensure_lane(ds, k, c, err) != 0 || ensure_buffers(ds, k, c, err) != 0) return -1;
+    if (ln.used) CKE(err, cudaStreamWaitEvent(ln.s, ln.done, 0));
+    CKE(err, cudaMemcpyAsync(ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
+    CKE(err, cudaEventRecord(ln.copied, ln.s));
+    CKE(err, cudaStreamWaitEvent(cs, ln.copied, 0));
+    if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, cs);
+    else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, c, cs);
+    const bool time_it = cur + c == hi;
+    if (time_it) CKE(err, cudaEventRecord(ds.tev[0], cs));
+    if (run_chunk_faulted(ds, ln.d_in, c, cur, ln.d_out, net_.is_cnv ? ln.d_cls : nullptr, ncls, cs, ln.act, fp, err) != 0) return -1;
+    if (time_it) { CKE(err, cudaEventRecord(ds.tev[1], cs)); timed = true; *last_imgs = c; }
+    CKE(err, cudaEventRecord(ln.done, cs));
+    ln.used = true;
+    ln.pend_off = cur; ln.pend_n = c;
+    cur += c;
+    ci++;
+  }
+  // faults scheduled at or after this shard's end still persist on this device
+  for (int grp = 0; grp < 9; grp++)
+    if (fp.gcur[grp] < fp.gtime[grp].size())
+      launch_patch_apply(ds.d_layers, net_.is_cnv, ds.d_patches + fp.goff[grp] + fp.gcur[grp], (int)(fp.gtime[grp].size() - fp.gcur[grp]), cs);
+  for (auto& ln : ds.lane) if (flush_lane(ln) != 0) return -1;
+  for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.s));
   CKE(err, cudaStreamSynchronize(cs));
   CKE(err, cudaGetLastError());
   if (check_status(ds, err) != 0) return -1;
-  float total = 0;
-  for (size_t i = 0; i < timed.size(); i++) {
-    float ms = 0;
-    CKE(err, cudaEventElapsedTime(&ms, timed[i].a, timed[i].b));
-    total += ms;
-    if (i + 1 == timed.size()) { *last_ms = ms; *last_imgs = timed[i].n; }
-  }
-  *dev_ms = total;
+  if (timed) CKE(err, cudaEventElapsedTime(last_ms, ds.tev[0], ds.tev[1]));
   return 0;
 }
 

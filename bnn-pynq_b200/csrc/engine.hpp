@@ -1,5 +1,5 @@
-// The CUDA runtime behind the C ABI: per-device replicated parameters, one in-order compute stream and a few copy lanes per
-// device, activation buffers grown on demand, stream-ordered fault epochs with in-place operand patches, and contiguous sharding
+// The CUDA runtime behind the C ABI: per-device replicated parameters, a few chunk pipelines (lanes) per device, buffers grown on
+// demand, stream-ordered fault epochs with in-place operand patches, and contiguous sharding
 // of an image batch over the visible GPUs (no collective; one feeder thread per device).
 // Replaces the host library's accelerator glue: FoldedMVInit/Deinit, FoldedMVOffloadBinarized (rawhls-offload.cpp:54-94),
 // testPrebuiltCIFAR10_multiple_images / _from_image (foldedmv-offload.h:316-416),
@@ -19,6 +19,7 @@ namespace bnnb {
 
 struct DeviceState;
 struct TapCtx;
+struct FaultPlan;
 
 class Engine {
  public:
@@ -44,7 +45,7 @@ class Engine {
   // Host-buffer inference.  `input`: CNV n x 3073-byte CIFAR records, LFC n x 784 pixel bytes.
   // classes (n, multi-image rule) / scores (CNV: n x 64 int16) / words (LFC: n x uint64) may be null.
   // usec_per_image: device time of the inference kernels only (the reference's timed region, foldedmv-offload.h:389-392): per
-  // device the sum of the CUDA-event durations of its chunks on its in-order compute stream, max over devices, / n.
+  // device the union of its chunks' CUDA-event intervals (lanes overlap), max over devices, / n.
   // Batches are sharded in contiguous ranges over the devices, but never thinner than kMinShard images per device.
   int infer_host(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, float* usec_per_image);
 
@@ -97,14 +98,18 @@ class Engine {
   int upload(DeviceState& ds, std::string& err);
   int check_status(DeviceState& ds, std::string& err);
   int apply_patches(const std::vector<Patch>& patches);                 // all uploaded devices, stream-ordered
-  int ensure_buffers(DeviceState& ds, int images, std::string& err);    // d_in + activation ping-pong for `images` per chunk
-  int ensure_lane(DeviceState& ds, int lane, int images, std::string& err);
+  int ensure_buffers(DeviceState& ds, int lane, int images, std::string& err);  // lane's d_in + activation ping-pong
+  int ensure_lane(DeviceState& ds, int lane, int images, std::string& err);     // lane's staging buffers
   int ensure_patch_cap(DeviceState& ds, size_t count, std::string& err);
-  void plan_formats(const DeviceState& ds, bool per_layer, bool tensor_taps, int* fam, int* ofmt, bool* fused01) const;
+  void plan_formats(const DeviceState& ds, bool per_layer, bool tensor_taps, int* fam, int* ofmt, bool* fused01, bool no_tiles = false) const;
+  int run_chunk_faulted(DeviceState& ds, const void* d_in, int n, long long img0, void* d_out, int* d_classes, int ncls, cudaStream_t s,
+                        uint32_t** bufs, FaultPlan& fp, std::string& err);
   int run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s, TapCtx* tap,
                 uint32_t** bufs, std::string& err);
   int run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, int16_t* scores, uint64_t* words,
                 const Segments* seg, float* dev_ms, float* last_ms, int* last_imgs, std::string& err);
+  int run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, uint64_t* words, const Segments& seg,
+                        float* last_ms, int* last_imgs, std::string& err);
   int run_sharded(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, const Segments* seg,
                   float* dev_ms_max, float* last_ms, int* last_imgs);
   int chunk_images(bool host = false) const;
