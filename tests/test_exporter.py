@@ -4,8 +4,9 @@ The reference exporter (bnn/src/training/finnthesizer.py) is Python 2 and needs 
 Parity is pinned on its OUTPUTS instead: the parameter sets the reference ships (copied under tests/golden/params) were written by
 that exporter.  For each of the five networks the test unfolds the shipped files into logical matrices with its own code, builds a
 training archive whose batch-norm parameters lead to exactly those weights and thresholds (half of the neurons through the
-negative-slope branch), runs the exporter and compares every file byte for byte.  The threshold arithmetic itself is checked on
-hand-computed cases."""
+negative-slope branch), runs the exporter and compares every file byte for byte.  The batch-norm folding arithmetic itself is
+pinned to the reference's own functions: tests/golden/make_golden_exporter.py executed makeFCBNComplex / makeFCBNComplex_QNN /
+makeConvBNComplex / quantize (finnthesizer.py:149-330) here and committed their outputs (test_bn_folding_equals_reference_functions)."""
 import os
 import sys
 
@@ -237,3 +238,34 @@ def test_load_npz_runs_on_the_gpu_like_the_oracle_on_the_exported_directory(net,
         got = c.classify_pixels(data)
     assert np.array_equal(got, o.classes(data, 10))
     assert len(c.classes) == 10
+
+
+# ---- pinned to the reference exporter's own arithmetic ------------------------------------------------------------------------------
+def _ref_cases():
+    sys.path.insert(0, os.path.join(GOLDEN))
+    import make_golden_exporter as mg
+    return mg
+
+
+def test_bn_folding_equals_reference_functions():
+    """bnn.finnthesizer's make_fc_bn / make_fc_bn_qnn / make_conv_bn / quantize against tests/golden/exporter_ref.npz, which
+    tests/golden/make_golden_exporter.py produced by executing the reference's own makeFCBNComplex, makeFCBNComplex_QNN,
+    makeConvBNComplex and quantize (bnn/src/training/finnthesizer.py:149-330) on the same seeded batch-norm parameters: thresholds
+    and (flipped, quantised) weights element for element, float32 and float64 archives, every precision combination the five
+    networks' drivers use."""
+    mg, f = _ref_cases(), _fth()
+    g = np.load(os.path.join(GOLDEN, "exporter_ref.npz"))
+    for kind, name, kw in mg.cases():
+        w, bias, beta, gamma, mean, invstd = mg.inputs(kind, name, kw)
+        if kind == "fc":
+            W, T = f.make_fc_bn(w, bias, beta, gamma, mean, invstd, kw["w_int"], kw["w_fract"], use_popcount=kw["popcount"])
+        elif kind == "fcq":
+            W, T = f.make_fc_bn_qnn(w, bias, beta, gamma, mean, invstd, kw["w_fract"], kw["a_fract"], kw["w_int"], kw["a_int"], kw["tb"], kw["tib"])
+        else:
+            W, T = f.make_conv_bn(w, bias, beta, gamma, mean, invstd, kw["inter"], kw["w_fract"], kw["a_fract"], 0, kw["w_int"], kw["a_int"], 8,
+                                  use_popcount=kw["popcount"], thres_bits=kw["tb"], thres_int_bits=kw["tib"])
+        assert np.array_equal(np.asarray(W, np.float64), g[name + "/W"]), name + ": weights"
+        assert np.array_equal(np.asarray(T, np.float64).reshape(g[name + "/T"].shape), g[name + "/T"]), name + ": thresholds"
+    xs = g["quantize/x"]
+    for (i, fr) in ((1, 0), (2, 0), (1, 1), (2, 2)):
+        assert np.array_equal(np.asarray(f.quantize(xs, i, fr), np.float64), g["quantize/%d_%d" % (i, fr)]), (i, fr)
