@@ -22,6 +22,20 @@ NETWORK_CNVW1A2 = "cnvW1A2"
 NETWORK_CNVW2A2 = "cnvW2A2"
 NETWORK_LFCW1A1 = "lfcW1A1"
 NETWORK_LFCW1A2 = "lfcW1A2"
+# The fork's hardened variants (bnn/bnn.py:41-53): the names exist so that campaign scripts import cleanly, but RUNTIME_CUDA does not
+# build them.  They replicate or interleave the FPGA's parameter BRAMs (TMR majority vote, interleaved weight words) and compute the
+# same function as their base network only while no fault is injected, so a faults.py campaign on them is NOT reproduced by the base
+# network: asking for one is an explicit error (DESIGN.md "out of scope").
+NETWORK_CNVW1A1_INTERLEAVED = "cnvW1A1-interleaved"
+NETWORK_CNVW1A1_RESILIENT_INTERLEAVED = "cnvW1A1-resilient-interleaved"
+NETWORK_CNVW1A1_TMR = "cnvW1A1-TMR"
+NETWORK_CNVW1A2_INTERLEAVED = "cnvW1A2-interleaved"
+NETWORK_CNVW1A2_RESILIENT_INTERLEAVED = "cnvW1A2-resilient-interleaved"
+NETWORK_CNVW2A2_INTERLEAVED = "cnvW2A2-interleaved"
+NETWORK_CNVW2A2_RESILIENT_INTERLEAVED = "cnvW2A2-resilient-interleaved"
+NETWORK_CNVW2A2_TMR = "cnvW2A2-TMR"
+NETWORK_LFCW1A2_INTERLEAVED = "lfcW1A2-interleaved"
+HARDENED_SUFFIXES = ("-TMR", "-interleaved", "-resilient-interleaved")
 
 BNN_ROOT_DIR = os.path.dirname(os.path.realpath(__file__))
 BNN_LIB_DIR = os.environ.get("BNN_B200_LIB_DIR", os.path.join(os.path.dirname(BNN_ROOT_DIR), "lib"))
@@ -78,6 +92,10 @@ class PynqBNN:
     def __init__(self, runtime, network, load_overlay=True):
         if runtime in (RUNTIME_HW, RUNTIME_SW):
             raise RuntimeError("runtime %r needs a PYNQ board; this package provides %r" % (runtime, RUNTIME_CUDA))
+        if network.endswith(HARDENED_SUFFIXES):
+            raise NotImplementedError("hardened variant %r is not supported by %s: it models FPGA parameter-memory redundancy "
+                                      "(TMR vote / interleaved words); use the base network %r for fault-free inference"
+                                      % (network, RUNTIME_CUDA, network.split("-")[0]))
         dllname = "{0}-{1}.so".format(runtime, network)
         if dllname not in _libraries:
             path = os.path.join(BNN_LIB_DIR, dllname)

@@ -139,3 +139,13 @@ def test_bind_host_to_device_never_raises():
             "assert r is not None or after == before; print('ok')") % os.path.join(ROOT, "bnn-pynq_b200")
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr
+
+
+def test_hardened_variants_are_named_and_refused_explicitly():
+    """The fork's -TMR / -interleaved networks (bnn/bnn.py:41-53) are exported names but an explicit NotImplementedError on the CUDA
+    runtime - not a misleading 'library not built' message."""
+    sys.path.insert(0, os.path.join(ROOT, "bnn-pynq_b200"))
+    import bnn
+    assert bnn.NETWORK_CNVW1A1_TMR == "cnvW1A1-TMR" and bnn.NETWORK_LFCW1A2_INTERLEAVED == "lfcW1A2-interleaved"
+    with pytest.raises(NotImplementedError, match="hardened variant"):
+        bnn.PynqBNN(bnn.RUNTIME_CUDA, bnn.NETWORK_CNVW1A1_TMR)

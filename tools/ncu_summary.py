@@ -2,7 +2,12 @@
 """Condense ncu exports into the tracked summaries under profiles/.
   tools/ncu_summary.py launches <launches.csv> <out.csv>     per-kernel launch count, total device time, share of the run
   tools/ncu_summary.py full <report.ncu-rep> <out.csv>       one row per profiled launch with the metrics DESIGN.md quotes
+  tools/ncu_summary.py traffic <full-summary.csv> <net> <images_per_launch>
+                                                             DRAM bytes of the network's dominant kernel (longest launch of the
+                                                             summary) -> profiles/traffic.json, which bench.py's roofline.traffic reads
 """
+import json
+import os
 import csv
 import subprocess
 import sys
@@ -50,5 +55,27 @@ def full(rep, dst):
             w.writerow([r[c][:90] if c == cols[0] else r[c] for c in cols])
 
 
+def traffic(summary_csv, net, images_per_launch):
+    rows = list(csv.reader(open(summary_csv)))
+    h, units = rows[0], rows[1]
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1, "nsecond": 1, "us": 1e3, "usecond": 1e3, "ms": 1e6, "msecond": 1e6, "s": 1e9, "second": 1e9}
+    num = lambda r, c: float(r[h.index(c)].replace(",", "")) * scale.get(units[h.index(c)], 1)   # the summary keeps ncu's units row
+    body = [r for r in rows[2:] if len(r) == len(h)]
+    top = max(body, key=lambda r: num(r, "gpu__time_duration.sum"))
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "traffic.json")
+    try:
+        d = json.load(open(path))
+    except Exception:
+        d = {}
+    d[net] = {"kernel": top[0], "dram_bytes_read": int(num(top, "dram__bytes_read.sum")), "dram_bytes_write": int(num(top, "dram__bytes_write.sum")),
+              "images_per_launch": int(images_per_launch), "duration_ns": int(num(top, "gpu__time_duration.sum")),
+              "source": "profiles/" + os.path.basename(summary_csv)}
+    json.dump(d, open(path, "w"), indent=1, sort_keys=True)
+    print(json.dumps(d[net]))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    if sys.argv[1] == "traffic":
+        traffic(sys.argv[2], sys.argv[3], sys.argv[4])
+    else:
+        {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
