@@ -32,6 +32,7 @@ _SIGS = {
     "bnnb_tap_act_size": (C.c_size_t, [C.c_void_p]),
     "bnnb_tap": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "bnnb_infer_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "bnnb_infer_device_static": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "bnnb_prep_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "bnnb_sync": (C.c_int, [C.c_void_p, C.c_int]),
     "bnnb_last_launches": (C.c_int, [C.c_void_p]),
@@ -184,6 +185,10 @@ class Runtime:
     # device-resident path (pointers are integers, e.g. torch.Tensor.data_ptr())
     def infer_device(self, d_in, n, d_out, d_classes=0, number_class=10, stream=0, slot=0):
         self._ck(self.L.bnnb_infer_device(self.h, slot, d_in, n, d_out, d_classes or None, number_class, stream or None))
+
+    def infer_device_static(self, d_in, n, d_out, d_classes=0, number_class=10, stream=0, slot=0):
+        """infer_device without any allocation: activation scratch in the library's static 32 MiB device array (include/bnn_b200.h)."""
+        self._ck(self.L.bnnb_infer_device_static(self.h, slot, d_in, n, d_out, d_classes or None, number_class, stream or None))
 
     def prep_device(self, d_raw, n, d_in, stream=0, slot=0):
         self._ck(self.L.bnnb_prep_device(self.h, slot, d_raw, n, d_in, stream or None))

@@ -90,6 +90,10 @@ int bnnb_infer_device(bnnb_ctx* c, int slot, const void* d_in, int n, void* d_ou
   GUARD(c);
   TRY return wrap(c, c->eng->infer_device(slot, d_in, n, d_out, d_cls, ncls, (cudaStream_t)stream)); CATCH(c, -1)
 }
+int bnnb_infer_device_static(bnnb_ctx* c, int slot, const void* d_in, int n, void* d_out, int* d_cls, int ncls, void* stream) {
+  GUARD(c);
+  TRY return wrap(c, c->eng->infer_device_static(slot, d_in, n, d_out, d_cls, ncls, (cudaStream_t)stream)); CATCH(c, -1)
+}
 int bnnb_prep_device(bnnb_ctx* c, int slot, const void* d_raw, int n, void* d_in, void* stream) {
   GUARD(c);
   TRY return wrap(c, c->eng->prep_device(slot, d_raw, n, d_in, (cudaStream_t)stream)); CATCH(c, -1)

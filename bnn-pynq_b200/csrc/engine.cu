@@ -553,6 +553,66 @@ int Engine::infer_device(int slot, const void* d_in, int n, void* d_out, int* d_
   return 0;
 }
 
+// ---- device-resident inference that allocates nothing (no counterpart in the reference) ----
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the
+// inter-layer activation scratch - the two ping-pong buffers infer_device takes from cudaMalloc - lives in ONE file-scope device
+// array of kStaticScratchBytes, which every GPU that loads this library holds until the process exits.  In host code the array's
+// name is only a host-side stand-in for the symbol, not a device address: the address is taken per device with
+// cudaGetSymbolAddress (device current, return code checked) and that pointer is what the kernels receive.
+// Every call shares the array and finds the previous call's contents in it.  Nothing in it has to start at zero: each layer kernel
+// writes every activation it later reads, and the rows of a 128-image e2m1 tile beyond the batch hold stale but finite codes that
+// feed accumulator rows which are never stored - so nothing is cleared.  Calls that overlap on the GPU (two streams, two contexts
+// of this library on one device) race on the array: serialise them.
+static constexpr size_t kStaticScratchHalf = (size_t)16 << 20;            // one ping-pong buffer
+static constexpr size_t kStaticScratchBytes = 2 * kStaticScratchHalf;     // 32 MiB per GPU
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[64] = {};   // per device id: the array's device address, resolved once
+
+int Engine::static_max_images() const {
+  const size_t per = act_bytes(128) / 128;     // act_bytes rounds the batch up to whole 128-image tiles
+  return (int)(kStaticScratchHalf / per / 128 * 128);
+}
+
+int Engine::infer_device_static(int slot, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t stream) {
+  if (!loaded_) { err_ = "load_parameters has not been called"; return -1; }
+  if (slot < 0 || slot >= (int)dev_.size()) { err_ = "bad device slot"; return -1; }
+  DeviceState& ds = *dev_[slot];
+  if (!ds.ready) {  // the parameter upload allocates: it belongs to an ordinary call made beforehand, never to this entry point
+    err_ = "bnnb_infer_device_static allocates nothing, so the device must hold the parameters already: make one ordinary call "
+           "(bnnb_infer_device / bnnb_classify_*) on this device after bnnb_load_parameters first";
+    return -1;
+  }
+  if (profile_) { err_ = "bnnb_infer_device_static: per-layer profiling creates CUDA events; disable it (bnnb_profile_enable(c, 0))"; return -1; }
+  if (ds.id < 0 || ds.id >= 64) { err_ = "bnnb_infer_device_static: device id out of range"; return -1; }
+  if (n <= 0) { last_launches_ = 0; return 0; }
+  const int max_n = static_max_images();
+  if (n > max_n || act_bytes(n) > kStaticScratchHalf) {
+    err_ = "bnnb_infer_device_static: " + std::to_string(n) + " images exceed the static scratch (" + std::to_string(kStaticScratchBytes >> 20) +
+           " MiB per GPU = at most " + std::to_string(max_n) + " images per call for " + net_.name + "); split the batch or use bnnb_infer_device";
+    return -1;
+  }
+  CK(cudaSetDevice(ds.id));
+  unsigned char* base;
+  {
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[ds.id]) {  // set-up, once per device, with that device current
+      void* p = nullptr;
+      CK(cudaGetSymbolAddress(&p, g_static_scratch));
+      if (!p) { err_ = "cudaGetSymbolAddress returned a null address for the static scratch"; return -1; }
+      g_static_ptr[ds.id] = (unsigned char*)p;
+    }
+    base = g_static_ptr[ds.id];
+  }
+  uint32_t* bufs[2] = {reinterpret_cast<uint32_t*>(base), reinterpret_cast<uint32_t*>(base + kStaticScratchHalf)};
+  cudaStream_t s = stream ? stream : ds.compute;
+  const int r = run_chunk(ds, d_in, n, d_out, d_classes, ncls, s, nullptr, bufs, err_);
+  if (r < 0) return -1;
+  last_launches_ = r;
+  CK(cudaGetLastError());
+  return 0;
+}
+
 int Engine::prep_device(int slot, const void* d_raw, int n, void* d_in, cudaStream_t stream) {
   if (ensure_devices() != 0) return -1;
   if (slot < 0 || slot >= (int)dev_.size()) { err_ = "bad device slot"; return -1; }

@@ -59,6 +59,11 @@ class Engine {
   // BlackBoxJam reads it (CNV int8 HWC 3072 B/img; LFC 104 B/img), `d_out` what it writes (CNV 64 x int16; LFC uint64),
   // `d_classes` optional int32 (CNV only).  Enqueued on `stream` (0 = the engine's own stream); returns without syncing.
   int infer_device(int slot, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t stream);
+  // infer_device without any allocation: the activation scratch is a static 32 MiB device array (engine.cu), so n is limited to
+  // static_max_images() per call, the device must already hold the parameters (one ordinary call made before), and calls that overlap
+  // on one GPU race on the shared array.  No counterpart in the reference.
+  int infer_device_static(int slot, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t stream);
+  int static_max_images() const;
   // raw records / pixels (device) -> layer-0 input (device)
   int prep_device(int slot, const void* d_raw, int n, void* d_in, cudaStream_t stream);
   // Waits for the slot's streams and reports a kernel that gave up waiting on an mbarrier (device status flag) as an error.

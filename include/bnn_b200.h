@@ -115,7 +115,21 @@ int bnnb_tap(bnnb_ctx* c, const uint8_t* input, int n, int32_t* acc, int8_t* act
  * d_classes: optional int32 (CNV).  All device pointers on device slot `slot`; stream: a cudaStream_t (NULL = the library's).
  * Asynchronous: call bnnb_sync or synchronise the stream.  bnnb_last_launches: kernels enqueued by the last call. */
 int bnnb_infer_device(bnnb_ctx* c, int slot, const void* d_in, int n, void* d_out, int* d_classes, int number_class, void* stream);
-int bnnb_prep_device(bnnb_ctx* c, int slot, const void* d_raw, int n, void* d_in, void* stream);  /* records/pixels -> layer-0 input */
+int bnnb_prep_device(bnnb_ctx* c, int slot, const void* d_raw, int n, void* d_in, void* stream);
+/* bnnb_infer_device that allocates NOTHING.  No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same
+ * results, same asynchrony as bnnb_infer_device; the inter-layer activation scratch is a static device array of 32 MiB that every GPU
+ * which loads the library holds until the process exits, so:
+ *   - n is limited per call by that array (two buffers of 16 MiB, each holding the widest inter-layer tensor in any format a core
+ *     may plan): 512 images for cnvW1A1, 1 152 for cnvW1A2 / cnvW2A2, 32 768 for lfcW1A1, 65 536 for lfcW1A2; more is refused
+ *     (-1) with the limit in bnnb_last_error;
+ *   - the device must already hold the parameters: make one ordinary call (bnnb_infer_device / bnnb_classify_*) on that device
+ *     after bnnb_load_parameters, outside any capture - the upload allocates, this call never does (no cudaMalloc / cudaFree, no
+ *     allocating library routine; per-layer profiling must be off).  Its first call on a device also looks the array's address up
+ *     (cudaGetSymbolAddress: no allocation): make that first call outside graph capture too;
+ *   - every call shares the array and finds the previous call's contents; nothing in it needs clearing (each kernel writes every
+ *     activation it reads).  Calls that overlap on one GPU - two streams, two contexts - race on it: serialise them. */
+int bnnb_infer_device_static(bnnb_ctx* c, int slot, const void* d_in, int n, void* d_out, int* d_classes, int number_class, void* stream);  /* records/pixels -> layer-0 input */
 /* Waits for the device and fails if a kernel gave up waiting on an mbarrier since the last check (results invalid). */
 int bnnb_sync(bnnb_ctx* c, int slot);
 int bnnb_last_launches(bnnb_ctx* c);
