@@ -135,34 +135,40 @@ __global__ void k_patch_apply(const DevLayer* __restrict__ Ls, int is_cnv, const
     const uint64_t oldw = *wfw;
     __syncwarp();
     if (lane == 0) *wfw = e.value;
-    __syncwarp();  // the folded word is visible to the whole warp: everything below re-derives from it
+    // Everything below derives from the patch's own value (the fields of columns k0..k1-1), never from the folded memory: a chain of
+    // dependent global loads per bit made one patch cost tens of microseconds, and the fault path pays it once per fault.
+    const uint32_t fmask = (1u << d.wbits) - 1;
+    auto fld = [&](int k) { return (int)((e.value >> ((k - k0) * d.wbits)) & fmask); };  // k in [k0, k1)
     if (is_cnv && e.layer == 0) {  // int8x4 words [64][8], K = 27 padded to 32
-      for (int k = k0 + lane; k < k1; k += 32)
-        reinterpret_cast<int8_t*>(L.wp)[row * 32 + k] = (int8_t)weight_value(weight_field(L.wf, d, row, k), d.wbits);
+      for (int k = k0 + lane; k < k1; k += 32) reinterpret_cast<int8_t*>(L.wp)[row * 32 + k] = (int8_t)weight_value(fld(k), d.wbits);
       __syncwarp();
       continue;
     }
-    {  // popc planes: uint32 [plane][K/32][N]
+    {  // popc planes: uint32 [plane][K/32][N]: the bits of the range replaced inside the (at most two) words it touches
       const int w0 = k0 >> 5, nwd = ((k1 - 1) >> 5) - w0 + 1;
       for (int j = lane; j < nwd * d.wbits; j += 32) {
         const int plane = j / nwd, kw = w0 + j % nwd;
-        uint32_t w = 0;
-        for (int b = 0; b < 32; b++) w |= (uint32_t)((weight_field(L.wf, d, row, kw * 32 + b) >> plane) & 1) << b;
-        L.wp[((size_t)plane * L.kwords + kw) * d.N + row] = w;
+        const int lo = max(k0, kw * 32), hi = min(k1, kw * 32 + 32);
+        uint32_t bits = 0, m = 0;
+        for (int k = lo; k < hi; k++) { bits |= (uint32_t)((fld(k) >> plane) & 1) << (k & 31); m |= 1u << (k & 31); }
+        uint32_t* wp = L.wp + ((size_t)plane * L.kwords + kw) * d.N + row;
+        *wp = (*wp & ~m) | bits;
       }
     }
     if (L.w8)
-      for (int k = k0 + lane; k < k1; k += 32) L.w8[(size_t)row * L.kpad + k] = (int8_t)weight_value(weight_field(L.wf, d, row, k), d.wbits);
+      for (int k = k0 + lane; k < k1; k += 32) L.w8[(size_t)row * L.kpad + k] = (int8_t)weight_value(fld(k), d.wbits);
     if (L.w4) {
-      const int b0 = k0 >> 1, b1 = (k1 - 1) >> 1;  // bytes (two nibbles each; the neighbour nibble is re-derived, not read)
+      const int b0 = k0 >> 1, b1 = (k1 - 1) >> 1;  // bytes (two nibbles each); a nibble outside the range keeps its old code
       for (int kb = b0 + lane; kb <= b1; kb += 32) {
-        uint32_t byte = 0;
+        uint8_t* bp = L.w4 + (size_t)row * (L.kpad / 2) + kb;
+        uint32_t byte = *bp;
         for (int h = 0; h < 2; h++) {
           const int k = 2 * kb + h;
-          const int v = k < d.K ? weight_value(weight_field(L.wf, d, row, k), d.wbits) : 0;
-          byte |= (v == 0 ? 0x0u : (v == 1 ? 0x2u : (v == -1 ? 0xAu : 0xCu))) << (4 * h);
+          if (k < k0 || k >= k1) continue;
+          const int v = weight_value(fld(k), d.wbits);
+          byte = (byte & ~(0xFu << (4 * h))) | ((v == 0 ? 0x0u : (v == 1 ? 0x2u : (v == -1 ? 0xAu : 0xCu))) << (4 * h));
         }
-        L.w4[(size_t)row * (L.kpad / 2) + kb] = (uint8_t)byte;
+        *bp = (uint8_t)byte;
       }
       __syncwarp();
       if (L.w4s && L.kpad % 64 == 0 && d.N % 64 == 0) {  // slab copy: 16-byte units [N/NB][K/64][2][NB]
