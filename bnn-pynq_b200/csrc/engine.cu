@@ -20,12 +20,13 @@ namespace bnnb {
   } while (0)
 #define CK(call) CKE(err_, call)
 
+static constexpr int kLanes = 4;  // chunk pipelines per device (see Lane)
+
 // Chunk pipelines ("lanes") per device, each an in-order stream of its own: H2D copy -> quantise/pack -> layer kernels -> results.
 // The copy of chunk i+1..i+3 overlaps the compute of chunk i, and consecutive chunks' kernels overlap their ramp-up / ramp-down
 // (every kernel here is a persistent full-GPU kernel with a prologue of several microseconds: one in-order compute stream for all
 // chunks cost the host-buffer path 17 %).  The parameter stream (`compute`) carries uploads and fault patches; lanes wait for it
 // by event.
-static constexpr int kLanes = 4;
 
 struct Lane {
   cudaStream_t s = nullptr;
@@ -36,7 +37,6 @@ struct Lane {
   int* d_cls = nullptr;
   int cap = 0;                // images the staging buffers (d_raw, d_out, d_cls) hold
   int act_cap = 0;            // images d_in / act hold
-  cudaEvent_t done = nullptr, copied = nullptr;  // fault epochs: the chunk's kernels (parameter stream) / its input copy (lane stream)
   bool used = false;
   // results of the chunk in flight, copied back when the lane is next needed (a device-to-pageable copy blocks the host: issuing it
   // right after the chunk would stop the feeder from running ahead)
@@ -48,8 +48,13 @@ struct DeviceState {
   bool ready = false;         // streams, parameter buffers and the parameter upload exist
   cudaStream_t compute = nullptr;  // parameter stream: uploads, fault patches, taps, default stream of the device-resident path
   Lane lane[kLanes];
-  DevLayer L[9];
+  DevLayer L[9];              // parameter set 0: what every path uses; the state that persists between calls
   DevLayer* d_layers = nullptr;
+  unsigned char* arena = nullptr;  // set 0's arrays and its DevLayer table live in one allocation, so that a set is cloned by one copy
+  size_t arena_bytes = 0;
+  // Fault epochs: lane k >= 1 works on its own clone of the parameters (taken from set 0 at the start of the call) and applies every
+  // patch to it in its own image order, so lanes never have to be ordered against each other (run_shard_faulted)
+  struct ParamSet { unsigned char* arena = nullptr; DevLayer L[9]; DevLayer* d_layers = nullptr; } clone[kLanes - 1];
   DevPatch* d_patches = nullptr;
   size_t patch_cap = 0;
   int* d_status = nullptr;    // set by a kernel whose mbarrier wait timed out: mapped pinned host memory (device alias of h_status)
@@ -75,8 +80,6 @@ struct DeviceState {
     if (compute) cudaStreamSynchronize(compute);
     for (auto& ln : lane) {
       if (ln.s) { cudaStreamSynchronize(ln.s); cudaStreamDestroy(ln.s); }
-      if (ln.done) cudaEventDestroy(ln.done);
-      if (ln.copied) cudaEventDestroy(ln.copied);
       cudaFree(ln.d_raw); cudaFree(ln.d_in); cudaFree(ln.act[0]); cudaFree(ln.act[1]); cudaFree(ln.d_out); cudaFree(ln.d_cls);
       ln = Lane();
     }
@@ -86,6 +89,8 @@ struct DeviceState {
     d_patches = nullptr; patch_cap = 0;
     for (void* p : params) cudaFree(p);
     params.clear();
+    arena = nullptr; arena_bytes = 0;
+    for (auto& c : clone) c = ParamSet();
     for (cudaEvent_t e : tev) cudaEventDestroy(e);
     tev.clear();
     if (h_status) cudaFreeHost(h_status);
@@ -118,7 +123,7 @@ struct FaultPlan {
   int group_of_layer[9] = {};
   std::vector<uint32_t> gtime[9];   // patch times of the group, ascending
   size_t goff[9] = {};              // the group's offset in the device patch array
-  size_t gcur[9] = {};              // next patch of the group to apply
+  size_t gcur[kLanes][9] = {};      // per lane (= per parameter set): next patch of the group to apply
 };
 
 static int round_cap(int images) {  // buffer capacities grow in powers of two from 128 images
@@ -221,6 +226,34 @@ int Engine::ensure_devices() {
   return 0;
 }
 
+// Lays one parameter set out in an arena starting at `base` (256-byte aligned pieces): every layer's folded memories and derived
+// operands, then the DevLayer table the patch kernel reads.  Returns the arena size; base may be null to measure only.
+static size_t carve_params(const NetDesc& net, unsigned char* base, DevLayer* L, DevLayer** table) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) { unsigned char* p = base + off; off += (std::max<size_t>(bytes, 16) + 255) / 256 * 256; return p; };
+  for (int i = 0; i < net.nlayers; i++) {
+    const LayerDesc& l = net.L[i];
+    DevLayer& D = L[i];
+    D.d = l;
+    D.kwords = l.K / 32;
+    D.kpad = (l.K + 31) / 32 * 32;
+    D.wf = (uint64_t*)take((size_t)l.pe * l.wmem * 8);
+    D.tf = (int32_t*)take((size_t)l.pe * l.tmem * std::max(l.nthr, 1) * 4);
+    const bool l0 = net.is_cnv && i == 0;
+    D.wp = (uint32_t*)take(l0 ? (size_t)64 * 8 * 4 : (size_t)l.wbits * D.kwords * l.N * 4);
+    D.w8 = nullptr; D.w4 = nullptr; D.w4s = nullptr; D.thr_tc = nullptr;
+    if (!l0) {  // operands of the tensor-core paths
+      D.w8 = (int8_t*)take((size_t)l.N * D.kpad);
+      D.w4 = (uint8_t*)take((size_t)l.N * D.kpad / 2);
+      D.w4s = (uint8_t*)take((size_t)l.N * D.kpad / 2);
+      D.thr_tc = (int32_t*)take((size_t)l.N * 2 * 4);
+    }
+    D.thr = (int32_t*)take((size_t)l.N * 2 * 4);
+  }
+  *table = (DevLayer*)take(sizeof(DevLayer) * 9);
+  return off;
+}
+
 // First use of a device (or first use after release / load_parameters): streams, parameter buffers, upload + on-device re-pack.
 int Engine::upload(DeviceState& ds, std::string& err) {
   CKE(err, cudaSetDevice(ds.id));
@@ -228,32 +261,12 @@ int Engine::upload(DeviceState& ds, std::string& err) {
     CKE(err, cudaStreamCreateWithFlags(&ds.compute, cudaStreamNonBlocking));
     for (auto& ln : ds.lane) {
       CKE(err, cudaStreamCreateWithFlags(&ln.s, cudaStreamNonBlocking));
-      CKE(err, cudaEventCreateWithFlags(&ln.done, cudaEventDisableTiming));
-      CKE(err, cudaEventCreateWithFlags(&ln.copied, cudaEventDisableTiming));
     }
-    bool ok = true;
-    for (int i = 0; i < net_.nlayers; i++) {
-      const LayerDesc& l = net_.L[i];
-      DevLayer& D = ds.L[i];
-      D.d = l;
-      D.kwords = l.K / 32;
-      D.kpad = (l.K + 31) / 32 * 32;
-      D.wf = (uint64_t*)ds.alloc((size_t)l.pe * l.wmem * 8, true);
-      D.tf = (int32_t*)ds.alloc((size_t)l.pe * l.tmem * std::max(l.nthr, 1) * 4, true);
-      const bool l0 = net_.is_cnv && i == 0;
-      D.wp = (uint32_t*)ds.alloc(l0 ? (size_t)64 * 8 * 4 : (size_t)l.wbits * D.kwords * l.N * 4, true);
-      D.w8 = nullptr; D.w4 = nullptr; D.w4s = nullptr; D.thr_tc = nullptr;
-      if (!l0) {  // operands of the tensor-core paths
-        D.w8 = (int8_t*)ds.alloc((size_t)l.N * D.kpad, true);
-        D.w4 = (uint8_t*)ds.alloc((size_t)l.N * D.kpad / 2, true);
-        D.w4s = (uint8_t*)ds.alloc((size_t)l.N * D.kpad / 2, true);
-        D.thr_tc = (int32_t*)ds.alloc((size_t)l.N * 2 * 4, true);
-        ok = ok && D.w8 && D.w4 && D.w4s && D.thr_tc;
-      }
-      D.thr = (int32_t*)ds.alloc((size_t)l.N * 2 * 4, true);
-      ok = ok && D.wf && D.tf && D.wp && D.thr;
-    }
-    ds.d_layers = (DevLayer*)ds.alloc(sizeof(DevLayer) * 9, true);
+    DevLayer* tbl = nullptr;
+    ds.arena_bytes = carve_params(net_, nullptr, ds.L, &tbl);
+    ds.arena = (unsigned char*)ds.alloc(ds.arena_bytes, true);
+    const bool ok = ds.arena != nullptr;
+    if (ok) carve_params(net_, ds.arena, ds.L, &ds.d_layers);
     if (cudaHostAlloc((void**)&ds.h_status, 4, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) ds.h_status = nullptr;
     if (ds.h_status) { *ds.h_status = 0; if (cudaHostGetDevicePointer((void**)&ds.d_status, ds.h_status, 0) != cudaSuccess) ds.d_status = nullptr; }
     if (!ok || !ds.d_layers || !ds.d_status) { err = "cudaMalloc failed (parameters, device " + std::to_string(ds.id) + ")"; ds.destroy(); return -1; }
@@ -476,12 +489,13 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
   return launches;
 }
 
-// One chunk through every layer with fault epochs (images [img0, img0 + n) of the call): each kernel is launched once per run of
+// One chunk through every layer with fault epochs (images [img0, img0 + n) of the call), on parameter set PL / d_layers, which
+// belongs to `lane`: each kernel is launched once per run of
 // images between two fault times OF ITS OWN LAYER(S), the patches due at the start of a run applied just before it on the same
 // stream (k_patch_apply rewrites only that layer's operands).  Activations travel as bit planes or per-image e2m1 planes (no
 // 128-image tiles), so a run is a pointer offset into the chunk's buffers.
-int Engine::run_chunk_faulted(DeviceState& ds, const void* d_in, int n, long long img0, void* d_out, int* d_classes, int ncls,
-                              cudaStream_t s, uint32_t** bufs, FaultPlan& fp, std::string& err) {
+int Engine::run_chunk_faulted(DeviceState& ds, const DevLayer* PL, DevLayer* d_layers, int lane, const void* d_in, int n, long long img0,
+                              void* d_out, int* d_classes, int ncls, cudaStream_t s, uint32_t** bufs, FaultPlan& fp, std::string& err) {
   int fam[9], ofmt[9];
   bool fused01;
   plan_formats(ds, false, false, fam, ofmt, &fused01, true);
@@ -500,25 +514,26 @@ int Engine::run_chunk_faulted(DeviceState& ds, const void* d_in, int n, long lon
     const size_t ostr = out_stride(i);
     const int grp = i, ifmt = (i > 0 && !fused) ? ofmt[i - 1] : ACT_BITS;
     const std::vector<uint32_t>& gt = fp.gtime[grp];
+    size_t& gc = fp.gcur[lane][grp];
     int a = 0;
     while (a < n) {
-      const size_t b = fp.gcur[grp];
-      while (fp.gcur[grp] < gt.size() && (long long)gt[fp.gcur[grp]] <= img0 + a) fp.gcur[grp]++;
-      if (fp.gcur[grp] > b) launch_patch_apply(ds.d_layers, net_.is_cnv, ds.d_patches + fp.goff[grp] + b, (int)(fp.gcur[grp] - b), s);
+      const size_t b = gc;
+      while (gc < gt.size() && (long long)gt[gc] <= img0 + a) gc++;
+      if (gc > b) launch_patch_apply(d_layers, net_.is_cnv, ds.d_patches + fp.goff[grp] + b, (int)(gc - b), s);
       int nxt = n;
-      if (fp.gcur[grp] < gt.size() && (long long)gt[fp.gcur[grp]] < img0 + n) nxt = (int)((long long)gt[fp.gcur[grp]] - img0);
+      if (gc < gt.size() && (long long)gt[gc] < img0 + n) nxt = (int)((long long)gt[gc] - img0);
       const int c = nxt - a;
       const uint8_t* in_p = cur + (size_t)a * cur_stride;
       uint32_t* out_p = (uint32_t*)(out + (size_t)a * ostr);
       bool ok = true;
-      if (fused) ok = launch_cnv01_tc(ds.L[0], ds.L[1], (const int8_t*)in_p, out_p, c, ds.num_sms, core_ == 2, ofmt[1], ds.d_status, Tap01(), s);
-      else if (net_.is_cnv && i == 0) launch_conv0(ds.L[0], (const int8_t*)in_p, out_p, c, nullptr, ds.num_sms, s);
-      else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], ds.d_status, nullptr, s)) {}
-      else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], ds.d_status, nullptr, s)) {}
-      else if (core_ >= 1 && launch_conv_tc(ds.L[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ds.d_status, nullptr, s)) {}
-      else if (core_ >= 1 && launch_gemm_tc(ds.L[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ds.d_status, nullptr, s)) {}
+      if (fused) ok = launch_cnv01_tc(PL[0], PL[1], (const int8_t*)in_p, out_p, c, ds.num_sms, core_ == 2, ofmt[1], ds.d_status, Tap01(), s);
+      else if (net_.is_cnv && i == 0) launch_conv0(PL[0], (const int8_t*)in_p, out_p, c, nullptr, ds.num_sms, s);
+      else if (fam[i] == 1 && launch_conv_f4(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], ds.d_status, nullptr, s)) {}
+      else if (fam[i] == 2 && launch_gemm_f4(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], ds.d_status, nullptr, s)) {}
+      else if (core_ >= 1 && launch_conv_tc(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ds.d_status, nullptr, s)) {}
+      else if (core_ >= 1 && launch_gemm_tc(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ds.d_status, nullptr, s)) {}
       else if (ifmt != ACT_BITS || ofmt[i] != ACT_BITS) ok = false;
-      else launch_layer_popc(ds.L[i], (const uint32_t*)in_p, out_p, c, nullptr, ds.num_sms, s);
+      else launch_layer_popc(PL[i], (const uint32_t*)in_p, out_p, c, nullptr, ds.num_sms, s);
       const cudaError_t le = cudaGetLastError();
       if (!ok || le != cudaSuccess) { err = "layer " + std::to_string(i) + " launch (fault epochs): " + (ok ? cudaGetErrorString(le) : "no kernel for the planned format"); return -1; }
       a = nxt;
@@ -737,16 +752,19 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
   return 0;
 }
 
-// A shard with fault epochs.  Copies still run on the lanes (H2D of chunk i+1.. overlaps the compute of chunk i), but every chunk's
-// kernels and patches run on the parameter stream, in image order: the patches rewrite operands in place, so the chunks' kernels must
-// not overlap.  Chunks are NOT cut at fault times - run_chunk_faulted splits only the kernel of the faulted layer.
+// A shard with fault epochs.  The lanes run exactly as without faults - each its own in-order stream, copies and kernels of
+// consecutive chunks overlapping - because every lane owns a parameter set: lane 0 the device's set 0, lane k a clone taken at the
+// start of the call.  A lane applies EVERY patch to its own set, in time order, just before its first kernel run that starts at or
+// after the patch's time (run_chunk_faulted); it processes its chunks in increasing image order, so its set is always the
+// parameter state of the images it is working on, and no lane ever has to wait for another.  Chunks are not cut at fault times:
+// only the kernel of the faulted layer is split.  At the end lane 0 applies what is left, so set 0 carries every fault onwards.
 int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, uint64_t* words, const Segments& seg,
                               float* last_ms, int* last_imgs, std::string& err) {
   DeviceState& ds = *dev_[g];
   const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
   const int chunk = chunk_images(true);
-  cudaStream_t cs = ds.compute;
   for (auto& ln : ds.lane) { ln.used = false; ln.pend_off = -1; }
+  for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.s));
   // patches by kernel (group), time order kept
   FaultPlan fp;
   {
@@ -762,16 +780,29 @@ int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int n
         if (fp.group_of_layer[seg.patches[i].layer] == grp) { grouped.push_back(seg.patches[i]); fp.gtime[grp].push_back(seg.ptime[i]); }
     }
     if (!grouped.empty()) {
-      for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.s));
       if (ensure_patch_cap(ds, grouped.size(), err) != 0) return -1;
-      CKE(err, cudaMemcpyAsync(ds.d_patches, grouped.data(), grouped.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, cs));
-      CKE(err, cudaStreamSynchronize(cs));  // `grouped` dies with this block
+      CKE(err, cudaMemcpyAsync(ds.d_patches, grouped.data(), grouped.size() * sizeof(DevPatch), cudaMemcpyHostToDevice, ds.compute));
     }
+    CKE(err, cudaStreamSynchronize(ds.compute));  // `grouped` dies with this block; set 0 is quiescent before it is cloned
   }
-  auto flush_lane = [&](Lane& ln) -> int {  // results of the lane's chunk in flight -> host, after its kernels
+  auto param_set = [&](int k, const DevLayer** PL, DevLayer** tbl) -> int {  // lane k's set; clones are (re)taken from set 0 on first use
+    if (k == 0 || seg.patches.empty()) { *PL = ds.L; *tbl = ds.d_layers; return 0; }
+    DeviceState::ParamSet& c = ds.clone[k - 1];
+    if (!c.arena) {
+      c.arena = (unsigned char*)ds.alloc(ds.arena_bytes, true);
+      if (!c.arena) { err = "cudaMalloc failed (parameter clone, device " + std::to_string(ds.id) + ")"; return -1; }
+      carve_params(net_, c.arena, c.L, &c.d_layers);
+    }
+    if (!ds.lane[k].used) {  // first chunk of this lane in this call
+      CKE(err, cudaMemcpyAsync(c.arena, ds.arena, ds.arena_bytes, cudaMemcpyDeviceToDevice, ds.lane[k].s));
+      CKE(err, cudaMemcpyAsync(c.d_layers, c.L, sizeof(DevLayer) * 9, cudaMemcpyHostToDevice, ds.lane[k].s));  // the table points into the clone
+    }
+    *PL = c.L; *tbl = c.d_layers;
+    return 0;
+  };
+  auto flush_lane = [&](Lane& ln) -> int {  // results of the lane's chunk in flight -> host
     if (ln.pend_off < 0) return 0;
     const int off = ln.pend_off, c = ln.pend_n;
-    CKE(err, cudaStreamWaitEvent(ln.s, ln.done, 0));
     if (net_.is_cnv) CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.s));
     else CKE(err, cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.s));
     ln.pend_off = -1;
@@ -790,31 +821,30 @@ int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int n
     if (rem <= chunk + chunk / 2 && rem > 4096) c = std::min(chunk, (rem / 2 + 1023) / 1024 * 1024);
     const int k = ci % kLanes;
     Lane& ln = ds.lane[k];
-    if (flush_lane(ln) != 0) return -1;  // also orders this lane's next copy after the kernels that read its buffers
+    if (flush_lane(ln) != 0) return -1;
     if (ensure_lane(ds, k, c, err) != 0 || ensure_buffers(ds, k, c, err) != 0) return -1;
-    if (ln.used) CKE(err, cudaStreamWaitEvent(ln.s, ln.done, 0));
+    const DevLayer* PL;
+    DevLayer* tbl;
+    if (param_set(k, &PL, &tbl) != 0) return -1;
     CKE(err, cudaMemcpyAsync(ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
-    CKE(err, cudaEventRecord(ln.copied, ln.s));
-    CKE(err, cudaStreamWaitEvent(cs, ln.copied, 0));
-    if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, cs);
-    else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, c, cs);
+    if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, ln.s);
+    else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, c, ln.s);
     const bool time_it = cur + c == hi;
-    if (time_it) CKE(err, cudaEventRecord(ds.tev[0], cs));
-    if (run_chunk_faulted(ds, ln.d_in, c, cur, ln.d_out, net_.is_cnv ? ln.d_cls : nullptr, ncls, cs, ln.act, fp, err) != 0) return -1;
-    if (time_it) { CKE(err, cudaEventRecord(ds.tev[1], cs)); timed = true; *last_imgs = c; }
-    CKE(err, cudaEventRecord(ln.done, cs));
+    if (time_it) CKE(err, cudaEventRecord(ds.tev[0], ln.s));
+    if (run_chunk_faulted(ds, PL, tbl, k, ln.d_in, c, cur, ln.d_out, net_.is_cnv ? ln.d_cls : nullptr, ncls, ln.s, ln.act, fp, err) != 0) return -1;
+    if (time_it) { CKE(err, cudaEventRecord(ds.tev[1], ln.s)); timed = true; *last_imgs = c; }
     ln.used = true;
     ln.pend_off = cur; ln.pend_n = c;
     cur += c;
     ci++;
   }
-  // faults scheduled at or after this shard's end still persist on this device
+  // faults scheduled at or after the last run of lane 0 (or of this shard) still persist: set 0 takes the rest
   for (int grp = 0; grp < 9; grp++)
-    if (fp.gcur[grp] < fp.gtime[grp].size())
-      launch_patch_apply(ds.d_layers, net_.is_cnv, ds.d_patches + fp.goff[grp] + fp.gcur[grp], (int)(fp.gtime[grp].size() - fp.gcur[grp]), cs);
+    if (fp.gcur[0][grp] < fp.gtime[grp].size())
+      launch_patch_apply(ds.d_layers, net_.is_cnv, ds.d_patches + fp.goff[grp] + fp.gcur[0][grp], (int)(fp.gtime[grp].size() - fp.gcur[0][grp]), ds.lane[0].s);
   for (auto& ln : ds.lane) if (flush_lane(ln) != 0) return -1;
   for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.s));
-  CKE(err, cudaStreamSynchronize(cs));
+  CKE(err, cudaStreamSynchronize(ds.compute));
   CKE(err, cudaGetLastError());
   if (check_status(ds, err) != 0) return -1;
   if (timed) CKE(err, cudaEventElapsedTime(last_ms, ds.tev[0], ds.tev[1]));

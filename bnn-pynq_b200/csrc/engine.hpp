@@ -1,5 +1,5 @@
 // The CUDA runtime behind the C ABI: per-device replicated parameters, a few chunk pipelines (lanes) per device, buffers grown on
-// demand, stream-ordered fault epochs with in-place operand patches, and contiguous sharding
+// demand, fault epochs as in-place operand patches on a per-lane parameter set, and contiguous sharding
 // of an image batch over the visible GPUs (no collective; one feeder thread per device).
 // Replaces the host library's accelerator glue: FoldedMVInit/Deinit, FoldedMVOffloadBinarized (rawhls-offload.cpp:54-94),
 // testPrebuiltCIFAR10_multiple_images / _from_image (foldedmv-offload.h:316-416),
@@ -107,8 +107,8 @@ class Engine {
   int ensure_lane(DeviceState& ds, int lane, int images, std::string& err);     // lane's staging buffers
   int ensure_patch_cap(DeviceState& ds, size_t count, std::string& err);
   void plan_formats(const DeviceState& ds, bool per_layer, bool tensor_taps, int* fam, int* ofmt, bool* fused01, bool no_tiles = false) const;
-  int run_chunk_faulted(DeviceState& ds, const void* d_in, int n, long long img0, void* d_out, int* d_classes, int ncls, cudaStream_t s,
-                        uint32_t** bufs, FaultPlan& fp, std::string& err);
+  int run_chunk_faulted(DeviceState& ds, const DevLayer* PL, DevLayer* d_layers, int lane, const void* d_in, int n, long long img0, void* d_out,
+                        int* d_classes, int ncls, cudaStream_t s, uint32_t** bufs, FaultPlan& fp, std::string& err);
   int run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s, TapCtx* tap,
                 uint32_t** bufs, std::string& err);
   int run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, int16_t* scores, uint64_t* words,
