@@ -45,3 +45,12 @@ for target, name in ((0, "weights"), (1, "thresholds")):
         call(empty)
         t = call(fl)
         print("%-10s layer %d: %4d faults  %.2f ms  -> %.1f us per fault" % (name, layer, fl.shape[0], t * 1e3, (t - clean) * 1e6 / fl.shape[0]))
+
+# the bench's case: every layer and both memories in one schedule (BASELINE configs[4] density: one fault per 1 024 images)
+for rep in range(3):
+    fl = rt.schedule_faults(n, nf, word_size=1, target=-1, seed=3)
+    rt.load_parameters(params_dir(net))
+    call(empty)
+    t = call(fl)
+    grp = np.bincount(fl[:, 2].astype(np.int64), minlength=9)
+    print("any layer (rep %d): %4d faults  %.2f ms  -> %.1f us per fault   faults per layer %s" % (rep, fl.shape[0], t * 1e3, (t - clean) * 1e6 / fl.shape[0], grp.tolist()))
