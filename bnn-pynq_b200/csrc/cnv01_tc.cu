@@ -46,6 +46,26 @@ constexpr bool kMma = false;  // experiment: MMAs compiled out (commits kept)
 #else
 constexpr bool kMma = true;
 #endif
+#ifdef BNNB_NOMMA0
+constexpr bool kMma0 = false;  // experiment: layer-0 MMAs only compiled out
+#else
+constexpr bool kMma0 = kMma;
+#endif
+#ifdef BNNB_NOMMA1
+constexpr bool kMma1 = false;  // experiment: layer-1 MMAs only compiled out
+#else
+constexpr bool kMma1 = kMma;
+#endif
+#ifdef BNNB_NOPLANE
+constexpr bool kPlane = false;  // experiment: window-plane build compiled out (hand-offs kept)
+#else
+constexpr bool kPlane = true;
+#endif
+#ifdef BNNB_NOPOOL
+constexpr bool kPool = false;   // experiment: max-pool + store compiled out (hand-offs kept)
+#else
+constexpr bool kPool = true;
+#endif
 constexpr int NH = BNNB_NH;                   // helper warps (window planes, max-pool + store)
 constexpr int NT01 = (8 + 8 + 3 + NH) * 32;   // threads per CTA
 
@@ -56,7 +76,11 @@ template <int OUTM, bool F4> struct Smem01 {
   static constexpr int L1_B = 9 * NPL * 64 * 16;       // weights 64 x 576
   static constexpr int BITS = L1_TILES * 128 * 2 * OPL * 4;
   static constexpr int NBITS = F4 ? 2 : 1;             // bit-row buffers (the int8 variant has no room for a second one)
-  static constexpr int OFF_A = 0, OFF_B1 = 2 * L1_A, OFF_P = OFF_B1 + L1_B, OFF_IMG = OFF_P + 2 * P_BYTES, OFF_B0 = OFF_IMG + 2 * IMG_BYTES,
+  // FOLD variant (fp4, 1-bit outputs): each window plane is followed by a plane of constant rows {64, 1, 0, ...}: the fourth K chunk of
+  // layer 0, against which the weights carry the thresholds (thr = 64*a + b), so that the MMAs leave thr - S without any pre-load
+  static constexpr bool FOLD = F4 && OUTM == OUT_BIT;
+  static constexpr int P_STRIDE = FOLD ? 2 * P_BYTES : P_BYTES;
+  static constexpr int OFF_A = 0, OFF_B1 = 2 * L1_A, OFF_P = OFF_B1 + L1_B, OFF_IMG = OFF_P + 2 * P_STRIDE, OFF_B0 = OFF_IMG + 2 * IMG_BYTES,
                        OFF_BITS = OFF_B0 + B0_BYTES, OFF_THR = OFF_BITS + NBITS * BITS, TOTAL = OFF_THR + 2 * 64 * 2 * 4;
 };
 
@@ -98,12 +122,16 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
 #ifndef BNNB_L0S
 #define BNNB_L0S 2
 #endif
-  // layer-0 accumulator slots (TMEM columns 256, 320, 384).  A tile's round trip (issue -> MMAs behind layer 1's in the in-order
-  // pipe -> epilogue -> slot free) is ~1000 clocks: the slots in flight set layer 0's tile rate, which paces the whole kernel
+  // layer-0 accumulator slots (TMEM columns 256, 320, ...).  A tile's round trip (issue -> MMAs -> hand-off -> epilogue -> hand-off)
+  // is ~1000 clocks.  Round-2 measurements: the kernel is bound by this hand-off skeleton, not by the tensor pipe (all
+  // MMAs compiled out: 1.19 of 1.35 ms); more slots (3, 4, 5), teams on alternate tiles, one polling warp per group and one arrival
+  // per warp were all SLOWER - whatever lengthens the path layer-0 accumulator -> l0_done costs more than it frees.
   constexpr int L0_SLOTS = BNNB_L0S;
   // FOLD: the thresholds are folded into the accumulators, arranged so that the SIGN BIT of the result is the decision thr < acc.
-  // Layer 0: column n is pre-loaded with thr[n] (clamped to the reachable range, so the result fits 16 bits) and the MMAs run on
-  // negated weights: thr - S < 0 <=> decision 1.  The epilogue reads the accumulators with .pack::16b (two channels per
+  // Layer 0: the thresholds ride in the MMA itself - the fourth K chunk of the second MMA reads a plane of constant rows {64, 1, 0..}
+  // against weight columns (a, b) with 64*a + b = thr[n] (clamped to the reachable range, so the result fits 16 bits) - and the
+  // MMAs run on negated weights: the accumulator is thr - S, negative <=> decision 1, with no pre-load to write and wait for in the
+  // epilogue chain (round 2: 1.39 -> 1.35 ms).  The epilogue reads the accumulators with .pack::16b (two channels per
   // register), turns four signs into four 0x00 / 0xFF bytes with one PRMT and merges two such words into eight operand nibbles
   // with one LOP3: three ALU instructions per eight channels.  A set decision is therefore the e2m1 code 0xF = -6.0, not 1.0:
   // layer 1 accumulates -6 * (its true sum) onto a pre-load of 6 * thr + 3 (exact in fp32), negative <=> thr < sum, and its
@@ -136,6 +164,12 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
+    if (FOLD && ky == 3 && j < 2) {  // threshold columns against the constant plane {64, 1}: 64*a + b = the clamped threshold
+      const int t = L0.thr[2 * n];   // |S| <= 27 * 128: thresholds outside [-3457, 3456] decide like the nearest bound
+      const int th = t == INT_MAX ? 3456 : max(min(t >> 1, 3456), -3457);  // thr < 2S  <=>  floor(thr/2) < S
+      sB0[(size_t)3 * (64 * 16) + n * 16 + j] = (uint8_t)(int8_t)(j == 0 ? (th >> 6) : (th & 63));
+      continue;
+    }
     sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)(FOLD ? -v : v);  // FOLD: the MMAs subtract (see below)
   }
   for (int i = tid; i < 128; i += NT01) {
@@ -146,7 +180,12 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     else sthr1[i] = t1;
   }
   for (int i = tid; i < 2 * L1_A / 16; i += NT01) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
-  for (int i = tid; i < (2 * P_BYTES + 2 * IMG_BYTES) / 16; i += NT01) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < (2 * S::P_STRIDE + 2 * IMG_BYTES) / 16; i += NT01) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
+  if (FOLD) {  // the constant planes
+    __syncthreads();
+    for (int i = tid; i < 2 * P_ROWS; i += NT01)
+      reinterpret_cast<uint4*>(sP + (size_t)(i / P_ROWS) * S::P_STRIDE + P_BYTES)[i % P_ROWS] = make_uint4(0x00000140u, 0, 0, 0);  // bytes 64, 1, 0, ...
+  }
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
     for (int i = 0; i < 2; i++) {
@@ -156,7 +195,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 8); }
     for (int i = 0; i < L0_SLOTS; i++) { tc::mbar_init(&f0[i], 1); tc::mbar_init(&e0[i], 8); }
-    tc::mbar_init(&pre_done, 2);
+    tc::mbar_init(&pre_done, 1);  // layer 1's accumulator pre-loads (FOLD)
     tc::mbar_init_fence();
   }
   tc::fence_async_smem();
@@ -191,9 +230,9 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     if (!failed && !tc::mbar_wait(&img_full[buf], par)) failed = true;
     if (kk >= 2 && !failed && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
     const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
-    uint8_t* sPk = sP + (size_t)buf * P_BYTES;
+    uint8_t* sPk = sP + (size_t)buf * S::P_STRIDE;
 #pragma unroll 4
-    for (int m = hx; m < 1024 + 64; m += NH * 32) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
+    for (int m = hx; kPlane && m < 1024 + 64; m += NH * 32) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
       const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
       uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
       if (w + 4 < IMG_BYTES / 4) { x0 = iw[w]; x1 = iw[w + 1]; x2 = iw[w + 2]; x3 = iw[w + 3]; x4 = iw[w + 4]; }
@@ -210,17 +249,6 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
 #pragma unroll
     for (int c = 0; c < 32; c++)  // |S| <= 27 * 128: thresholds outside [-3457, 3456] decide like the nearest bound
       thrA[c] = FOLD ? max(min(sthr0[2 * (team * 32 + c)], 3456), -3457) : sthr0[2 * (team * 32 + c)];
-    auto preload0 = [&](int slot) {  // this warp's lane quarter and channel half of layer-0 accumulator `slot`
-      tc::tmem_st32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
-      tc::tmem_st_wait();
-    };
-    if (FOLD) {
-#pragma unroll
-      for (int slot = 0; slot < L0_SLOTS; slot++) preload0(slot);
-      tc::fence_before_sync();
-      half_sync(2);
-      if (ht == 0) tc::mbar_arrive(&pre_done);
-    }
     int s0 = 0;
     uint32_t p0 = 0;
     for (int k = 0; k < K; k++) {
@@ -330,7 +358,6 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
             td[1] = F4 ? make_uint4(0, 0, 0, 0) : *reinterpret_cast<const uint4*>(row + L1_PLANE);
           }
         }
-        if (FOLD && kEpi) preload0(slot);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&e0[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
@@ -350,7 +377,9 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
       const bool leader = tc::elect_one();
       // descriptor words: every operand here has SBO = 128; the start field (16-byte units) is the only part that moves
       const uint32_t d_hi = tc::desc_hi(128);
-      const uint32_t p_lo[2] = {tc::desc_lo(sP_u, 32 * 16), tc::desc_lo(sP_u + P_BYTES, 32 * 16)};
+      const uint32_t p_lo[2] = {tc::desc_lo(sP_u, 32 * 16), tc::desc_lo(sP_u + S::P_STRIDE, 32 * 16)};
+      // FOLD: the second MMA's chunks are ky = 2 and the constant plane one plane further on (LBO = P_BYTES)
+      const uint32_t p2_lo[2] = {tc::desc_lo(sP_u, FOLD ? P_BYTES : 32 * 16), tc::desc_lo(sP_u + S::P_STRIDE, FOLD ? P_BYTES : 32 * 16)};
       const uint32_t a1_lo[2] = {tc::desc_lo(sA_u, L1_PLANE), tc::desc_lo(sA_u + L1_A, L1_PLANE)};
       const uint32_t b0_lo = tc::desc_lo(sB0_u, 64 * 16), b1_lo = tc::desc_lo(sB1_u, 64 * 16);
       for (int k = 0; k < 2 && k < K; k++)
@@ -381,8 +410,8 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
         const uint32_t a0 = p_lo[buf] + (uint32_t)(t * 128);  // descriptor start fields are in 16-byte units: one row = 1
         if (leader) {
-          if (kMma) tc::mma_i8_lh(acc, a0, d_hi, b0_lo, d_hi, idesc, FOLD ? 1u : 0u);            // ky 0, 1
-          if (kMma) tc::mma_i8_lh(acc, a0 + 64, d_hi, b0_lo + 2 * 64, d_hi, idesc, 1u);          // ky 2, zero chunk
+          if (kMma0) tc::mma_i8_lh(acc, a0, d_hi, b0_lo, d_hi, idesc, 0u);                                              // ky 0, 1
+          if (kMma0) tc::mma_i8_lh(acc, p2_lo[buf] + (uint32_t)(t * 128 + 64), d_hi, b0_lo + 2 * 64, d_hi, idesc, 1u);  // ky 2, zero / threshold chunk
           tc::commit(&f0[slot]);
           TR(1, k, t);
           if (t == L0_TILES - 1) tc::commit(&p_empty[buf]);
@@ -400,7 +429,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         const uint32_t acc = tmem + (uint32_t)slot * 64;
         bool firstmma = true;
         if (leader && F4) {
-          if (kMma) tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, FOLD ? 1u : 0u);
+          if (kMma1) tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, FOLD ? 1u : 0u);
           tc::commit(&full[slot]);
           TR(4, k, t);
         } else if (leader) {
@@ -557,7 +586,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
       if (!failed && !tc::mbar_wait(&bits_full[bb], (uint32_t)(k / S::NBITS) & 1)) failed = true;
       // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
 #pragma unroll 2
-      for (int i = hx; i < 196 * 2; i += NH * 32) {
+      for (int i = hx; kPool && i < 196 * 2; i += NH * 32) {
         const int j = i & 1, op = i >> 1, oy = op / 14, ox = op % 14;
         const uint32_t* r00 = sbk + (size_t)((2 * oy) * 30 + 2 * ox) * WPP;
         const uint32_t *r01 = r00 + WPP, *r10 = r00 + 30 * WPP, *r11 = r10 + WPP;

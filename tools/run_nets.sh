@@ -3,7 +3,7 @@
 v=$1; shift
 for n in "$@"; do
   if [ "$v" = "-" ]; then unset BNN_B200_LIB_DIR; else export BNN_B200_LIB_DIR=$PWD/variants/$v; fi
-  python bench.py --net $n --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/n_${v}_$n.out 2> gpurun_out/n_${v}_$n.err
+  python bench.py --net $n --steps 10 --warmup 3 --lean > gpurun_out/n_${v}_$n.out 2> gpurun_out/n_${v}_$n.err
   python - <<PY
 import json
 for l in open("gpurun_out/n_${v}_$n.out"):

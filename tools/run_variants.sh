@@ -1,7 +1,7 @@
 #!/bin/bash
 # on the GPU box: tools/run_variants.sh v1 v2 ... -> bench line summary (+ PROF01 lines if the variant prints them)
 for v in "$@"; do
-  BNNB_BENCH_NOCHECK=$NOCHECK BNN_B200_LIB_DIR=$PWD/variants/$v python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/v_$v.out 2> gpurun_out/v_$v.err
+  BNNB_BENCH_NOCHECK=$NOCHECK BNN_B200_LIB_DIR=$PWD/variants/$v python bench.py --steps 5 --warmup 3 --lean > gpurun_out/v_$v.out 2> gpurun_out/v_$v.err
   echo "== $v"
   grep PROF01 gpurun_out/v_$v.out | grep -E "warp (0|8|16|18) " | tail -4 | cut -c1-260
   python - <<PY
