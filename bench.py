@@ -642,11 +642,18 @@ def main():
         # other ranks wait at the barrier
         rt.release()
         barrier()
+        # the idle ranks wait on the HOST (rendezvous store): an NCCL barrier would park a spinning kernel on their GPUs, which rank 0's
+        # engine is about to use
+        from datetime import timedelta
+        store = dist.distributed_c10d._get_default_store()
         if rank == 0:
             try:
                 out["e2e_one_process"] = one_process_e2e(native, L, a.net, world, B, max(a.steps // 2, 3))
             except Exception as e:
                 out["e2e_one_process"] = {"error": str(e)}
+            store.set("bnnb_one_process_done", "1")
+        else:
+            store.wait(["bnnb_one_process_done"], timedelta(minutes=15))
         barrier()
     if rank == 0 and world > 1:
         try:
