@@ -21,6 +21,7 @@ _SIGS = {
     "bnnb_device_bytes": (C.c_size_t, [C.c_void_p, C.c_int]),
     "bnnb_classify_cifar": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "bnnb_classify_mnist": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "bnnb_classify_packed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "bnnb_classify_with_fault_list": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "bnnb_schedule_faults": (C.c_int, [C.c_void_p, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_void_p, C.c_uint, C.c_longlong, C.c_void_p, C.c_int]),
     "bnnb_inject_fault": (C.c_int, [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_uint]),
@@ -137,6 +138,19 @@ class Runtime:
         self._ck(self.L.bnnb_classify_mnist(self.h, _p(px), n, number_class, _p(cls), _p(words), C.byref(us)))
         self._usec = us.value
         return (cls, words) if want_words else cls
+
+    def classify_packed(self, packed, number_class=10, want_raw=False):
+        """Inputs already in BlackBoxJam's format: uint8 [n, 104] (LFC, see pack_mnist) or int8 [n, 3072] HWC (CNV).  Returns classes
+        (and with want_raw the int16 scores [n, 64] / the uint64 output words)."""
+        a = np.ascontiguousarray(packed).view(np.uint8).reshape(-1, self.in_bytes)
+        n = a.shape[0]
+        cls = np.zeros(n, np.int32)
+        sc = np.zeros((n, 64), np.int16) if (want_raw and self.is_cnv) else None
+        words = np.zeros(n, np.uint64) if (want_raw and not self.is_cnv) else None
+        us = C.c_float(0)
+        self._ck(self.L.bnnb_classify_packed(self.h, _p(a), n, number_class, _p(cls), _p(sc), _p(words), C.byref(us)))
+        self._usec = us.value
+        return (cls, sc if self.is_cnv else words) if want_raw else cls
 
     def classify(self, data, number_class=10):
         return self.classify_cifar(data, number_class) if self.is_cnv else self.classify_mnist(data, number_class)
@@ -266,6 +280,15 @@ class Runtime:
     @property
     def out_bytes(self):
         return self.L.bnnb_out_bytes(self.h)
+
+
+def pack_mnist(pixels):
+    """binarizeAndPack on the host (foldedmv-offload.cpp:82-98): uint8 [n, 784] -> uint8 [n, 104]; bit k = (pixel k >= 128), LSB first,
+    784 -> 832 bits zero padded."""
+    px = np.ascontiguousarray(pixels, np.uint8).reshape(-1, 784)
+    bits = np.zeros((px.shape[0], 832), np.uint8)
+    bits[:, :784] = px >= 128
+    return np.ascontiguousarray(np.packbits(bits, axis=1, bitorder="little"))
 
 
 def microbench(which):

@@ -58,6 +58,13 @@ int bnnb_classify_mnist(bnnb_ctx* c, const uint8_t* px, int n, int ncls, int* cl
   if (c->eng->net().is_cnv) return fail(c, "not an LFC network");
   TRY return wrap(c, c->eng->infer_host(px, n, ncls, classes, nullptr, words, usec)); CATCH(c, -1)
 }
+int bnnb_classify_packed(bnnb_ctx* c, const uint8_t* packed, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, float* usec) {
+  GUARD(c);
+  TRY
+  const bool cnv = c->eng->net().is_cnv;
+  return wrap(c, c->eng->infer_host_packed(packed, n, ncls, classes, cnv ? scores : nullptr, cnv ? nullptr : words, usec));
+  CATCH(c, -1)
+}
 int bnnb_classify_with_fault_list(bnnb_ctx* c, const uint8_t* input, int n, int ncls, const uint32_t* faults, int nf, int* classes, float* usec) {
   GUARD(c);
   TRY

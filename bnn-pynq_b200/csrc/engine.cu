@@ -671,7 +671,7 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
   CKE(err, cudaSetDevice(ds.id));
   if (!ds.ready && upload(ds, err) != 0) return -1;
   if (seg) { *dev_ms = 0; return run_shard_faulted(g, lo, hi, input, ncls, classes, words, *seg, last_ms, last_imgs, err); }
-  const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
+  const size_t raw_bytes = packed_ ? (size_t)net_.in_bytes : (net_.is_cnv ? 3073 : 784);  // packed_: the caller hands over BlackBoxJam's own input
   const int chunk = chunk_images(true);
   for (auto& ln : ds.lane) { ln.used = false; ln.pend_off = -1; }
   auto flush_lane = [&](Lane& ln) -> int {  // results of the lane's chunk in flight -> host
@@ -712,8 +712,9 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
       Lane& ln = ds.lane[k];
       if (flush_lane(ln) != 0) return -1;
       if (ensure_lane(ds, k, c, err) != 0 || ensure_buffers(ds, k, c, err) != 0) return -1;
-      CKE(err, cudaMemcpyAsync(ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
-      if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, ln.s);
+      CKE(err, cudaMemcpyAsync(packed_ ? ln.d_in : (void*)ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
+      if (packed_) {}
+      else if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, ln.s);
       else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, c, ln.s);
       const bool time_it = true;
       Timed t{nullptr, nullptr, c};
@@ -761,7 +762,7 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
 int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, uint64_t* words, const Segments& seg,
                               float* last_ms, int* last_imgs, std::string& err) {
   DeviceState& ds = *dev_[g];
-  const size_t raw_bytes = net_.is_cnv ? 3073 : 784;
+  const size_t raw_bytes = packed_ ? (size_t)net_.in_bytes : (net_.is_cnv ? 3073 : 784);  // packed_: the caller hands over BlackBoxJam's own input
   const int chunk = chunk_images(true);
   for (auto& ln : ds.lane) { ln.used = false; ln.pend_off = -1; }
   for (auto& ln : ds.lane) CKE(err, cudaStreamSynchronize(ln.s));
@@ -826,8 +827,9 @@ int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int n
     const DevLayer* PL;
     DevLayer* tbl;
     if (param_set(k, &PL, &tbl) != 0) return -1;
-    CKE(err, cudaMemcpyAsync(ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
-    if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, ln.s);
+    CKE(err, cudaMemcpyAsync(packed_ ? ln.d_in : (void*)ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
+    if (packed_) {}
+    else if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, ln.s);
     else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, c, ln.s);
     const bool time_it = cur + c == hi;
     if (time_it) CKE(err, cudaEventRecord(ds.tev[0], ln.s));
@@ -899,6 +901,16 @@ int Engine::infer_host(const uint8_t* input, int n, int ncls, int* classes, int1
   if (!net_.is_cnv && classes)
     for (int i = 0; i < n; i++) classes[i] = lfc_class_multi(words[i], ncls);
   return 0;
+}
+
+// The same call on inputs the caller has already prepared as BlackBoxJam reads them (LFC: 104 bytes = 832 bits per image, what
+// binarizeAndPack leaves, foldedmv-offload.cpp:82-98; CNV: 3 072 int8 HWC bytes, quantiseAndPack<8,1>, foldedmv-offload.h:129-144):
+// no quantise / pack kernel, and for LFC 7.5x fewer bytes over PCIe.
+int Engine::infer_host_packed(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, float* usec) {
+  packed_ = true;
+  const int rc = infer_host(input, n, ncls, classes, scores, words, usec);
+  packed_ = false;
+  return rc;
 }
 
 int Engine::infer_host_with_faults(const uint8_t* input, int n, int ncls, const std::vector<Fault>& faults_in, int* classes,

@@ -49,6 +49,9 @@ class Engine {
   // Batches are sharded in contiguous ranges over the devices, but never thinner than kMinShard images per device.
   int infer_host(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, float* usec_per_image);
 
+  // infer_host on inputs already in BlackBoxJam's format (LFC 104 B / CNV 3 072 B per image): no preparation kernel.
+  int infer_host_packed(const uint8_t* input, int n, int ncls, int* classes, int16_t* scores, uint64_t* words, float* usec_per_image);
+
   // Same, with faults applied between image segments ("epochs"): every fault with time i is applied before image i,
   // cumulatively, and they persist afterwards (faults.h:115-148).  All devices apply every fault; each runs only its shard.
   // usec_per_image: device time per image of the last segment (the reference reports its last single-image call).
@@ -130,6 +133,7 @@ class Engine {
   bool profile_ = false;
   int core_ = 2;
   bool fuse01_ = true;
+  bool packed_ = false;  // the host-buffer call in progress takes prepared inputs (infer_host_packed)
   struct ProfEv { cudaEvent_t a, b; int layer, dev; };
   std::vector<ProfEv> prof_;
   std::mutex prof_mu_;

@@ -84,6 +84,13 @@ size_t bnnb_device_bytes(bnnb_ctx* c, int slot);   /* bytes currently allocated 
 int bnnb_classify_cifar(bnnb_ctx* c, const uint8_t* records, int n, int number_class, int* classes, int16_t* scores, float* usec_per_image);
 int bnnb_classify_mnist(bnnb_ctx* c, const uint8_t* pixels, int n, int number_class, int* classes, uint64_t* words, float* usec_per_image);
 
+/* The same call on inputs the caller prepared itself, exactly as BlackBoxJam reads them (bnnb_in_bytes per image): LFC 104 bytes =
+ * 832 bits, bit k of the image = (pixel k >= 128), LSB first, what binarizeAndPack leaves (foldedmv-offload.cpp:82-98) - the reference
+ * packs on the host too; CNV 3 072 int8 bytes HWC, what quantiseAndPack<8,1> leaves (foldedmv-offload.h:129-144).  No preparation kernel;
+ * for LFC 7.5x fewer bytes cross PCIe.  scores (CNV) / words (LFC): whichever applies, the other is ignored; both may be NULL. */
+int bnnb_classify_packed(bnnb_ctx* c, const uint8_t* packed, int n, int number_class, int* classes, int16_t* scores, uint64_t* words,
+                         float* usec_per_image);
+
 /* Deterministic fault list: nf x 5 uint32 {time, target (1 weights | 2 thresholds), layer, bit, word_size}, the arguments of the
  * reference's inject_fault (foldedmv-offload.h:169-214); a fault with time i is applied before image i, cumulatively (faults.h:138-146).
  * word_size is used as given (the reference's bool collapse, faults.h:42, is applied by bnnb_schedule_faults only). */

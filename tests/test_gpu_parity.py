@@ -138,6 +138,28 @@ def test_structured_inputs(net, core):
     assert np.array_equal(cls, o.classes(d))
 
 
+@pytest.mark.parametrize("net", NETS)
+def test_prepared_inputs_equal_raw_inputs(net):
+    """bnnb_classify_packed: inputs in BlackBoxJam's own format (LFC 104-byte binarizeAndPack words, CNV int8 HWC) give the results
+    of the raw-input call, through the chunk pipeline (ragged size) and with an empty batch."""
+    from bnn import native
+    rt, o = runtime(net), Oracle(net)
+    d = data_for(net, 9001, 17)
+    if net.startswith("cnv"):
+        packed = o.quantise(d)                       # the pinned oracle's quantiseAndPack<8,1>
+        cls, raw = rt.classify_packed(packed, 10, want_raw=True)
+        wcls, wraw = rt.classify_cifar(d, 10, want_scores=True)
+        assert np.array_equal(raw[:512], o.cnv_scores(d[:512]))
+    else:
+        packed = native.pack_mnist(d)
+        assert packed.shape == (9001, 104)
+        cls, raw = rt.classify_packed(packed, 10, want_raw=True)
+        wcls, wraw = rt.classify_mnist(d, 10, want_words=True)
+        assert np.array_equal(raw, o.lfc_words(d))
+    assert np.array_equal(raw, wraw) and np.array_equal(cls, wcls)
+    assert rt.classify_packed(packed[:0], 10).shape == (0,)
+
+
 @pytest.mark.parametrize("net", ["cnvW1A1", "lfcW1A1"])
 def test_small_calls_take_little_memory_and_release_frees_it(net):
     """A one-image call sets up ONE device with buffers for one small chunk; release() (what deinit() calls) frees every device
