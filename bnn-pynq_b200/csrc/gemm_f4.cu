@@ -220,6 +220,13 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
           for (int s0 = 0; s0 < g.ks; s0 += GG) {  // one ring slot = GG slabs (fewer at the end of the block)
             if (!failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
             const int s1 = min(s0 + GG, g.ks);
+#ifndef BNNB_GEMM_NO_MMA8
+            // a full group whose operand quarters are all in (every channel block but a tile's first): one asm block of eight MMAs
+            if (GG == 8 && s1 - s0 == 8 && (nb > 0 || qn == 4)) {
+              if (leader)
+                tc::mma8_mxf4<256, NB * 2>(acc, a_lo + (uint32_t)(2 * s0) * 128, b_lo + (uint32_t)(r * GG) * (SLAB / 16), d_hi, idesc, sf, (FOLD || s0 > 0) ? 1u : 0u);
+            } else
+#endif
             for (int s = s0; s < s1; s++) {
               // slab s lies in quarter q with ((q+1)*ks)/4 > s: wait for the quarters up to it (first channel block of a tile only)
               while (nb == 0 && qn < 4 && (s >= (qn * g.ks) / 4)) {
@@ -329,7 +336,10 @@ bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, i
   g.cw = d.ifm_ch / 32; g.ipl = INM == IN_TERN ? 2 : 1;
   g.a_bytes = g.kch * 2048;
   const int thr = 2 * d.N * 4, budget = 224 * 1024, slot_bytes = GG * NB * 32, ring_min = 2 * slot_bytes;
-  g.nbuf = 2 * g.a_bytes + 2 * ring_min + thr <= budget ? 2 : 1;  // two operand buffers only if four ring slots remain
+  // two operand buffers only if four ring slots remain beside them: the weight stream needs bytes in flight more than the operand
+  // tile needs a second buffer (measured round 2: two slots + two buffers 0.063 ms against four slots + one buffer 0.056 ms per
+  // 1024 x 1024 layer; slots of four slabs instead of eight: 0.072 ms)
+  g.nbuf = 2 * g.a_bytes + 2 * ring_min + thr <= budget ? 2 : 1;
   if (g.nbuf * g.a_bytes + ring_min + thr > budget) return false;
   g.ring = (budget - g.nbuf * g.a_bytes - thr) / slot_bytes;
   if (g.ring > GF_RING_MAX) g.ring = GF_RING_MAX;

@@ -297,3 +297,40 @@ __device__ __forceinline__ void mma9_mxf4(uint32_t tmem_d, uint32_t a_lo, uint32
 #undef BNNB_TAP
 }
 }}  // namespace bnnb::tc
+
+// ---- one ring slot of the K-streamed GEMM = eight kind::mxf4 MMAs in a single asm block -----------------------------------------------
+// Same reason as mma9_mxf4: the issuing thread is the scarce resource.  Slab j of the group: A advances by ASTEP 16-byte units (two
+// 2 KB chunks of the operand tile), B by BSTEP units (one slab of the ring slot).  acc_first: accumulate flag of the first MMA.
+namespace bnnb { namespace tc {
+template <int ASTEP, int BSTEP>
+__device__ __forceinline__ void mma8_mxf4(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t d_hi, uint32_t idesc, uint32_t sf, uint32_t acc_first) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, q;\n\t"
+      ".reg .b32 al, bl;\n\t"
+      ".reg .b64 a, b;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "setp.eq.b32 q, 0, 0;\n\t"
+      "mov.b64 a, {%1, %3};\n\t"
+      "mov.b64 b, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], p;\n\t"
+      "add.u32 al, %1, %7;\n\t add.u32 bl, %2, %14;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "add.u32 al, %1, %8;\n\t add.u32 bl, %2, %15;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "add.u32 al, %1, %9;\n\t add.u32 bl, %2, %16;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "add.u32 al, %1, %10;\n\t add.u32 bl, %2, %17;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "add.u32 al, %1, %11;\n\t add.u32 bl, %2, %18;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "add.u32 al, %1, %12;\n\t add.u32 bl, %2, %19;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "add.u32 al, %1, %13;\n\t add.u32 bl, %2, %20;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(d_hi), "r"(idesc), "r"(sf), "r"(acc_first), "n"(ASTEP), "n"(2 * ASTEP), "n"(3 * ASTEP), "n"(4 * ASTEP), "n"(5 * ASTEP),
+      "n"(6 * ASTEP), "n"(7 * ASTEP), "n"(BSTEP), "n"(2 * BSTEP), "n"(3 * BSTEP), "n"(4 * BSTEP), "n"(5 * BSTEP), "n"(6 * BSTEP), "n"(7 * BSTEP)
+      : "memory");
+}
+}}  // namespace bnnb::tc
