@@ -79,7 +79,8 @@ template <int OUTM, bool F4> struct Smem01 {
   // FOLD variant (fp4, 1-bit outputs): each window plane is followed by a plane of constant rows {64, 1, 0, ...}: the fourth K chunk of
   // layer 0, against which the weights carry the thresholds (thr = 64*a + b), so that the MMAs leave thr - S without any pre-load
   static constexpr bool FOLD = F4 && OUTM == OUT_BIT;
-  static constexpr int P_STRIDE = FOLD ? 2 * P_BYTES : P_BYTES;
+  static constexpr bool TFOLD = F4 && OUTM == OUT_TERN;  // the 2-bit counterpart (see the kernel)
+  static constexpr int P_STRIDE = F4 ? 2 * P_BYTES : P_BYTES;
   static constexpr int OFF_A = 0, OFF_B1 = 2 * L1_A, OFF_P = OFF_B1 + L1_B, OFF_IMG = OFF_P + 2 * P_STRIDE, OFF_B0 = OFF_IMG + 2 * IMG_BYTES,
                        OFF_BITS = OFF_B0 + B0_BYTES, OFF_THR = OFF_BITS + NBITS * BITS, TOTAL = OFF_THR + 2 * 64 * 2 * 4;
 };
@@ -98,6 +99,9 @@ __device__ __forceinline__ uint32_t sign_bytes(uint32_t a, uint32_t b) {
   asm("prmt.b32 %0, %1, %2, 0xFDB9;" : "=r"(d) : "r"(a), "r"(b));
   return d;
 }
+// TFOLD: accumulator column p of layer 1 holds channel (p & 32) + 8 * (p & 3) + ((p & 31) >> 2): columns 4g .. 4g+3 = channels g, 8+g,
+// 16+g, 24+g of the 32-channel half, so that one PRMT over two .pack::16b registers yields the four bytes of a 32-channel bit word
+__device__ __forceinline__ int tfold_channel(int p) { return (p & 32) + 8 * (p & 3) + ((p & 31) >> 2); }
 __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 
 // Warp roles (736 threads): warps 0-7 = half A (layer-1 epilogue, pool, store), warps 8-15 = half B (layer-0 epilogue into the
@@ -137,6 +141,15 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
   // layer 1 accumulates -6 * (its true sum) onto a pre-load of 6 * thr + 3 (exact in fp32), negative <=> thr < sum, and its
   // epilogue is one funnel shift per channel instead of compare + select + insert.
   constexpr bool FOLD = F4 && OUTM == OUT_BIT;
+  // TFOLD (fp4, 2-bit outputs): the same machinery carries the FIRST threshold, biased so that the low 16 bits of every accumulator
+  // are U = thr0 - S + 32768 in [0, 65536) - layer 0 through the constant plane {64, 1, 127, 127} (64a + b + 2 * 127 * 127 = thr0 +
+  // 32768), layer 1 through a pre-load of 1.5 * 2^23 + 32768 + thr0 (the float's low mantissa bits ARE the integer; the tensor core's
+  // fp32 accumulation is exact down to the last mantissa bit, measured) and negated weights.  The epilogues read two channels per
+  // register (.pack::16b); bit 15 of a half is NOT (thr0 < S), and ONE packed add of (thr1 - thr0) per channel pair gives the same
+  // for the second threshold (no half leaves [0, 65536), so nothing carries).  PRMT turns four such bits into byte masks: twelve
+  // ALU instructions per eight channels instead of thirty-two, and no threshold is fetched from shared memory per tile.
+  constexpr bool TFOLD = F4 && OUTM == OUT_TERN;
+  constexpr bool CP = FOLD || TFOLD;  // thresholds ride in the accumulators: constant plane, negated sums, permuted operand nibbles
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t full[4], empty[4], l0_done[2][L0_TILES], abuf_empty[2], f0[L0_SLOTS], e0[L0_SLOTS], p_full[2], p_empty[2], img_full[2], bits_full[2], bits_empty[2],
       pre_done;
@@ -154,23 +167,25 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
   for (int i = tid; i < 64 * 9 * S::NPL; i += NT01) {  // layer-1 weights -> chunk-major operand layout
-    const int n = i % 64, kc = i / 64;
+    const int p = i % 64, kc = i / 64, n = TFOLD ? tfold_channel(p) : p;  // accumulator column p holds channel n
     const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
     uint4 wv = *reinterpret_cast<const uint4*>(src + kc * 16);
-    if (FOLD) { wv.x = fold_nibble_order(wv.x); wv.y = fold_nibble_order(wv.y); wv.z = fold_nibble_order(wv.z); wv.w = fold_nibble_order(wv.w); }
-    *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + n) * 16) = wv;
+    if (CP) { wv.x = fold_nibble_order(wv.x); wv.y = fold_nibble_order(wv.y); wv.z = fold_nibble_order(wv.z); wv.w = fold_nibble_order(wv.w); }
+    if (TFOLD) { wv.x ^= 0x88888888u; wv.y ^= 0x88888888u; wv.z ^= 0x88888888u; wv.w ^= 0x88888888u; }  // e2m1 sign bits: the MMAs subtract
+    *reinterpret_cast<uint4*>(sB1 + ((size_t)kc * 64 + p) * 16) = wv;
   }
   for (int i = tid; i < 64 * 64; i += NT01) {  // layer-0 weights: k = ky*16 + j, j = kx*3 + c < 9; L0.wp holds int8x4 words [64][8], k natural
     const int n = i / 64, k = i % 64, ky = k / 16, j = k % 16;
     int8_t v = 0;
     if (ky < 3 && j < 9) v = reinterpret_cast<const int8_t*>(L0.wp)[n * 32 + ky * 9 + j];
-    if (FOLD && ky == 3 && j < 2) {  // threshold columns against the constant plane {64, 1}: 64*a + b = the clamped threshold
+    if (CP && ky == 3 && j < (TFOLD ? 4 : 2)) {  // threshold columns against the constant plane {64, 1, 127, 127}
       const int t = L0.thr[2 * n];   // |S| <= 27 * 128: thresholds outside [-3457, 3456] decide like the nearest bound
-      const int th = t == INT_MAX ? 3456 : max(min(t >> 1, 3456), -3457);  // thr < 2S  <=>  floor(thr/2) < S
-      sB0[(size_t)3 * (64 * 16) + n * 16 + j] = (uint8_t)(int8_t)(j == 0 ? (th >> 6) : (th & 63));
+      int th = t == INT_MAX ? 3456 : max(min(t >> 1, 3456), -3457);  // thr < 2S  <=>  floor(thr/2) < S
+      if (TFOLD) th += 32768 - 2 * 127 * 127;                        // 64*a + b + 127*127 + 127*127 = thr + 32768
+      sB0[(size_t)3 * (64 * 16) + n * 16 + j] = (uint8_t)(int8_t)(j == 0 ? (th >> 6) : (j == 1 ? (th & 63) : 127));
       continue;
     }
-    sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)(FOLD ? -v : v);  // FOLD: the MMAs subtract (see below)
+    sB0[(size_t)(k / 16) * (64 * 16) + n * 16 + (k % 16)] = (uint8_t)(CP ? -v : v);  // the MMAs subtract (see above)
   }
   for (int i = tid; i < 128; i += NT01) {
     const int t = L0.thr[i];
@@ -181,10 +196,10 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
   }
   for (int i = tid; i < 2 * L1_A / 16; i += NT01) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // incl. pad pixels
   for (int i = tid; i < (2 * S::P_STRIDE + 2 * IMG_BYTES) / 16; i += NT01) reinterpret_cast<uint4*>(sP)[i] = make_uint4(0, 0, 0, 0);
-  if (FOLD) {  // the constant planes
+  if (CP) {  // the constant planes
     __syncthreads();
     for (int i = tid; i < 2 * P_ROWS; i += NT01)
-      reinterpret_cast<uint4*>(sP + (size_t)(i / P_ROWS) * S::P_STRIDE + P_BYTES)[i % P_ROWS] = make_uint4(0x00000140u, 0, 0, 0);  // bytes 64, 1, 0, ...
+      reinterpret_cast<uint4*>(sP + (size_t)(i / P_ROWS) * S::P_STRIDE + P_BYTES)[i % P_ROWS] = make_uint4(0x7F7F0140u, 0, 0, 0);  // bytes 64, 1, 127, 127, 0, ...
   }
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
@@ -248,7 +263,16 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     int thrA[32];  // first thresholds in registers: the epilogue's shared-memory traffic competes with the MMA operand reads
 #pragma unroll
     for (int c = 0; c < 32; c++)  // |S| <= 27 * 128: thresholds outside [-3457, 3456] decide like the nearest bound
-      thrA[c] = FOLD ? max(min(sthr0[2 * (team * 32 + c)], 3456), -3457) : sthr0[2 * (team * 32 + c)];
+      thrA[c] = CP ? max(min(sthr0[2 * (team * 32 + c)], 3456), -3457) : sthr0[2 * (team * 32 + c)];
+    uint32_t D0[16];  // TFOLD: (thr1 - thr0) of channels 2j (low half) and 2j+1 (high half), both clamped like thr0
+    if (TFOLD) {
+#pragma unroll
+      for (int j = 0; j < 16; j++) {
+        const int da = max(min(sthr0[2 * (team * 32 + 2 * j) + 1], 3456), -3457) - thrA[2 * j];
+        const int db = max(min(sthr0[2 * (team * 32 + 2 * j + 1) + 1], 3456), -3457) - thrA[2 * j + 1];
+        D0[j] = (uint32_t)db * 65536u + (uint32_t)da;
+      }
+    }
     int s0 = 0;
     uint32_t p0 = 0;
     for (int k = 0; k < K; k++) {
@@ -280,48 +304,26 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
             v[q] = (lo & 0x0F0F0F0Fu) | (hi & 0xF0F0F0F0u);
           }
           if (valid) *reinterpret_cast<uint4*>(sA + (size_t)team * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+        } else if (TFOLD) {
+          uint32_t h[16];  // h[j]: U = thr0 - S + 32768 of channels 2j (low half) and 2j+1 (high half); bit 15 of a half = NOT (thr0 < S)
+          tc::tmem_ld32_pack16(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, h);
+          tc::tmem_ld_wait_dep16(h);
+          uint32_t v[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const uint32_t y0 = h[4 * q] + D0[4 * q], y1 = h[4 * q + 1] + D0[4 * q + 1], y2 = h[4 * q + 2] + D0[4 * q + 2], y3 = h[4 * q + 3] + D0[4 * q + 3];
+            // nibble masks (FOLD's nibble order) of NOT t0 and NOT t1
+            const uint32_t m0 = (sign_bytes(h[4 * q], h[4 * q + 1]) & 0x0F0F0F0Fu) | (sign_bytes(h[4 * q + 2], h[4 * q + 3]) & 0xF0F0F0F0u);
+            const uint32_t m1 = (sign_bytes(y0, y1) & 0x0F0F0F0Fu) | (sign_bytes(y2, y3) & 0xF0F0F0F0u);
+            // neither threshold exceeded -> 0xA (-1.0), both -> 0x2 (+1.0), one -> 0x0
+            v[q] = (~(m0 ^ m1) & 0xAAAAAAAAu) & (m0 | 0x22222222u);
+          }
+          if (valid) *reinterpret_cast<uint4*>(sA + (size_t)team * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
         } else {
         tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, r);
         tc::tmem_ld_wait_dep(r);
         }
-        if (FOLD) {
-        } else if (F4 && OUTM == OUT_TERN) {
-          // ternary: decision t = (thr < S) is the sign of thr - S.  The top nibbles of thr0 - S and thr1 - S are shifted in (bit 3 of
-          // a nibble = t0 / t1): one subtraction and one funnel shift per channel and threshold, then per eight channels
-          // both -> 0x2 (+1), neither -> 0xA (-1), one -> 0x0.  (Was two compares + table look-up + insert: the epilogue is ALU-bound.)
-          uint32_t v[4];
-#pragma unroll
-          for (int q = 0; q < 4; q++) {
-            uint32_t n0 = 0, n1 = 0;
-#pragma unroll
-            for (int e = 7; e >= 0; e--) {
-              const int c = q * 8 + e, sv = (int)r[c];
-              n0 = __funnelshift_l((uint32_t)(thrA[c] - sv), n0, 4);
-              n1 = __funnelshift_l((uint32_t)(sthr0[2 * (team * 32 + c) + 1] - sv), n1, 4);
-            }
-            const uint32_t both = n0 & n1 & 0x88888888u, none = ~(n0 | n1) & 0x88888888u;
-            v[q] = (both >> 2) | none | (none >> 2);
-          }
-          if (valid) *reinterpret_cast<uint4*>(sA + (size_t)team * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
-        } else if (F4) {  // 32 channels = 32 e2m1 nibbles = one uint4 store into plane `team`: 1 -> 0x2, 0 -> 0x0, -1 -> 0xA
-          uint32_t v[4];
-#pragma unroll
-          for (int q = 0; q < 4; q++) {
-            uint32_t wv = 0;
-#pragma unroll
-            for (int e = 0; e < 8; e++) {
-              const int c = q * 8 + e, n = team * 32 + c;
-              const int sv = (int)r[c];
-              if (OUTM == OUT_TERN) {
-                const int cnt = (thrA[c] < sv) + (sthr0[2 * n + 1] < sv);  // 0, 1, 2 -> -1, 0, +1
-                wv |= ((0x20Au >> (4 * cnt)) & 0xFu) << (4 * e);
-              } else {
-                if (thrA[c] < sv) wv |= 0x2u << (4 * e);
-              }
-            }
-            v[q] = wv;
-          }
-          if (valid) *reinterpret_cast<uint4*>(sA + (size_t)team * L1_PLANE + (size_t)(y * 30 + x) * 16) = make_uint4(v[0], v[1], v[2], v[3]);
+        if (CP) {  // done above
         } else {
 #pragma unroll
           for (int c16 = 0; c16 < 2; c16++) {  // one 16-channel chunk = one uint4 store
@@ -344,14 +346,14 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         }
         if (TAP) {  // parity taps: the MMA sum S = sum w*q of every valid pixel and channel, and the operand row just written
           const long long img = first + (long long)k * stride;
-          if (FOLD) {  // the accumulator holds thr - S in 32 bits (the epilogue above read only its low halves)
+          if (CP) {  // the accumulator holds thr - S (+ 32768) in 32 bits (the epilogue above read only its low halves)
             tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + L0_ACC + (uint32_t)slot * 64 + team * 32, r);
             tc::tmem_ld_wait_dep(r);
           }
           if (valid) {
             int32_t* ta = tp.acc0 + ((size_t)img * 900 + (y * 30 + x)) * 64 + team * 32;
 #pragma unroll
-            for (int c = 0; c < 32; c++) ta[c] = FOLD ? thrA[c] - (int)r[c] : (int)r[c];
+            for (int c = 0; c < 32; c++) ta[c] = CP ? thrA[c] + (TFOLD ? 32768 : 0) - (int)r[c] : (int)r[c];
             const uint8_t* row = sA + (size_t)(F4 ? team : 2 * team) * L1_PLANE + (size_t)(y * 30 + x) * 16;
             uint4* td = tp.act0 + ((size_t)img * 900 + (y * 30 + x)) * 4 + 2 * team;
             td[0] = *reinterpret_cast<const uint4*>(row);
@@ -379,7 +381,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
       const uint32_t d_hi = tc::desc_hi(128);
       const uint32_t p_lo[2] = {tc::desc_lo(sP_u, 32 * 16), tc::desc_lo(sP_u + S::P_STRIDE, 32 * 16)};
       // FOLD: the second MMA's chunks are ky = 2 and the constant plane one plane further on (LBO = P_BYTES)
-      const uint32_t p2_lo[2] = {tc::desc_lo(sP_u, FOLD ? P_BYTES : 32 * 16), tc::desc_lo(sP_u + S::P_STRIDE, FOLD ? P_BYTES : 32 * 16)};
+      const uint32_t p2_lo[2] = {tc::desc_lo(sP_u, CP ? P_BYTES : 32 * 16), tc::desc_lo(sP_u + S::P_STRIDE, CP ? P_BYTES : 32 * 16)};
       const uint32_t a1_lo[2] = {tc::desc_lo(sA_u, L1_PLANE), tc::desc_lo(sA_u + L1_A, L1_PLANE)};
       const uint32_t b0_lo = tc::desc_lo(sB0_u, 64 * 16), b1_lo = tc::desc_lo(sB1_u, 64 * 16);
       for (int k = 0; k < 2 && k < K; k++)
@@ -387,7 +389,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
           tc::mbar_expect_tx(&img_full[k], 3072);
           tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
         }
-      if (FOLD && !failed && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
+      if (CP && !failed && !tc::mbar_wait(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
       int s0 = 0;
       uint32_t p0 = 0;
       auto issue_l0 = [&](int k, int t) {
@@ -429,7 +431,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         const uint32_t acc = tmem + (uint32_t)slot * 64;
         bool firstmma = true;
         if (leader && F4) {
-          if (kMma1) tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, FOLD ? 1u : 0u);
+          if (kMma1) tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, CP ? 1u : 0u);
           tc::commit(&full[slot]);
           TR(4, k, t);
         } else if (leader) {
@@ -438,7 +440,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
           const uint32_t off = (uint32_t)((tap / 3) * 30 + tap % 3 + t * 128) * 16;
           if (F4) {
             tc::mma_mxf4_lh(acc, a_lo + (uint32_t)((tap / 3) * 30 + tap % 3), d_hi, b1_lo + (uint32_t)(tap * 2 * 64), d_hi, idesc_f4, sf, sf,
-                            (FOLD || !firstmma) ? 1u : 0u);
+                            (CP || !firstmma) ? 1u : 0u);
             firstmma = false;
           } else {
 #pragma unroll
@@ -487,14 +489,26 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     acc_t thrA[32];
 #pragma unroll
     for (int c = 0; c < 32; c++) {
-      const acc_t t = sthr1t[2 * (team * 32 + c)];
+      const acc_t t = sthr1t[2 * (TFOLD ? tfold_channel(team * 32 + c) : team * 32 + c)];
       thrA[c] = FOLD ? (acc_t)((float)t > 1.0e38f ? 3.0e38f : 6.0f * (float)t + 3.0f) : t;  // 6 * (thr + 1/2); the sentinel never fires
+      // TFOLD pre-load: 1.5 * 2^23 + 32768 + thr0 (|S| <= 2 * 576: thresholds outside [-1153, 1152] decide like the nearest bound)
+      if (TFOLD) thrA[c] = (acc_t)(12582912.0f + 32768.0f + fminf(fmaxf((float)t, -1153.0f), 1152.0f));
+    }
+    uint32_t D1[16];  // TFOLD: (thr1 - thr0) of columns 2j (low half) and 2j+1 (high half)
+    if (TFOLD) {
+#pragma unroll
+      for (int j = 0; j < 16; j++) {
+        const float a0 = (float)thrA[2 * j] - (12582912.0f + 32768.0f), b0 = (float)thrA[2 * j + 1] - (12582912.0f + 32768.0f);
+        const float a1 = fminf(fmaxf((float)sthr1t[2 * tfold_channel(team * 32 + 2 * j) + 1], -1153.0f), 1152.0f);
+        const float b1 = fminf(fmaxf((float)sthr1t[2 * tfold_channel(team * 32 + 2 * j + 1) + 1], -1153.0f), 1152.0f);
+        D1[j] = (uint32_t)(int)(b1 - b0) * 65536u + (uint32_t)(int)(a1 - a0);
+      }
     }
     auto preload1 = [&](int slot) {
       tc::tmem_st32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, reinterpret_cast<const uint32_t(&)[32]>(thrA[0]));
       tc::tmem_st_wait();
     };
-    if (FOLD) {
+    if (CP) {
 #pragma unroll
       for (int slot = 0; slot < 4; slot++) preload1(slot);
       tc::fence_before_sync();
@@ -511,12 +525,24 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
         uint32_t r[32];
-        if (kEpi || !FOLD) {
+        if ((kEpi || !FOLD) && (!TFOLD || TAP)) {
           tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, r);
           tc::tmem_ld_wait_dep(r);
         }
         uint32_t b0 = 0, b1 = 0;
         if (FOLD && !kEpi) {
+        } else if (TFOLD) {
+          uint32_t h[16];  // low 16 bits of the accumulators = U = thr0 - S + 32768, columns 2j / 2j+1 in the halves
+          tc::tmem_ld32_pack16(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, h);
+          tc::tmem_ld_wait_dep16(h);
+          uint32_t n0 = 0, n1 = 0;  // bit c = NOT (thr0 < S) / NOT (thr1 < S) of channel c
+#pragma unroll
+          for (int g = 0; g < 8; g++) {  // registers 2g, 2g+1 = channels g, 8+g, 16+g, 24+g -> bit g of the four bytes
+            n0 |= sign_bytes(h[2 * g], h[2 * g + 1]) & (0x01010101u << g);
+            n1 |= sign_bytes(h[2 * g] + D1[2 * g], h[2 * g + 1] + D1[2 * g + 1]) & (0x01010101u << g);
+          }
+          b0 = ~(n0 ^ n1);  // not zero: both thresholds exceeded, or neither
+          b1 = ~(n0 | n1);  // +1: both
         } else if (FOLD) {
           uint32_t q0 = 0, q1 = 0, q2 = 0, q3 = 0;  // four independent chains (a lone chain of 32 dependent shifts is pure latency)
 #pragma unroll
@@ -525,22 +551,6 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
             q2 = __funnelshift_l(r[16 + c], q2, 1); q3 = __funnelshift_l(r[24 + c], q3, 1);
           }
           b0 = __byte_perm(q0, q1, 0x1140) | __byte_perm(q2, q3, 0x4011);
-        } else if (F4 && OUTM == OUT_TERN) {  // sign bits of thr - acc (f4_common.cuh: tern_planes), first thresholds from registers
-          uint32_t u0[4] = {0, 0, 0, 0}, u1[4] = {0, 0, 0, 0};
-          const float* th1 = reinterpret_cast<const float*>(sthr1) + 2 * (team * 32) + 1;
-#pragma unroll
-          for (int q = 0; q < 4; q++) {
-#pragma unroll
-            for (int e = 7; e >= 0; e--) {
-              const float sv = __uint_as_float(r[8 * q + e]);
-              u0[q] = __funnelshift_l(__float_as_uint((float)thrA[8 * q + e] - sv), u0[q], 1);
-              u1[q] = __funnelshift_l(__float_as_uint(th1[2 * (8 * q + e)] - sv), u1[q], 1);
-            }
-          }
-          const uint32_t t0 = __byte_perm(u0[0], u0[1], 0x1140) | __byte_perm(u0[2], u0[3], 0x4011);
-          const uint32_t t1 = __byte_perm(u1[0], u1[1], 0x1140) | __byte_perm(u1[2], u1[3], 0x4011);
-          b0 = ~(t0 ^ t1);
-          b1 = t0 & t1;
         } else {
 #pragma unroll
           for (int c = 0; c < 32; c++) {
@@ -558,12 +568,13 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
             int32_t* ta = tp.acc1 + ((size_t)(first + (long long)k * stride) * 784 + (y * 28 + x)) * 64 + team * 32;
 #pragma unroll
             for (int c = 0; c < 32; c++) {
-              if (FOLD) ta[c] = __float2int_rn(__fdiv_rn((float)thrA[c] - __uint_as_float(r[c]), 6.0f));
+              if (TFOLD) ta[tfold_channel(c)] = (int)(__float_as_uint((float)thrA[c]) - r[c]);  // both are 0x4B400000 + integer
+              else if (FOLD) ta[c] = __float2int_rn(__fdiv_rn((float)thrA[c] - __uint_as_float(r[c]), 6.0f));
               else ta[c] = F4 ? __float2int_rn(__uint_as_float(r[c])) : (int)r[c];
             }
           }
         }
-        if (FOLD && kEpi) preload1(slot);
+        if (CP && kEpi) preload1(slot);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)

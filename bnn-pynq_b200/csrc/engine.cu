@@ -1082,11 +1082,11 @@ int Engine::tap_host(const uint8_t* input, int n, int32_t* acc, int8_t* act) {
             int8_t v;
             if (from_act0) {
               const uint4* row = hact0.data() + ((size_t)k * 900 + p) * 4;
-              if (core_ == 2) {  // e2m1 codes, 32 channels per uint4 (entries 0 and 2); 1-bit nets: FOLD nibble order and code 0xF
+              if (core_ == 2) {  // e2m1 codes, 32 channels per uint4 (entries 0 and 2), in the fused kernel's nibble order; 1-bit nets: code 0xF
                 const bool fold = l.out_mode == OUT_BIT;
                 const uint32_t* w = reinterpret_cast<const uint32_t*>(&row[2 * (ch >> 5)]);
                 const int c32 = ch & 31, wi = c32 >> 3, e = c32 & 7;
-                const int nib = fold ? ((e & 3) * 2 + (e >> 2)) : e;  // FOLD: nibble 2k = channel k, nibble 2k+1 = channel 4+k
+                const int nib = (e & 3) * 2 + (e >> 2);  // nibble 2k = channel k, nibble 2k+1 = channel 4+k
                 v = e2m1_act((w[wi] >> (4 * nib)) & 0xF, fold);
               } else {           // int8 operands, 16 channels per uint4
                 v = reinterpret_cast<const int8_t*>(&row[ch >> 4])[ch & 15];
