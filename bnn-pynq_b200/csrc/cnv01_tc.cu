@@ -609,8 +609,8 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         } else {
           const uint32_t P = r00[2 + j] | r01[2 + j] | r10[2 + j] | r11[2 + j];
           const uint32_t M = (r00[j] & ~r00[2 + j]) & (r01[j] & ~r01[2 + j]) & (r10[j] & ~r10[2 + j]) & (r11[j] & ~r11[2 + j]);
-          dst[j] = P | M;
-          dst[2 + j] = P;
+          if (out_fmt == ACT_F4P) reinterpret_cast<uint4*>(out)[((size_t)img * 2 + j) * 196 + op] = f4_from_tern(P | M, P);  // [img][plane][pixel]
+          else { dst[j] = P | M; dst[2 + j] = P; }
         }
       }
       __syncwarp();
@@ -651,7 +651,7 @@ static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
 
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt,
                      int* status, const Tap01& tp, cudaStream_t s) {
-  if (out_fmt != ACT_BITS && !(out_fmt == ACT_F4P && L1.d.out_mode == OUT_BIT)) return false;
+  if (out_fmt != ACT_BITS && out_fmt != ACT_F4P) return false;
   if (n_img <= 0 || !L1.w8 || !L1.w4 || !L1.thr_tc || L0.d.N != 64 || L1.d.N != 64 || L1.d.ifm_dim != 30) return false;
   const int grid = n_img < num_sms ? n_img : num_sms;
   const bool bit = L1.d.out_mode == OUT_BIT;

@@ -78,6 +78,11 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   // FOLD (1-bit outputs): accumulators are pre-loaded with -(thr + 1/2) and every MMA accumulates; the sign bit of the result is
   // the negated decision, harvested with one funnel shift per channel (see cnv01_tc.cu)
   constexpr bool FOLD = OUTM == OUT_BIT;
+  // TPRE (2-bit outputs): the pre-load carries the FIRST threshold, biased so that the low 16 bits of the accumulator hold the decision in
+  // bit 15; the epilogue reads two channels per register and gets the second threshold with one packed add (f4_common.cuh)
+  constexpr bool TPRE = OUTM == OUT_TERN;
+  constexpr bool ACC = FOLD || TPRE;     // the MMAs accumulate onto a pre-load
+  constexpr int SMAX = 2 * 9 * C;        // |S| <= K * max|w| * max|a|
 
   constexpr int NT = Cfg::NT;
   for (int i = tid; i < NT * KCT; i += 640) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
@@ -87,7 +92,12 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   for (int i = tid; i < 2 * NT; i += 640) {
     const int t = L.thr_tc[i];
     const float tf = t == INT_MAX ? 3.0e38f : (float)t;
-    sthr[(i & 1) * NT + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
+    if (!TPRE) sthr[(i & 1) * NT + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
+    else if (i < NT) sthr[i] = tern_preload(L.thr_tc[2 * i], SMAX);                   // [0, NT): pre-loads
+    else if (i < NT + NT / 2) {                                                        // [NT, NT + NT/2): (thr0 - thr1) of channels 2j, 2j+1
+      const int j = i - NT;
+      reinterpret_cast<uint32_t*>(sthr)[i] = tern_delta(L.thr_tc[4 * j], L.thr_tc[4 * j + 1], L.thr_tc[4 * j + 2], L.thr_tc[4 * j + 3], SMAX);
+    }
   }
   for (int i = tid; i < 2 * Cfg::A_BYTES / 16; i += 640) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // pad pixels stay 0
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
@@ -108,7 +118,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
 #ifdef BNNB_CONV_PRE_SMEM
   constexpr bool PRE_REG = false;
 #else
-  constexpr bool PRE_REG = FOLD && NWG == 1 && NS == 1;
+  constexpr bool PRE_REG = ACC && NWG == 1 && NS == 1;
 #endif
   uint32_t pre[32];
   if (PRE_REG) {
@@ -137,7 +147,12 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     }
     tc::tmem_st_wait();
   };
-  if (FOLD && warp < 16)
+  uint32_t dl[16];  // TPRE, one word per warp and one channel block: the deltas live in registers too
+  if (TPRE && PRE_REG) {
+#pragma unroll
+    for (int c = 0; c < 16; c++) dl[c] = reinterpret_cast<const uint32_t*>(sthr)[NT + ((warp < 16 ? eg : 0) * NG) / 2 + c];
+  }
+  if (ACC && warp < 16)
     for (int slot = 0; slot < Cfg::SLOTS; slot++) preload(slot, slot % NS);
   tc::fence_before_sync();
   __syncthreads();
@@ -209,7 +224,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
 #pragma unroll
             for (int s = 0; s < Cfg::KC / 2; s++)
               tc::mma9_mxf4<IDIM, Cfg::KC * NT>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NT), d_hi, idesc, sf,
-                                               (FOLD || s > 0) ? 1u : 0u);
+                                               (ACC || s > 0) ? 1u : 0u);
             tc::commit(&full[slot]);
           }
           __syncwarp();
@@ -233,24 +248,36 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N + (uint32_t)eg * NG;
         uint32_t b0[NWG], b1[NWG];
         uint4 c4[NWG];  // e2m1 codes instead of bits when the consumer is another fp4 kernel
-        const bool codes = FOLD && !POOL && out_fmt != ACT_BITS;
+        const bool codes = ACC && !POOL && out_fmt != ACT_BITS;
         uint32_t r[2][32];
-        tc::tmem_ld32(trow, r[0]);
+        if (!TPRE) tc::tmem_ld32(trow, r[0]);
 #pragma unroll
         for (int j = 0; j < NWG; j++) {
-          tc::tmem_ld_wait_dep(r[j & 1]);
-          if (j + 1 < NWG) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
           uint32_t w0 = 0, w1 = 0;
           c4[j] = make_uint4(0, 0, 0, 0);
-          if (codes) {
+          if (TPRE) {
+            uint32_t hh[16];
+            tc::tmem_ld32_pack16(trow + j * 32, hh);
+            if (!PRE_REG) {  // the deltas of this block and word, from shared memory while the load is in flight
+              const uint4* dp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(sthr) + NT + (h * N + eg * NG + j * 32) / 2);
+#pragma unroll
+              for (int q = 0; q < 4; q++) { const uint4 v = dp[q]; dl[4 * q] = v.x; dl[4 * q + 1] = v.y; dl[4 * q + 2] = v.z; dl[4 * q + 3] = v.w; }
+            }
+            tc::tmem_ld_wait_dep16(hh);
+            if (codes) c4[j] = tern_codes16(hh, dl);
+            else tern_planes16(hh, dl, w0, w1);
+            if (TAP) { tc::tmem_ld32(trow + j * 32, r[j & 1]); tc::tmem_ld_wait_dep(r[j & 1]); }
+          } else {
+          tc::tmem_ld_wait_dep(r[j & 1]);
+          if (j + 1 < NWG) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
+          }
+          if (TPRE) {
+          } else if (codes) {
             c4[j] = f4_from_signs(r[j & 1]);
           } else if (FOLD) {
 #pragma unroll
             for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
             w0 = ~w0;
-          } else {
-            const float* th = sthr + h * N + eg * NG + j * 32;
-            tern_planes(r[j & 1], th, th + NT, w0, w1);
           }
           b0[j] = w0;
           b1[j] = w1;
@@ -260,11 +287,11 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
               int32_t* ta = tap + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * NT + h * N + eg * NG + j * 32;
               const float* pv = sthr + h * N + eg * NG + j * 32;
 #pragma unroll
-              for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (FOLD ? pv[c] : 0.0f));
+              for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (ACC ? pv[c] : 0.0f));
             }
           }
         }
-        if (FOLD) preload(slot, (gt + Cfg::SLOTS) % NS);
+        if (ACC) preload(slot, (gt + Cfg::SLOTS) % NS);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
@@ -329,8 +356,14 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
               constexpr int H = NWT / 4;
               const uint4 P = or4(or4(r00[H + q], r01[H + q]), or4(r10[H + q], r11[H + q]));
               const uint4 M = and4(and4(andn4(r00[q], r00[H + q]), andn4(r01[q], r01[H + q])), and4(andn4(r10[q], r10[H + q]), andn4(r11[q], r11[H + q])));
-              dst[q] = or4(P, M);
-              dst[H + q] = P;
+              if (out_fmt == ACT_F4P) {  // [img][plane][pixel], planes 4q .. 4q+3, as e2m1 codes
+                uint4* out4 = reinterpret_cast<uint4*>(out) + ((size_t)(img0 + gi) * NWT + 4 * q) * PP + op;
+                out4[0] = expand_fp4<IN_TERN>(P.x | M.x, P.x); out4[PP] = expand_fp4<IN_TERN>(P.y | M.y, P.y);
+                out4[2 * PP] = expand_fp4<IN_TERN>(P.z | M.z, P.z); out4[3 * PP] = expand_fp4<IN_TERN>(P.w | M.w, P.w);
+              } else {
+                dst[q] = or4(P, M);
+                dst[H + q] = P;
+              }
             }
           }
         }
@@ -378,7 +411,6 @@ bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
                     cudaStream_t s) {
   const LayerDesc& d = L.d;
   if (!conv_f4_supports(d) || !L.w4 || !L.thr_tc || n_img <= 0) return false;
-  if ((in_fmt != ACT_BITS || out_fmt != ACT_BITS) && d.out_mode != OUT_BIT) return false;  // the fp4 interchange formats are for 1-bit activations
   if (in_fmt == ACT_F4T || (d.pool && out_fmt == ACT_F4T)) return false;
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {

@@ -183,7 +183,7 @@ size_t Engine::act_bytes(int images) const {
     const LayerDesc& l = net_.L[i];
     const size_t px = (size_t)out_dim(l) * out_dim(l);
     per = std::max(per, px * out_words_per_pixel(l) * 4);
-    if (l.out_mode == OUT_BIT) per = std::max(per, px * l.N / 2);
+    if (l.out_mode == OUT_BIT || l.out_mode == OUT_TERN) per = std::max(per, px * l.N / 2);  // e2m1 codes (ACT_F4P / ACT_F4T)
   }
   return (size_t)((images + 127) / 128 * 128) * per;
 }
@@ -410,7 +410,7 @@ void Engine::plan_formats(const DeviceState& ds, bool per_layer, bool tensor_tap
     const LayerDesc& p = net_.L[i];
     const LayerDesc& c = net_.L[i + 1];
     const bool producer_f4 = fam[i] != 0 || (*fused01 && i == 1 && core_ == 2);
-    if (!producer_f4 || p.out_mode != OUT_BIT || c.in_mode != IN_XNOR) continue;
+    if (!producer_f4 || !((p.out_mode == OUT_BIT && c.in_mode == IN_XNOR) || (p.out_mode == OUT_TERN && c.in_mode == IN_TERN))) continue;
     if (fam[i + 1] == 1 && fam[i] != 2) ofmt[i] = ACT_F4P;                        // conv consumer: image planes
     if (fam[i + 1] == 2 && !p.pool && !(*fused01 && i == 1) && !no_tiles) ofmt[i] = ACT_F4T;   // gemm consumer: 128-image tiles
   }

@@ -60,6 +60,8 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
                                                      int in_fmt, int out_fmt, int* __restrict__ status, int32_t* __restrict__ tap) {
   constexpr int SLAB = NB * 32, SLOTS = 3, SF_COL = 384, NW = NB / 32, EXP = 192, U = 4;  // EXP expander threads, U loads in flight each
   constexpr bool FOLD = OUTM == OUT_BIT;
+  constexpr bool TPRE = OUTM == OUT_TERN;  // 2-bit outputs: biased pre-load + packed 16-bit epilogue (f4_common.cuh)
+  constexpr bool ACC = FOLD || TPRE;       // the MMAs accumulate onto a pre-load
   constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t full[SLOTS], empty[SLOTS], a_part[2][4], a_empty[2], ring_full[GF_RING_MAX], ring_empty[GF_RING_MAX];
@@ -74,7 +76,13 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
     const int t = L.thr_tc[i];
     float tf = t == INT_MAX ? 3.0e38f : (float)t;
     if (OUTM == OUT_SCORE) tf = (float)t;
-    sthr[(i & 1) * g.N + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
+    const int smax = 2 * g.K;  // |S| <= K * max|w| * max|a|
+    if (!TPRE) sthr[(i & 1) * g.N + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
+    else if (i < g.N) sthr[i] = tern_preload(L.thr_tc[2 * i], smax);                 // [0, N): pre-loads
+    else if (i < g.N + g.N / 2) {                                                    // [N, N + N/2): (thr0 - thr1) of channels 2j, 2j+1
+      const int j = i - g.N;
+      reinterpret_cast<uint32_t*>(sthr)[i] = tern_delta(L.thr_tc[4 * j], L.thr_tc[4 * j + 1], L.thr_tc[4 * j + 2], L.thr_tc[4 * j + 3], smax);
+    }
   }
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
@@ -109,7 +117,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
   const int ntiles = (n_img + 127) / 128;
   const int T = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;  // tiles of this CTA
   // FOLD: the accumulator slot of the j-th channel block overall (j = tile_local * nblk + nb) holds that block's pre-load
-  if (FOLD && warp < 4)
+  if (ACC && warp < 4)
     for (int j = 0; j < SLOTS && j < T * g.nblk; j++) preload(j, j % g.nblk);
   tc::fence_before_sync();
   __syncthreads();
@@ -224,7 +232,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
             // a full group whose operand quarters are all in (every channel block but a tile's first): one asm block of eight MMAs
             if (GG == 8 && s1 - s0 == 8 && (nb > 0 || qn == 4)) {
               if (leader)
-                tc::mma8_mxf4<256, NB * 2>(acc, a_lo + (uint32_t)(2 * s0) * 128, b_lo + (uint32_t)(r * GG) * (SLAB / 16), d_hi, idesc, sf, (FOLD || s0 > 0) ? 1u : 0u);
+                tc::mma8_mxf4<256, NB * 2>(acc, a_lo + (uint32_t)(2 * s0) * 128, b_lo + (uint32_t)(r * GG) * (SLAB / 16), d_hi, idesc, sf, (ACC || s0 > 0) ? 1u : 0u);
             } else
 #endif
             for (int s = s0; s < s1; s++) {
@@ -235,7 +243,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
                 qn++;
               }
               if (leader)
-                tc::mma_mxf4_lh(acc, a_lo + (uint32_t)(2 * s) * 128, d_hi, b_lo + (uint32_t)(r * GG + (s - s0)) * (SLAB / 16), d_hi, idesc, sf, sf, (FOLD || s > 0) ? 1u : 0u);
+                tc::mma_mxf4_lh(acc, a_lo + (uint32_t)(2 * s) * 128, d_hi, b_lo + (uint32_t)(r * GG + (s - s0)) * (SLAB / 16), d_hi, idesc, sf, sf, (ACC || s > 0) ? 1u : 0u);
             }
             if (leader) tc::commit(&ring_empty[r]);
             if (++r == g.ring) { r = 0; rpar ^= 1u; }
@@ -260,17 +268,32 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * NB;
         uint32_t b0[NW], b1[NW];
         uint4 c4[NW];  // e2m1 codes instead of bits when the consumer is another gemm_f4 launch
-        const bool codes = FOLD && out_fmt == ACT_F4T;
+        const bool codes = ACC && out_fmt == ACT_F4T;
         uint32_t r[2][32];
-        tc::tmem_ld32(trow, r[0]);
+        uint32_t hh[2][16];
+        if (TPRE) tc::tmem_ld32_pack16(trow, hh[0]);
+        else tc::tmem_ld32(trow, r[0]);
 #pragma unroll
         for (int j = 0; j < NW; j++) {
-          tc::tmem_ld_wait_dep(r[j & 1]);
-          if (j + 1 < NW) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
           const float* th = sthr + nb * NB + j * 32;
           uint32_t w0 = 0, w1 = 0;
           c4[j] = make_uint4(0, 0, 0, 0);
-          if (OUTM == OUT_SCORE) {  // PassThroughActivation<ap_uint<16>>: (S + offset) mod 2^16, offset = #negative weights for 1-bit inputs
+          if (TPRE) {
+            uint32_t dl[16];  // the deltas of this block and word, from shared memory while the load is in flight
+            const uint4* dp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(sthr) + g.N + (nb * NB + j * 32) / 2);
+#pragma unroll
+            for (int q = 0; q < 4; q++) { const uint4 v = dp[q]; dl[4 * q] = v.x; dl[4 * q + 1] = v.y; dl[4 * q + 2] = v.z; dl[4 * q + 3] = v.w; }
+            tc::tmem_ld_wait_dep16(hh[j & 1]);
+            if (j + 1 < NW) tc::tmem_ld32_pack16(trow + (j + 1) * 32, hh[(j + 1) & 1]);
+            if (codes) c4[j] = tern_codes16(hh[j & 1], dl);
+            else tern_planes16(hh[j & 1], dl, w0, w1);
+            if (TAP) { tc::tmem_ld32(trow + j * 32, r[j & 1]); tc::tmem_ld_wait_dep(r[j & 1]); }
+          } else {
+          tc::tmem_ld_wait_dep(r[j & 1]);
+          if (j + 1 < NW) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
+          }
+          if (TPRE) {
+          } else if (OUTM == OUT_SCORE) {  // PassThroughActivation<ap_uint<16>>: (S + offset) mod 2^16, offset = #negative weights for 1-bit inputs
             if (img < n_img) {
               int16_t* o16 = reinterpret_cast<int16_t*>(out) + (size_t)img * g.N + nb * NB + j * 32;
 #pragma unroll
@@ -291,18 +314,16 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
 #pragma unroll
             for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
             w0 = ~w0;
-          } else {
-            tern_planes(r[j & 1], th, th + g.N, w0, w1);
           }
           b0[j] = w0;
           b1[j] = w1;
           if (TAP && img < n_img) {  // parity taps (TAP instantiation only): the MMA sum of every channel, pre-load un-folded
             int32_t* ta = tap + (size_t)img * g.N + nb * NB + j * 32;
 #pragma unroll
-            for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (FOLD ? th[c] : 0.0f));
+            for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (ACC ? th[c] : 0.0f));
           }
         }
-        if (FOLD && gb + SLOTS < T * g.nblk) preload(slot, (gb + SLOTS) % g.nblk);
+        if (ACC && gb + SLOTS < T * g.nblk) preload(slot, (gb + SLOTS) % g.nblk);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
@@ -392,8 +413,8 @@ bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
   const LayerDesc& d = L.d;
   if (!gemm_f4_supports(L) || n_img <= 0) return false;
   if (in_fmt == ACT_F4P || out_fmt == ACT_F4P) return false;
-  if (in_fmt == ACT_F4T && d.in_mode != IN_XNOR) return false;
-  if (out_fmt == ACT_F4T && d.out_mode != OUT_BIT) return false;
+  if (in_fmt == ACT_F4T && d.in_mode != IN_XNOR && d.in_mode != IN_TERN) return false;  // {0,1} / {-1,0,+1} codes as the producer wrote them
+  if (out_fmt == ACT_F4T && d.out_mode != OUT_BIT && d.out_mode != OUT_TERN) return false;
   return gemm_f4_block(d) == 128 ? launch_nb<128>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s) : launch_nb<64>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
 }
 
