@@ -33,6 +33,12 @@ constexpr int P_BYTES = P_ROWS * 16;
 constexpr int IMG_BYTES = 3072 + 64;          // image + slack for the 16-byte windows of the last rows
 constexpr int B0_BYTES = 4 * 64 * 16;         // layer-0 weights: 4 chunks x 64 rows x 16 bytes
 constexpr int L1_TILES = 7, L0_TILES = 8;
+#ifndef BNNB_PLANEU
+#define BNNB_PLANEU 1
+#endif
+#ifndef BNNB_POOLU
+#define BNNB_POOLU 1
+#endif
 #ifndef BNNB_NH
 #define BNNB_NH 4
 #endif
@@ -66,6 +72,8 @@ constexpr bool kPool = false;   // experiment: max-pool + store compiled out (ha
 #else
 constexpr bool kPool = true;
 #endif
+constexpr int PLANEU = BNNB_PLANEU;           // unroll of the window-plane loop
+constexpr int POOLU = BNNB_POOLU;             // unroll of the pool loop
 constexpr int NH = BNNB_NH;                   // helper warps (window planes, max-pool + store)
 constexpr int NT01 = (8 + 8 + 3 + NH) * 32;   // threads per CTA
 
@@ -246,7 +254,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     if (kk >= 2 && !failed && !tc::mbar_wait(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
     const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
     uint8_t* sPk = sP + (size_t)buf * S::P_STRIDE;
-#pragma unroll 4
+#pragma unroll PLANEU
     for (int m = hx; kPlane && m < 1024 + 64; m += NH * 32) {  // rows up to 957 + 64 are read by valid outputs; the rest only need to be defined
       const int b = 3 * m, w = b >> 2, sh = (b & 3) * 8;
       uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, x4 = 0;
@@ -596,7 +604,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
       const uint32_t* sbk = sbits + (size_t)bb * (S::BITS / 4);
       if (!failed && !tc::mbar_wait(&bits_full[bb], (uint32_t)(k / S::NBITS) & 1)) failed = true;
       // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
-#pragma unroll 2
+#pragma unroll POOLU
       for (int i = hx; kPool && i < 196 * 2; i += NH * 32) {
         const int j = i & 1, op = i >> 1, oy = op / 14, ox = op % 14;
         const uint32_t* r00 = sbk + (size_t)((2 * oy) * 30 + 2 * ox) * WPP;
