@@ -75,13 +75,11 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   constexpr int NWG = Cfg::NW / 4;  // 32-channel words per epilogue group
   constexpr int NG = N / 4;         // channels per epilogue group
   constexpr int KCT = 9 * Cfg::KC;
-  // FOLD (1-bit outputs): accumulators are pre-loaded with -(thr + 1/2) and every MMA accumulates; the sign bit of the result is
-  // the negated decision, harvested with one funnel shift per channel (see cnv01_tc.cu)
-  constexpr bool FOLD = OUTM == OUT_BIT;
-  // TPRE (2-bit outputs): the pre-load carries the FIRST threshold, biased so that the low 16 bits of the accumulator hold the decision in
-  // bit 15; the epilogue reads two channels per register and gets the second threshold with one packed add (f4_common.cuh)
-  constexpr bool TPRE = OUTM == OUT_TERN;
-  constexpr bool ACC = FOLD || TPRE;     // the MMAs accumulate onto a pre-load
+  // The accumulators are pre-loaded with the (first) threshold, biased so that the low 16 bits of the result hold the decision
+  // thr < S in bit 15 (f4_common.cuh), and every MMA accumulates.  The epilogue reads two channels per register (.pack::16b: the
+  // TMEM read port, 64 B per clock and SM, bounds a 128 x 128 tile read as 32-bit words at 1024 clocks against 576 of MMAs) and
+  // turns sign bits into codes / bit words with PRMT; 2-bit outputs get the second threshold with one packed add.
+  constexpr bool TERN = OUTM == OUT_TERN;
   constexpr int SMAX = 2 * 9 * C;        // |S| <= K * max|w| * max|a|
 
   constexpr int NT = Cfg::NT;
@@ -90,11 +88,8 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     *reinterpret_cast<uint4*>(sb + ((size_t)kc * NT + n) * 16) = *reinterpret_cast<const uint4*>(L.w4 + (size_t)n * (L.kpad / 2) + kc * 16);
   }
   for (int i = tid; i < 2 * NT; i += 640) {
-    const int t = L.thr_tc[i];
-    const float tf = t == INT_MAX ? 3.0e38f : (float)t;
-    if (!TPRE) sthr[(i & 1) * NT + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
-    else if (i < NT) sthr[i] = tern_preload(L.thr_tc[2 * i], SMAX);                   // [0, NT): pre-loads
-    else if (i < NT + NT / 2) {                                                        // [NT, NT + NT/2): (thr0 - thr1) of channels 2j, 2j+1
+    if (i < NT) sthr[i] = tern_preload(L.thr_tc[2 * i], SMAX);                        // [0, NT): pre-loads
+    else if (TERN && i < NT + NT / 2) {                                                        // [NT, NT + NT/2): (thr0 - thr1) of channels 2j, 2j+1
       const int j = i - NT;
       reinterpret_cast<uint32_t*>(sthr)[i] = tern_delta(L.thr_tc[4 * j], L.thr_tc[4 * j + 1], L.thr_tc[4 * j + 2], L.thr_tc[4 * j + 3], SMAX);
     }
@@ -118,7 +113,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
 #ifdef BNNB_CONV_PRE_SMEM
   constexpr bool PRE_REG = false;
 #else
-  constexpr bool PRE_REG = ACC && NWG == 1 && NS == 1;
+  constexpr bool PRE_REG = NWG == 1 && NS == 1;
 #endif
   uint32_t pre[32];
   if (PRE_REG) {
@@ -147,12 +142,12 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     }
     tc::tmem_st_wait();
   };
-  uint32_t dl[16];  // TPRE, one word per warp and one channel block: the deltas live in registers too
-  if (TPRE && PRE_REG) {
+  uint32_t dl[16];  // 2-bit outputs, one word per warp and one channel block: the deltas live in registers too
+  if (TERN && PRE_REG) {
 #pragma unroll
     for (int c = 0; c < 16; c++) dl[c] = reinterpret_cast<const uint32_t*>(sthr)[NT + ((warp < 16 ? eg : 0) * NG) / 2 + c];
   }
-  if (ACC && warp < 16)
+  if (warp < 16)
     for (int slot = 0; slot < Cfg::SLOTS; slot++) preload(slot, slot % NS);
   tc::fence_before_sync();
   __syncthreads();
@@ -224,7 +219,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
 #pragma unroll
             for (int s = 0; s < Cfg::KC / 2; s++)
               tc::mma9_mxf4<IDIM, Cfg::KC * NT>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NT), d_hi, idesc, sf,
-                                               (ACC || s > 0) ? 1u : 0u);
+                                               1u);
             tc::commit(&full[slot]);
           }
           __syncwarp();
@@ -248,37 +243,29 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N + (uint32_t)eg * NG;
         uint32_t b0[NWG], b1[NWG];
         uint4 c4[NWG];  // e2m1 codes instead of bits when the consumer is another fp4 kernel
-        const bool codes = ACC && !POOL && out_fmt != ACT_BITS;
-        uint32_t r[2][32];
-        if (!TPRE) tc::tmem_ld32(trow, r[0]);
+        const bool codes = !POOL && out_fmt != ACT_BITS;
+        uint32_t r[32];  // TAP only
+        uint32_t hh[2][16];
+        tc::tmem_ld32_pack16(trow, hh[0]);
 #pragma unroll
         for (int j = 0; j < NWG; j++) {
           uint32_t w0 = 0, w1 = 0;
           c4[j] = make_uint4(0, 0, 0, 0);
-          if (TPRE) {
-            uint32_t hh[16];
-            tc::tmem_ld32_pack16(trow + j * 32, hh);
-            if (!PRE_REG) {  // the deltas of this block and word, from shared memory while the load is in flight
-              const uint4* dp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(sthr) + NT + (h * N + eg * NG + j * 32) / 2);
+          if (TERN && !PRE_REG) {  // the deltas of this block and word, from shared memory while the load is in flight
+            const uint4* dp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(sthr) + NT + (h * N + eg * NG + j * 32) / 2);
 #pragma unroll
-              for (int q = 0; q < 4; q++) { const uint4 v = dp[q]; dl[4 * q] = v.x; dl[4 * q + 1] = v.y; dl[4 * q + 2] = v.z; dl[4 * q + 3] = v.w; }
-            }
-            tc::tmem_ld_wait_dep16(hh);
-            if (codes) c4[j] = tern_codes16(hh, dl);
-            else tern_planes16(hh, dl, w0, w1);
-            if (TAP) { tc::tmem_ld32(trow + j * 32, r[j & 1]); tc::tmem_ld_wait_dep(r[j & 1]); }
+            for (int q = 0; q < 4; q++) { const uint4 v = dp[q]; dl[4 * q] = v.x; dl[4 * q + 1] = v.y; dl[4 * q + 2] = v.z; dl[4 * q + 3] = v.w; }
+          }
+          tc::tmem_ld_wait_dep16(hh[j & 1]);
+          if (j + 1 < NWG) tc::tmem_ld32_pack16(trow + (j + 1) * 32, hh[(j + 1) & 1]);  // in flight while word j is formed
+          if (TERN) {
+            if (codes) c4[j] = tern_codes16(hh[j & 1], dl);
+            else tern_planes16(hh[j & 1], dl, w0, w1);
           } else {
-          tc::tmem_ld_wait_dep(r[j & 1]);
-          if (j + 1 < NWG) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
+            if (codes) c4[j] = bin_codes16(hh[j & 1]);
+            else w0 = tern_bit_word(hh[j & 1]);
           }
-          if (TPRE) {
-          } else if (codes) {
-            c4[j] = f4_from_signs(r[j & 1]);
-          } else if (FOLD) {
-#pragma unroll
-            for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
-            w0 = ~w0;
-          }
+          if (TAP) { tc::tmem_ld32(trow + j * 32, r); tc::tmem_ld_wait_dep(r); }
           b0[j] = w0;
           b1[j] = w1;
           if (TAP) {  // parity taps (TAP instantiation only): the MMA sum of every valid output pixel and channel, pre-load un-folded
@@ -287,11 +274,11 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
               int32_t* ta = tap + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * NT + h * N + eg * NG + j * 32;
               const float* pv = sthr + h * N + eg * NG + j * 32;
 #pragma unroll
-              for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (ACC ? pv[c] : 0.0f));
+              for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[c]) - pv[c]);
             }
           }
         }
-        if (ACC) preload(slot, (gt + Cfg::SLOTS) % NS);
+        preload(slot, (gt + Cfg::SLOTS) % NS);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)

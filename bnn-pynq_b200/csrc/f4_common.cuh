@@ -84,6 +84,13 @@ __device__ __forceinline__ uint4 tern_codes16(const uint32_t (&h)[16], const uin
   }
   return make_uint4(v[0], v[1], v[2], v[3]);
 }
+// 1-bit outputs, 32 channels -> 16 bytes of e2m1 {0, +1}
+__device__ __forceinline__ uint4 bin_codes16(const uint32_t (&h)[16]) {
+  uint32_t v[4];
+#pragma unroll
+  for (int q = 0; q < 4; q++) v[q] = tern_nibble_mask(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]) & 0x22222222u;
+  return make_uint4(v[0], v[1], v[2], v[3]);
+}
 // one decision of 32 channels as a bit word (channel c at bit c)
 __device__ __forceinline__ uint32_t tern_bit_word(const uint32_t (&y)[16]) {
   uint32_t lo = 0, hi = 0;

@@ -59,9 +59,10 @@ template <int NB, int INM, int OUTM, bool TAP>
 __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                      int in_fmt, int out_fmt, int* __restrict__ status, int32_t* __restrict__ tap) {
   constexpr int SLAB = NB * 32, SLOTS = 3, SF_COL = 384, NW = NB / 32, EXP = 192, U = 4;  // EXP expander threads, U loads in flight each
-  constexpr bool FOLD = OUTM == OUT_BIT;
-  constexpr bool TPRE = OUTM == OUT_TERN;  // 2-bit outputs: biased pre-load + packed 16-bit epilogue (f4_common.cuh)
-  constexpr bool ACC = FOLD || TPRE;       // the MMAs accumulate onto a pre-load
+  // thresholded outputs: the accumulators are pre-loaded with the (first) threshold, biased so that bit 15 of the result's low half is
+  // the decision; the epilogue reads two channels per register (.pack::16b) and forms codes / bit words with PRMT (f4_common.cuh)
+  constexpr bool TERN = OUTM == OUT_TERN;
+  constexpr bool ACC = OUTM != OUT_SCORE;  // the MMAs accumulate onto a pre-load
   constexpr int OPL = OUTM == OUT_TERN ? 2 : 1;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t full[SLOTS], empty[SLOTS], a_part[2][4], a_empty[2], ring_full[GF_RING_MAX], ring_empty[GF_RING_MAX];
@@ -77,9 +78,9 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
     float tf = t == INT_MAX ? 3.0e38f : (float)t;
     if (OUTM == OUT_SCORE) tf = (float)t;
     const int smax = 2 * g.K;  // |S| <= K * max|w| * max|a|
-    if (!TPRE) sthr[(i & 1) * g.N + (i >> 1)] = FOLD ? -(tf + 0.5f) : tf;
+    if (!ACC) sthr[(i & 1) * g.N + (i >> 1)] = tf;
     else if (i < g.N) sthr[i] = tern_preload(L.thr_tc[2 * i], smax);                 // [0, N): pre-loads
-    else if (i < g.N + g.N / 2) {                                                    // [N, N + N/2): (thr0 - thr1) of channels 2j, 2j+1
+    else if (TERN && i < g.N + g.N / 2) {                                                    // [N, N + N/2): (thr0 - thr1) of channels 2j, 2j+1
       const int j = i - g.N;
       reinterpret_cast<uint32_t*>(sthr)[i] = tern_delta(L.thr_tc[4 * j], L.thr_tc[4 * j + 1], L.thr_tc[4 * j + 2], L.thr_tc[4 * j + 3], smax);
     }
@@ -116,7 +117,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
   };
   const int ntiles = (n_img + 127) / 128;
   const int T = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;  // tiles of this CTA
-  // FOLD: the accumulator slot of the j-th channel block overall (j = tile_local * nblk + nb) holds that block's pre-load
+  // pre-loads: the accumulator slot of the j-th channel block overall (j = tile_local * nblk + nb) holds that block's pre-load
   if (ACC && warp < 4)
     for (int j = 0; j < SLOTS && j < T * g.nblk; j++) preload(j, j % g.nblk);
   tc::fence_before_sync();
@@ -269,32 +270,36 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
         uint32_t b0[NW], b1[NW];
         uint4 c4[NW];  // e2m1 codes instead of bits when the consumer is another gemm_f4 launch
         const bool codes = ACC && out_fmt == ACT_F4T;
-        uint32_t r[2][32];
+        uint32_t r[2][32];  // scores, TAP
         uint32_t hh[2][16];
-        if (TPRE) tc::tmem_ld32_pack16(trow, hh[0]);
+        if (ACC) tc::tmem_ld32_pack16(trow, hh[0]);
         else tc::tmem_ld32(trow, r[0]);
 #pragma unroll
         for (int j = 0; j < NW; j++) {
           const float* th = sthr + nb * NB + j * 32;
           uint32_t w0 = 0, w1 = 0;
           c4[j] = make_uint4(0, 0, 0, 0);
-          if (TPRE) {
-            uint32_t dl[16];  // the deltas of this block and word, from shared memory while the load is in flight
-            const uint4* dp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(sthr) + g.N + (nb * NB + j * 32) / 2);
+          if (ACC) {
+            uint32_t dl[16];  // 2-bit outputs: the deltas of this block and word, from shared memory while the load is in flight
+            if (TERN) {
+              const uint4* dp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(sthr) + g.N + (nb * NB + j * 32) / 2);
 #pragma unroll
-            for (int q = 0; q < 4; q++) { const uint4 v = dp[q]; dl[4 * q] = v.x; dl[4 * q + 1] = v.y; dl[4 * q + 2] = v.z; dl[4 * q + 3] = v.w; }
+              for (int q = 0; q < 4; q++) { const uint4 v = dp[q]; dl[4 * q] = v.x; dl[4 * q + 1] = v.y; dl[4 * q + 2] = v.z; dl[4 * q + 3] = v.w; }
+            }
             tc::tmem_ld_wait_dep16(hh[j & 1]);
             if (j + 1 < NW) tc::tmem_ld32_pack16(trow + (j + 1) * 32, hh[(j + 1) & 1]);
-            if (codes) c4[j] = tern_codes16(hh[j & 1], dl);
-            else tern_planes16(hh[j & 1], dl, w0, w1);
+            if (TERN) {
+              if (codes) c4[j] = tern_codes16(hh[j & 1], dl);
+              else tern_planes16(hh[j & 1], dl, w0, w1);
+            } else {
+              if (codes) c4[j] = bin_codes16(hh[j & 1]);
+              else w0 = tern_bit_word(hh[j & 1]);
+            }
             if (TAP) { tc::tmem_ld32(trow + j * 32, r[j & 1]); tc::tmem_ld_wait_dep(r[j & 1]); }
           } else {
-          tc::tmem_ld_wait_dep(r[j & 1]);
-          if (j + 1 < NW) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
-          }
-          if (TPRE) {
-          } else if (OUTM == OUT_SCORE) {  // PassThroughActivation<ap_uint<16>>: (S + offset) mod 2^16, offset = #negative weights for 1-bit inputs
-            if (img < n_img) {
+            tc::tmem_ld_wait_dep(r[j & 1]);
+            if (j + 1 < NW) tc::tmem_ld32(trow + (j + 1) * 32, r[(j + 1) & 1]);  // in flight while word j is formed
+            if (img < n_img) {  // PassThroughActivation<ap_uint<16>>: (S + offset) mod 2^16, offset = #negative weights for 1-bit inputs
               int16_t* o16 = reinterpret_cast<int16_t*>(out) + (size_t)img * g.N + nb * NB + j * 32;
 #pragma unroll
               for (int c = 0; c < 32; c += 8) {
@@ -308,12 +313,6 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
                 *reinterpret_cast<uint4*>(o16 + c) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
               }
             }
-          } else if (codes) {
-            c4[j] = f4_from_signs(r[j & 1]);
-          } else if (FOLD) {
-#pragma unroll
-            for (int c = 31; c >= 0; c--) w0 = __funnelshift_l(r[j & 1][c], w0, 1);  // sign bits, channel c at bit c
-            w0 = ~w0;
           }
           b0[j] = w0;
           b1[j] = w1;
