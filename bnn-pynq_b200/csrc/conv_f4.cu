@@ -33,6 +33,21 @@ struct F4Cfg {
   static constexpr int SF_COL = 384, PD = POOL ? OD / 2 : OD;
 };
 
+// experiment switches (results wrong, hand-offs kept): -DBNNB_CONV_STRIP=<bits> 1: no MMAs, 2: no TMEM loads + harvest, 4: no pre-load,
+// 8: no global stores, 16: no input copies
+#ifndef BNNB_CONV_STRIP
+#define BNNB_CONV_STRIP 0
+#endif
+constexpr int kStrip = BNNB_CONV_STRIP;
+#ifndef BNNB_G2T
+#define BNNB_G2T 9
+#endif
+#ifndef BNNB_G3T
+#define BNNB_G3T 6
+#endif
+#ifndef BNNB_CONV_EGS
+#define BNNB_CONV_EGS 0
+#endif
 __device__ __forceinline__ void hsync(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 
 // 8 bits -> 8 nibbles (bit i at position 4i)
@@ -64,6 +79,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
                                                      int in_fmt, int out_fmt, int* __restrict__ status, int32_t* __restrict__ tap) {
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
+  static_assert(BNNB_CONV_EGS == 4 || BNNB_CONV_EGS == 2 || BNNB_CONV_EGS == 0, "epilogue groups");
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t full[4], empty[4], abuf_full[2], abuf_empty[2];
   __shared__ uint32_t tmem_base;
@@ -71,9 +87,13 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   float* sthr = reinterpret_cast<float*>(smem + Cfg::OFF_THR);  // [2][N]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int role = warp < 16 ? 0 : (warp < 19 ? 1 : 2), ht = tid & 127, hw = warp & 3;
-  const int eg = (warp >> 2) & 3;  // epilogue group (role 0): output channels [eg*N/4, (eg+1)*N/4) of the block
-  constexpr int NWG = Cfg::NW / 4;  // 32-channel words per epilogue group
-  constexpr int NG = N / 4;         // channels per epilogue group
+  // epilogue warps (role 0): EGS channel groups x TEAMS tile teams of four warps (one per TMEM lane quarter); team t takes the tiles
+  // with gt % TEAMS == t, group eg the output channels [eg*N/EGS, (eg+1)*N/EGS) of the block
+  // (measured: 1-bit outputs 2 x 2 - the fixed per-tile cost of a warp is halved; 2-bit outputs 4 x 1 - their longer harvest per channel dominates)
+  constexpr int EGS = BNNB_CONV_EGS ? BNNB_CONV_EGS : (OUTM == OUT_BIT ? 2 : 4), TEAMS = 4 / EGS;
+  const int eg = ((warp >> 2) & 3) % EGS, team = ((warp >> 2) & 3) / EGS;
+  constexpr int NWG = Cfg::NW / EGS;  // 32-channel words per epilogue group
+  constexpr int NG = N / EGS;         // channels per epilogue group
   constexpr int KCT = 9 * Cfg::KC;
   // The accumulators are pre-loaded with the (first) threshold, biased so that the low 16 bits of the result hold the decision
   // thr < S in bit 15 (f4_common.cuh), and every MMA accumulates.  The epilogue reads two channels per register (.pack::16b: the
@@ -98,7 +118,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
   if (tid == 0) {
     for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], in_fmt == ACT_F4P ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); }
-    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 16); }
+    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4 * EGS); }
     tc::mbar_init_fence();
   }
   tc::fence_async_smem();
@@ -148,7 +168,8 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     for (int c = 0; c < 16; c++) dl[c] = reinterpret_cast<const uint32_t*>(sthr)[NT + ((warp < 16 ? eg : 0) * NG) / 2 + c];
   }
   if (warp < 16)
-    for (int slot = 0; slot < Cfg::SLOTS; slot++) preload(slot, slot % NS);
+    for (int slot = 0; slot < Cfg::SLOTS; slot++)
+      if (slot % TEAMS == team) preload(slot, slot % NS);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -171,10 +192,10 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
           uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
           const int valid = n_img - img0 < G ? n_img - img0 : G;  // rows of missing images keep stale (finite) codes; never stored
-          tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)valid * CW * IMG_PLANE);
+          if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)valid * CW * IMG_PLANE);
           for (int gi = 0; gi < valid; gi++)
             for (int j = 0; j < CW; j++)
-              tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE + (size_t)gi * IMG_PLANE, in4 + ((size_t)(img0 + gi) * CW + j) * IMG_PLANE, IMG_PLANE,
+              if (!(kStrip & 16)) tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE + (size_t)gi * IMG_PLANE, in4 + ((size_t)(img0 + gi) * CW + j) * IMG_PLANE, IMG_PLANE,
                            &abuf_full[buf]);
         }
       }
@@ -218,7 +239,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           if (leader) {  // nine taps per asm block (tcgen05.cuh: mma9_mxf4), once per pair of operand planes
 #pragma unroll
             for (int s = 0; s < Cfg::KC / 2; s++)
-              tc::mma9_mxf4<IDIM, Cfg::KC * NT>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NT), d_hi, idesc, sf,
+              if (!(kStrip & 1)) tc::mma9_mxf4<IDIM, Cfg::KC * NT>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NT), d_hi, idesc, sf,
                                                1u);
             tc::commit(&full[slot]);
           }
@@ -237,6 +258,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
       for (int vt = 0; vt < Cfg::TILES * NS; vt++) {
         const int t = vt / NS, h = vt % NS;
         const int gt = k * Cfg::TILES * NS + vt, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
+        if (TEAMS > 1 && gt % TEAMS != team) continue;
         if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
@@ -246,11 +268,12 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         const bool codes = !POOL && out_fmt != ACT_BITS;
         uint32_t r[32];  // TAP only
         uint32_t hh[2][16];
-        tc::tmem_ld32_pack16(trow, hh[0]);
+        if (!(kStrip & 2)) tc::tmem_ld32_pack16(trow, hh[0]);
 #pragma unroll
         for (int j = 0; j < NWG; j++) {
           uint32_t w0 = 0, w1 = 0;
           c4[j] = make_uint4(0, 0, 0, 0);
+          if (kStrip & 2) { b0[j] = b1[j] = 0; continue; }
           if (TERN && !PRE_REG) {  // the deltas of this block and word, from shared memory while the load is in flight
             const uint4* dp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(sthr) + NT + (h * N + eg * NG + j * 32) / 2);
 #pragma unroll
@@ -278,7 +301,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
             }
           }
         }
-        preload(slot, (gt + Cfg::SLOTS) % NS);
+        if (!(kStrip & 4)) preload(slot, (gt + Cfg::SLOTS) % NS);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
@@ -288,8 +311,8 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         } else {  // straight to global: one output pixel (half of its channels) per thread
           const int gi = m / Cfg::PXI, rem = m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
           const bool valid = m < Cfg::ROWS && y < OD && x < OD && img0 + gi < n_img;
-          if (valid && !codes) row = out + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * WPP;
-          if (valid && codes) {
+          if (valid && !codes && !(kStrip & 8)) row = out + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * WPP;
+          if (valid && codes && !(kStrip & 8)) {
             const size_t img = (size_t)(img0 + gi);
             const int px = y * OD + x;
             uint4* out4 = reinterpret_cast<uint4*>(out);
@@ -402,11 +425,11 @@ bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {
     if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, 6, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, BNNB_G2T, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
   }
   if (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) {
     if (a1) return launch_cfg<128, 128, 1, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, 4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, BNNB_G3T, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
   }
   if (d.ifm_ch == 128 && d.N == 256 && d.ifm_dim == 5 && !d.pool) {  // two channel blocks of 128 share the operand planes
     if (a1) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);

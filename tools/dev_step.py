@@ -26,7 +26,15 @@ d_out = torch.empty(B * rt.out_bytes, dtype=torch.uint8, device=dev)
 d_cls = torch.empty(B, dtype=torch.int32, device=dev)
 torch.cuda.synchronize()
 rt.prep_device(d_raw.data_ptr(), B, d_in.data_ptr())
+prof = os.environ.get("DEV_STEP_PROFILE")
+if prof:  # per-layer CUDA-event times (after one warm-up step)
+    rt.infer_device(d_in.data_ptr(), B, d_out.data_ptr(), d_cls.data_ptr() if cnv else 0, 10)
+    rt.sync()
+    rt.profile_enable(True)
 for _ in range(steps):
     rt.infer_device(d_in.data_ptr(), B, d_out.data_ptr(), d_cls.data_ptr() if cnv else 0, 10)
 rt.sync()
+if prof:
+    ms, cnt = rt.profile_collect()
+    print(prof, net, "layer_ms", [round(float(x) / steps, 3) for x in ms], "total %.3f" % (float(sum(ms)) / steps))
 print("done: %d steps x %d images" % (steps, B))
