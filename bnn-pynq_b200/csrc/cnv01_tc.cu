@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
 
   // ---- one-time setup -------------------------------------------------------------------------------------------------
   for (int i = tid; i < 64 * 9 * S::NPL; i += NT01) {  // layer-1 weights -> chunk-major operand layout
-    const int p = i % 64, kc = i / 64, n = TFOLD ? tfold_channel(p) : p;  // accumulator column p holds channel n
+    const int p = i % 64, kc = i / 64, n = CP ? tfold_channel(p) : p;  // accumulator column p holds channel n
     const uint8_t* src = F4 ? L1.w4 + (size_t)n * (L1.kpad / 2) : reinterpret_cast<const uint8_t*>(L1.w8) + (size_t)n * L1.kpad;
     uint4 wv = *reinterpret_cast<const uint4*>(src + kc * 16);
     if (CP) { wv.x = fold_nibble_order(wv.x); wv.y = fold_nibble_order(wv.y); wv.z = fold_nibble_order(wv.z); wv.w = fold_nibble_order(wv.w); }
@@ -497,8 +497,12 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     acc_t thrA[32];
 #pragma unroll
     for (int c = 0; c < 32; c++) {
-      const acc_t t = sthr1t[2 * (TFOLD ? tfold_channel(team * 32 + c) : team * 32 + c)];
-      thrA[c] = FOLD ? (acc_t)((float)t > 1.0e38f ? 3.0e38f : 6.0f * (float)t + 3.0f) : t;  // 6 * (thr + 1/2); the sentinel never fires
+      const acc_t t = sthr1t[2 * (CP ? tfold_channel(team * 32 + c) : team * 32 + c)];
+      thrA[c] = t;
+      // FOLD pre-load: 1.5 * 2^23 + 32768 + 6 * thr + 5.  Layer 0 writes a set decision as the code 0xF = -6.0, so the MMAs leave
+      // U = 6 * thr + 5 - 6 * S + 32768 in the low 16 bits: bit 15 clear <=> 6 * S > 6 * thr + 5 <=> thr < S  (|S| <= 576: thresholds
+      // outside [-577, 576] decide like the nearest bound, and the "no threshold" sentinel never fires)
+      if (FOLD) thrA[c] = (acc_t)(12582912.0f + 32768.0f + 5.0f + 6.0f * fminf(fmaxf((float)t, -577.0f), 576.0f));
       // TFOLD pre-load: 1.5 * 2^23 + 32768 + thr0 (|S| <= 2 * 576: thresholds outside [-1153, 1152] decide like the nearest bound)
       if (TFOLD) thrA[c] = (acc_t)(12582912.0f + 32768.0f + fminf(fmaxf((float)t, -1153.0f), 1152.0f));
     }
@@ -533,7 +537,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
         uint32_t r[32];
-        if ((kEpi || !FOLD) && (!TFOLD || TAP)) {
+        if (!CP || TAP) {
           tc::tmem_ld32(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, r);
           tc::tmem_ld_wait_dep(r);
         }
@@ -552,13 +556,13 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
           b0 = ~(n0 ^ n1);  // not zero: both thresholds exceeded, or neither
           b1 = ~(n0 | n1);  // +1: both
         } else if (FOLD) {
-          uint32_t q0 = 0, q1 = 0, q2 = 0, q3 = 0;  // four independent chains (a lone chain of 32 dependent shifts is pure latency)
+          uint32_t h[16];  // low 16 bits of the accumulators, columns 2j / 2j+1 in the halves: bit 15 = NOT (thr < S)
+          tc::tmem_ld32_pack16(tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 64 + team * 32, h);
+          tc::tmem_ld_wait_dep16(h);
+          uint32_t n0 = 0;
 #pragma unroll
-          for (int c = 7; c >= 0; c--) {
-            q0 = __funnelshift_l(r[c], q0, 1); q1 = __funnelshift_l(r[8 + c], q1, 1);
-            q2 = __funnelshift_l(r[16 + c], q2, 1); q3 = __funnelshift_l(r[24 + c], q3, 1);
-          }
-          b0 = __byte_perm(q0, q1, 0x1140) | __byte_perm(q2, q3, 0x4011);
+          for (int g = 0; g < 8; g++) n0 |= sign_bytes(h[2 * g], h[2 * g + 1]) & (0x01010101u << g);  // channels g, 8+g, 16+g, 24+g
+          b0 = ~n0;
         } else {
 #pragma unroll
           for (int c = 0; c < 32; c++) {
@@ -570,14 +574,14 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         }
         if (kEpi || !FOLD) sbk[(size_t)m * WPP + team] = b0;
         if (OUTM == OUT_TERN) sbk[(size_t)m * WPP + 2 + team] = b1;
-        if (TAP) {  // parity taps: the MMA sum of every valid output pixel and channel (FOLD: un-fold 6*thr + 3 - 6*S)
+        if (TAP) {  // parity taps: the MMA sum of every valid output pixel and channel (pre-load un-folded)
           const int y = m / 30, x = m - y * 30;
           if (y < 28 && x < 28) {
             int32_t* ta = tp.acc1 + ((size_t)(first + (long long)k * stride) * 784 + (y * 28 + x)) * 64 + team * 32;
 #pragma unroll
             for (int c = 0; c < 32; c++) {
               if (TFOLD) ta[tfold_channel(c)] = (int)(__float_as_uint((float)thrA[c]) - r[c]);  // both are 0x4B400000 + integer
-              else if (FOLD) ta[c] = __float2int_rn(__fdiv_rn((float)thrA[c] - __uint_as_float(r[c]), 6.0f));
+              else if (FOLD) ta[tfold_channel(c)] = (int)(__float_as_uint((float)thrA[c]) - r[c]) / 6;       // pre-load - accumulator = 6 * S
               else ta[c] = F4 ? __float2int_rn(__uint_as_float(r[c])) : (int)r[c];
             }
           }
