@@ -12,6 +12,7 @@
 //   warp  19        MMA issuer, up to three tiles ahead (three TMEM accumulator slots)
 // decoupled by mbarriers only: abuf_full / abuf_empty per operand buffer, full / empty per accumulator slot.
 #include <climits>
+#include <cstdlib>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
 #include "f4_common.cuh"
@@ -74,14 +75,14 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
   return make_uint4(v[0], v[1], v[2], v[3]);
 }
 
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool TAP>
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool TAP, bool PAIR>
 __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                      int in_fmt, int out_fmt, int* __restrict__ status, int32_t* __restrict__ tap) {
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
   static_assert(BNNB_CONV_EGS == 4 || BNNB_CONV_EGS == 2 || BNNB_CONV_EGS == 0, "epilogue groups");
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t full[4], empty[4], abuf_full[2], abuf_empty[2];
+  __shared__ __align__(8) uint64_t full[4], empty[4], abuf_full[2], abuf_empty[2], peer_full[2];
   __shared__ uint32_t tmem_base;
   uint8_t* sb = smem + Cfg::OFF_B;
   float* sthr = reinterpret_cast<float*>(smem + Cfg::OFF_THR);  // [2][N]
@@ -103,9 +104,16 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   constexpr int SMAX = 2 * 9 * C;        // |S| <= K * max|w| * max|a|
 
   constexpr int NT = Cfg::NT;
-  for (int i = tid; i < NT * KCT; i += 640) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
-    const int n = i % NT, kc = i / NT;
-    *reinterpret_cast<uint4*>(sb + ((size_t)kc * NT + n) * 16) = *reinterpret_cast<const uint4*>(L.w4 + (size_t)n * (L.kpad / 2) + kc * 16);
+  // PAIR (cta_group::2, ACT_F4P inputs): the two CTAs of a cluster - the two SMs of a TPC - run every MMA together with M = 256: each
+  // keeps its own image group (operand rows, accumulator lanes) and HALF of every channel block's weight rows, so an MMA costs each
+  // SM 32 + 32 shared-memory wavefronts instead of 32 + 64 (these shapes are operand-fetch-bound: 64 per 64 clocks of math at N = 128).
+  // The leader (rank 0) issues and commits to both CTAs' barriers; the follower's loader and epilogue warps arrive on the leader's.
+  const uint32_t rank = PAIR ? tc::cluster_ctarank() : 0;
+  constexpr int NTL = PAIR ? NT / 2 : NT, NL = PAIR ? N / 2 : N;  // weight rows this CTA holds: per layer, per channel block
+  for (int i = tid; i < NTL * KCT; i += 640) {  // weights (packed e2m1, [N][K/2]) -> chunk-major operand layout
+    const int nl = i % NTL, kc = i / NTL;
+    const int n = PAIR ? (nl / NL) * N + (int)rank * NL + nl % NL : nl;
+    *reinterpret_cast<uint4*>(sb + ((size_t)kc * NTL + nl) * 16) = *reinterpret_cast<const uint4*>(L.w4 + (size_t)n * (L.kpad / 2) + kc * 16);
   }
   for (int i = tid; i < 2 * NT; i += 640) {
     if (i < NT) sthr[i] = tern_preload(L.thr_tc[2 * i], SMAX);                        // [0, NT): pre-loads
@@ -115,15 +123,17 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     }
   }
   for (int i = tid; i < 2 * Cfg::A_BYTES / 16; i += 640) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);  // pad pixels stay 0
-  if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
+  if (PAIR) tc::cluster_sync();  // both CTAs are resident before the paired allocation
+  if (warp == 0) { if (PAIR) tc::tmem_alloc_pair(&tmem_base, 512); else tc::tmem_alloc(&tmem_base, 512); }
   if (tid == 0) {
-    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], in_fmt == ACT_F4P ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); }
-    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 4 * EGS); }
+    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], in_fmt == ACT_F4P ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); tc::mbar_init(&peer_full[i], 1); }
+    for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], (PAIR ? 2 : 1) * 4 * EGS); }
     tc::mbar_init_fence();
   }
   tc::fence_async_smem();
   tc::fence_before_sync();
   __syncthreads();
+  if (PAIR) tc::cluster_sync();  // the peer's barriers are initialised and its weights staged before anything crosses
   tc::fence_after_sync();
   const uint32_t tmem = tmem_base;
   if (warp < 4) tc::tmem_fill16(tmem + ((uint32_t)(warp * 32) << 16) + Cfg::SF_COL, 0x7f7f7f7fu);  // every scale factor = 1.0 (ue8m0)
@@ -172,12 +182,17 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
       if (slot % TEAMS == team) preload(slot, slot % NS);
   tc::fence_before_sync();
   __syncthreads();
+  if (PAIR) tc::cluster_sync();  // the peer's pre-loads are in place before the leader's first MMA accumulates onto them
   tc::fence_after_sync();
-  const uint32_t idesc = tc::make_idesc_mxf4(128, N);
+  const uint32_t idesc = tc::make_idesc_mxf4(PAIR ? 256 : 128, N);
   const uint32_t sa_u0 = tc::smem_u32(smem), sb_u = tc::smem_u32(sb), sf = tmem + Cfg::SF_COL;
   bool failed = false;
   const int ngroups = (n_img + G - 1) / G;
-  const int K = (int)blockIdx.x < ngroups ? (ngroups - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;  // groups of this CTA
+  // groups of this CTA: k-th group = gfirst + k * gstride (PAIR: the cluster takes pairs of groups, rank r the r-th of each pair; both
+  // CTAs run the same number of rounds - a group past the end is empty: nothing loaded, nothing stored)
+  const int nunits = PAIR ? (ngroups + 1) / 2 : ngroups, unit0 = PAIR ? (int)blockIdx.x >> 1 : (int)blockIdx.x, ustride = PAIR ? (int)gridDim.x >> 1 : (int)gridDim.x;
+  const int K = unit0 < nunits ? (nunits - unit0 + ustride - 1) / ustride : 0;
+  const int gfirst = PAIR ? 2 * unit0 + (int)rank : unit0, gstride = PAIR ? 2 * ustride : ustride;
 
   if (role == 1) {
     // ---- operand planes of group k+1: ACT_F4P input = one TMA bulk copy per (image, plane), issued by one thread; ACT_BITS input
@@ -188,20 +203,24 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
         constexpr uint32_t IMG_PLANE = Cfg::PXI * 16;  // bytes of one plane of one image
         for (int k = 0; k < K; k++) {
-          const int img0 = ((int)blockIdx.x + k * (int)gridDim.x) * G, buf = k & 1;
+          const int img0 = (gfirst + k * gstride) * G, buf = k & 1;
           if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
           uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
-          const int valid = n_img - img0 < G ? n_img - img0 : G;  // rows of missing images keep stale (finite) codes; never stored
+          const int valid = n_img - img0 < G ? (n_img - img0 > 0 ? n_img - img0 : 0) : G;  // rows of missing images keep stale (finite) codes; never stored
           if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)valid * CW * IMG_PLANE);
           for (int gi = 0; gi < valid; gi++)
             for (int j = 0; j < CW; j++)
               if (!(kStrip & 16)) tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE + (size_t)gi * IMG_PLANE, in4 + ((size_t)(img0 + gi) * CW + j) * IMG_PLANE, IMG_PLANE,
                            &abuf_full[buf]);
+          if (PAIR && rank != 0) {  // the follower tells the leader's issuer once its planes have landed
+            if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+            tc::mbar_arrive_remote(&peer_full[buf], 0);
+          }
         }
       }
     } else
     for (int k = 0; k < K; k++) {
-      const int img0 = ((int)blockIdx.x + k * (int)gridDim.x) * G, buf = k & 1;
+      const int img0 = (gfirst + k * gstride) * G, buf = k & 1;
       if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
       uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
 #pragma unroll 4
@@ -221,31 +240,32 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   } else if (role == 2) {
     // ---- issuer: the whole warp runs the schedule (uniform control flow), one elected lane issues; descriptors as (lo, hi) words
     // so that the address arithmetic per MMA is one add (a lone thread issues about one instruction per five clocks) ------------
-    {
+    if (!PAIR || rank == 0) {
       const bool leader = tc::elect_one();
       const uint32_t d_hi = tc::desc_hi(128);
       const uint32_t a_lo[2] = {tc::desc_lo(sa_u0, Cfg::PLANE), tc::desc_lo(sa_u0 + Cfg::A_BYTES, Cfg::PLANE)};
-      const uint32_t b_lo = tc::desc_lo(sb_u, NT * 16);
+      const uint32_t b_lo = tc::desc_lo(sb_u, NTL * 16);
       for (int k = 0; k < K; k++) {
         const int buf = k & 1;
         if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        if (PAIR && !failed && !tc::mbar_wait(&peer_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
         for (int vt = 0; vt < Cfg::TILES * NS; vt++) {  // virtual tile = (row tile t, channel block h)
           const int t = vt / NS, h = vt % NS;
           const int gt = k * Cfg::TILES * NS + vt, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
           if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * N;
-          const uint32_t at = a_lo[buf] + (uint32_t)(t * 128), bt = b_lo + (uint32_t)(h * N);
+          const uint32_t at = a_lo[buf] + (uint32_t)(t * 128), bt = b_lo + (uint32_t)(h * NL);
           if (leader) {  // nine taps per asm block (tcgen05.cuh: mma9_mxf4), once per pair of operand planes
 #pragma unroll
             for (int s = 0; s < Cfg::KC / 2; s++)
-              if (!(kStrip & 1)) tc::mma9_mxf4<IDIM, Cfg::KC * NT>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NT), d_hi, idesc, sf,
+              if (!(kStrip & 1)) tc::mma9_mxf4<IDIM, Cfg::KC * NTL, PAIR ? 2 : 1>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NTL), d_hi, idesc, sf,
                                                1u);
-            tc::commit(&full[slot]);
+            if (PAIR) tc::commit_pair(&full[slot]); else tc::commit(&full[slot]);
           }
           __syncwarp();
         }
-        if (leader) tc::commit(&abuf_empty[buf]);
+        if (leader) { if (PAIR) tc::commit_pair(&abuf_empty[buf]); else tc::commit(&abuf_empty[buf]); }
         __syncwarp();
       }
     }
@@ -254,7 +274,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     uint32_t* sbits = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_BITS);
     constexpr int NW = Cfg::NW, NWT = Cfg::NWT, WPP = Cfg::WPP;
     for (int k = 0; k < K; k++) {
-      const int img0 = ((int)blockIdx.x + k * (int)gridDim.x) * G;
+      const int img0 = (gfirst + k * gstride) * G;
       for (int vt = 0; vt < Cfg::TILES * NS; vt++) {
         const int t = vt / NS, h = vt % NS;
         const int gt = k * Cfg::TILES * NS + vt, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
@@ -304,7 +324,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         if (!(kStrip & 4)) preload(slot, (gt + Cfg::SLOTS) % NS);
         tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's share of the accumulator has been read (and re-loaded)
+        if (lane == 0) { if (PAIR && rank != 0) tc::mbar_arrive_remote(&empty[slot], 0); else tc::mbar_arrive(&empty[slot]); }  // this warp's share has been read (and re-loaded)
         uint32_t* row = nullptr;
         if (POOL) {
           row = sbits + (size_t)m * WPP;
@@ -384,7 +404,8 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   if (failed && status) *status = 1;
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+  if (PAIR) tc::cluster_sync();  // the leader's MMAs read this CTA's shared memory and write its accumulators until the very end
+  if (warp == 0) { if (PAIR) tc::tmem_dealloc_pair(tmem, 512); else tc::tmem_dealloc(tmem, 512); }
 }
 
 template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
@@ -395,13 +416,38 @@ bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img,
   static_assert(Cfg::SLOTS * N <= Cfg::SF_COL, "TMEM budget");
   const int ngroups = (n_img + G - 1) / G;
   const int grid = ngroups < num_sms ? ngroups : num_sms;
+  // CTA pairs where they pay.  Measured, ms per 65 536 images, single -> paired: 1-bit layers 2 / 3 / 4: 0.335 -> 0.334, 0.413 -> 0.425,
+  // 0.166 -> 0.140; 2-bit: 0.461 -> 0.503, 0.460 -> 0.398, 0.191 -> 0.176.  BNN_B200_CONV_PAIR=<mask> overrides (bit 0 / 1 / 2: layer 2 / 3 / 4)
+  static const int pair_env = getenv("BNN_B200_CONV_PAIR") ? atoi(getenv("BNN_B200_CONV_PAIR")) : -1;
+  const int pair_mask = pair_env >= 0 ? pair_env : (OUTM == OUT_TERN ? 6 : 4), pair_bit = NS == 2 ? 4 : (POOL ? 2 : 1);
+  if (in_fmt == ACT_F4P && ngroups >= 2 && (pair_mask & pair_bit)) {  // a cluster of two per TPC, each pair takes two image groups per round
+    const int npairs = (ngroups + 1) / 2, maxpairs = num_sms / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * (npairs < maxpairs ? npairs : maxpairs));
+    cfg.blockDim = dim3(640);
+    cfg.dynamicSmemBytes = Cfg::SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    if (tap) {
+      auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, true>;
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+      return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, status, tap) == cudaSuccess;
+    }
+    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, true>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+    return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, status, (int32_t*)nullptr) == cudaSuccess;
+  }
   if (tap) {  // parity taps: the TAP instantiation of the same kernel
-    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true>;
+    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, false>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
     kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status, tap);
     return true;
   }
-  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false>;
+  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, false>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
   kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status, nullptr);
   return true;

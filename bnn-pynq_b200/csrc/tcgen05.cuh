@@ -60,6 +60,51 @@ __device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// ---- CTA pairs (cta_group::2): two CTAs of a cluster, one per SM of a TPC, run ONE MMA of M = 256: each keeps its own 128 operand
+// rows and accumulator lanes and HALF of the B rows; the leader (cluster rank 0) issues, commits are multicast to both ----------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `cta` of the cluster.  (Default semantics, release at CTA scope: a
+// cluster-scope release would wait for the warp's outstanding global stores - measured +50 % on the paired conv kernels.)
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t"
+      "}\n" ::"r"(smem_u32(bar)), "r"(cta)
+      : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void commit_pair(uint64_t* bar) {  // both CTAs' barrier at this offset
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)), "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_dst, uint32_t ncols) {  // the same warp of BOTH CTAs, same smem_dst offset
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
@@ -103,6 +148,18 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
         if (mbar_try_wait(bar, parity)) return true;
     }
     const uint64_t now = global_timer_ns();  // every 2^14 polls (tens of microseconds)
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > BNNB_WAIT_NS) return false;
+  }
+}
+
+// the same for a barrier that CTAs of the cluster arrive on (acquire at cluster scope)
+__device__ __forceinline__ bool mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint64_t t0 = 0;
+  for (;;) {
+    for (uint32_t i = 0; i < (1u << 14); i++)
+      if (mbar_try_wait_cluster(bar, parity)) return true;
+    const uint64_t now = global_timer_ns();
     if (t0 == 0) t0 = now;
     else if (now - t0 > BNNB_WAIT_NS) return false;
   }
@@ -260,41 +317,42 @@ __device__ __forceinline__ void mma_i8_lh(uint32_t tmem_d, uint32_t alo, uint32_
 //   a_lo: descriptor low word of the tile's first operand row; tap (ky,kx) starts (ky*IDIM + kx) rows further (16-byte units)
 //   b_lo: low word of tap 0's weight block; consecutive taps are BSTEP 16-byte units apart
 namespace bnnb { namespace tc {
-template <int IDIM, int BSTEP>
-__device__ __forceinline__ void mma9_mxf4(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t d_hi, uint32_t idesc, uint32_t sf, uint32_t acc_first) {
-#define BNNB_TAP(T)                                                                                            \
-  "add.u32 al, %1, " #T "*0+%7+0;\n\t"
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p, q;\n\t"
-      ".reg .b32 al, bl;\n\t"
-      ".reg .b64 a, b;\n\t"
-      "setp.ne.b32 p, %6, 0;\n\t"
-      "setp.eq.b32 q, 0, 0;\n\t"
-      "mov.b64 a, {%1, %3};\n\t"
-      "mov.b64 b, {%2, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], p;\n\t"
-      "add.u32 al, %1, 1;\n\t add.u32 bl, %2, %7;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
-      "add.u32 al, %1, 2;\n\t add.u32 bl, %2, %8;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
-      "add.u32 al, %1, %15;\n\t add.u32 bl, %2, %9;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
-      "add.u32 al, %1, %16;\n\t add.u32 bl, %2, %10;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
-      "add.u32 al, %1, %17;\n\t add.u32 bl, %2, %11;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
-      "add.u32 al, %1, %18;\n\t add.u32 bl, %2, %12;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
-      "add.u32 al, %1, %19;\n\t add.u32 bl, %2, %13;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
-      "add.u32 al, %1, %20;\n\t add.u32 bl, %2, %14;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
-      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
-      "}\n" ::"r"(tmem_d),
-      "r"(a_lo), "r"(b_lo), "r"(d_hi), "r"(idesc), "r"(sf), "r"(acc_first), "n"(BSTEP), "n"(2 * BSTEP), "n"(3 * BSTEP), "n"(4 * BSTEP), "n"(5 * BSTEP),
-      "n"(6 * BSTEP), "n"(7 * BSTEP), "n"(8 * BSTEP), "n"(IDIM), "n"(IDIM + 1), "n"(IDIM + 2), "n"(2 * IDIM), "n"(2 * IDIM + 1), "n"(2 * IDIM + 2)
+#define BNNB_MMA9_BODY(CG)                                                                                     \
+  asm volatile( \
+      "{\n\t" \
+      ".reg .pred p, q;\n\t" \
+      ".reg .b32 al, bl;\n\t" \
+      ".reg .b64 a, b;\n\t" \
+      "setp.ne.b32 p, %6, 0;\n\t" \
+      "setp.eq.b32 q, 0, 0;\n\t" \
+      "mov.b64 a, {%1, %3};\n\t" \
+      "mov.b64 b, {%2, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], p;\n\t" \
+      "add.u32 al, %1, 1;\n\t add.u32 bl, %2, %7;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
+      "add.u32 al, %1, 2;\n\t add.u32 bl, %2, %8;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
+      "add.u32 al, %1, %15;\n\t add.u32 bl, %2, %9;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
+      "add.u32 al, %1, %16;\n\t add.u32 bl, %2, %10;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
+      "add.u32 al, %1, %17;\n\t add.u32 bl, %2, %11;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
+      "add.u32 al, %1, %18;\n\t add.u32 bl, %2, %12;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
+      "add.u32 al, %1, %19;\n\t add.u32 bl, %2, %13;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
+      "add.u32 al, %1, %20;\n\t add.u32 bl, %2, %14;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
+      "}\n" ::"r"(tmem_d), \
+      "r"(a_lo), "r"(b_lo), "r"(d_hi), "r"(idesc), "r"(sf), "r"(acc_first), "n"(BSTEP), "n"(2 * BSTEP), "n"(3 * BSTEP), "n"(4 * BSTEP), "n"(5 * BSTEP), \
+      "n"(6 * BSTEP), "n"(7 * BSTEP), "n"(8 * BSTEP), "n"(IDIM), "n"(IDIM + 1), "n"(IDIM + 2), "n"(2 * IDIM), "n"(2 * IDIM + 1), "n"(2 * IDIM + 2) \
       : "memory");
-#undef BNNB_TAP
+template <int IDIM, int BSTEP, int CG = 1>
+__device__ __forceinline__ void mma9_mxf4(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t d_hi, uint32_t idesc, uint32_t sf, uint32_t acc_first) {
+  if (CG == 2) { BNNB_MMA9_BODY(2); }
+  else { BNNB_MMA9_BODY(1); }
+#undef BNNB_MMA9_BODY
 }
 }}  // namespace bnnb::tc
 
