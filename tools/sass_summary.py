@@ -13,7 +13,7 @@ from collections import Counter, OrderedDict
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "bnn-pynq_b200")
 HOT = ("k_cnv01_tc", "k_conv_f4", "k_gemm_f4", "k_conv_tc", "k_gemm_tc", "k_layer_popc", "k_conv0", "k_patch_apply", "k_prep_cifar", "k_prep_mnist")
-MNEMONICS = ("UTCOMMA", "UTCIMMA", "UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTCBAR", "UBLKCP", "UTMALDG", "SYNCS", "POPC", "LOP3", "SHF", "PRMT", "IMMA", "IDP")
+MNEMONICS = ("UTCOMMA", "UTCOMMA.2CTA", "UTCBAR.2CTA", "UTCIMMA", "UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTCBAR", "UBLKCP", "UTMALDG", "SYNCS", "POPC", "LOP3", "SHF", "PRMT", "IMMA", "IDP")
 SHOW = ("UTCOMMA", "UTCIMMA", "LDTM", "STTM", "UBLKCP", "UTCBAR")
 
 
@@ -58,12 +58,15 @@ def main():
         name = dm.get(mangled, mangled)
         if not any(h + "<" in name or h + "(" in name for h in HOT):
             continue
-        tap = re.search(r"(\(bool\)1|true)>\(", name) is not None and ("k_cnv01_tc" in name or "k_conv_f4" in name or "k_gemm_f4" in name)
+        # TAP flag: the last template argument of k_cnv01_tc / k_gemm_f4, the last but one of k_conv_f4 (whose last is PAIR)
+        m = re.search(r"((?:\(bool\)[01]|true|false)(?:, (?:\(bool\)[01]|true|false))?)>\(", name)
+        flags = [f in ("(bool)1", "true") for f in m.group(1).split(", ")] if m else []
+        tap = bool(flags) and (flags[0] if ("k_conv_f4" in name and len(flags) == 2) else flags[-1]) and ("k_cnv01_tc" in name or "k_conv_f4" in name or "k_gemm_f4" in name)
         cnt = Counter()
         first = {}
         for i, ins in enumerate(body):
             for mn in MNEMONICS:
-                if re.search(r"\b%s\b|\b%s\." % (mn, mn), ins):
+                if (mn in ins) if "." in mn else re.search(r"\b%s\b|\b%s\." % (mn, mn), ins):
                     cnt[mn] += 1
                     first.setdefault(mn, ins)
         if not tap:
