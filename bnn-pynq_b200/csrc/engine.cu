@@ -37,6 +37,7 @@ struct Lane {
   int* d_cls = nullptr;
   int cap = 0;                // images the staging buffers (d_raw, d_out, d_cls) hold
   int act_cap = 0;            // images d_in / act hold
+  size_t act_size = 0;        // bytes of each act buffer (the size per image depends on the compute core, see act_bytes)
   bool used = false;
   // results of the chunk in flight, copied back when the lane is next needed (a device-to-pageable copy blocks the host: issuing it
   // right after the chunk would stop the feeder from running ahead)
@@ -169,8 +170,8 @@ int Engine::check_status(DeviceState& ds, std::string& err) {
 int Engine::chunk_images(bool host) const {
   if (const char* e = std::getenv(host ? "BNN_B200_HOST_CHUNK" : "BNN_B200_CHUNK")) { int v = std::atoi(e); if (v > 0) return v; }
   if (!net_.is_cnv) return host ? 32768 : 65536;
+  if (core_ >= 1 && fuse01_) return host ? 8192 : 65536;
   const bool tern = net_.L[1].out_mode == OUT_TERN;
-  if (core_ >= 1 && fuse01_) return host ? 8192 : (tern ? 32768 : 65536);
   // LOP3+POPC path: layer 0's output (7 200 / 14 400 B per image) exists in global memory; keep it inside the 126 MB L2
   return tern ? 2048 : 4096;
 }
@@ -179,7 +180,9 @@ int Engine::chunk_images(bool host) const {
 // (bit planes everywhere; e2m1 operand planes, 4 bits per value and 128-image tiles, between fp4 kernels of a 1-bit network).
 size_t Engine::act_bytes(int images) const {
   size_t per = 16;
-  for (int i = 0; i + 1 < net_.nlayers; i++) {
+  // CNV on the tensor cores: layer 0's output lives in the fused kernel's shared memory, never in these buffers
+  const int first = (net_.is_cnv && core_ >= 1 && fuse01_) ? 1 : 0;
+  for (int i = first; i + 1 < net_.nlayers; i++) {
     const LayerDesc& l = net_.L[i];
     const size_t px = (size_t)out_dim(l) * out_dim(l);
     per = std::max(per, px * out_words_per_pixel(l) * 4);
@@ -299,16 +302,18 @@ int Engine::load_parameters(const std::string& dir) {
 // Lane k's layer-0 input and activation ping-pong for chunks of `images` (grown on demand, powers of two).
 int Engine::ensure_buffers(DeviceState& ds, int k, int images, std::string& err) {
   Lane& ln = ds.lane[k];
-  if (images <= ln.act_cap) return 0;
-  const int cap = round_cap(images);
+  if (images <= ln.act_cap && act_bytes(images) <= ln.act_size) return 0;
+  const int cap = std::max(round_cap(images), ln.act_cap);
+  const size_t size = std::max(act_bytes(cap), ln.act_size);  // never shrinks: a later call on another core may need more per image
   CKE(err, cudaStreamSynchronize(ln.s));
   CKE(err, cudaStreamSynchronize(ds.compute));
   ds.release(ln.d_in, (size_t)ln.act_cap * net_.in_bytes);
-  for (int j = 0; j < 2; j++) ds.release(ln.act[j], ln.act_cap ? act_bytes(ln.act_cap) : 0);
+  for (int j = 0; j < 2; j++) ds.release(ln.act[j], ln.act_size);
   ln.act_cap = 0;
+  ln.act_size = 0;
   ln.d_in = ds.alloc((size_t)cap * net_.in_bytes, false);
-  ln.act[0] = (uint32_t*)ds.alloc(act_bytes(cap), false);
-  ln.act[1] = (uint32_t*)ds.alloc(act_bytes(cap), false);
+  ln.act[0] = (uint32_t*)ds.alloc(size, false);
+  ln.act[1] = (uint32_t*)ds.alloc(size, false);
   if (!ln.d_in || !ln.act[0] || !ln.act[1]) {
     cudaFree(ln.d_in); cudaFree(ln.act[0]); cudaFree(ln.act[1]);
     ln.d_in = nullptr; ln.act[0] = ln.act[1] = nullptr;
@@ -316,6 +321,7 @@ int Engine::ensure_buffers(DeviceState& ds, int k, int images, std::string& err)
     return -1;
   }
   ln.act_cap = cap;
+  ln.act_size = size;
   return 0;
 }
 
@@ -458,7 +464,9 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
       if (tap) { tap->fused01 = true; tap->raw[0] = tap->raw[1] = 1; tap->ofmt[0] = ACT_BITS; tap->ofmt[1] = ofmt[1]; }
     } else {
       if (profile_) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
-      if (tap) { tap_acc = tap->acc; }
+      // the activation buffers of the ordinary path are sized WITHOUT layer 0's output (act_bytes): no silent fall-back there
+      if (!tap) { err = "the fused layer-0/1 kernel refused the launch (" + std::to_string(n) + " images)"; return -1; }
+      tap_acc = tap->acc;
       fused01 = false;
     }
   }

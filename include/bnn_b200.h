@@ -127,8 +127,8 @@ int bnnb_prep_device(bnnb_ctx* c, int slot, const void* d_raw, int n, void* d_in
  * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same
  * results, same asynchrony as bnnb_infer_device; the inter-layer activation scratch is a static device array of 32 MiB that every GPU
  * which loads the library holds until the process exits, so:
- *   - n is limited per call by that array (two buffers of 16 MiB, each holding the widest inter-layer tensor in any format a core
- *     may plan): 512 images for cnvW1A1, 1 152 for cnvW1A2 / cnvW2A2, 32 768 for lfcW1A1, 65 536 for lfcW1A2; more is refused
+ *   - n is limited per call by that array (two buffers of 16 MiB, each holding the widest inter-layer tensor the compute core in use
+ *     writes to global memory): 1 792 images for cnvW1A1 / cnvW1A2 / cnvW2A2, 32 768 for lfcW1A1 / lfcW1A2 on the default core; more is refused
  *     (-1) with the limit in bnnb_last_error;
  *   - the device must already hold the parameters: make one ordinary call (bnnb_infer_device / bnnb_classify_*) on that device
  *     after bnnb_load_parameters, outside any capture - the upload allocates, this call never does (no cudaMalloc / cudaFree, no
