@@ -26,6 +26,12 @@ namespace {
 // and epilogue bodies compiled out took as long as the full one (lfcW1A1, 1024 x 1024 layer: 0.117 vs 0.128 ms; groups of 2 / 4 /
 // 8 slabs: 0.086 / 0.071 / 0.058 ms).  The ring takes whatever shared memory is left (bytes in flight set the rate of the stream).
 constexpr int GG = BNNB_GG;
+// experiment switches (results wrong, hand-offs kept): -DBNNB_GEMM_STRIP=<bits> 1: no MMAs, 2: no accumulator reads / harvest / stores,
+// 4: no pre-load, 8: no weight copies, 16: no operand expansion
+#ifndef BNNB_GEMM_STRIP
+#define BNNB_GEMM_STRIP 0
+#endif
+constexpr int kGStrip = BNNB_GEMM_STRIP;
 constexpr int GF_RING_MAX = 32;
 
 // 8 bits -> 8 nibbles (bit i at position 4i)
@@ -204,6 +210,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
         const int qg = gg % per_tile, nb = qg / ngrp, gi = qg - nb * ngrp;
         const int s0 = gi * GG, cnt = min(GG, g.ks - s0);
         if (gg >= g.ring && !failed && !tc::mbar_wait(&ring_empty[lane], rpar)) failed = true;
+        if (kGStrip & 8) { tc::mbar_arrive(&ring_full[lane]); rpar ^= 1u; continue; }
         tc::mbar_expect_tx(&ring_full[lane], (uint32_t)cnt * SLAB);
         tc::bulk_g2s(dst, L.w4s + (size_t)(nb * g.ks + s0) * SLAB, (uint32_t)cnt * SLAB, &ring_full[lane]);  // the slabs of a block are consecutive
         rpar ^= 1u;
@@ -231,9 +238,13 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
             const int s1 = min(s0 + GG, g.ks);
 #ifndef BNNB_GEMM_NO_MMA8
             // a full group whose operand quarters are all in (every channel block but a tile's first): one asm block of eight MMAs
-            if (GG == 8 && s1 - s0 == 8 && (nb > 0 || qn == 4)) {
-              if (leader)
-                tc::mma8_mxf4<256, NB * 2>(acc, a_lo + (uint32_t)(2 * s0) * 128, b_lo + (uint32_t)(r * GG) * (SLAB / 16), d_hi, idesc, sf, (ACC || s0 > 0) ? 1u : 0u);
+            if (GG % 8 == 0 && s1 - s0 == GG && (nb > 0 || qn == 4)) {
+              if (leader && !(kGStrip & 1)) {
+#pragma unroll
+                for (int e = 0; e < GG / 8; e++)
+                  tc::mma8_mxf4<256, NB * 2>(acc, a_lo + (uint32_t)(2 * (s0 + 8 * e)) * 128, b_lo + (uint32_t)(r * GG + 8 * e) * (SLAB / 16), d_hi, idesc, sf,
+                                             (ACC || s0 + e > 0) ? 1u : 0u);
+              }
             } else
 #endif
             for (int s = s0; s < s1; s++) {
@@ -243,7 +254,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
                 tc::fence_after_sync();
                 qn++;
               }
-              if (leader)
+              if (leader && !(kGStrip & 1))
                 tc::mma_mxf4_lh(acc, a_lo + (uint32_t)(2 * s) * 128, d_hi, b_lo + (uint32_t)(r * GG + (s - s0)) * (SLAB / 16), d_hi, idesc, sf, sf, (ACC || s > 0) ? 1u : 0u);
             }
             if (leader) tc::commit(&ring_empty[r]);
@@ -272,13 +283,15 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
         const bool codes = ACC && out_fmt == ACT_F4T;
         uint32_t r[2][32];  // scores, TAP
         uint32_t hh[2][16];
-        if (ACC) tc::tmem_ld32_pack16(trow, hh[0]);
+        if (kGStrip & 2) {}
+        else if (ACC) tc::tmem_ld32_pack16(trow, hh[0]);
         else tc::tmem_ld32(trow, r[0]);
 #pragma unroll
         for (int j = 0; j < NW; j++) {
           const float* th = sthr + nb * NB + j * 32;
           uint32_t w0 = 0, w1 = 0;
           c4[j] = make_uint4(0, 0, 0, 0);
+          if (kGStrip & 2) { b0[j] = b1[j] = 0; continue; }
           if (ACC) {
             uint32_t dl[16];  // 2-bit outputs: the deltas of this block and word, from shared memory while the load is in flight
             if (TERN) {
@@ -322,7 +335,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
             for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (ACC ? th[c] : 0.0f));
           }
         }
-        if (ACC && gb + SLOTS < T * g.nblk) preload(slot, (gb + SLOTS) % g.nblk);
+        if (ACC && !(kGStrip & 4) && gb + SLOTS < T * g.nblk) preload(slot, (gb + SLOTS) % g.nblk);
         tc::fence_before_sync();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
