@@ -233,7 +233,29 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * NB;
           int qn = 0;
-          for (int s0 = 0; s0 < g.ks; s0 += GG) {  // one ring slot = GG slabs (fewer at the end of the block)
+          int s_begin = 0;
+#ifndef BNNB_GEMM_NO_LEAN
+          // every channel block but a tile's first (all operand quarters are in): the full groups in a loop stripped to wait, one asm
+          // block of eight MMAs, commit - the issuing thread retires an instruction every 6-7 clocks, and the general loop below
+          // spends more of them per group than the eight MMAs take to run
+          if (GG == 8 && nb > 0) {
+            const int nfull = g.ks / GG;
+            uint32_t a = a_lo;
+            for (int gi = 0; gi < nfull; gi++) {
+              if (!failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
+              if (leader) {
+                if (!(kGStrip & 1)) tc::mma8_mxf4<256, NB * 2>(acc, a, b_lo + (uint32_t)r * (GG * (SLAB / 16)), d_hi, idesc, sf, (ACC || gi > 0) ? 1u : 0u);
+                tc::commit(&ring_empty[r]);
+              }
+              a += 2 * GG * 128;
+              if (++r == g.ring) { r = 0; rpar ^= 1u; }
+            }
+            __syncwarp();
+            s_begin = nfull * GG;
+            qn = 4;
+          }
+#endif
+          for (int s0 = s_begin; s0 < g.ks; s0 += GG) {  // one ring slot = GG slabs (fewer at the end of the block)
             if (!failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
             const int s1 = min(s0 + GG, g.ks);
 #ifndef BNNB_GEMM_NO_MMA8
