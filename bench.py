@@ -338,8 +338,6 @@ def measure_network(native, L, net, local_rank, steps, B):
     rt = native.Runtime(net, params_dir(net), devices=[local_rank])
     cnv = net.startswith("cnv")
     raw_w = 3073 if cnv else 784
-    if cnv and not net.endswith("W1A1"):
-        B = min(B, 32768)
     host, host_ptr = native.pinned_array(B * raw_w)
     host[:] = np.random.default_rng(5).integers(0, 256, B * raw_w, dtype=np.uint8)
     dev = torch.device("cuda", local_rank)
