@@ -794,18 +794,26 @@ int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int n
     }
     CKE(err, cudaStreamSynchronize(ds.compute));  // `grouped` dies with this block; set 0 is quiescent before it is cloned
   }
-  auto param_set = [&](int k, const DevLayer** PL, DevLayer** tbl) -> int {  // lane k's set; clones are (re)taken from set 0 on first use
-    if (k == 0 || seg.patches.empty()) { *PL = ds.L; *tbl = ds.d_layers; return 0; }
+  // The clones of set 0 for lanes 1.. are taken HERE, before any lane has enqueued a patch: taken lazily at a lane's first chunk they
+  // raced with lane 0 already patching set 0 (a torn copy - weights of a word from before a patch, its threshold offset from after -
+  // makes the lane apply that patch's offset twice: a few wrong images per million, seen on the second device of a two-device run).
+  const bool multi_chunk = hi - lo > 4096;  // the loop below cuts anything larger into at least two chunks (two lanes)
+  if (!seg.patches.empty() && multi_chunk) {
+    for (int k = 1; k < kLanes; k++) {
+      DeviceState::ParamSet& c = ds.clone[k - 1];
+      if (!c.arena) {
+        c.arena = (unsigned char*)ds.alloc(ds.arena_bytes, true);
+        if (!c.arena) { err = "cudaMalloc failed (parameter clone, device " + std::to_string(ds.id) + ")"; return -1; }
+        carve_params(net_, c.arena, c.L, &c.d_layers);
+      }
+      CKE(err, cudaMemcpyAsync(c.arena, ds.arena, ds.arena_bytes, cudaMemcpyDeviceToDevice, ds.compute));
+      CKE(err, cudaMemcpyAsync(c.d_layers, c.L, sizeof(DevLayer) * 9, cudaMemcpyHostToDevice, ds.compute));  // the table points into the clone
+    }
+    CKE(err, cudaStreamSynchronize(ds.compute));
+  }
+  auto param_set = [&](int k, const DevLayer** PL, DevLayer** tbl) -> int {  // lane k's parameter set
+    if (k == 0 || seg.patches.empty() || !multi_chunk) { *PL = ds.L; *tbl = ds.d_layers; return 0; }
     DeviceState::ParamSet& c = ds.clone[k - 1];
-    if (!c.arena) {
-      c.arena = (unsigned char*)ds.alloc(ds.arena_bytes, true);
-      if (!c.arena) { err = "cudaMalloc failed (parameter clone, device " + std::to_string(ds.id) + ")"; return -1; }
-      carve_params(net_, c.arena, c.L, &c.d_layers);
-    }
-    if (!ds.lane[k].used) {  // first chunk of this lane in this call
-      CKE(err, cudaMemcpyAsync(c.arena, ds.arena, ds.arena_bytes, cudaMemcpyDeviceToDevice, ds.lane[k].s));
-      CKE(err, cudaMemcpyAsync(c.d_layers, c.L, sizeof(DevLayer) * 9, cudaMemcpyHostToDevice, ds.lane[k].s));  // the table points into the clone
-    }
     *PL = c.L; *tbl = c.d_layers;
     return 0;
   };
