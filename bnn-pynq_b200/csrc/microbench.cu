@@ -83,8 +83,8 @@ BNNB_MB_KERNEL(mb_fmnmx, "min.f32 %0, %0, %1;")
 
 extern "C" double bnnb_microbench(int which, double* clock_mhz) {
   cudaDeviceProp prop;
-  if (cudaGetDeviceProperties(&prop, 0) != cudaSuccess) return -1;
-  cudaSetDevice(0);
+  int dev = 0;  // the calling thread's current device (a per-GPU process under torchrun has its own one current: never switch it)
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return -1;
   const int blocks = prop.multiProcessorCount * 4, threads = 512;
   uint32_t* out; long long* cyc;
   if (cudaMalloc(&out, (size_t)blocks * threads * 4) != cudaSuccess) return -1;
@@ -166,7 +166,6 @@ __global__ void __launch_bounds__(256) k_tmem_rate(int warps, int iters, int sto
 
 extern "C" double bnnb_tmem_rate(int warps, int store) {
   long long* cyc; uint32_t* sink;
-  cudaSetDevice(0);
   if (cudaMalloc(&cyc, 8) != cudaSuccess) return -1;
   cudaMalloc(&sink, 4);
   const int iters = 4096;
@@ -206,7 +205,6 @@ __global__ void __launch_bounds__(64) k_mbar_pingpong(int iters, int mode, long 
 
 extern "C" double bnnb_mbar_roundtrip(int mode) {
   long long* cyc;
-  cudaSetDevice(0);
   if (cudaMalloc(&cyc, 8) != cudaSuccess) return -1;
   const int iters = 20000;
   k_mbar_pingpong<<<1, 64>>>(iters, mode, cyc);
@@ -244,7 +242,6 @@ __global__ void __launch_bounds__(32) k_tmem_pack_probe(const uint32_t* in, uint
 
 extern "C" int bnnb_tmem_pack_probe(const uint32_t* in, uint32_t* out) {
   uint32_t *di, *dout;
-  cudaSetDevice(0);
   if (cudaMalloc(&di, 32 * 32 * 4) != cudaSuccess) return -1;
   cudaMalloc(&dout, 32 * 16 * 4);
   cudaMemcpy(di, in, 32 * 32 * 4, cudaMemcpyHostToDevice);

@@ -72,7 +72,6 @@ extern "C" int bnnb_tc_probe(const int8_t* A, const int8_t* B, int32_t* D, int r
   const size_t smem = (size_t)(K / 16) * (rows_a + N) * 16;
   if (smem > 200 * 1024) return -1;
   int8_t *dA, *dB; int32_t* dD; long long* dC; int* dS;
-  cudaSetDevice(0);
   if (cudaMalloc(&dA, (size_t)rows_a * K) != cudaSuccess) return -1;
   cudaMalloc(&dB, (size_t)N * K); cudaMalloc(&dD, (size_t)128 * N * 4); cudaMalloc(&dC, 8); cudaMalloc(&dS, 4);
   cudaMemcpy(dA, A, (size_t)rows_a * K, cudaMemcpyHostToDevice);
@@ -195,7 +194,6 @@ extern "C" int bnnb_tc_probe_fp4_mix(const uint8_t* A, const uint8_t* B, int32_t
   const size_t smem = (size_t)(K / 32) * (rows_a + N) * 16;
   if (smem > 200 * 1024) return -1;
   uint8_t *dA, *dB; int32_t* dD; long long* dC; int* dS;
-  cudaSetDevice(0);
   if (cudaMalloc(&dA, (size_t)rows_a * K / 2) != cudaSuccess) return -1;
   cudaMalloc(&dB, (size_t)N * K / 2); cudaMalloc(&dD, (size_t)128 * N * 4); cudaMalloc(&dC, 8); cudaMalloc(&dS, 4);
   cudaMemcpy(dA, A, (size_t)rows_a * K / 2, cudaMemcpyHostToDevice);
@@ -270,7 +268,6 @@ __global__ void __launch_bounds__(128) k_tc_rate_fp4(int N, int taps, int iters,
 extern "C" double bnnb_tc_rate_fp4(int N, int taps) {
   if (N % 32 || N < 32 || N > 128) return -1;
   long long* dC; int* dS;
-  cudaSetDevice(0);
   if (cudaMalloc(&dC, 8) != cudaSuccess) return -1;
   cudaMalloc(&dS, 4);
   cudaMemset(dS, 0, 4);
