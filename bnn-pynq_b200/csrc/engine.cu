@@ -494,6 +494,7 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     cur = out;
   }
   if (net_.is_cnv && d_classes) { launch_cnv_classes((const int16_t*)d_out, n, ncls, d_classes, s); launches++; }
+  if (!net_.is_cnv && d_classes) { launch_lfc_classes((const uint64_t*)d_out, n, ncls, d_classes, s); launches++; }
   return launches;
 }
 
@@ -550,6 +551,7 @@ int Engine::run_chunk_faulted(DeviceState& ds, const DevLayer* PL, DevLayer* d_l
     cur_stride = ostr;
   }
   if (net_.is_cnv && d_classes) launch_cnv_classes((const int16_t*)d_out, n, ncls, d_classes, s);
+  if (!net_.is_cnv && d_classes) launch_lfc_classes((const uint64_t*)d_out, n, ncls, d_classes, s);
   return 0;
 }
 
@@ -661,17 +663,6 @@ int Engine::sync(int slot) {
   return check_status(ds, err_);
 }
 
-// LFC class decode, multi-image rule (foldedmv-offload.cpp:202-220): (unsigned) log2(word & mask), 0 when no bit is set.
-static int lfc_class_multi(uint64_t w, int ncls) {
-  const uint64_t mask = ncls >= 64 ? ~0ull : (ncls <= 0 ? 0 : (~0ull >> (64 - ncls)));
-  w &= mask;
-  if (!w) return 0;
-  // below 2^32 floor(log2) of the double is the index of the top bit (2^k - 1 is far enough from 2^k for k <= 32); the libm call
-  // costs ~20 ns per image, which at 65 536 images per call was most of the LFC host path's time beyond its copies
-  if (w < (1ull << 32)) return 31 - __builtin_clz((unsigned)w);
-  return (int)(unsigned)std::log2((double)w);
-}
-
 // One device's shard [lo, hi): chunks go round-robin through the lanes (with fault epochs: run_shard_faulted).
 int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, int16_t* scores, uint64_t* words,
                       const Segments* seg, float* dev_ms, float* last_ms, int* last_imgs, std::string& err) {
@@ -688,8 +679,9 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
     if (net_.is_cnv) {
       if (scores) CKE(err, cudaMemcpyAsync(scores + (size_t)off * 64, ln.d_out, (size_t)c * 128, cudaMemcpyDeviceToHost, ln.s));
       if (classes) CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.s));
-    } else if (words) {
-      CKE(err, cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.s));
+    } else {  // LFC: the classes are decoded on the device (4 B per image back instead of 8, no host pass over the words)
+      if (words) CKE(err, cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.s));
+      if (classes) CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.s));
     }
     ln.pend_off = -1;
     return 0;
@@ -727,7 +719,7 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
       const bool time_it = true;
       Timed t{nullptr, nullptr, c};
       if (time_it) { if (timing_pair(&t.a, &t.b) != 0) return -1; CKE(err, cudaEventRecord(t.a, ln.s)); }
-      if (run_chunk(ds, ln.d_in, c, ln.d_out, (net_.is_cnv && classes) ? ln.d_cls : nullptr, ncls, ln.s, nullptr, ln.act, err) < 0) return -1;
+      if (run_chunk(ds, ln.d_in, c, ln.d_out, classes ? ln.d_cls : nullptr, ncls, ln.s, nullptr, ln.act, err) < 0) return -1;
       if (time_it) { CKE(err, cudaEventRecord(t.b, ln.s)); timed.push_back(t); }
       ln.used = true;
       ln.pend_off = cur; ln.pend_n = c;
@@ -820,8 +812,8 @@ int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int n
   auto flush_lane = [&](Lane& ln) -> int {  // results of the lane's chunk in flight -> host
     if (ln.pend_off < 0) return 0;
     const int off = ln.pend_off, c = ln.pend_n;
-    if (net_.is_cnv) CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.s));
-    else CKE(err, cudaMemcpyAsync(words + off, ln.d_out, (size_t)c * 8, cudaMemcpyDeviceToHost, ln.s));
+    CKE(err, cudaMemcpyAsync(classes + off, ln.d_cls, (size_t)c * 4, cudaMemcpyDeviceToHost, ln.s));
+    (void)words;
     ln.pend_off = -1;
     return 0;
   };
@@ -849,7 +841,7 @@ int Engine::run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int n
     else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, c, ln.s);
     const bool time_it = cur + c == hi;
     if (time_it) CKE(err, cudaEventRecord(ds.tev[0], ln.s));
-    if (run_chunk_faulted(ds, PL, tbl, k, ln.d_in, c, cur, ln.d_out, net_.is_cnv ? ln.d_cls : nullptr, ncls, ln.s, ln.act, fp, err) != 0) return -1;
+    if (run_chunk_faulted(ds, PL, tbl, k, ln.d_in, c, cur, ln.d_out, ln.d_cls, ncls, ln.s, ln.act, fp, err) != 0) return -1;
     if (time_it) { CKE(err, cudaEventRecord(ds.tev[1], ln.s)); timed = true; *last_imgs = c; }
     ln.used = true;
     ln.pend_off = cur; ln.pend_n = c;
@@ -908,14 +900,10 @@ int Engine::infer_host(const uint8_t* input, int n, int ncls, int* classes, int1
   if (ensure_devices() != 0) return -1;
   if (usec) *usec = 0;
   if (n <= 0) return 0;
-  std::vector<uint64_t> tmp_words;
-  if (!net_.is_cnv && !words && classes) { tmp_words.resize(n); words = tmp_words.data(); }
   float worst = 0, last_ms = 0;
   int last_imgs = 0;
   if (run_sharded(input, n, ncls, classes, scores, words, nullptr, &worst, &last_ms, &last_imgs) != 0) return -1;
   if (usec) *usec = worst * 1000.0f / (float)n;
-  if (!net_.is_cnv && classes)
-    for (int i = 0; i < n; i++) classes[i] = lfc_class_multi(words[i], ncls);
   return 0;
 }
 
@@ -949,13 +937,9 @@ int Engine::infer_host_with_faults(const uint8_t* input, int n, int ncls, const 
     if (pm_->inject(f.target, f.layer, f.bit, f.word_size, &p)) { seg.patches.push_back(p); seg.ptime.push_back(f.time); }
   }
   if (n <= 0) return apply_patches(seg.patches);
-  std::vector<uint64_t> words;
-  if (!net_.is_cnv) words.resize(n);
   float worst = 0, last_ms = 0;
   int last_imgs = 0;
-  if (run_sharded(input, n, ncls, classes, nullptr, net_.is_cnv ? nullptr : words.data(), &seg, &worst, &last_ms, &last_imgs) != 0) return -1;
-  if (!net_.is_cnv)
-    for (int i = 0; i < n; i++) classes[i] = lfc_class_multi(words[i], ncls);
+  if (run_sharded(input, n, ncls, classes, nullptr, nullptr, &seg, &worst, &last_ms, &last_imgs) != 0) return -1;
   // the reference reports the time of its LAST single-image call: device time per image of the last segment
   if (usec) *usec = last_imgs > 0 ? last_ms * 1000.0f / (float)last_imgs : 0.f;
   return 0;

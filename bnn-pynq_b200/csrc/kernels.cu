@@ -540,6 +540,22 @@ void launch_cnv_classes(const int16_t* scores, int n, int ncls, int* classes, cu
   k_cnv_classes<<<(n + 255) / 256, 256, 0, s>>>(scores, n, ncls, classes);
 }
 
+// LFC class decode on the device, multi-image rule (foldedmv-offload.cpp:202-220): (unsigned) log2(word & mask), 0 when no bit is set;
+// (below 2^32 the index of the top bit; above, floor(log2) of the word rounded to double, as the reference's libm call gives it)
+__global__ void k_lfc_classes(const uint64_t* __restrict__ words, int n, uint64_t mask, int* __restrict__ cls) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint64_t w = words[i] & mask;
+    int c = 0;
+    if (w) c = w < (1ull << 32) ? 31 - __clz((unsigned)w) : (int)(unsigned)log2((double)w);
+    cls[i] = c;
+  }
+}
+void launch_lfc_classes(const uint64_t* words, int n, int ncls, int* classes, cudaStream_t s) {
+  if (n <= 0) return;
+  const uint64_t mask = ncls >= 64 ? ~0ull : (ncls <= 0 ? 0 : (~0ull >> (64 - ncls)));
+  k_lfc_classes<<<(n + 255) / 256, 256, 0, s>>>(words, n, mask, classes);
+}
+
 void kernels_init_device() {}
 
 }  // namespace bnnb

@@ -74,6 +74,7 @@ bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
 
 // ---- class decode for CNV (multi-image rule, foldedmv-offload.h:398-406) ----
 void launch_cnv_classes(const int16_t* scores, int n, int ncls, int* classes, cudaStream_t s);
+void launch_lfc_classes(const uint64_t* words, int n, int ncls, int* classes, cudaStream_t s);
 
 // opt-in to large dynamic shared memory for every kernel (call once per device)
 void kernels_init_device();
