@@ -1,6 +1,8 @@
-// Fused CNV layers 0+1 on tcgen05.mma kind::i8: int8 image -> conv3x3 (3->64) -> threshold -> conv3x3 (64->64) -> threshold
-// -> 2x2 max-pool -> bit-packed 14x14x64 output.  Layer 0's activations never exist in bit-packed form or in global memory:
-// its epilogue writes them as int8 straight into layer 1's UMMA operand planes in shared memory.
+// Fused CNV layers 0+1: int8 image -> conv3x3 (3->64, tcgen05.mma kind::i8) -> threshold -> conv3x3 (64->64, kind::mxf4 with unit
+// scales, or kind::i8 on core 1) -> threshold -> 2x2 max-pool -> 14x14x64 output as e2m1 operand planes (ACT_F4P) or bit-packed.
+// Layer 0's activations never exist in bit-packed form or in global memory: its epilogue writes them as e2m1 nibbles (int8 on core 1)
+// straight into layer 1's UMMA operand planes in shared memory.  Both layers' thresholds ride in the accumulators (constant operand
+// plane for layer 0, biased pre-load for layer 1) and both epilogues read 16 bits per channel (see FOLD / TFOLD in the kernel).
 //
 // Replaces (cnvW1A1/hw/top.cpp:210-217): Mem2Stream + DataWidthConverters + ConvLayer_Batch L0 + ConvLayer_Batch L1 +
 // StreamingMaxPool_Batch.

@@ -5,12 +5,16 @@
 //
 // Same implicit GEMM as conv_tc.cu (operand planes of 16 bytes = 32 channels per pixel, tap (ky,kx) = descriptor start shifted by
 // (ky*IDIM+kx) pixels), now one K=64 MMA per 64 input channels per tap, and a warp-specialised CTA (one per SM, 640 threads):
-//   warps 0-15      four epilogue groups of four warps, one per quarter of the channel block (a lone warp retires an instruction
-//                   every 6-7 clocks, so the per-tile epilogue is split until it is shorter than the tile's MMAs): TMEM -> decision
-//                   bits or e2m1 codes -> global (pooled layers: via smem)
-//   warps 16-18     expander: bit-packed activations of group g+1 (global, L2) -> fp4 operand planes, other buffer
+//   warps 0-15      epilogue: groups of four warps (one per TMEM lane quarter), either four channel quarters on every tile or two
+//                   channel halves x two teams on alternate tiles (a lone warp retires an instruction every 6-7 clocks, so the
+//                   per-tile epilogue is split until it is shorter than the tile's MMAs): TMEM (packed 16-bit reads of accumulators
+//                   that carry the threshold in a biased pre-load, f4_common.cuh) -> e2m1 codes or decision bits -> global
+//                   (pooled layers: via smem)
+//   warps 16-18     operand planes of group g+1 into the other buffer: TMA bulk copies when the producer wrote e2m1 planes
+//                   (ACT_F4P; one thread), else expansion of bit-packed activations (global, L2) -> fp4 operand planes
 //   warp  19        MMA issuer, up to three tiles ahead (three TMEM accumulator slots)
 // decoupled by mbarriers only: abuf_full / abuf_empty per operand buffer, full / empty per accumulator slot.
+// PAIR instantiation: two CTAs of a cluster run every MMA together (tcgen05 cta_group::2, M = 256), see the kernel.
 #include <climits>
 #include <cstdlib>
 #include "kernels.cuh"

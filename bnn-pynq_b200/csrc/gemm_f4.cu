@@ -2,9 +2,11 @@
 // small-integer MMA of conv_f4.cu, K-streamed.  Rows = images (tiles of 128), columns = output channels in blocks of NB.
 //
 // Warp-specialised persistent CTA (384 threads), decoupled by mbarriers only:
-//   warps 0-3  epilogue: TMEM -> decision bits / scores -> global
-//   warps 4-9  expander: bit-packed activations of tile i+1 -> e2m1 operand planes [K/32][128 rows][16 B], handed to the issuer
-//              in four K quarters so that the MMAs of a tile start while its tail is still being expanded
+//   warps 0-3  epilogue: TMEM (thresholded layers: packed 16-bit reads of accumulators that carry the threshold in a biased pre-load,
+//              f4_common.cuh) -> e2m1 codes (ACT_F4T) / decision bits / 16-bit scores -> global
+//   warps 4-9  operand tile i+1 -> planes [K/32][128 rows][16 B], handed to the issuer in four K quarters so that the MMAs of a tile
+//              start while its tail is still arriving: four TMA bulk copies when the producer wrote e2m1 tiles (ACT_F4T; one
+//              thread), else expansion of bit-packed activations
 //   warp  10   loader: weight slabs (NB x 64 e2m1 = NB*32 bytes, pre-arranged in operand layout by k_repack_w4s) by TMA bulk
 //              copy into a ring of R slots, running ahead of the MMAs
 //   warp  11   issuer: one K=64 MMA per slab; accumulator slots (3) let the next channel block start while one drains
