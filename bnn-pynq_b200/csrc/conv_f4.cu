@@ -39,7 +39,7 @@ struct F4Cfg {
 };
 
 // experiment switches (results wrong, hand-offs kept): -DBNNB_CONV_STRIP=<bits> 1: no MMAs, 2: no TMEM loads + harvest, 4: no pre-load,
-// 8: no global stores, 16: no input copies
+// 8: no global stores, 16: no input copies, 32: no pooling (its barriers kept), 64: no pooling barriers either
 #ifndef BNNB_CONV_STRIP
 #define BNNB_CONV_STRIP 0
 #endif
@@ -364,10 +364,10 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           }
         }
       }
-      if (POOL) {
+      if (POOL && !(kStrip & 64)) {
         asm volatile("bar.sync 1, 512;" ::: "memory");
         constexpr int PP = Cfg::PD * Cfg::PD;
-        for (int i = tid; i < G * PP; i += 512) {  // one pooled output pixel per thread
+        for (int i = tid; i < G * PP && !(kStrip & 32); i += 512) {  // one pooled output pixel per thread
           const int gi = i / PP, op = i - gi * PP, oy = op / Cfg::PD, ox = op - oy * Cfg::PD;
           if (img0 + gi >= n_img) continue;
           const uint4* r00 = reinterpret_cast<const uint4*>(sbits + (size_t)(gi * Cfg::PXI + (2 * oy) * IDIM + 2 * ox) * WPP);
