@@ -441,7 +441,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         const uint32_t acc = tmem + (uint32_t)slot * 64;
         bool firstmma = true;
         if (leader && F4) {
-          if (kMma1) tc::mma9_mxf4<30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, CP ? 1u : 0u);
+          if (kMma1) tc::mma9_mxf4<1, 30, 2 * 64>(acc, a_lo, b1_lo, d_hi, idesc_f4, sf, CP ? 1u : 0u);
           tc::commit(&full[slot]);
           TR(4, k, t);
         } else if (leader) {

@@ -24,10 +24,16 @@
 namespace bnnb {
 namespace {
 
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
+// IL: the G images of a group are interleaved pixel by pixel (operand row = pixel * G + image; ACT_F4I input or expanded bits): the rows
+// whose outputs can be valid form a prefix of OROWS rows and only its tiles are computed; tap (ky, kx) = (ky * IDIM + kx) * G rows on.
+// !IL: rows in image order (row = image * PXI + pixel; ACT_F4P input: one bulk copy per image plane - the fault-epoch path, whose
+// kernel runs start at arbitrary images, uses this one).
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool IL>
 struct F4Cfg {
-  static constexpr int PXI = IDIM * IDIM, ROWS = G * PXI, TILES = (ROWS + 127) / 128, MAXSHIFT = 2 * IDIM + 2;
-  static constexpr int PITCH = (TILES * 128 + MAXSHIFT + 7) / 8 * 8;
+  static constexpr int PXI = IDIM * IDIM, ROWS = G * PXI, XS = IL ? G : 1, YS = IDIM * XS, MAXSHIFT = 2 * YS + 2 * XS;
+  static constexpr int OROWS = IL ? ((OD - 1) * IDIM + OD) * G : ROWS;  // rows 0 .. OROWS-1 hold every valid output
+  static constexpr int TILES = (OROWS + 127) / 128;
+  static constexpr int PITCH = ((TILES * 128 + MAXSHIFT > ROWS ? TILES * 128 + MAXSHIFT : ROWS) + 7) / 8 * 8;
   static constexpr int KC = C / 32;  // 16-byte chunks (32 fp4 channels) per tap
   static constexpr int NT = N * NS;  // output channels of the layer: NS blocks of N (one MMA accumulator each)
   static constexpr int PLANE = PITCH * 16, A_BYTES = KC * PLANE, B_BYTES = 9 * KC * NT * 16;
@@ -46,6 +52,9 @@ struct F4Cfg {
 constexpr int kStrip = BNNB_CONV_STRIP;
 #ifndef BNNB_G2T
 #define BNNB_G2T 9
+#endif
+#ifndef BNNB_G4
+#define BNNB_G4 19
 #endif
 #ifndef BNNB_G3T
 #define BNNB_G3T 6
@@ -79,10 +88,11 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
   return make_uint4(v[0], v[1], v[2], v[3]);
 }
 
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool TAP, bool PAIR>
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool TAP, bool PAIR, bool IL>
 __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
-                                                     int in_fmt, int out_fmt, int* __restrict__ status, int32_t* __restrict__ tap) {
-  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
+                                                     int in_fmt, int out_fmt, int og, int* __restrict__ status, int32_t* __restrict__ tap) {
+  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, IL>;
+  const uint32_t og_magic = f4i_magic(og > 0 ? og : 1);  // ACT_F4I output: the consumer's images per group
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
   static_assert(BNNB_CONV_EGS == 4 || BNNB_CONV_EGS == 2 || BNNB_CONV_EGS == 0, "epilogue groups");
   extern __shared__ __align__(128) uint8_t smem[];
@@ -130,7 +140,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   if (PAIR) tc::cluster_sync();  // both CTAs are resident before the paired allocation
   if (warp == 0) { if (PAIR) tc::tmem_alloc_pair(&tmem_base, 512); else tc::tmem_alloc(&tmem_base, 512); }
   if (tid == 0) {
-    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], in_fmt == ACT_F4P ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); tc::mbar_init(&peer_full[i], 1); }
+    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], (in_fmt == ACT_F4P || in_fmt == ACT_F4I) ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); tc::mbar_init(&peer_full[i], 1); }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], (PAIR ? 2 : 1) * 4 * EGS); }
     tc::mbar_init_fence();
   }
@@ -202,7 +212,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     // ---- operand planes of group k+1: ACT_F4P input = one TMA bulk copy per (image, plane), issued by one thread; ACT_BITS input
     // = three warps expanding bit-packed activations ------------------------------------------------------------------------
     constexpr int CW = C / 32;
-    if (in_fmt == ACT_F4P) {
+    if (in_fmt == ACT_F4P || in_fmt == ACT_F4I) {
       if (tid == 512) {
         const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
         constexpr uint32_t IMG_PLANE = Cfg::PXI * 16;  // bytes of one plane of one image
@@ -211,11 +221,18 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
           uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
           const int valid = n_img - img0 < G ? (n_img - img0 > 0 ? n_img - img0 : 0) : G;  // rows of missing images keep stale (finite) codes; never stored
+          if (IL) {  // ACT_F4I: the group's plane j is one contiguous block [pixel][image] (slots of missing images hold stale codes)
+            const int cp = valid > 0 ? CW : 0;
+            if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)cp * G * IMG_PLANE);
+            for (int j = 0; j < cp; j++)
+              if (!(kStrip & 16)) tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE, in4 + ((size_t)(img0 / G) * CW + j) * (G * IMG_PLANE), G * IMG_PLANE, &abuf_full[buf]);
+          } else {
           if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)valid * CW * IMG_PLANE);
           for (int gi = 0; gi < valid; gi++)
             for (int j = 0; j < CW; j++)
               if (!(kStrip & 16)) tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE + (size_t)gi * IMG_PLANE, in4 + ((size_t)(img0 + gi) * CW + j) * IMG_PLANE, IMG_PLANE,
                            &abuf_full[buf]);
+          }
           if (PAIR && rank != 0) {  // the follower tells the leader's issuer once its planes have landed
             if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
             tc::mbar_arrive_remote(&peer_full[buf], 0);
@@ -229,13 +246,14 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
       uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
 #pragma unroll 4
       for (int i = tid - 512; i < Cfg::ROWS * CW; i += 96) {
-        const int j = i % CW, m = i / CW, gi = m / Cfg::PXI;
+        const int j = i % CW, mi = i / CW, gi = mi / Cfg::PXI, px = mi - gi * Cfg::PXI;  // (image, pixel) in the order of the global tensor
         uint32_t w0 = 0, w1 = 0;
         if (img0 + gi < n_img) {
-          const size_t base = ((size_t)(img0 + gi) * Cfg::PXI + (m - gi * Cfg::PXI)) * (CW * Cfg::IPL);
+          const size_t base = ((size_t)(img0 + gi) * Cfg::PXI + px) * (CW * Cfg::IPL);
           w0 = __ldg(in + base + j);
           if (INM == IN_TERN) w1 = __ldg(in + base + CW + j);
         }
+        const int m = IL ? px * G + gi : mi;  // operand row
         *reinterpret_cast<uint4*>(sa + (size_t)j * Cfg::PLANE + (size_t)m * 16) = expand_fp4<INM>(w0, w1);
       }
       tc::fence_async_smem();
@@ -263,7 +281,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           if (leader) {  // nine taps per asm block (tcgen05.cuh: mma9_mxf4), once per pair of operand planes
 #pragma unroll
             for (int s = 0; s < Cfg::KC / 2; s++)
-              if (!(kStrip & 1)) tc::mma9_mxf4<IDIM, Cfg::KC * NTL, PAIR ? 2 : 1>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NTL), d_hi, idesc, sf,
+              if (!(kStrip & 1)) tc::mma9_mxf4<Cfg::XS, Cfg::YS, Cfg::KC * NTL, PAIR ? 2 : 1>(acc, at + (uint32_t)(2 * s * (Cfg::PLANE / 16)), bt + (uint32_t)(2 * s * NTL), d_hi, idesc, sf,
                                                1u);
             if (PAIR) tc::commit_pair(&full[slot]); else tc::commit(&full[slot]);
           }
@@ -289,7 +307,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N + (uint32_t)eg * NG;
         uint32_t b0[NWG], b1[NWG];
         uint4 c4[NWG];  // e2m1 codes instead of bits when the consumer is another fp4 kernel
-        const bool codes = !POOL && out_fmt != ACT_BITS;
+        const bool codes = !POOL && out_fmt != ACT_BITS;  // ACT_F4P / ACT_F4I / ACT_F4T
         uint32_t r[32];  // TAP only
         uint32_t hh[2][16];
         if (!(kStrip & 2)) tc::tmem_ld32_pack16(trow, hh[0]);
@@ -316,8 +334,8 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           b0[j] = w0;
           b1[j] = w1;
           if (TAP) {  // parity taps (TAP instantiation only): the MMA sum of every valid output pixel and channel, pre-load un-folded
-            const int gi = m / Cfg::PXI, rem = m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
-            if (m < Cfg::ROWS && y < OD && x < OD && img0 + gi < n_img) {
+            const int gi = IL ? m % G : m / Cfg::PXI, rem = IL ? m / G : m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
+            if (m < Cfg::OROWS && y < OD && x < OD && img0 + gi < n_img) {
               int32_t* ta = tap + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * NT + h * N + eg * NG + j * 32;
               const float* pv = sthr + h * N + eg * NG + j * 32;
 #pragma unroll
@@ -333,17 +351,21 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         if (POOL) {
           row = sbits + (size_t)m * WPP;
         } else {  // straight to global: one output pixel (half of its channels) per thread
-          const int gi = m / Cfg::PXI, rem = m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
-          const bool valid = m < Cfg::ROWS && y < OD && x < OD && img0 + gi < n_img;
+          const int gi = IL ? m % G : m / Cfg::PXI, rem = IL ? m / G : m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
+          const bool valid = m < Cfg::OROWS && y < OD && x < OD && img0 + gi < n_img;
           if (valid && !codes && !(kStrip & 8)) row = out + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * WPP;
           if (valid && codes && !(kStrip & 8)) {
             const size_t img = (size_t)(img0 + gi);
             const int px = y * OD + x;
             uint4* out4 = reinterpret_cast<uint4*>(out);
+            // ACT_F4I: one division per thread and tile, 32-bit index arithmetic (the launcher refuses tensors of 2^31 rows or more)
+            const uint32_t fgrp = __umulhi((uint32_t)img, og_magic), fil = (uint32_t)img - fgrp * (uint32_t)og;
+            const uint32_t fbase = ((fgrp * NWT + (uint32_t)(h * NW + eg * NWG)) * (OD * OD) + (uint32_t)px) * (uint32_t)og + fil, fstep = (uint32_t)(OD * OD) * (uint32_t)og;
 #pragma unroll
             for (int j = 0; j < NWG; j++) {
               const int pj = h * NW + eg * NWG + j;  // 32-channel plane of this layer's output
               if (out_fmt == ACT_F4P) out4[(img * NWT + pj) * (OD * OD) + px] = c4[j];
+              else if (out_fmt == ACT_F4I) out4[fbase + (uint32_t)j * fstep] = c4[j];
               else out4[((img >> 7) * (OD * OD * NWT) + (size_t)(px * NWT + pj)) * 128 + (img & 127)] = c4[j];  // ACT_F4T
             }
           }
@@ -370,8 +392,8 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         for (int i = tid; i < G * PP && !(kStrip & 32); i += 512) {  // one pooled output pixel per thread
           const int gi = i / PP, op = i - gi * PP, oy = op / Cfg::PD, ox = op - oy * Cfg::PD;
           if (img0 + gi >= n_img) continue;
-          const uint4* r00 = reinterpret_cast<const uint4*>(sbits + (size_t)(gi * Cfg::PXI + (2 * oy) * IDIM + 2 * ox) * WPP);
-          const uint4 *r01 = r00 + WPP / 4, *r10 = r00 + (size_t)IDIM * (WPP / 4), *r11 = r10 + WPP / 4;
+          const uint4* r00 = reinterpret_cast<const uint4*>(sbits + (size_t)(IL ? ((2 * oy) * IDIM + 2 * ox) * G + gi : gi * Cfg::PXI + (2 * oy) * IDIM + 2 * ox) * WPP);
+          const uint4 *r01 = r00 + (size_t)Cfg::XS * (WPP / 4), *r10 = r00 + (size_t)Cfg::YS * (WPP / 4), *r11 = r10 + (size_t)Cfg::XS * (WPP / 4);
           uint4* dst = reinterpret_cast<uint4*>(out + ((size_t)(img0 + gi) * PP + op) * WPP);
           auto or4 = [](uint4 a, uint4 b) { return make_uint4(a.x | b.x, a.y | b.y, a.z | b.z, a.w | b.w); };
           auto and4 = [](uint4 a, uint4 b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); };
@@ -383,6 +405,10 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
               if (out_fmt == ACT_F4P) {  // [img][plane][pixel], planes 4q .. 4q+3
                 uint4* out4 = reinterpret_cast<uint4*>(out) + ((size_t)(img0 + gi) * NWT + 4 * q) * PP + op;
                 out4[0] = f4_from_bits(o.x); out4[PP] = f4_from_bits(o.y); out4[2 * PP] = f4_from_bits(o.z); out4[3 * PP] = f4_from_bits(o.w);
+              } else if (out_fmt == ACT_F4I) {  // [img / og][plane][pixel][img % og]
+                uint4* out4 = reinterpret_cast<uint4*>(out) + f4i_index((uint32_t)(img0 + gi), 4 * q, op, NWT, PP, og, og_magic);
+                const size_t ps = (size_t)PP * og;
+                out4[0] = f4_from_bits(o.x); out4[ps] = f4_from_bits(o.y); out4[2 * ps] = f4_from_bits(o.z); out4[3 * ps] = f4_from_bits(o.w);
               } else {
                 dst[q] = o;
               }
@@ -390,10 +416,12 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
               constexpr int H = NWT / 4;
               const uint4 P = or4(or4(r00[H + q], r01[H + q]), or4(r10[H + q], r11[H + q]));
               const uint4 M = and4(and4(andn4(r00[q], r00[H + q]), andn4(r01[q], r01[H + q])), and4(andn4(r10[q], r10[H + q]), andn4(r11[q], r11[H + q])));
-              if (out_fmt == ACT_F4P) {  // [img][plane][pixel], planes 4q .. 4q+3, as e2m1 codes
-                uint4* out4 = reinterpret_cast<uint4*>(out) + ((size_t)(img0 + gi) * NWT + 4 * q) * PP + op;
-                out4[0] = expand_fp4<IN_TERN>(P.x | M.x, P.x); out4[PP] = expand_fp4<IN_TERN>(P.y | M.y, P.y);
-                out4[2 * PP] = expand_fp4<IN_TERN>(P.z | M.z, P.z); out4[3 * PP] = expand_fp4<IN_TERN>(P.w | M.w, P.w);
+              if (out_fmt == ACT_F4P || out_fmt == ACT_F4I) {  // planes 4q .. 4q+3, as e2m1 codes
+                const size_t ps = out_fmt == ACT_F4P ? (size_t)PP : (size_t)PP * og;
+                uint4* out4 = reinterpret_cast<uint4*>(out) +
+                              (out_fmt == ACT_F4P ? ((size_t)(img0 + gi) * NWT + 4 * q) * PP + op : f4i_index((uint32_t)(img0 + gi), 4 * q, op, NWT, PP, og, og_magic));
+                out4[0] = expand_fp4<IN_TERN>(P.x | M.x, P.x); out4[ps] = expand_fp4<IN_TERN>(P.y | M.y, P.y);
+                out4[2 * ps] = expand_fp4<IN_TERN>(P.z | M.z, P.z); out4[3 * ps] = expand_fp4<IN_TERN>(P.w | M.w, P.w);
               } else {
                 dst[q] = or4(P, M);
                 dst[H + q] = P;
@@ -412,10 +440,10 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   if (warp == 0) { if (PAIR) tc::tmem_dealloc_pair(tmem, 512); else tc::tmem_dealloc(tmem, 512); }
 }
 
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
-bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
-                cudaStream_t s) {
-  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool IL>
+bool launch_il(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int og, int* status, int32_t* tap,
+               cudaStream_t s) {
+  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, IL>;
   static_assert(Cfg::SMEM <= 226 * 1024, "shared memory budget");
   static_assert(Cfg::SLOTS * N <= Cfg::SF_COL, "TMEM budget");
   const int ngroups = (n_img + G - 1) / G;
@@ -424,7 +452,7 @@ bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img,
   // 0.166 -> 0.140; 2-bit: 0.461 -> 0.503, 0.460 -> 0.398, 0.191 -> 0.176.  BNN_B200_CONV_PAIR=<mask> overrides (bit 0 / 1 / 2: layer 2 / 3 / 4)
   static const int pair_env = getenv("BNN_B200_CONV_PAIR") ? atoi(getenv("BNN_B200_CONV_PAIR")) : -1;
   const int pair_mask = pair_env >= 0 ? pair_env : (OUTM == OUT_TERN ? 6 : 4), pair_bit = NS == 2 ? 4 : (POOL ? 2 : 1);
-  if (in_fmt == ACT_F4P && ngroups >= 2 && (pair_mask & pair_bit)) {  // a cluster of two per TPC, each pair takes two image groups per round
+  if ((in_fmt == ACT_F4P || in_fmt == ACT_F4I) && ngroups >= 2 && (pair_mask & pair_bit)) {  // a cluster of two per TPC, each pair takes two image groups per round
     const int npairs = (ngroups + 1) / 2, maxpairs = num_sms / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * (npairs < maxpairs ? npairs : maxpairs));
@@ -437,24 +465,32 @@ bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img,
     cfg.attrs = at;
     cfg.numAttrs = 1;
     if (tap) {
-      auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, true>;
+      auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, true, IL>;
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-      return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, status, tap) == cudaSuccess;
+      return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, og, status, tap) == cudaSuccess;
     }
-    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, true>;
+    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, true, IL>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-    return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, status, (int32_t*)nullptr) == cudaSuccess;
+    return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, og, status, (int32_t*)nullptr) == cudaSuccess;
   }
   if (tap) {  // parity taps: the TAP instantiation of the same kernel
-    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, false>;
+    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, false, IL>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-    kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status, tap);
+    kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, tap);
     return true;
   }
-  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, false>;
+  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, false, IL>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-  kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, status, nullptr);
+  kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, nullptr);
   return true;
+}
+
+// rows in image order for ACT_F4P inputs (one bulk copy per image plane), interleaved for ACT_F4I and bit inputs
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
+bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int og, int* status, int32_t* tap,
+                cudaStream_t s) {
+  if (in_fmt == ACT_F4P) return launch_il<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
+  return launch_il<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
 }
 
 }  // namespace
@@ -467,23 +503,33 @@ bool conv_f4_supports(const LayerDesc& d) {
          (d.ifm_ch == 128 && d.N == 256 && d.ifm_dim == 5 && !d.pool);
 }
 
-bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+// images per group of the layer's kernel: what a producer needs to write ACT_F4I for it (0: not a conv_f4 layer)
+int conv_f4_group(const LayerDesc& d) {
+  if (!conv_f4_supports(d)) return 0;
+  const bool tern = d.out_mode == OUT_TERN;
+  if (d.ifm_dim == 14) return tern ? BNNB_G2T : 9;
+  if (d.ifm_dim == 12) return tern ? BNNB_G3T : 6;
+  return BNNB_G4;
+}
+
+bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int og, int* status, int32_t* tap,
                     cudaStream_t s) {
   const LayerDesc& d = L.d;
   if (!conv_f4_supports(d) || !L.w4 || !L.thr_tc || n_img <= 0) return false;
-  if (in_fmt == ACT_F4T || (d.pool && out_fmt == ACT_F4T)) return false;
+  if (in_fmt == ACT_F4T || ((d.pool) && out_fmt == ACT_F4T)) return false;
+  if (out_fmt == ACT_F4I && (og <= 0 || (long long)(n_img + og) * (d.N / 32) * d.ofm_dim * d.ofm_dim >= (1ll << 31))) return false;
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {
-    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, BNNB_G2T, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
+    if (a2) return launch_cfg<64, 128, 1, 14, 12, false, BNNB_G2T, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
   }
   if (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) {
-    if (a1) return launch_cfg<128, 128, 1, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, BNNB_G3T, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+    if (a1) return launch_cfg<128, 128, 1, 12, 10, true, 6, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
+    if (a2) return launch_cfg<128, 128, 1, 12, 10, true, BNNB_G3T, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
   }
   if (d.ifm_ch == 128 && d.N == 256 && d.ifm_dim == 5 && !d.pool) {  // two channel blocks of 128 share the operand planes
-    if (a1) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-    if (a2) return launch_cfg<128, 128, 2, 5, 3, false, 15, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+    if (a1) return launch_cfg<128, 128, 2, 5, 3, false, BNNB_G4, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
+    if (a2) return launch_cfg<128, 128, 2, 5, 3, false, BNNB_G4, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
   }
   return false;
 }

@@ -188,7 +188,8 @@ size_t Engine::act_bytes(int images) const {
     per = std::max(per, px * out_words_per_pixel(l) * 4);
     if (l.out_mode == OUT_BIT || l.out_mode == OUT_TERN) per = std::max(per, px * l.N / 2);  // e2m1 codes (ACT_F4P / ACT_F4T)
   }
-  return (size_t)((images + 127) / 128 * 128) * per;
+  // CNV: + 20 images, an ACT_F4I tensor is written in whole groups of the consumer's G <= 19 images
+  return (size_t)((images + 127) / 128 * 128 + (net_.is_cnv ? 20 : 0)) * per;
 }
 
 int Engine::set_devices(const int* ids, int n) {
@@ -417,7 +418,9 @@ void Engine::plan_formats(const DeviceState& ds, bool per_layer, bool tensor_tap
     const LayerDesc& c = net_.L[i + 1];
     const bool producer_f4 = fam[i] != 0 || (*fused01 && i == 1 && core_ == 2);
     if (!producer_f4 || !((p.out_mode == OUT_BIT && c.in_mode == IN_XNOR) || (p.out_mode == OUT_TERN && c.in_mode == IN_TERN))) continue;
-    if (fam[i + 1] == 1 && fam[i] != 2) ofmt[i] = ACT_F4P;                        // conv consumer: image planes
+    if (fam[i + 1] == 1 && fam[i] != 2) ofmt[i] = (no_tiles || (*fused01 && i == 1)) ? ACT_F4P : ACT_F4I;
+    // (conv consumer: image planes, interleaved per group of the consumer - except after the fused kernel, whose pool helpers the
+    // scattered stores slowed by 3-10 %, and in fault epochs, whose kernel runs start at arbitrary images)
     if (fam[i + 1] == 2 && !p.pool && !(*fused01 && i == 1) && !no_tiles) ofmt[i] = ACT_F4T;   // gemm consumer: 128-image tiles
   }
 }
@@ -478,7 +481,7 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     int raw = 1;
     ProfEv pe = prof_begin(i);
     if (net_.is_cnv && i == 0) { launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s); raw = 0; }
-    else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], ds.d_status, tp, s)) {}
+    else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], last ? 0 : conv_f4_group(net_.L[i + 1]), ds.d_status, tp, s)) {}
     else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], ds.d_status, tp, s)) {}
     else if (core_ >= 1 && !popc_only && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, tp, s)) {}
     else if (core_ >= 1 && !popc_only && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, tp, s)) {}
@@ -537,7 +540,7 @@ int Engine::run_chunk_faulted(DeviceState& ds, const DevLayer* PL, DevLayer* d_l
       bool ok = true;
       if (fused) ok = launch_cnv01_tc(PL[0], PL[1], (const int8_t*)in_p, out_p, c, ds.num_sms, core_ == 2, ofmt[1], ds.d_status, Tap01(), s);
       else if (net_.is_cnv && i == 0) launch_conv0(PL[0], (const int8_t*)in_p, out_p, c, nullptr, ds.num_sms, s);
-      else if (fam[i] == 1 && launch_conv_f4(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], ds.d_status, nullptr, s)) {}
+      else if (fam[i] == 1 && launch_conv_f4(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], 0, ds.d_status, nullptr, s)) {}
       else if (fam[i] == 2 && launch_gemm_f4(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ifmt, ofmt[i], ds.d_status, nullptr, s)) {}
       else if (core_ >= 1 && launch_conv_tc(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ds.d_status, nullptr, s)) {}
       else if (core_ >= 1 && launch_gemm_tc(PL[i], (const uint32_t*)in_p, out_p, c, ds.num_sms, ds.d_status, nullptr, s)) {}
@@ -595,8 +598,8 @@ static std::mutex g_static_mu;
 static unsigned char* g_static_ptr[64] = {};   // per device id: the array's device address, resolved once
 
 int Engine::static_max_images() const {
-  const size_t per = act_bytes(128) / 128;     // act_bytes rounds the batch up to whole 128-image tiles
-  return (int)(kStaticScratchHalf / per / 128 * 128);
+  const size_t per = (act_bytes(256) - act_bytes(128)) / 128;  // bytes per image (act_bytes: whole 128-image tiles + slack)
+  return (int)((kStaticScratchHalf / per - (net_.is_cnv ? 20 : 0)) / 128 * 128);   // act_bytes: whole 128-image tiles + its slack
 }
 
 int Engine::infer_device_static(int slot, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t stream) {
@@ -1093,6 +1096,10 @@ int Engine::tap_host(const uint8_t* input, int n, int32_t* acc, int8_t* act) {
               }
             } else if (tap.ofmt[i] == ACT_F4P) {   // uint4 [img][plane][pixel]
               const uint32_t* w = reinterpret_cast<const uint32_t*>(&h4[((size_t)k * nw + (ch >> 5)) * px + p]);
+              v = e2m1_act((w[(ch & 31) >> 3] >> (4 * (ch & 7))) & 0xF, false);
+            } else if (tap.ofmt[i] == ACT_F4I) {   // uint4 [img/G][plane][pixel][img%G], G = the consumer's images per group
+              const int G = conv_f4_group(net_.L[i + 1]);
+              const uint32_t* w = reinterpret_cast<const uint32_t*>(&h4[(((size_t)(k / G) * nw + (ch >> 5)) * px + p) * G + k % G]);
               v = e2m1_act((w[(ch & 31) >> 3] >> (4 * (ch & 7))) & 0xF, false);
             } else if (tap.ofmt[i] == ACT_F4T) {   // uint4 [img/128][chunk = pixel*C/32 + plane][img%128]
               const uint32_t* w = reinterpret_cast<const uint32_t*>(&h4[((size_t)(k >> 7) * (px * nw) + (size_t)(p * nw + (ch >> 5))) * 128 + (k & 127)]);

@@ -13,7 +13,17 @@
 
 namespace bnnb {
 
-enum ActFmt : int { ACT_BITS = 0, ACT_F4P = 1, ACT_F4T = 2 };
+enum ActFmt : int { ACT_BITS = 0, ACT_F4P = 1, ACT_F4T = 2, ACT_F4I = 3 };
+
+// ACT_F4I: ACT_F4P with the images of a group interleaved pixel by pixel: uint4 [img/G][plane][pixel][img%G], G = the CONSUMER's
+// images per group.  A consumer conv then stages a whole group's plane with one bulk copy AND its operand rows are ordered
+// (pixel, image): the rows whose outputs can be valid - pixel index up to (OD-1)*IDIM + OD - form a prefix, so the tiles behind it
+// (the bottom rows of every image, 14-45 % of the MMAs of these layers) are never computed.
+__host__ __device__ inline uint32_t f4i_magic(int g) { return (uint32_t)((1ull << 32) / (uint32_t)g) + 1u; }  // img / g = umulhi(img, magic), img < 2^32 / g
+__device__ __forceinline__ size_t f4i_index(uint32_t img, int plane, int px, int nplanes, int npx, int g, uint32_t magic) {
+  const uint32_t grp = __umulhi(img, magic), il = img - grp * (uint32_t)g;
+  return (((size_t)grp * nplanes + plane) * npx + px) * g + il;
+}
 
 // 8 bits -> 8 nibbles (bit i at position 4i)
 __device__ __forceinline__ uint32_t f4_spread8(uint32_t x) {

@@ -55,8 +55,10 @@ void launch_thr_tc(const DevLayer& L, cudaStream_t s);
 // in_fmt / out_fmt: ActFmt of f4_common.cuh (ACT_BITS everywhere except between fp4 kernels of a 1-bit network)
 bool conv_f4_supports(const LayerDesc& d);
 // tap (parity tests; null in production): int32 MMA sums [img][ofm_dim^2][N], pre-loads un-folded
-bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
+// og: images per group of the consumer when out_fmt == ACT_F4I (conv_f4_group of the next layer)
+bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int og, int* status, int32_t* tap,
                     cudaStream_t s);
+int conv_f4_group(const LayerDesc& d);
 // fully-connected layers on kind::mxf4 (gemm_f4.cu); gemm_f4_block = channel block width NB of the slab layout
 int gemm_f4_block(const LayerDesc& d);
 bool gemm_f4_supports(const DevLayer& L);

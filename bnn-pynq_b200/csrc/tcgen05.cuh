@@ -314,7 +314,8 @@ __device__ __forceinline__ void mma_i8_lh(uint32_t tmem_d, uint32_t alo, uint32_
 // ---- one 3x3 tile = nine kind::mxf4 MMAs in a single asm block ---------------------------------------------------------------------
 // The issuing thread is the scarcest resource of these kernels (about one instruction per 5-7 clocks, ncu), so the whole tap loop is
 // handed to ptxas as one block: both descriptors keep their high words, the low words advance by immediates.
-//   a_lo: descriptor low word of the tile's first operand row; tap (ky,kx) starts (ky*IDIM + kx) rows further (16-byte units)
+//   a_lo: descriptor low word of the tile's first operand row; tap (ky,kx) starts ky*YS + kx*XS rows further (16-byte units): XS = 1,
+//         YS = image width for rows in image order; XS = G, YS = width*G for G images interleaved pixel by pixel (conv_f4.cu)
 //   b_lo: low word of tap 0's weight block; consecutive taps are BSTEP 16-byte units apart
 namespace bnnb { namespace tc {
 #define BNNB_MMA9_BODY(CG)                                                                                     \
@@ -328,27 +329,27 @@ namespace bnnb { namespace tc {
       "mov.b64 a, {%1, %3};\n\t" \
       "mov.b64 b, {%2, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], p;\n\t" \
-      "add.u32 al, %1, 1;\n\t add.u32 bl, %2, %7;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "add.u32 al, %1, %15;\n\t add.u32 bl, %2, %7;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
-      "add.u32 al, %1, 2;\n\t add.u32 bl, %2, %8;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "add.u32 al, %1, %16;\n\t add.u32 bl, %2, %8;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
-      "add.u32 al, %1, %15;\n\t add.u32 bl, %2, %9;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "add.u32 al, %1, %17;\n\t add.u32 bl, %2, %9;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
-      "add.u32 al, %1, %16;\n\t add.u32 bl, %2, %10;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "add.u32 al, %1, %18;\n\t add.u32 bl, %2, %10;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
-      "add.u32 al, %1, %17;\n\t add.u32 bl, %2, %11;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "add.u32 al, %1, %19;\n\t add.u32 bl, %2, %11;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
-      "add.u32 al, %1, %18;\n\t add.u32 bl, %2, %12;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "add.u32 al, %1, %20;\n\t add.u32 bl, %2, %12;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
-      "add.u32 al, %1, %19;\n\t add.u32 bl, %2, %13;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "add.u32 al, %1, %21;\n\t add.u32 bl, %2, %13;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
-      "add.u32 al, %1, %20;\n\t add.u32 bl, %2, %14;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
+      "add.u32 al, %1, %22;\n\t add.u32 bl, %2, %14;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t" \
       "tcgen05.mma.cta_group::" #CG ".kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t" \
       "}\n" ::"r"(tmem_d), \
       "r"(a_lo), "r"(b_lo), "r"(d_hi), "r"(idesc), "r"(sf), "r"(acc_first), "n"(BSTEP), "n"(2 * BSTEP), "n"(3 * BSTEP), "n"(4 * BSTEP), "n"(5 * BSTEP), \
-      "n"(6 * BSTEP), "n"(7 * BSTEP), "n"(8 * BSTEP), "n"(IDIM), "n"(IDIM + 1), "n"(IDIM + 2), "n"(2 * IDIM), "n"(2 * IDIM + 1), "n"(2 * IDIM + 2) \
+      "n"(6 * BSTEP), "n"(7 * BSTEP), "n"(8 * BSTEP), "n"(XS), "n"(2 * XS), "n"(YS), "n"(YS + XS), "n"(YS + 2 * XS), "n"(2 * YS), "n"(2 * YS + XS), "n"(2 * YS + 2 * XS) \
       : "memory");
-template <int IDIM, int BSTEP, int CG = 1>
+template <int XS, int YS, int BSTEP, int CG = 1>
 __device__ __forceinline__ void mma9_mxf4(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t d_hi, uint32_t idesc, uint32_t sf, uint32_t acc_first) {
   if (CG == 2) { BNNB_MMA9_BODY(2); }
   else { BNNB_MMA9_BODY(1); }
