@@ -15,6 +15,7 @@
 //   warp  19        MMA issuer, up to three tiles ahead (three TMEM accumulator slots)
 // decoupled by mbarriers only: abuf_full / abuf_empty per operand buffer, full / empty per accumulator slot.
 // PAIR instantiation: two CTAs of a cluster run every MMA together (tcgen05 cta_group::2, M = 256), see the kernel.
+#include <cuda.h>  // CUtensorMap (the type and the encoder's signature only: the entry point comes from cudaGetDriverEntryPoint)
 #include <climits>
 #include <cstdlib>
 #include "kernels.cuh"
@@ -90,7 +91,8 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
 
 template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool TAP, bool PAIR, bool IL>
 __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
-                                                     int in_fmt, int out_fmt, int og, int* __restrict__ status, int32_t* __restrict__ tap) {
+                                                     int in_fmt, int out_fmt, int og, int* __restrict__ status, int32_t* __restrict__ tap,
+                                                     const __grid_constant__ CUtensorMap tmap) {
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, IL>;
   const uint32_t og_magic = f4i_magic(og > 0 ? og : 1);  // ACT_F4I output: the consumer's images per group
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
@@ -140,7 +142,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   if (PAIR) tc::cluster_sync();  // both CTAs are resident before the paired allocation
   if (warp == 0) { if (PAIR) tc::tmem_alloc_pair(&tmem_base, 512); else tc::tmem_alloc(&tmem_base, 512); }
   if (tid == 0) {
-    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], (in_fmt == ACT_F4P || in_fmt == ACT_F4I) ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); tc::mbar_init(&peer_full[i], 1); }
+    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], (in_fmt == ACT_F4P || in_fmt == ACT_F4I || in_fmt == ACT_F4PM) ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); tc::mbar_init(&peer_full[i], 1); }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], (PAIR ? 2 : 1) * 4 * EGS); }
     tc::mbar_init_fence();
   }
@@ -212,7 +214,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     // ---- operand planes of group k+1: ACT_F4P input = one TMA bulk copy per (image, plane), issued by one thread; ACT_BITS input
     // = three warps expanding bit-packed activations ------------------------------------------------------------------------
     constexpr int CW = C / 32;
-    if (in_fmt == ACT_F4P || in_fmt == ACT_F4I) {
+    if (in_fmt == ACT_F4P || in_fmt == ACT_F4I || in_fmt == ACT_F4PM) {
       if (tid == 512) {
         const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
         constexpr uint32_t IMG_PLANE = Cfg::PXI * 16;  // bytes of one plane of one image
@@ -221,7 +223,14 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
           uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
           const int valid = n_img - img0 < G ? (n_img - img0 > 0 ? n_img - img0 : 0) : G;  // rows of missing images keep stale (finite) codes; never stored
-          if (IL) {  // ACT_F4I: the group's plane j is one contiguous block [pixel][image] (slots of missing images hold stale codes)
+          if (IL && in_fmt == ACT_F4PM) {
+            // ACT_F4P tensor [img][plane][pixel][16 B] read through a 4-D tensor map with dimensions (16 B, image, pixel, plane): one
+            // box of (16 B, G images, all pixels, one plane) lands in shared memory in box order = rows (pixel, image); images past
+            // the end of the tensor are filled with zeros
+            if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)CW * G * IMG_PLANE);
+            for (int j = 0; j < CW; j++)
+              if (!(kStrip & 16)) tc::tma_load_4d(sa + (size_t)j * Cfg::PLANE, &tmap, 0, img0, 0, j, &abuf_full[buf]);
+          } else if (IL) {  // ACT_F4I: the group's plane j is one contiguous block [pixel][image] (slots of missing images hold stale codes)
             const int cp = valid > 0 ? CW : 0;
             if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)cp * G * IMG_PLANE);
             for (int j = 0; j < cp; j++)
@@ -440,6 +449,26 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   if (warp == 0) { if (PAIR) tc::tmem_dealloc_pair(tmem, 512); else tc::tmem_dealloc(tmem, 512); }
 }
 
+// Tensor map over an ACT_F4P tensor uint4 [n_img][planes][px], dimensions (16 bytes, image, pixel, plane), box (16, g, px, 1): the
+// box lands in shared memory with dimension 0 fastest, i.e. as operand rows (pixel, image).  cuTensorMapEncodeTiled is taken from
+// the driver through the runtime (no link against libcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+bool encode_f4p_map(CUtensorMap* m, const void* base, int n_img, int planes, int px, int g) {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  if (!fn) return false;
+  const cuuint64_t dims[4] = {16, (cuuint64_t)n_img, (cuuint64_t)px, (cuuint64_t)planes};
+  const cuuint64_t strides[3] = {(cuuint64_t)planes * px * 16, 16, (cuuint64_t)px * 16};  // bytes, dimensions 1 .. 3
+  const cuuint32_t box[4] = {16, (cuuint32_t)g, (cuuint32_t)px, 1}, estr[4] = {1, 1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool IL>
 bool launch_il(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int og, int* status, int32_t* tap,
                cudaStream_t s) {
@@ -448,11 +477,13 @@ bool launch_il(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, 
   static_assert(Cfg::SLOTS * N <= Cfg::SF_COL, "TMEM budget");
   const int ngroups = (n_img + G - 1) / G;
   const int grid = ngroups < num_sms ? ngroups : num_sms;
+  CUtensorMap tmap = {};
+  if (in_fmt == ACT_F4PM && !encode_f4p_map(&tmap, in, n_img, C / 32, IDIM * IDIM, G)) return false;
   // CTA pairs where they pay.  Measured, ms per 65 536 images, single -> paired: 1-bit layers 2 / 3 / 4: 0.335 -> 0.334, 0.413 -> 0.425,
   // 0.166 -> 0.140; 2-bit: 0.461 -> 0.503, 0.460 -> 0.398, 0.191 -> 0.176.  BNN_B200_CONV_PAIR=<mask> overrides (bit 0 / 1 / 2: layer 2 / 3 / 4)
   static const int pair_env = getenv("BNN_B200_CONV_PAIR") ? atoi(getenv("BNN_B200_CONV_PAIR")) : -1;
   const int pair_mask = pair_env >= 0 ? pair_env : (OUTM == OUT_TERN ? 6 : 4), pair_bit = NS == 2 ? 4 : (POOL ? 2 : 1);
-  if ((in_fmt == ACT_F4P || in_fmt == ACT_F4I) && ngroups >= 2 && (pair_mask & pair_bit)) {  // a cluster of two per TPC, each pair takes two image groups per round
+  if ((in_fmt == ACT_F4P || in_fmt == ACT_F4I || in_fmt == ACT_F4PM) && ngroups >= 2 && (pair_mask & pair_bit)) {  // a cluster of two per TPC, each pair takes two image groups per round
     const int npairs = (ngroups + 1) / 2, maxpairs = num_sms / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * (npairs < maxpairs ? npairs : maxpairs));
@@ -467,21 +498,21 @@ bool launch_il(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, 
     if (tap) {
       auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, true, IL>;
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-      return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, og, status, tap) == cudaSuccess;
+      return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, og, status, tap, tmap) == cudaSuccess;
     }
     auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, true, IL>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-    return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, og, status, (int32_t*)nullptr) == cudaSuccess;
+    return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, og, status, (int32_t*)nullptr, tmap) == cudaSuccess;
   }
   if (tap) {  // parity taps: the TAP instantiation of the same kernel
     auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, false, IL>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-    kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, tap);
+    kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, tap, tmap);
     return true;
   }
   auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, false, IL>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-  kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, nullptr);
+  kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, nullptr, tmap);
   return true;
 }
 
@@ -517,6 +548,7 @@ bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
   const LayerDesc& d = L.d;
   if (!conv_f4_supports(d) || !L.w4 || !L.thr_tc || n_img <= 0) return false;
   if (in_fmt == ACT_F4T || ((d.pool) && out_fmt == ACT_F4T)) return false;
+  if (in_fmt == ACT_F4P) in_fmt = ACT_F4PM;  // image planes are always staged through the tensor map (interleaved rows)
   if (out_fmt == ACT_F4I && (og <= 0 || (long long)(n_img + og) * (d.N / 32) * d.ofm_dim * d.ofm_dim >= (1ll << 31))) return false;
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {

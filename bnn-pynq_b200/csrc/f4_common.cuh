@@ -13,7 +13,8 @@
 
 namespace bnnb {
 
-enum ActFmt : int { ACT_BITS = 0, ACT_F4P = 1, ACT_F4T = 2, ACT_F4I = 3 };
+enum ActFmt : int { ACT_BITS = 0, ACT_F4P = 1, ACT_F4T = 2, ACT_F4I = 3, ACT_F4PM = 4 };  // ACT_F4PM (conv_f4 input only): an ACT_F4P tensor
+                                                                    // staged in interleaved row order by a 4-D tiled TMA load (tensor map)
 
 // ACT_F4I: ACT_F4P with the images of a group interleaved pixel by pixel: uint4 [img/G][plane][pixel][img%G], G = the CONSUMER's
 // images per group.  A consumer conv then stages a whole group's plane with one bulk copy AND its operand rows are ordered

@@ -129,6 +129,13 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+// 4-D tiled TMA load (cuTensorMapEncodeTiled descriptor in kernel parameter space): box at coordinates (c0, c1, c2, c3) -> shared memory
+// in box order (dimension 0 fastest), bytes counted on the mbarrier
+__device__ __forceinline__ void tma_load_4d(void* dst_smem, const void* tmap, int c0, int c1, int c2, int c3, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst_smem)),
+               "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
 // bounded spin: returns false once the wait has lasted BNNB_WAIT_NS of wall time (%globaltimer; legitimate waits are microseconds,
 // also under profiler replay or time-slicing, where a poll count says nothing) so that a protocol bug cannot hang the GPU box.
 // The caller stops waiting after the first failure and raises the device status flag; the engine turns that into an error.
