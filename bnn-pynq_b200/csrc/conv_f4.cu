@@ -10,8 +10,9 @@
 //                   per-tile epilogue is split until it is shorter than the tile's MMAs): TMEM (packed 16-bit reads of accumulators
 //                   that carry the threshold in a biased pre-load, f4_common.cuh) -> e2m1 codes or decision bits -> global
 //                   (pooled layers: via smem)
-//   warps 16-18     operand planes of group g+1 into the other buffer: TMA bulk copies when the producer wrote e2m1 planes
-//                   (ACT_F4P; one thread), else expansion of bit-packed activations (global, L2) -> fp4 operand planes
+//   warps 16-18     operand planes of group g+1 into the other buffer, the group's images interleaved pixel by pixel: one tiled TMA
+//                   load per plane through a tensor map (ACT_F4P producer) or one bulk copy per plane (ACT_F4I producer), issued by
+//                   one thread; else expansion of bit-packed activations (global, L2) -> fp4 operand planes
 //   warp  19        MMA issuer, up to three tiles ahead (three TMEM accumulator slots)
 // decoupled by mbarriers only: abuf_full / abuf_empty per operand buffer, full / empty per accumulator slot.
 // PAIR instantiation: two CTAs of a cluster run every MMA together (tcgen05 cta_group::2, M = 256), see the kernel.
@@ -25,14 +26,14 @@
 namespace bnnb {
 namespace {
 
-// IL: the G images of a group are interleaved pixel by pixel (operand row = pixel * G + image; ACT_F4I input or expanded bits): the rows
-// whose outputs can be valid form a prefix of OROWS rows and only its tiles are computed; tap (ky, kx) = (ky * IDIM + kx) * G rows on.
-// !IL: rows in image order (row = image * PXI + pixel; ACT_F4P input: one bulk copy per image plane - the fault-epoch path, whose
-// kernel runs start at arbitrary images, uses this one).
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool IL>
+// The G images of a group are interleaved pixel by pixel: operand row = pixel * G + image (ACT_F4I input: one bulk copy per plane;
+// ACT_F4P input: one tiled TMA load per plane through a tensor map; bit input: expanded into that order).  The rows whose outputs
+// can be valid - pixel index up to (OD-1)*IDIM + OD - then form a prefix of OROWS rows, and only its tiles are computed (the bottom
+// rows of every image were 14-45 % of these layers' MMAs); tap (ky, kx) = descriptor start (ky * IDIM + kx) * G rows on.
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
 struct F4Cfg {
-  static constexpr int PXI = IDIM * IDIM, ROWS = G * PXI, XS = IL ? G : 1, YS = IDIM * XS, MAXSHIFT = 2 * YS + 2 * XS;
-  static constexpr int OROWS = IL ? ((OD - 1) * IDIM + OD) * G : ROWS;  // rows 0 .. OROWS-1 hold every valid output
+  static constexpr int PXI = IDIM * IDIM, ROWS = G * PXI, XS = G, YS = IDIM * XS, MAXSHIFT = 2 * YS + 2 * XS;
+  static constexpr int OROWS = ((OD - 1) * IDIM + OD) * G;  // rows 0 .. OROWS-1 hold every valid output
   static constexpr int TILES = (OROWS + 127) / 128;
   static constexpr int PITCH = ((TILES * 128 + MAXSHIFT > ROWS ? TILES * 128 + MAXSHIFT : ROWS) + 7) / 8 * 8;
   static constexpr int KC = C / 32;  // 16-byte chunks (32 fp4 channels) per tap
@@ -89,11 +90,11 @@ __device__ __forceinline__ uint4 expand_fp4(uint32_t w0, uint32_t w1) {
   return make_uint4(v[0], v[1], v[2], v[3]);
 }
 
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool TAP, bool PAIR, bool IL>
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool TAP, bool PAIR>
 __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                      int in_fmt, int out_fmt, int og, int* __restrict__ status, int32_t* __restrict__ tap,
                                                      const __grid_constant__ CUtensorMap tmap) {
-  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, IL>;
+  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   const uint32_t og_magic = f4i_magic(og > 0 ? og : 1);  // ACT_F4I output: the consumer's images per group
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
   static_assert(BNNB_CONV_EGS == 4 || BNNB_CONV_EGS == 2 || BNNB_CONV_EGS == 0, "epilogue groups");
@@ -142,7 +143,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   if (PAIR) tc::cluster_sync();  // both CTAs are resident before the paired allocation
   if (warp == 0) { if (PAIR) tc::tmem_alloc_pair(&tmem_base, 512); else tc::tmem_alloc(&tmem_base, 512); }
   if (tid == 0) {
-    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], (in_fmt == ACT_F4P || in_fmt == ACT_F4I || in_fmt == ACT_F4PM) ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); tc::mbar_init(&peer_full[i], 1); }
+    for (int i = 0; i < 2; i++) { tc::mbar_init(&abuf_full[i], (in_fmt == ACT_F4I || in_fmt == ACT_F4PM) ? 1 : 96); tc::mbar_init(&abuf_empty[i], 1); tc::mbar_init(&peer_full[i], 1); }
     for (int i = 0; i < 4; i++) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], (PAIR ? 2 : 1) * 4 * EGS); }
     tc::mbar_init_fence();
   }
@@ -211,10 +212,11 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   const int gfirst = PAIR ? 2 * unit0 + (int)rank : unit0, gstride = PAIR ? 2 * ustride : ustride;
 
   if (role == 1) {
-    // ---- operand planes of group k+1: ACT_F4P input = one TMA bulk copy per (image, plane), issued by one thread; ACT_BITS input
-    // = three warps expanding bit-packed activations ------------------------------------------------------------------------
+    // ---- operand planes of group k+1, rows interleaved (pixel, image): ACT_F4P input = one tiled TMA load per plane through the tensor
+    // map, ACT_F4I input = one bulk copy per plane (both issued by one thread); ACT_BITS input = three warps expanding bit-packed
+    // activations --------------------------------------------------------------------------------------------------------------
     constexpr int CW = C / 32;
-    if (in_fmt == ACT_F4P || in_fmt == ACT_F4I || in_fmt == ACT_F4PM) {
+    if (in_fmt == ACT_F4I || in_fmt == ACT_F4PM) {
       if (tid == 512) {
         const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
         constexpr uint32_t IMG_PLANE = Cfg::PXI * 16;  // bytes of one plane of one image
@@ -223,24 +225,18 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           if (k >= 2 && !failed && !tc::mbar_wait(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
           uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
           const int valid = n_img - img0 < G ? (n_img - img0 > 0 ? n_img - img0 : 0) : G;  // rows of missing images keep stale (finite) codes; never stored
-          if (IL && in_fmt == ACT_F4PM) {
+          if (in_fmt == ACT_F4PM) {
             // ACT_F4P tensor [img][plane][pixel][16 B] read through a 4-D tensor map with dimensions (16 B, image, pixel, plane): one
             // box of (16 B, G images, all pixels, one plane) lands in shared memory in box order = rows (pixel, image); images past
             // the end of the tensor are filled with zeros
             if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)CW * G * IMG_PLANE);
             for (int j = 0; j < CW; j++)
               if (!(kStrip & 16)) tc::tma_load_4d(sa + (size_t)j * Cfg::PLANE, &tmap, 0, img0, 0, j, &abuf_full[buf]);
-          } else if (IL) {  // ACT_F4I: the group's plane j is one contiguous block [pixel][image] (slots of missing images hold stale codes)
+          } else {  // ACT_F4I: the group's plane j is one contiguous block [pixel][image] (slots of missing images hold stale codes)
             const int cp = valid > 0 ? CW : 0;
             if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)cp * G * IMG_PLANE);
             for (int j = 0; j < cp; j++)
               if (!(kStrip & 16)) tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE, in4 + ((size_t)(img0 / G) * CW + j) * (G * IMG_PLANE), G * IMG_PLANE, &abuf_full[buf]);
-          } else {
-          if (kStrip & 16) tc::mbar_arrive(&abuf_full[buf]); else tc::mbar_expect_tx(&abuf_full[buf], (uint32_t)valid * CW * IMG_PLANE);
-          for (int gi = 0; gi < valid; gi++)
-            for (int j = 0; j < CW; j++)
-              if (!(kStrip & 16)) tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE + (size_t)gi * IMG_PLANE, in4 + ((size_t)(img0 + gi) * CW + j) * IMG_PLANE, IMG_PLANE,
-                           &abuf_full[buf]);
           }
           if (PAIR && rank != 0) {  // the follower tells the leader's issuer once its planes have landed
             if (!failed && !tc::mbar_wait(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
@@ -262,7 +258,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           w0 = __ldg(in + base + j);
           if (INM == IN_TERN) w1 = __ldg(in + base + CW + j);
         }
-        const int m = IL ? px * G + gi : mi;  // operand row
+        const int m = px * G + gi;  // operand row
         *reinterpret_cast<uint4*>(sa + (size_t)j * Cfg::PLANE + (size_t)m * 16) = expand_fp4<INM>(w0, w1);
       }
       tc::fence_async_smem();
@@ -343,7 +339,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
           b0[j] = w0;
           b1[j] = w1;
           if (TAP) {  // parity taps (TAP instantiation only): the MMA sum of every valid output pixel and channel, pre-load un-folded
-            const int gi = IL ? m % G : m / Cfg::PXI, rem = IL ? m / G : m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
+            const int gi = m % G, rem = m / G, y = rem / IDIM, x = rem - y * IDIM;
             if (m < Cfg::OROWS && y < OD && x < OD && img0 + gi < n_img) {
               int32_t* ta = tap + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * NT + h * N + eg * NG + j * 32;
               const float* pv = sthr + h * N + eg * NG + j * 32;
@@ -360,7 +356,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         if (POOL) {
           row = sbits + (size_t)m * WPP;
         } else {  // straight to global: one output pixel (half of its channels) per thread
-          const int gi = IL ? m % G : m / Cfg::PXI, rem = IL ? m / G : m - gi * Cfg::PXI, y = rem / IDIM, x = rem - y * IDIM;
+          const int gi = m % G, rem = m / G, y = rem / IDIM, x = rem - y * IDIM;
           const bool valid = m < Cfg::OROWS && y < OD && x < OD && img0 + gi < n_img;
           if (valid && !codes && !(kStrip & 8)) row = out + ((size_t)(img0 + gi) * (OD * OD) + y * OD + x) * WPP;
           if (valid && codes && !(kStrip & 8)) {
@@ -401,7 +397,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         for (int i = tid; i < G * PP && !(kStrip & 32); i += 512) {  // one pooled output pixel per thread
           const int gi = i / PP, op = i - gi * PP, oy = op / Cfg::PD, ox = op - oy * Cfg::PD;
           if (img0 + gi >= n_img) continue;
-          const uint4* r00 = reinterpret_cast<const uint4*>(sbits + (size_t)(IL ? ((2 * oy) * IDIM + 2 * ox) * G + gi : gi * Cfg::PXI + (2 * oy) * IDIM + 2 * ox) * WPP);
+          const uint4* r00 = reinterpret_cast<const uint4*>(sbits + (size_t)(((2 * oy) * IDIM + 2 * ox) * G + gi) * WPP);
           const uint4 *r01 = r00 + (size_t)Cfg::XS * (WPP / 4), *r10 = r00 + (size_t)Cfg::YS * (WPP / 4), *r11 = r10 + (size_t)Cfg::XS * (WPP / 4);
           uint4* dst = reinterpret_cast<uint4*>(out + ((size_t)(img0 + gi) * PP + op) * WPP);
           auto or4 = [](uint4 a, uint4 b) { return make_uint4(a.x | b.x, a.y | b.y, a.z | b.z, a.w | b.w); };
@@ -469,10 +465,10 @@ bool encode_f4p_map(CUtensorMap* m, const void* base, int n_img, int planes, int
             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM, bool IL>
-bool launch_il(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int og, int* status, int32_t* tap,
-               cudaStream_t s) {
-  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, IL>;
+template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
+bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int og, int* status, int32_t* tap,
+                cudaStream_t s) {
+  using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   static_assert(Cfg::SMEM <= 226 * 1024, "shared memory budget");
   static_assert(Cfg::SLOTS * N <= Cfg::SF_COL, "TMEM budget");
   const int ngroups = (n_img + G - 1) / G;
@@ -483,7 +479,7 @@ bool launch_il(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, 
   // 0.166 -> 0.140; 2-bit: 0.461 -> 0.503, 0.460 -> 0.398, 0.191 -> 0.176.  BNN_B200_CONV_PAIR=<mask> overrides (bit 0 / 1 / 2: layer 2 / 3 / 4)
   static const int pair_env = getenv("BNN_B200_CONV_PAIR") ? atoi(getenv("BNN_B200_CONV_PAIR")) : -1;
   const int pair_mask = pair_env >= 0 ? pair_env : (OUTM == OUT_TERN ? 6 : 4), pair_bit = NS == 2 ? 4 : (POOL ? 2 : 1);
-  if ((in_fmt == ACT_F4P || in_fmt == ACT_F4I || in_fmt == ACT_F4PM) && ngroups >= 2 && (pair_mask & pair_bit)) {  // a cluster of two per TPC, each pair takes two image groups per round
+  if ((in_fmt == ACT_F4I || in_fmt == ACT_F4PM) && ngroups >= 2 && (pair_mask & pair_bit)) {  // a cluster of two per TPC, each pair takes two image groups per round
     const int npairs = (ngroups + 1) / 2, maxpairs = num_sms / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * (npairs < maxpairs ? npairs : maxpairs));
@@ -496,32 +492,24 @@ bool launch_il(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, 
     cfg.attrs = at;
     cfg.numAttrs = 1;
     if (tap) {
-      auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, true, IL>;
+      auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, true>;
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
       return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, og, status, tap, tmap) == cudaSuccess;
     }
-    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, true, IL>;
+    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, true>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
     return cudaLaunchKernelEx(&cfg, kern, L, in, out, n_img, in_fmt, out_fmt, og, status, (int32_t*)nullptr, tmap) == cudaSuccess;
   }
   if (tap) {  // parity taps: the TAP instantiation of the same kernel
-    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, false, IL>;
+    auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true, false>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
     kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, tap, tmap);
     return true;
   }
-  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, false, IL>;
+  auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, false>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
   kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, nullptr, tmap);
   return true;
-}
-
-// rows in image order for ACT_F4P inputs (one bulk copy per image plane), interleaved for ACT_F4I and bit inputs
-template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int OUTM>
-bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int og, int* status, int32_t* tap,
-                cudaStream_t s) {
-  if (in_fmt == ACT_F4P) return launch_il<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
-  return launch_il<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, true>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
 }
 
 }  // namespace
