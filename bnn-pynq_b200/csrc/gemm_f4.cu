@@ -8,7 +8,7 @@
 //              start while its tail is still arriving: four TMA bulk copies when the producer wrote e2m1 tiles (ACT_F4T; one
 //              thread), else expansion of bit-packed activations
 //   warp  10   loader: weight slabs (NB x 64 e2m1 = NB*32 bytes, pre-arranged in operand layout by k_repack_w4s) by TMA bulk
-//              copy into a ring of R slots, running ahead of the MMAs
+//              copy into a ring of R slots, running ahead of the MMAs (the warp walks the groups in ring order, converged)
 //   warp  11   issuer: one K=64 MMA per slab; accumulator slots (3) let the next channel block start while one drains
 // Replaces StreamingFCLayer_Batch / ConvLayer_Batch + ThresholdsActivation / PassThroughActivation for these layers
 // (fclayer.h:83-111, convlayer.h:85-121, activations.hpp:85-148).
@@ -200,22 +200,27 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
     }
   } else if (role == 2) {
     // ---- loader: weight slabs in MMA order, R slots ahead ----------------------------------------------------------------------
-    // One lane per ring slot (lane l owns slot l: groups l, l + ring, l + 2 ring, ...), so the copies of a whole ring are issued
-    // by one pass of the warp instead of one thread's ~40 instructions per copy
-    if (lane < g.ring) {
+    // The slots come free in ring order, so the warp walks the groups in order, CONVERGED (every lane polls the same barrier; one
+    // elected lane arms it and issues the copy).  With one lane per slot the lanes diverged, each spinning on its own barrier, and a
+    // freed slot waited for its lane's turn.
+    {
+      const bool leader = tc::elect_one();
       const int ngrp = (g.ks + GG - 1) / GG;      // groups per channel block (the last one may be short)
-      const int per_tile = g.nblk * ngrp;
-      const int total = T * per_tile;
+      const int total = T * g.nblk * ngrp;
+      int r = 0, nb = 0, gi = 0;
       uint32_t rpar = 1;                           // parity to wait for on ring_empty = parity of the slot's previous use
-      uint8_t* dst = ring + (size_t)lane * (GG * SLAB);
-      for (int gg = lane; gg < total; gg += g.ring) {
-        const int qg = gg % per_tile, nb = qg / ngrp, gi = qg - nb * ngrp;
+      for (int gg = 0; gg < total; gg++) {
         const int s0 = gi * GG, cnt = min(GG, g.ks - s0);
-        if (gg >= g.ring && !failed && !tc::mbar_wait(&ring_empty[lane], rpar)) failed = true;
-        if (kGStrip & 8) { tc::mbar_arrive(&ring_full[lane]); rpar ^= 1u; continue; }
-        tc::mbar_expect_tx(&ring_full[lane], (uint32_t)cnt * SLAB);
-        tc::bulk_g2s(dst, L.w4s + (size_t)(nb * g.ks + s0) * SLAB, (uint32_t)cnt * SLAB, &ring_full[lane]);  // the slabs of a block are consecutive
-        rpar ^= 1u;
+        if (gg >= g.ring && !failed && !tc::mbar_wait(&ring_empty[r], rpar)) failed = true;
+        if (leader) {
+          if (kGStrip & 8) tc::mbar_arrive(&ring_full[r]);
+          else {
+            tc::mbar_expect_tx(&ring_full[r], (uint32_t)cnt * SLAB);
+            tc::bulk_g2s(ring + (size_t)r * (GG * SLAB), L.w4s + (size_t)(nb * g.ks + s0) * SLAB, (uint32_t)cnt * SLAB, &ring_full[r]);  // the slabs of a block are consecutive
+          }
+        }
+        if (++gi == ngrp) { gi = 0; if (++nb == g.nblk) nb = 0; }
+        if (++r == g.ring) { r = 0; rpar ^= 1u; }
       }
     }
   } else if (role == 3) {
