@@ -436,7 +436,6 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
   int fam[9], ofmt[9];
   bool fused01;
   plan_formats(ds, per_layer, per_layer && tap->tensor, fam, ofmt, &fused01);
-  static const bool f4pm = !(getenv("BNN_B200_NO_TMAP") && atoi(getenv("BNN_B200_NO_TMAP")));
   int32_t* tap_acc = tap ? tap->acc : nullptr;
   auto take_tap = [&](int i) {  // this layer's slice of the tap buffer
     int32_t* p = tap_acc;
@@ -482,8 +481,8 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     int raw = 1;
     ProfEv pe = prof_begin(i);
     if (net_.is_cnv && i == 0) { launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s); raw = 0; }
-    // (an ACT_F4P input - the fused kernel's output - is staged in interleaved row order through a tensor map: ACT_F4PM)
-    else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, (ifmt == ACT_F4P && f4pm) ? ACT_F4PM : ifmt, ofmt[i], last ? 0 : conv_f4_group(net_.L[i + 1]), ds.d_status, tp, s)) {}
+    // (an ACT_F4P input - the fused kernel's output - is staged in interleaved row order through a tensor map, conv_f4.cu)
+    else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], last ? 0 : conv_f4_group(net_.L[i + 1]), ds.d_status, tp, s)) {}
     else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], ds.d_status, tp, s)) {}
     else if (core_ >= 1 && !popc_only && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, tp, s)) {}
     else if (core_ >= 1 && !popc_only && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, tp, s)) {}
