@@ -52,8 +52,11 @@ struct F4Cfg {
 #define BNNB_CONV_STRIP 0
 #endif
 constexpr int kStrip = BNNB_CONV_STRIP;
+#ifndef BNNB_G2B
+#define BNNB_G2B 10
+#endif
 #ifndef BNNB_G2T
-#define BNNB_G2T 9
+#define BNNB_G2T 10
 #endif
 #ifndef BNNB_G4
 #define BNNB_G4 19
@@ -107,8 +110,9 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
   const int role = warp < 16 ? 0 : (warp < 19 ? 1 : 2), ht = tid & 127, hw = warp & 3;
   // epilogue warps (role 0): EGS channel groups x TEAMS tile teams of four warps (one per TMEM lane quarter); team t takes the tiles
   // with gt % TEAMS == t, group eg the output channels [eg*N/EGS, (eg+1)*N/EGS) of the block
-  // (measured: 1-bit outputs 2 x 2 - the fixed per-tile cost of a warp is halved; 2-bit outputs 4 x 1 - their longer harvest per channel dominates)
-  constexpr int EGS = BNNB_CONV_EGS ? BNNB_CONV_EGS : (OUTM == OUT_BIT ? 2 : 4), TEAMS = 4 / EGS;
+  // (measured with the interleaved layout, ms per 65 536 images 4 x 1 -> 2 x 2: layer 2 0.312 -> 0.305 (1-bit), 0.393 -> 0.374 (2-bit) - the
+  // fixed per-tile cost of a warp is halved; the pooled layer 3 0.375 -> 0.386, 0.375 -> 0.436 - its tiles are twice as long already)
+  constexpr int EGS = BNNB_CONV_EGS ? BNNB_CONV_EGS : (POOL ? 4 : (NS == 2 ? (OUTM == OUT_BIT ? 2 : 4) : 2)), TEAMS = 4 / EGS;
   const int eg = ((warp >> 2) & 3) % EGS, team = ((warp >> 2) & 3) / EGS;
   constexpr int NWG = Cfg::NW / EGS;  // 32-channel words per epilogue group
   constexpr int NG = N / EGS;         // channels per epilogue group
@@ -526,7 +530,7 @@ bool conv_f4_supports(const LayerDesc& d) {
 int conv_f4_group(const LayerDesc& d) {
   if (!conv_f4_supports(d)) return 0;
   const bool tern = d.out_mode == OUT_TERN;
-  if (d.ifm_dim == 14) return tern ? BNNB_G2T : 9;
+  if (d.ifm_dim == 14) return tern ? BNNB_G2T : BNNB_G2B;
   if (d.ifm_dim == 12) return tern ? BNNB_G3T : 6;
   return BNNB_G4;
 }
@@ -540,7 +544,7 @@ bool launch_conv_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_
   if (out_fmt == ACT_F4I && (og <= 0 || (long long)(n_img + og) * (d.N / 32) * d.ofm_dim * d.ofm_dim >= (1ll << 31))) return false;
   const bool a1 = d.in_mode == IN_XNOR && d.out_mode == OUT_BIT, a2 = d.in_mode == IN_TERN && d.out_mode == OUT_TERN;
   if (d.ifm_ch == 64 && d.N == 128 && d.ifm_dim == 14 && !d.pool) {
-    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, 9, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
+    if (a1) return launch_cfg<64, 128, 1, 14, 12, false, BNNB_G2B, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
     if (a2) return launch_cfg<64, 128, 1, 14, 12, false, BNNB_G2T, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, og, status, tap, s);
   }
   if (d.ifm_ch == 128 && d.N == 128 && d.ifm_dim == 12 && d.pool) {
