@@ -62,6 +62,8 @@ struct GemmGeom {
   int cw, ipl;                    // words per pixel and plane (C/32), input planes
   int a_bytes, off_ring, off_thr, ring;  // ring = slots of the weight ring (GG slabs each)
   int resident;                          // the whole layer's weights fit the ring: loaded once per CTA, every tile re-uses them
+  int* classes;                          // OUT_SCORE: optional class per image (first score strictly above a running max from 0,
+  int ncls;                              // over the first ncls scores: foldedmv-offload.h:398-406), written by the thread that holds the row
 };
 
 template <int NB, int INM, int OUTM, bool TAP>
@@ -303,6 +305,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
     const int nwt = g.N / 32;
     for (int tl = 0; tl < T; tl++) {
       const long long img = ((long long)blockIdx.x + (long long)tl * gridDim.x) * 128 + hw * 32 + lane;
+      int cls_max = 0, cls_arg = 0;  // OUT_SCORE with classes: running arg-max over this row's scores, channel order
       for (int nb = 0; nb < g.nblk; nb++) {
         const int gb = tl * g.nblk + nb, slot = gb % SLOTS, u = gb / SLOTS;
         if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
@@ -352,6 +355,9 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
                   const uint32_t lo = (uint32_t)(__float2int_rn(__uint_as_float(r[j & 1][c + 2 * e])) + __float2int_rn(th[c + 2 * e])) & 0xffff;
                   const uint32_t hi = (uint32_t)(__float2int_rn(__uint_as_float(r[j & 1][c + 2 * e + 1])) + __float2int_rn(th[c + 2 * e + 1])) & 0xffff;
                   pk[e] = lo | (hi << 16);
+                  const int ch = nb * NB + j * 32 + c + 2 * e, vlo = (int)(int16_t)lo, vhi = (int)(int16_t)hi;
+                  if (ch < g.ncls && vlo > cls_max) { cls_max = vlo; cls_arg = ch; }
+                  if (ch + 1 < g.ncls && vhi > cls_max) { cls_max = vhi; cls_arg = ch + 1; }
                 }
                 *reinterpret_cast<uint4*>(o16 + c) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
               }
@@ -365,6 +371,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
             for (int c = 0; c < 32; c++) ta[c] = __float2int_rn(__uint_as_float(r[j & 1][c]) - (ACC ? th[c] : 0.0f));
           }
         }
+        if (OUTM == OUT_SCORE && g.classes && nb == g.nblk - 1 && img < n_img) g.classes[img] = cls_arg;
         if (ACC && !(kGStrip & 4) && gb + SLOTS < T * g.nblk) preload(slot, (gb + SLOTS) % g.nblk);
         tc::fence_before_sync();
         __syncwarp();
@@ -392,9 +399,11 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
 
 template <int NB, int INM, int OUTM>
 bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
-              cudaStream_t s) {
+              cudaStream_t s, int* classes, int ncls) {
   const LayerDesc& d = L.d;
   GemmGeom g;
+  g.classes = OUTM == OUT_SCORE ? classes : nullptr;
+  g.ncls = ncls < 0 ? 0 : (ncls > d.N ? d.N : ncls);
   g.K = d.K; g.N = d.N; g.kch = d.K / 32; g.ks = d.K / 64; g.nblk = d.N / NB;
   g.cw = d.ifm_ch / 32; g.ipl = INM == IN_TERN ? 2 : 1;
   g.a_bytes = g.kch * 2048;
@@ -432,14 +441,14 @@ bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, i
 
 template <int NB>
 bool launch_nb(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
-               cudaStream_t s) {
+               cudaStream_t s, int* classes, int ncls) {
   const int im = L.d.in_mode, om = L.d.out_mode;
-  if (im == IN_XNOR && om == OUT_BIT) return launch_g<NB, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-  if (im == IN_XNOR && om == OUT_SCORE) return launch_g<NB, IN_XNOR, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-  if (im == IN_BIN && om == OUT_TERN) return launch_g<NB, IN_BIN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-  if (im == IN_TERN && om == OUT_TERN) return launch_g<NB, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-  if (im == IN_TERN && om == OUT_SCORE) return launch_g<NB, IN_TERN, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
-  if (im == IN_TERN && om == OUT_BIT) return launch_g<NB, IN_TERN, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+  if (im == IN_XNOR && om == OUT_BIT) return launch_g<NB, IN_XNOR, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s, classes, ncls);
+  if (im == IN_XNOR && om == OUT_SCORE) return launch_g<NB, IN_XNOR, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s, classes, ncls);
+  if (im == IN_BIN && om == OUT_TERN) return launch_g<NB, IN_BIN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s, classes, ncls);
+  if (im == IN_TERN && om == OUT_TERN) return launch_g<NB, IN_TERN, OUT_TERN>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s, classes, ncls);
+  if (im == IN_TERN && om == OUT_SCORE) return launch_g<NB, IN_TERN, OUT_SCORE>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s, classes, ncls);
+  if (im == IN_TERN && om == OUT_BIT) return launch_g<NB, IN_TERN, OUT_BIT>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s, classes, ncls);
   return false;
 }
 
@@ -457,13 +466,13 @@ bool gemm_f4_supports(const DevLayer& L) {
 }
 
 bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
-                    cudaStream_t s) {
+                    cudaStream_t s, int* classes, int ncls) {
   const LayerDesc& d = L.d;
   if (!gemm_f4_supports(L) || n_img <= 0) return false;
   if (in_fmt == ACT_F4P || out_fmt == ACT_F4P) return false;
   if (in_fmt == ACT_F4T && d.in_mode != IN_XNOR && d.in_mode != IN_TERN) return false;  // {0,1} / {-1,0,+1} codes as the producer wrote them
   if (out_fmt == ACT_F4T && d.out_mode != OUT_BIT && d.out_mode != OUT_TERN) return false;
-  return gemm_f4_block(d) == 128 ? launch_nb<128>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s) : launch_nb<64>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s);
+  return gemm_f4_block(d) == 128 ? launch_nb<128>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s, classes, ncls) : launch_nb<64>(L, in, out, n_img, num_sms, in_fmt, out_fmt, status, tap, s, classes, ncls);
 }
 
 }  // namespace bnnb

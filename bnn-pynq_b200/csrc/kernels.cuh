@@ -62,8 +62,10 @@ int conv_f4_group(const LayerDesc& d);
 // fully-connected layers on kind::mxf4 (gemm_f4.cu); gemm_f4_block = channel block width NB of the slab layout
 int gemm_f4_block(const LayerDesc& d);
 bool gemm_f4_supports(const DevLayer& L);
+// classes / ncls: a score layer (CNV layer 8) also writes the class of every image (the multi-image arg-max rule), saving the launch of
+// k_cnv_classes
 bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
-                    cudaStream_t s);
+                    cudaStream_t s, int* classes = nullptr, int ncls = 0);
 // K-streamed GEMM for FC / small conv layers (gemm_tc.cu)
 bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, int32_t* tap, cudaStream_t s);
 // fused CNV layers 0+1 (cnv01_tc.cu): int8 HWC image -> pooled, bit-packed layer-1 output
