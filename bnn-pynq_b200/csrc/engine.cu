@@ -484,8 +484,8 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     if (net_.is_cnv && i == 0) { launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s); raw = 0; }
     // (an ACT_F4P input - the fused kernel's output - is staged in interleaved row order through a tensor map, conv_f4.cu)
     else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], last ? 0 : conv_f4_group(net_.L[i + 1]), ds.d_status, tp, s)) {}
-    else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], ds.d_status, tp, s, (last && net_.is_cnv) ? d_classes : nullptr, ncls)) {
-      if (last && net_.is_cnv && d_classes) classes_done = true;  // the score layer's epilogue wrote the classes
+    else if (fam[i] == 2 && launch_gemm_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], ds.d_status, tp, s, last ? d_classes : nullptr, ncls)) {
+      if (last && d_classes && (net_.is_cnv || net_.L[i].N == 64)) classes_done = true;  // the last layer's epilogue wrote the classes
     }
     else if (core_ >= 1 && !popc_only && launch_conv_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, tp, s)) {}
     else if (core_ >= 1 && !popc_only && launch_gemm_tc(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ds.d_status, tp, s)) {}
@@ -501,7 +501,7 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     cur = out;
   }
   if (net_.is_cnv && d_classes && !classes_done) { launch_cnv_classes((const int16_t*)d_out, n, ncls, d_classes, s); launches++; }
-  if (!net_.is_cnv && d_classes) { launch_lfc_classes((const uint64_t*)d_out, n, ncls, d_classes, s); launches++; }
+  if (!net_.is_cnv && d_classes && !classes_done) { launch_lfc_classes((const uint64_t*)d_out, n, ncls, d_classes, s); launches++; }
   return launches;
 }
 

@@ -381,6 +381,11 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
 #pragma unroll
           for (int j = 0; j < NW; j++) out4[(size_t)j * 128] = c4[j];
         } else if (OUTM != OUT_SCORE && img < n_img) {
+          if (OUTM == OUT_BIT && NW == 2 && g.classes && g.nblk == 1) {
+            // LFC: the class of the 64-bit output word, multi-image rule (foldedmv-offload.cpp:202-220; same arithmetic as k_lfc_classes)
+            const uint64_t w = (((uint64_t)b0[1] << 32) | b0[0]) & (g.ncls >= 64 ? ~0ull : (g.ncls <= 0 ? 0ull : (~0ull >> (64 - g.ncls))));
+            g.classes[img] = !w ? 0 : (w < (1ull << 32) ? 31 - __clz((unsigned)w) : (int)(unsigned)log2((double)w));
+          }
           uint32_t* dst = out + (size_t)img * nwt * OPL + nb * NW;
 #pragma unroll
           for (int j = 0; j < NW; j += 2) {
@@ -402,7 +407,7 @@ bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, i
               cudaStream_t s, int* classes, int ncls) {
   const LayerDesc& d = L.d;
   GemmGeom g;
-  g.classes = OUTM == OUT_SCORE ? classes : nullptr;
+  g.classes = (OUTM == OUT_SCORE || (OUTM == OUT_BIT && d.N == 64)) ? classes : nullptr;  // CNV scores / the LFC output word
   g.ncls = ncls < 0 ? 0 : (ncls > d.N ? d.N : ncls);
   g.K = d.K; g.N = d.N; g.kch = d.K / 32; g.ks = d.K / 64; g.nblk = d.N / NB;
   g.cw = d.ifm_ch / 32; g.ipl = INM == IN_TERN ? 2 : 1;
