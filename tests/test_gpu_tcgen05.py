@@ -93,6 +93,33 @@ def test_fp4_accumulator_preload_is_exact(N, K):
     assert np.array_equal(~np.signbit(D[:, ok]), S[:, ok] > thr[None, ok])
 
 
+@pytest.mark.parametrize("N,K", [(64, 576), (128, 1152), (32, 2304)])
+def test_fp4_biased_preload_keeps_the_integer_in_the_low_mantissa_bits(N, K):
+    """The packed 16-bit epilogues (f4_common.cuh): the accumulator is pre-loaded with 1.5 * 2^23 + 32767 - thr, the MMAs add the exact
+    sum S, and the low 16 bits of the fp32 PATTERN are then the integer S - thr - 1 + 32768, whose bit 15 is the decision thr < S.
+    That needs the tensor core's fp32 accumulation to be exact down to the last mantissa bit at this magnitude: checked here for
+    +-1 / +-2 operands over the K of the real layers, and once more at 1.5 * 2^24 (ulp 2) with even products."""
+    from bnn import native
+    rng = np.random.default_rng(7 * N + K)
+    A = rng.integers(-1, 2, (128, K))
+    B = rng.integers(-2, 2, (N, K))
+    smax = 2 * K
+    thr = np.clip(rng.integers(-smax - 400, smax + 400, N), -smax - 1, smax).astype(np.int64)
+    bias = (12582912.0 + 32767.0 - thr).astype(np.float32)
+    assert np.array_equal(bias.astype(np.int64), 12582912 + 32767 - thr)          # the pre-loads themselves are exact floats
+    D, _ = native.tc_probe_fp4(A, B, 0, 1, bias=bias)
+    S = A.astype(np.int64) @ B.astype(np.int64).T
+    assert np.array_equal(D.astype(np.float64), (S + bias.astype(np.int64)[None, :]).astype(np.float64))
+    low = np.ascontiguousarray(D, np.float32).view(np.uint32) & 0xFFFF
+    assert np.array_equal(low, (S - thr[None, :] - 1 + 32768) & 0xFFFF)
+    assert np.array_equal((low >> 15) & 1, (thr[None, :] < S).astype(np.uint32))
+    # ulp 2: even products only, the accumulator's last mantissa bit still takes part
+    bias2 = (25165824.0 + 2.0 * (32767 - thr)).astype(np.float32)
+    D2, _ = native.tc_probe_fp4(A, 2 * (B // 2), 0, 1, bias=bias2)
+    S2 = A.astype(np.int64) @ (2 * (B // 2)).astype(np.int64).T
+    assert np.array_equal(D2.astype(np.float64), (S2 + bias2.astype(np.int64)[None, :]).astype(np.float64))
+
+
 def test_mma_kind_switch_cost_report():
     """Timing report: cost of interleaving kind::i8 MMAs among kind::mxf4 MMAs on the same tensor pipe.
     mix = g > 0: groups of g fp4 MMAs + one int8 MMA; mix = -g: the control, g + 1 fp4 MMAs per group."""
