@@ -1,6 +1,7 @@
 #include "engine.hpp"
 #include "f4_common.cuh"
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -707,6 +708,10 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
   };
   struct Timed { cudaEvent_t a, b; int n; };
   std::vector<Timed> timed;
+  // BNN_B200_TIMELINE=1: per chunk, when its copy started and when its kernels started / ended, on stderr (a measuring aid)
+  static const bool timeline = std::getenv("BNN_B200_TIMELINE") != nullptr;
+  std::vector<cudaEvent_t> copy_start;
+  const auto wall0 = std::chrono::steady_clock::now();
   int cur = lo, ci = 0;
   {
     while (cur < hi) {
@@ -719,6 +724,12 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
       Lane& ln = ds.lane[k];
       if (flush_lane(ln) != 0) return -1;
       if (ensure_lane(ds, k, c, err) != 0 || ensure_buffers(ds, k, c, err) != 0) return -1;
+      if (timeline) {
+        cudaEvent_t e;
+        CKE(err, cudaEventCreate(&e));
+        CKE(err, cudaEventRecord(e, ln.s));
+        copy_start.push_back(e);
+      }
       CKE(err, cudaMemcpyAsync(packed_ ? ln.d_in : (void*)ln.d_raw, input + (size_t)cur * raw_bytes, (size_t)c * raw_bytes, cudaMemcpyHostToDevice, ln.s));
       if (packed_) {}
       else if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, c, ln.s);
@@ -739,6 +750,18 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
   CKE(err, cudaStreamSynchronize(ds.compute));
   CKE(err, cudaGetLastError());
   if (check_status(ds, err) != 0) return -1;
+  if (timeline) {
+    const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+    std::fprintf(stderr, "[timeline] device %d images %d wall %.3f ms\n", ds.id, hi - lo, wall);
+    for (size_t i = 0; i < timed.size(); i++) {
+      float c0 = 0, a = 0, b = 0;
+      cudaEventElapsedTime(&c0, copy_start[0], copy_start[i]);
+      cudaEventElapsedTime(&a, copy_start[0], timed[i].a);
+      cudaEventElapsedTime(&b, copy_start[0], timed[i].b);
+      std::fprintf(stderr, "[timeline]   chunk %2zu n %5d copy from %.3f kernels %.3f .. %.3f ms\n", i, timed[i].n, c0, a, b);
+    }
+    for (auto e : copy_start) cudaEventDestroy(e);
+  }
   // Device time of the call = the time during which at least one chunk's layer kernels were in flight: the union of the chunks'
   // [start, end] intervals (lanes overlap; a plain sum would count the overlap several times, and the gaps in which every lane waits
   // for its copy are not kernel time).
