@@ -137,6 +137,7 @@ static int round_cap(int images) {  // buffer capacities grow in powers of two f
 Engine::Engine(const NetDesc& net) : net_(net), pm_(new ParamMirror(net)) {
   if (const char* e = std::getenv("BNN_B200_CORE")) core_ = std::strcmp(e, "popc") == 0 ? 0 : (std::strcmp(e, "i8") == 0 ? 1 : 2);
   if (const char* e = std::getenv("BNN_B200_FUSE01")) fuse01_ = std::atoi(e) != 0;
+  if (const char* e = std::getenv("BNN_B200_CHAIN")) chain_ = std::atoi(e) != 0;
 }
 
 Engine::~Engine() { dev_.clear(); }
@@ -482,6 +483,16 @@ int Engine::run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int
     const int ifmt = i > 0 ? ofmt[i - 1] : ACT_BITS;
     int raw = 1;
     ProfEv pe = prof_begin(i);
+    // the trailing fully-connected layers in one launch (fc_chain.cu), from the first layer whose run qualifies and fits
+    if (!per_layer && chain_ && fam[i] == 2 && !last && ifmt == ACT_F4T &&
+        launch_fc_chain(&ds.L[i], net_.nlayers - i, (const uint32_t*)cur, (uint32_t*)d_out, n, ds.num_sms, ifmt, ds.d_status, s, d_classes, ncls)) {
+      prof_end(pe);
+      const cudaError_t le = cudaGetLastError();
+      if (le != cudaSuccess) { err = "layers " + std::to_string(i) + "... (chain) launch: " + cudaGetErrorString(le); return -1; }
+      launches++;
+      if (d_classes) classes_done = true;
+      break;
+    }
     if (net_.is_cnv && i == 0) { launch_conv0(ds.L[0], (const int8_t*)cur, out, n, tp, ds.num_sms, s); raw = 0; }
     // (an ACT_F4P input - the fused kernel's output - is staged in interleaved row order through a tensor map, conv_f4.cu)
     else if (fam[i] == 1 && launch_conv_f4(ds.L[i], (const uint32_t*)cur, out, n, ds.num_sms, ifmt, ofmt[i], last ? 0 : conv_f4_group(net_.L[i + 1]), ds.d_status, tp, s)) {}

@@ -133,6 +133,7 @@ class Engine {
   bool profile_ = false;
   int core_ = 2;
   bool fuse01_ = true;
+  bool chain_ = true;     // trailing fully-connected layers in one launch (fc_chain.cu); BNN_B200_CHAIN=0 launches them one by one
   bool packed_ = false;  // the host-buffer call in progress takes prepared inputs (infer_host_packed)
   struct ProfEv { cudaEvent_t a, b; int layer, dev; };
   std::vector<ProfEv> prof_;

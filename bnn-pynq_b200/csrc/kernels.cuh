@@ -66,6 +66,10 @@ bool gemm_f4_supports(const DevLayer& L);
 // k_cnv_classes
 bool launch_gemm_f4(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int out_fmt, int* status, int32_t* tap,
                     cudaStream_t s, int* classes = nullptr, int ncls = 0);
+// a run of gemm_f4 layers ending in the network's output layer, in one launch (fc_chain.cu): L[0..nl), first operand as ACT_F4T tiles;
+// false when the run does not qualify (the caller launches the layers one by one)
+bool launch_fc_chain(const DevLayer* L, int nl, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int in_fmt, int* status, cudaStream_t s,
+                     int* classes, int ncls);
 // K-streamed GEMM for FC / small conv layers (gemm_tc.cu)
 bool launch_gemm_tc(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, int num_sms, int* status, int32_t* tap, cudaStream_t s);
 // fused CNV layers 0+1 (cnv01_tc.cu): int8 HWC image -> pooled, bit-packed layer-1 output
