@@ -64,6 +64,15 @@ struct DeviceState {
   std::vector<void*> params;  // parameter-lifetime allocations
   std::vector<cudaEvent_t> tev;
   size_t bytes = 0;
+  // The one-image call (bnn.py's inference()): record -> device, quantise, every layer, class -> host as ONE CUDA graph launch on
+  // lane 0 instead of ten stream operations; key = everything the captured nodes hold by value (run_single).
+  struct SingleGraph {
+    cudaGraphExec_t exec = nullptr;
+    std::vector<uint64_t> key;
+    bool warm = false, disabled = false;
+    uint8_t* h_in = nullptr;   // pinned staging: one record in, scores / word + class out
+    uint8_t* h_out = nullptr;
+  } single;
 
   void* alloc(size_t n, bool param) {
     void* p = nullptr;
@@ -95,6 +104,10 @@ struct DeviceState {
     for (auto& c : clone) c = ParamSet();
     for (cudaEvent_t e : tev) cudaEventDestroy(e);
     tev.clear();
+    if (single.exec) cudaGraphExecDestroy(single.exec);
+    if (single.h_in) cudaFreeHost(single.h_in);
+    if (single.h_out) cudaFreeHost(single.h_out);
+    single = SingleGraph();
     if (h_status) cudaFreeHost(h_status);
     d_layers = nullptr; d_status = nullptr; h_status = nullptr;
     bytes = 0;
@@ -682,6 +695,71 @@ int Engine::sync(int slot) {
   return check_status(ds, err_);
 }
 
+// One image through a captured CUDA graph.  Returns 0 (done), -1 (error) or 1 (this call must take the ordinary path: the first
+// one-image call of a configuration runs there, which also loads every kernel and sizes the lane's buffers - nothing a capture may
+// do - and a device that refuses the capture stays there for good).  BNN_B200_NO_GRAPH=1 switches the path off.
+int Engine::run_single(DeviceState& ds, const uint8_t* rec, size_t raw_bytes, int ncls, int* classes, int16_t* scores, uint64_t* words,
+                       float* dev_ms, std::string& err) {
+  static const bool off = std::getenv("BNN_B200_NO_GRAPH") != nullptr || std::getenv("BNN_B200_TIMELINE") != nullptr;
+  DeviceState::SingleGraph& sg = ds.single;
+  if (off || sg.disabled) return 1;
+  Lane& ln = ds.lane[0];
+  if (ensure_lane(ds, 0, 1, err) != 0 || ensure_buffers(ds, 0, 1, err) != 0) return -1;
+  const std::vector<uint64_t> key = {(uint64_t)(uintptr_t)ln.d_raw, (uint64_t)(uintptr_t)ln.d_in, (uint64_t)(uintptr_t)ln.act[0], (uint64_t)(uintptr_t)ln.act[1],
+                                     (uint64_t)(uintptr_t)ln.d_out, (uint64_t)(uintptr_t)ln.d_cls, (uint64_t)(uintptr_t)ds.arena, (uint64_t)ncls,
+                                     (uint64_t)packed_, (uint64_t)core_, (uint64_t)fuse01_, (uint64_t)chain_};
+  if (key != sg.key) {  // a new configuration: its first call runs the ordinary path
+    if (sg.exec) { cudaGraphExecDestroy(sg.exec); sg.exec = nullptr; }
+    sg.key = key;
+    sg.warm = false;
+  }
+  if (!sg.warm) { sg.warm = true; return 1; }
+  if (!sg.h_in) {
+    if (cudaHostAlloc((void**)&sg.h_in, 4096, cudaHostAllocPortable) != cudaSuccess || cudaHostAlloc((void**)&sg.h_out, 256, cudaHostAllocPortable) != cudaSuccess) {
+      cudaGetLastError();
+      sg.disabled = true;
+      return 1;
+    }
+  }
+  if (!sg.exec) {
+    if (cudaStreamBeginCapture(ln.s, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); sg.disabled = true; return 1; }
+    cudaMemcpyAsync(packed_ ? ln.d_in : (void*)ln.d_raw, sg.h_in, raw_bytes, cudaMemcpyHostToDevice, ln.s);
+    if (packed_) {}
+    else if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, 1, ln.s);
+    else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, 1, ln.s);
+    std::string cerr;
+    const int r = run_chunk(ds, ln.d_in, 1, ln.d_out, ln.d_cls, ncls, ln.s, nullptr, ln.act, cerr);
+    cudaMemcpyAsync(sg.h_out, ln.d_out, (size_t)net_.out_bytes, cudaMemcpyDeviceToHost, ln.s);
+    cudaMemcpyAsync(sg.h_out + 128, ln.d_cls, 4, cudaMemcpyDeviceToHost, ln.s);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(ln.s, &graph);
+    if (r < 0 || ce != cudaSuccess || !graph || cudaGraphInstantiate(&sg.exec, graph, 0) != cudaSuccess) {
+      if (graph) cudaGraphDestroy(graph);
+      cudaGetLastError();
+      sg.exec = nullptr;
+      sg.disabled = true;
+      return 1;
+    }
+    cudaGraphDestroy(graph);
+  }
+  while (ds.tev.size() < 2) {
+    cudaEvent_t e;
+    CKE(err, cudaEventCreate(&e));
+    ds.tev.push_back(e);
+  }
+  std::memcpy(sg.h_in, rec, raw_bytes);
+  CKE(err, cudaEventRecord(ds.tev[0], ln.s));
+  CKE(err, cudaGraphLaunch(sg.exec, ln.s));
+  CKE(err, cudaEventRecord(ds.tev[1], ln.s));
+  CKE(err, cudaStreamSynchronize(ln.s));
+  if (check_status(ds, err) != 0) return -1;
+  if (net_.is_cnv) { if (scores) std::memcpy(scores, sg.h_out, 128); }
+  else if (words) std::memcpy(words, sg.h_out, 8);
+  if (classes) std::memcpy(classes, sg.h_out + 128, 4);
+  CKE(err, cudaEventElapsedTime(dev_ms, ds.tev[0], ds.tev[1]));
+  return 0;
+}
+
 // One device's shard [lo, hi): chunks go round-robin through the lanes (with fault epochs: run_shard_faulted).
 int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, int16_t* scores, uint64_t* words,
                       const Segments* seg, float* dev_ms, float* last_ms, int* last_imgs, std::string& err) {
@@ -691,6 +769,11 @@ int Engine::run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int
   if (seg) { *dev_ms = 0; return run_shard_faulted(g, lo, hi, input, ncls, classes, words, *seg, last_ms, last_imgs, err); }
   const size_t raw_bytes = packed_ ? (size_t)net_.in_bytes : (net_.is_cnv ? 3073 : 784);  // packed_: the caller hands over BlackBoxJam's own input
   const int chunk = chunk_images(true);
+  if (hi - lo == 1 && !profile_) {
+    const int rs = run_single(ds, input + (size_t)lo * raw_bytes, raw_bytes, ncls, classes ? classes + lo : nullptr, scores ? scores + (size_t)lo * 64 : nullptr,
+                              words ? words + lo : nullptr, dev_ms, err);
+    if (rs <= 0) { *last_ms = *dev_ms; *last_imgs = 1; return rs; }  // 1: not on the graph path (first call, capture refused)
+  }
   for (auto& ln : ds.lane) { ln.used = false; ln.pend_off = -1; }
   auto flush_lane = [&](Lane& ln) -> int {  // results of the lane's chunk in flight -> host
     if (ln.pend_off < 0) return 0;

@@ -114,6 +114,8 @@ class Engine {
                         int* d_classes, int ncls, cudaStream_t s, uint32_t** bufs, FaultPlan& fp, std::string& err);
   int run_chunk(DeviceState& ds, const void* d_in, int n, void* d_out, int* d_classes, int ncls, cudaStream_t s, TapCtx* tap,
                 uint32_t** bufs, std::string& err);
+  int run_single(DeviceState& ds, const uint8_t* rec, size_t raw_bytes, int ncls, int* classes, int16_t* scores, uint64_t* words, float* dev_ms,
+                 std::string& err);
   int run_shard(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, int16_t* scores, uint64_t* words,
                 const Segments* seg, float* dev_ms, float* last_ms, int* last_imgs, std::string& err);
   int run_shard_faulted(int g, int lo, int hi, const uint8_t* input, int ncls, int* classes, uint64_t* words, const Segments& seg,
