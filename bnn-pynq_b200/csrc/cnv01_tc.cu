@@ -129,6 +129,7 @@ __device__ __forceinline__ void half_sync(int id) { asm volatile("bar.sync %0, 2
 template <int OUTM, bool F4, bool TAP>  // OUT_BIT: 1-bit activations (W1A1); OUT_TERN: ternary activations (W1A2 / W2A2)
 __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, const int8_t* __restrict__ in, uint32_t* __restrict__ out,
                                                       int n_img, int out_fmt, int* __restrict__ status, Tap01 tp) {
+  tc::griddep_launch();  // dependents (programmatic dependent launch) may start their prologues now
   using S = Smem01<OUTM, F4>;
   constexpr int L1_A = S::L1_A;
   constexpr uint32_t SF_COL = 448;  // TMEM columns of the unit scale factors (F4)
@@ -394,6 +395,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
       const uint32_t p2_lo[2] = {tc::desc_lo(sP_u, CP ? P_BYTES : 32 * 16), tc::desc_lo(sP_u + S::P_STRIDE, CP ? P_BYTES : 32 * 16)};
       const uint32_t a1_lo[2] = {tc::desc_lo(sA_u, L1_PLANE), tc::desc_lo(sA_u + L1_A, L1_PLANE)};
       const uint32_t b0_lo = tc::desc_lo(sB0_u, 64 * 16), b1_lo = tc::desc_lo(sB1_u, 64 * 16);
+      if (warp == 18) tc::griddep_wait();  // the images are the kernel below's output (programmatic dependent launch)
       for (int k = 0; k < 2 && k < K; k++)
         if (leader && warp == 18) {
           tc::mbar_expect_tx(&img_full[k], 3072);
@@ -660,7 +662,7 @@ static void launch01(const DevLayer& L0, const DevLayer& L1, const int8_t* in, u
     return;
   }
   cudaFuncSetAttribute(k_cnv01_tc<OUTM, F4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
-  k_cnv01_tc<OUTM, F4, false><<<grid, NT01, S::TOTAL, s>>>(L0, L1, in, out, n_img, out_fmt, status, tp);
+  launch_maybe_pdl(k_cnv01_tc<OUTM, F4, false>, grid, NT01, S::TOTAL, s, L0, L1, in, out, n_img, out_fmt, status, tp);
 }
 
 bool launch_cnv01_tc(const DevLayer& L0, const DevLayer& L1, const int8_t* in, uint32_t* out, int n_img, int num_sms, bool fp4, int out_fmt,

@@ -97,6 +97,7 @@ template <int C, int N, int NS, int IDIM, int OD, bool POOL, int G, int INM, int
 __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                      int in_fmt, int out_fmt, int og, int* __restrict__ status, int32_t* __restrict__ tap,
                                                      const __grid_constant__ CUtensorMap tmap) {
+  tc::griddep_launch();  // dependents (programmatic dependent launch) may start their prologues now
   using Cfg = F4Cfg<C, N, NS, IDIM, OD, POOL, G, INM, OUTM>;
   const uint32_t og_magic = f4i_magic(og > 0 ? og : 1);  // ACT_F4I output: the consumer's images per group
   static_assert(Cfg::NW % 4 == 0, "pooled rows of decision bits are moved as uint4");
@@ -220,6 +221,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     // map, ACT_F4I input = one bulk copy per plane (both issued by one thread); ACT_BITS input = three warps expanding bit-packed
     // activations --------------------------------------------------------------------------------------------------------------
     constexpr int CW = C / 32;
+    tc::griddep_wait();  // the input is the kernel below's output (programmatic dependent launch)
     if (in_fmt == ACT_F4I || in_fmt == ACT_F4PM) {
       if (tid == 512) {
         const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
@@ -512,7 +514,7 @@ bool launch_cfg(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img,
   }
   auto kern = k_conv_f4<C, N, NS, IDIM, OD, POOL, G, INM, OUTM, false, false>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-  kern<<<grid, 640, Cfg::SMEM, s>>>(L, in, out, n_img, in_fmt, out_fmt, og, status, nullptr, tmap);
+  launch_maybe_pdl(kern, grid, 640, Cfg::SMEM, s, L, in, out, n_img, in_fmt, out_fmt, og, status, (int32_t*)nullptr, tmap);
   return true;
 }
 

@@ -728,7 +728,10 @@ int Engine::run_single(DeviceState& ds, const uint8_t* rec, size_t raw_bytes, in
     else if (net_.is_cnv) launch_prep_cifar(ln.d_raw, (int8_t*)ln.d_in, 1, ln.s);
     else launch_prep_mnist(ln.d_raw, (uint32_t*)ln.d_in, 1, ln.s);
     std::string cerr;
+    static const bool pdl = std::getenv("BNN_B200_NO_PDL") == nullptr;
+    tl_pdl = pdl;  // the layer kernels start together and wait for each other's output (kernels.cuh)
     const int r = run_chunk(ds, ln.d_in, 1, ln.d_out, ln.d_cls, ncls, ln.s, nullptr, ln.act, cerr);
+    tl_pdl = false;
     cudaMemcpyAsync(sg.h_out, ln.d_out, (size_t)net_.out_bytes, cudaMemcpyDeviceToHost, ln.s);
     cudaMemcpyAsync(sg.h_out + 128, ln.d_cls, 4, cudaMemcpyDeviceToHost, ln.s);
     cudaGraph_t graph = nullptr;

@@ -38,6 +38,7 @@ struct ChainGeom {
 template <bool TERN, int LASTM>
 __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                       int* __restrict__ status) {
+  tc::griddep_launch();  // dependents (programmatic dependent launch) may start their prologues now
   constexpr int SLOTS = CH_SLOTS;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t full[SLOTS], empty[SLOTS], a_part[2][4], a_empty[2], a_ready[CH_MAX][8], ring_full[CH_RING_MAX],
@@ -117,6 +118,7 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
   if (warp == 4) {
     // ---- first operand tile of every tile of this CTA: four TMA bulk copies, one per K quarter (the producer wrote ACT_F4T) -------
     if (lane == 0) {
+      tc::griddep_wait();  // the input is the kernel below's output (programmatic dependent launch)
       const int ks = g.ks[0];
       for (int tl = 0; tl < T; tl++) {
         const int buf = tl % g.nbuf0, use = tl / g.nbuf0;
@@ -399,7 +401,7 @@ bool launch_fc_chain(const DevLayer* L, int nl, const uint32_t* in, uint32_t* ou
   const int lastm = L[nl - 1].d.out_mode;
   auto go = [&](auto kern) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    kern<<<grid, 256, smem, s>>>(g, reinterpret_cast<const uint8_t*>(in), out, n_img, status);
+    launch_maybe_pdl(kern, grid, 256, (size_t)smem, s, g, reinterpret_cast<const uint8_t*>(in), out, n_img, status);
   };
   if (hidden == OUT_TERN) { if (lastm == OUT_SCORE) go(k_fc_chain<true, OUT_SCORE>); else go(k_fc_chain<true, OUT_BIT>); }
   else { if (lastm == OUT_SCORE) go(k_fc_chain<false, OUT_SCORE>); else go(k_fc_chain<false, OUT_BIT>); }

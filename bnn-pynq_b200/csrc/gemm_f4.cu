@@ -69,6 +69,7 @@ struct GemmGeom {
 template <int NB, int INM, int OUTM, bool TAP>
 __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n_img,
                                                      int in_fmt, int out_fmt, int* __restrict__ status, int32_t* __restrict__ tap) {
+  tc::griddep_launch();  // dependents (programmatic dependent launch) may start their prologues now
   constexpr int SLAB = NB * 32, SLOTS = 3, SF_COL = 384, NW = NB / 32, EXP = 192, U = 4;  // EXP expander threads, U loads in flight each
   // thresholded outputs: the accumulators are pre-loaded with the (first) threshold, biased so that bit 15 of the result's low half is
   // the decision; the epilogue reads two channels per register (.pack::16b) and forms codes / bit words with PRMT (f4_common.cuh)
@@ -141,6 +142,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
   if (role == 1) {
     // ---- expander: tile tl -> operand buffer tl % nbuf ------------------------------------------------------------------------
     const int et = tid - 128;  // 0..191
+    tc::griddep_wait();  // the input is the kernel below's output (programmatic dependent launch)
     if (in_fmt == ACT_F4T) {
       // the producer wrote this tile's operand planes already (ACT_F4T): four TMA bulk copies, one per K quarter
       if (et == 0) {
@@ -440,7 +442,7 @@ bool launch_g(const DevLayer& L, const uint32_t* in, uint32_t* out, int n_img, i
   }
   auto kern = k_gemm_f4<NB, INM, OUTM, false>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  kern<<<grid, 384, smem, s>>>(L, g, in, out, n_img, in_fmt, out_fmt, status, nullptr);
+  launch_maybe_pdl(kern, grid, 384, (size_t)smem, s, L, g, in, out, n_img, in_fmt, out_fmt, status, (int32_t*)nullptr);
   return true;
 }
 

@@ -8,6 +8,7 @@
 #include <cstdio>
 
 namespace bnnb {
+thread_local bool tl_pdl = false;
 
 // ------------------------------------------------------------------------------------------------------------
 // Parameter re-pack: folded [pe][wmem] words -> K-major planes / int8 operands / int32 thresholds.
@@ -209,6 +210,7 @@ __device__ __forceinline__ int cifar_q(int c) {
 // One image per CTA iteration: the 3 073-byte record (not even 4-byte aligned) is staged in shared memory with aligned 32-bit loads,
 // then every thread emits whole output words (4 interleaved bytes through the quantisation LUT), coalesced.
 __global__ void __launch_bounds__(256) k_prep_cifar(const uint8_t* __restrict__ rec, int8_t* __restrict__ q, int n) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // the one-image graph: the first layer kernel may start its prologue
   __shared__ int8_t lut[256];
   __shared__ __align__(16) uint8_t buf[3073 + 7];
   lut[threadIdx.x & 255] = (int8_t)cifar_q(threadIdx.x & 255);
@@ -238,6 +240,7 @@ void launch_prep_cifar(const uint8_t* records, int8_t* q, int n, cudaStream_t s)
 }
 // pixels [n][784] -> bits [n][26 words]; bit = (byte >= 128)  <=>  (c/255)*2-1 >= 0 in float (foldedmv-offload.cpp:89-92)
 __global__ void k_prep_mnist(const uint8_t* __restrict__ px, uint32_t* __restrict__ bits, int n) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // the one-image graph: the first layer kernel may start its prologue
   const size_t total = (size_t)n * 26;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const size_t img = i / 26;

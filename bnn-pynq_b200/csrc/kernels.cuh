@@ -31,6 +31,33 @@ struct DevLayer {
   int kpad;             // K padded to a multiple of 32 (mma path)
 };
 
+// ---- launches -------------------------------------------------------------------------------------------------------------------
+// The one-image CUDA graph (engine.cu run_single) launches the layer kernels with programmatic dependent launch: every kernel of
+// the chain is resident at once, runs its prologue (weights and thresholds into shared memory, TMEM, barriers) and waits at
+// griddepcontrol.wait, in the thread that first reads the layer below, for that layer to finish.  Set per host thread around
+// run_chunk; every other path launches ordinarily (whole-GPU grids gain nothing, and early CTAs get in other lanes' way).
+extern thread_local bool tl_pdl;
+#ifdef __CUDACC__
+template <typename... P, typename... A>
+inline void launch_maybe_pdl(void (*kern)(P...), int grid, int block, size_t smem, cudaStream_t s, A... args) {
+  if (!tl_pdl) {
+    kern<<<grid, block, smem, s>>>(args...);
+    return;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kern, P(args)...);
+}
+#endif
+
 // ---- parameter re-pack (runs once per load_parameters and after every fault epoch for the touched layers) ----
 void launch_repack(const DevLayer& L, int is_cnv_layer0, cudaStream_t s);
 // one rewritten parameter word: {layer,is_thr,pe,ind,thresh,pad,value}

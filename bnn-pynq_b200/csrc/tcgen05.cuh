@@ -51,6 +51,11 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {  
 __device__ __forceinline__ void fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 // make generic-proxy shared-memory writes visible to the async proxy (tcgen05.mma operand reads)
+// programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization starts while its
+// predecessor in the stream still runs; griddep_wait blocks until the predecessor has completed and its writes are visible
+// (no-ops in an ordinary launch)
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
