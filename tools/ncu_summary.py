@@ -34,7 +34,7 @@ def launches(src, dst):
         a[0] += 1
         a[1] += float(r[iv].replace(",", ""))
     # the path's own kernels (bench.py also runs pipe micro-benchmarks, an L2 flush and the load-time re-pack kernels)
-    path = lambda k: any(x in k for x in ("k_cnv01", "k_conv", "k_gemm", "k_layer_popc", "k_prep_", "k_cnv_classes"))
+    path = lambda k: any(x in k for x in ("k_cnv01", "k_conv", "k_gemm", "k_fc_chain", "k_layer_popc", "k_prep_", "k_cnv_classes"))
     tot = sum(a[1] for k, a in agg.items() if path(k))
     with open(dst, "w", newline="") as f:
         w = csv.writer(f)

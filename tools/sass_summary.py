@@ -12,7 +12,7 @@ from collections import Counter, OrderedDict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "bnn-pynq_b200")
-HOT = ("k_cnv01_tc", "k_conv_f4", "k_gemm_f4", "k_conv_tc", "k_gemm_tc", "k_layer_popc", "k_conv0", "k_patch_apply", "k_prep_cifar", "k_prep_mnist")
+HOT = ("k_cnv01_tc", "k_conv_f4", "k_gemm_f4", "k_fc_chain", "k_conv_tc", "k_gemm_tc", "k_layer_popc", "k_conv0", "k_patch_apply", "k_prep_cifar", "k_prep_mnist")
 MNEMONICS = ("UTCOMMA", "UTCOMMA.2CTA", "UTCBAR.2CTA", "UTCIMMA", "UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTCBAR", "UBLKCP", "UTMALDG", "SYNCS", "POPC", "LOP3", "SHF", "PRMT", "IMMA", "IDP")
 SHOW = ("UTCOMMA", "UTCIMMA", "LDTM", "STTM", "UBLKCP", "UTCBAR")
 
