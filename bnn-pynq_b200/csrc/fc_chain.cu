@@ -19,7 +19,10 @@
 namespace bnnb {
 namespace {
 
-constexpr int CH_MAX = 4, CH_GG = 8, CH_SLOTS = 3, CH_SF_COL = 384, CH_RING_MAX = 16, CH_BLK_MAX = 32;
+#ifndef BNNB_CH_GG
+#define BNNB_CH_GG 8
+#endif
+constexpr int CH_MAX = 4, CH_GG = BNNB_CH_GG, CH_SLOTS = 3, CH_SF_COL = 384, CH_RING_MAX = 16, CH_BLK_MAX = 32;
 constexpr int CH_SLOT_BYTES = CH_GG * 128 * 32;  // one ring slot: eight K=64 slabs of 128 channels
 
 struct ChainGeom {
@@ -180,7 +183,7 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
             if (!failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
             const int cnt = min(CH_GG, ks - s0);
             const uint32_t b_lo = b_lo0 + (uint32_t)r * (CH_SLOT_BYTES / 16);
-            if (nb > 0 && cnt == CH_GG) {  // every operand slab of the tile is in: one asm block of eight MMAs
+            if (CH_GG == 8 && nb > 0 && cnt == CH_GG) {  // every operand slab of the tile is in: one asm block of eight MMAs
               if (leader) {
                 if (NBl == 128) tc::mma8_mxf4<256, 256>(acc, a_lo + (uint32_t)(2 * s0) * 128, b_lo, d_hi, idesc, sf, (accl || s0 > 0) ? 1u : 0u);
                 else tc::mma8_mxf4<256, 128>(acc, a_lo + (uint32_t)(2 * s0) * 128, b_lo, d_hi, idesc, sf, (accl || s0 > 0) ? 1u : 0u);
