@@ -12,6 +12,7 @@
 // lfcW1A1/hw/top.cpp:142-148; fclayer.h:83-111, activations.hpp:85-148).
 #include <algorithm>
 #include <climits>
+#include <cstdio>
 #include "kernels.cuh"
 #include "tcgen05.cuh"
 #include "f4_common.cuh"
@@ -117,6 +118,13 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
   tc::fence_after_sync();
   const uint32_t sa_u0 = tc::smem_u32(smem), ring_u = tc::smem_u32(ring), sf = tmem + CH_SF_COL;
   bool failed = false;
+#ifdef BNNB_CHAIN_TRACE
+  __shared__ long long tr[3][16][6];  // [role: 0 issuer, 1 epilogue, 2 loader][block of the traced tile][event]
+  constexpr int TRT = 1;              // the traced tile of CTA 0
+#define CTR(role, b, e) do { if (blockIdx.x == 0 && tl == TRT && lane == 0 && (b) < 16) tr[role][b][e] = clock64(); } while (0)
+#else
+#define CTR(role, b, e) do {} while (0)
+#endif
 
   if (warp == 4) {
     // ---- first operand tile of every tile of this CTA: four TMA bulk copies, one per K quarter (the producer wrote ACT_F4T) -------
@@ -151,6 +159,7 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
           for (int s0 = 0; s0 < ks; s0 += CH_GG, gg++) {
             const int cnt = min(CH_GG, ks - s0);
             if (gg >= g.ring && !failed && !tc::mbar_wait(&ring_empty[r], rpar)) failed = true;
+            if (s0 == 0) CTR(2, g.blk0[l] + nb, 0);
             if (leader) {
               tc::mbar_expect_tx(&ring_full[r], (uint32_t)(cnt * slab));
               tc::bulk_g2s(ring + (size_t)r * CH_SLOT_BYTES, g.w4s[l] + (size_t)(nb * ks + s0) * slab, (uint32_t)(cnt * slab), &ring_full[r]);
@@ -176,27 +185,56 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
         int qn = 0;
         for (int nb = 0; nb < g.nblk[l]; nb++) {
           const int gb = tl * nbt + g.blk0[l] + nb, slot = gb % SLOTS, u = gb / SLOTS;
+          CTR(0, g.blk0[l] + nb, 0);
           if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
+          CTR(0, g.blk0[l] + nb, 1);
           const uint32_t acc = tmem + (uint32_t)slot * 128;
           for (int s0 = 0; s0 < ks; s0 += CH_GG) {
             if (!failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
+            if (s0 == 0) CTR(0, g.blk0[l] + nb, 2);
             const int cnt = min(CH_GG, ks - s0);
             const uint32_t b_lo = b_lo0 + (uint32_t)r * (CH_SLOT_BYTES / 16);
-            if (CH_GG == 8 && nb > 0 && cnt == CH_GG) {  // every operand slab of the tile is in: one asm block of eight MMAs
-              if (leader) {
-                if (NBl == 128) tc::mma8_mxf4<256, 256>(acc, a_lo + (uint32_t)(2 * s0) * 128, b_lo, d_hi, idesc, sf, (accl || s0 > 0) ? 1u : 0u);
-                else tc::mma8_mxf4<256, 128>(acc, a_lo + (uint32_t)(2 * s0) * 128, b_lo, d_hi, idesc, sf, (accl || s0 > 0) ? 1u : 0u);
+            const uint32_t a_s0 = a_lo + (uint32_t)(2 * s0) * 128;
+            auto block = [&](int n, int e) {  // n MMAs in one asm block, from slab s0 + e of this group
+              const uint32_t aa = a_s0 + (uint32_t)(2 * e) * 128, bb = b_lo + (uint32_t)e * slab16, first = (accl || s0 + e > 0) ? 1u : 0u;
+              if (!leader) return;
+              if (NBl == 128) {
+                if (n == 8) tc::mma8_mxf4<256, 256>(acc, aa, bb, d_hi, idesc, sf, first);
+                else if (n == 4) tc::mma4_mxf4<256, 256>(acc, aa, bb, d_hi, idesc, sf, first);
+                else tc::mma2_mxf4<256, 256>(acc, aa, bb, d_hi, idesc, sf, first);
+              } else {
+                if (n == 8) tc::mma8_mxf4<256, 128>(acc, aa, bb, d_hi, idesc, sf, first);
+                else if (n == 4) tc::mma4_mxf4<256, 128>(acc, aa, bb, d_hi, idesc, sf, first);
+                else tc::mma2_mxf4<256, 128>(acc, aa, bb, d_hi, idesc, sf, first);
               }
+            };
+            if (nb > 0 && (cnt == 8 || cnt == 4)) {  // every operand slab of the tile is in: one asm block for the group
+              block(cnt, 0);
+            } else if (nb == 0 && l > 0 && (cnt & 1) == 0) {
+              // the tile's first block runs behind the layer below: slabs 2b, 2b+1 = the 128 channels of its block b
+              for (int e = 0; e < cnt; e += 2) {
+                if (!failed && !tc::mbar_wait(&a_ready[l][(s0 + e) >> 1], (uint32_t)tl & 1)) failed = true;
+                tc::fence_after_sync();
+                block(2, e);
+              }
+            } else if (nb == 0 && l == 0 && (cnt == 8 || cnt == 4)) {
+              // the chain's first operand tile arrives in K quarters: the quarters this group reads, then one asm block
+              while (qn < 4 && s0 + cnt - 1 >= (qn * ks) / 4) {
+                if (!failed && !tc::mbar_wait(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
+                qn++;
+              }
+              tc::fence_after_sync();
+              block(cnt, 0);
             } else {
               for (int s = s0; s < s0 + cnt; s++) {
-                if (nb == 0) {  // the tile's first block runs behind the operand as it arrives
+                if (nb == 0) {  // the first operand tile arrives in K quarters
                   if (l == 0) {
                     while (qn < 4 && s >= (qn * ks) / 4) {
                       if (!failed && !tc::mbar_wait(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
                       qn++;
                     }
-                  } else if ((s & 1) == 0) {  // slabs 2b, 2b+1 = the 128 channels of block b of the layer below
+                  } else if ((s & 1) == 0) {
                     if (!failed && !tc::mbar_wait(&a_ready[l][s >> 1], (uint32_t)tl & 1)) failed = true;
                   }
                   tc::fence_after_sync();
@@ -211,6 +249,7 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
           }
           if (leader) tc::commit(&full[slot]);
           __syncwarp();
+          CTR(0, g.blk0[l] + nb, 3);
         }
         if (l == g.rel_layer) {
           if (leader) tc::commit(&a_empty[buf]);
@@ -228,8 +267,10 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
         const float* st = sthr + g.thr_off[l];
         for (int nb = 0; nb < g.nblk[l]; nb++) {
           const int b = g.blk0[l] + nb, gb = tl * nbt + b, slot = gb % SLOTS, u = gb / SLOTS;
+          if (warp == 0) CTR(1, b, 0);
           if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
           tc::fence_after_sync();
+          if (warp == 0) CTR(1, b, 1);
           const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 128;
           uint4 c4[4];
           uint32_t word[2] = {0, 0};
@@ -289,6 +330,7 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
             word[0] = tern_bit_word(hh[0]);
             word[1] = tern_bit_word(hh[1]);
           }
+          if (warp == 0) CTR(1, b, 2);
           if (gb + SLOTS < T * nbt) {  // this slot's next user
             const int b2 = (b + SLOTS) % nbt;
             if (is_acc(blk_layer[b2])) preload(slot, blk_layer[b2], blk_nb[b2]);
@@ -296,12 +338,14 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
           tc::fence_before_sync();
           __syncwarp();
           if (lane == 0) tc::mbar_arrive(&empty[slot]);  // this warp's quarter of the accumulator has been read (and re-loaded)
+          if (warp == 0) CTR(1, b, 3);
           if (l < last) {
             uint4* dst = reinterpret_cast<uint4*>(smem + g.a_off[l + 1]) + (size_t)(nb * 4) * 128 + row;
 #pragma unroll
             for (int j = 0; j < 4; j++) dst[(size_t)j * 128] = c4[j];
             tc::fence_async_smem();  // generic-proxy stores, read by the tensor core's async proxy
             tc::mbar_arrive(&a_ready[l + 1][nb]);
+            if (warp == 0) CTR(1, b, 4);
           } else if (LASTM != OUT_SCORE && img < n_img) {
             // the class of the 64-bit word, multi-image rule (foldedmv-offload.cpp:202-220; same arithmetic as k_lfc_classes)
             if (g.classes) {
@@ -317,6 +361,15 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
   if (failed && status) *status = 1;
   tc::fence_before_sync();
   __syncthreads();
+#ifdef BNNB_CHAIN_TRACE
+  if (blockIdx.x == 0 && tid == 0 && T > TRT) {
+    const long long t0 = tr[0][0][0];
+    for (int b = 0; b < nbt && b < 16; b++)
+      printf("CHAIN b%d L%d: issuer slot-wait %lld slot %lld ring %lld committed %lld | epilogue wait %lld full %lld codes %lld released %lld handed %lld | loader %lld\n", b,
+             (int)blk_layer[b], tr[0][b][0] - t0, tr[0][b][1] - t0, tr[0][b][2] - t0, tr[0][b][3] - t0, tr[1][b][0] - t0, tr[1][b][1] - t0, tr[1][b][2] - t0,
+             tr[1][b][3] - t0, tr[1][b][4] - t0, tr[2][b][0] - t0);
+  }
+#endif
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 

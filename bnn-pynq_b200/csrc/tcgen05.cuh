@@ -147,11 +147,21 @@ __device__ __forceinline__ void tma_load_4d(void* dst_smem, const void* tmap, in
 #ifndef BNNB_WAIT_NS
 #define BNNB_WAIT_NS 2000000000ull
 #endif
+// TF (test first): one non-blocking mbarrier.test_wait before the try_wait loop.  A try_wait whose phase has already completed
+// still takes ~350 clocks to return; the test answers at once.  Pays where waits mostly find their barrier complete (the 1-bit fused
+// kernel 1.237 -> 1.18 ms, conv_f4 layer 3 0.370 -> 0.359), costs where they mostly do not (2-bit fused kernel 1.53 -> 1.57,
+// gemm_f4 +5 %), so each kernel chooses.
+template <bool TF = false>
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
   // eight polls per trip: the trip counter costs two ALU-pipe instructions, and the epilogue warps share that pipe
 #ifndef BNNB_POLLU
 #define BNNB_POLLU 8
 #endif
+  if (TF) {  // fast path: a barrier that has already completed its phase answers a non-blocking test at once
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (ok) return true;
+  }
   uint64_t t0 = 0;
   for (;;) {
     for (uint32_t i = 0; i < (1u << 14) / BNNB_POLLU; i++) {
@@ -402,6 +412,51 @@ __device__ __forceinline__ void mma8_mxf4(uint32_t tmem_d, uint32_t a_lo, uint32
       "}\n" ::"r"(tmem_d),
       "r"(a_lo), "r"(b_lo), "r"(d_hi), "r"(idesc), "r"(sf), "r"(acc_first), "n"(ASTEP), "n"(2 * ASTEP), "n"(3 * ASTEP), "n"(4 * ASTEP), "n"(5 * ASTEP),
       "n"(6 * ASTEP), "n"(7 * ASTEP), "n"(BSTEP), "n"(2 * BSTEP), "n"(3 * BSTEP), "n"(4 * BSTEP), "n"(5 * BSTEP), "n"(6 * BSTEP), "n"(7 * BSTEP)
+      : "memory");
+}
+}}  // namespace bnnb::tc
+
+// the same for four and for two slabs (fc_chain.cu: 256-wide layers, and a layer's first channel block, which follows the layer
+// below two slabs at a time).  Slab by slab with runtime indices the issuing thread needs ~260 clocks per MMA (six R2UR each).
+namespace bnnb { namespace tc {
+template <int ASTEP, int BSTEP>
+__device__ __forceinline__ void mma4_mxf4(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t d_hi, uint32_t idesc, uint32_t sf, uint32_t acc_first) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, q;\n\t"
+      ".reg .b32 al, bl;\n\t"
+      ".reg .b64 a, b;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "setp.eq.b32 q, 0, 0;\n\t"
+      "mov.b64 a, {%1, %3};\n\t"
+      "mov.b64 b, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], p;\n\t"
+      "add.u32 al, %1, %7;\n\t add.u32 bl, %2, %10;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "add.u32 al, %1, %8;\n\t add.u32 bl, %2, %11;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "add.u32 al, %1, %9;\n\t add.u32 bl, %2, %12;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(d_hi), "r"(idesc), "r"(sf), "r"(acc_first), "n"(ASTEP), "n"(2 * ASTEP), "n"(3 * ASTEP), "n"(BSTEP), "n"(2 * BSTEP), "n"(3 * BSTEP)
+      : "memory");
+}
+template <int ASTEP, int BSTEP>
+__device__ __forceinline__ void mma2_mxf4(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t d_hi, uint32_t idesc, uint32_t sf, uint32_t acc_first) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, q;\n\t"
+      ".reg .b32 al, bl;\n\t"
+      ".reg .b64 a, b;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "setp.eq.b32 q, 0, 0;\n\t"
+      "mov.b64 a, {%1, %3};\n\t"
+      "mov.b64 b, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], p;\n\t"
+      "add.u32 al, %1, %7;\n\t add.u32 bl, %2, %8;\n\t mov.b64 a, {al, %3};\n\t mov.b64 b, {bl, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], a, b, %4, [%5], [%5], q;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(d_hi), "r"(idesc), "r"(sf), "r"(acc_first), "n"(ASTEP), "n"(BSTEP)
       : "memory");
 }
 }}  // namespace bnnb::tc
