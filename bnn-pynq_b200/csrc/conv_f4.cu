@@ -52,10 +52,11 @@ struct F4Cfg {
 #define BNNB_CONV_STRIP 0
 #endif
 constexpr int kStrip = BNNB_CONV_STRIP;
-#ifndef BNNB_CONV_TF
-#define BNNB_CONV_TF 1
+// test-first mbarrier waits (tcgen05.cuh) by role: 1 loader, 2 issuer, 4 epilogue
+#ifndef BNNB_CONV_TFM
+#define BNNB_CONV_TFM 7
 #endif
-constexpr bool kTF = BNNB_CONV_TF != 0;  // test-first mbarrier waits (tcgen05.cuh)
+constexpr bool kTF_L = (BNNB_CONV_TFM & 1) != 0, kTF_I = (BNNB_CONV_TFM & 2) != 0, kTF_E = (BNNB_CONV_TFM & 4) != 0;
 #ifndef BNNB_G2B
 #define BNNB_G2B 10
 #endif
@@ -232,7 +233,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         constexpr uint32_t IMG_PLANE = Cfg::PXI * 16;  // bytes of one plane of one image
         for (int k = 0; k < K; k++) {
           const int img0 = (gfirst + k * gstride) * G, buf = k & 1;
-          if (k >= 2 && !failed && !tc::mbar_wait<kTF>(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
+          if (k >= 2 && !failed && !tc::mbar_wait<kTF_L>(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
           uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
           const int valid = n_img - img0 < G ? (n_img - img0 > 0 ? n_img - img0 : 0) : G;  // rows of missing images keep stale (finite) codes; never stored
           if (in_fmt == ACT_F4PM) {
@@ -249,7 +250,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
               if (!(kStrip & 16)) tc::bulk_g2s(sa + (size_t)j * Cfg::PLANE, in4 + ((size_t)(img0 / G) * CW + j) * (G * IMG_PLANE), G * IMG_PLANE, &abuf_full[buf]);
           }
           if (PAIR && rank != 0) {  // the follower tells the leader's issuer once its planes have landed
-            if (!failed && !tc::mbar_wait<kTF>(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+            if (!failed && !tc::mbar_wait<kTF_L>(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
             tc::mbar_arrive_remote(&peer_full[buf], 0);
           }
         }
@@ -257,7 +258,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
     } else
     for (int k = 0; k < K; k++) {
       const int img0 = (gfirst + k * gstride) * G, buf = k & 1;
-      if (k >= 2 && !failed && !tc::mbar_wait<kTF>(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
+      if (k >= 2 && !failed && !tc::mbar_wait<kTF_L>(&abuf_empty[buf], (uint32_t)((k >> 1) - 1) & 1)) failed = true;
       uint8_t* sa = smem + (size_t)buf * Cfg::A_BYTES;
 #pragma unroll 4
       for (int i = tid - 512; i < Cfg::ROWS * CW; i += 96) {
@@ -284,12 +285,12 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
       const uint32_t b_lo = tc::desc_lo(sb_u, NTL * 16);
       for (int k = 0; k < K; k++) {
         const int buf = k & 1;
-        if (!failed && !tc::mbar_wait<kTF>(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
-        if (PAIR && !failed && !tc::mbar_wait<kTF>(&peer_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        if (!failed && !tc::mbar_wait<kTF_I>(&abuf_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+        if (PAIR && !failed && !tc::mbar_wait<kTF_I>(&peer_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
         for (int vt = 0; vt < Cfg::TILES * NS; vt++) {  // virtual tile = (row tile t, channel block h)
           const int t = vt / NS, h = vt % NS;
           const int gt = k * Cfg::TILES * NS + vt, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
-          if (u >= 1 && !failed && !tc::mbar_wait<kTF>(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          if (u >= 1 && !failed && !tc::mbar_wait<kTF_I>(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * N;
           const uint32_t at = a_lo[buf] + (uint32_t)(t * 128), bt = b_lo + (uint32_t)(h * NL);
@@ -316,7 +317,7 @@ __global__ void __launch_bounds__(640, 1) k_conv_f4(DevLayer L, const uint32_t* 
         const int t = vt / NS, h = vt % NS;
         const int gt = k * Cfg::TILES * NS + vt, slot = gt % Cfg::SLOTS, u = gt / Cfg::SLOTS;
         if (TEAMS > 1 && gt % TEAMS != team) continue;
-        if (!failed && !tc::mbar_wait<kTF>(&full[slot], (uint32_t)u & 1)) failed = true;
+        if (!failed && !tc::mbar_wait<kTF_E>(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * N + (uint32_t)eg * NG;

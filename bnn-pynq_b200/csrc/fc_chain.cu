@@ -24,6 +24,11 @@ namespace {
 #define BNNB_CH_GG 8
 #endif
 constexpr int CH_MAX = 4, CH_GG = BNNB_CH_GG, CH_SLOTS = 3, CH_SF_COL = 384, CH_RING_MAX = 16, CH_BLK_MAX = 32;
+// test-first mbarrier waits (tcgen05.cuh) by role: 1 loaders, 2 issuer, 4 epilogue
+#ifndef BNNB_CHAIN_TFM
+#define BNNB_CHAIN_TFM 0
+#endif
+constexpr bool cTF_L = (BNNB_CHAIN_TFM & 1) != 0, cTF_I = (BNNB_CHAIN_TFM & 2) != 0, cTF_E = (BNNB_CHAIN_TFM & 4) != 0;
 constexpr int CH_SLOT_BYTES = CH_GG * 128 * 32;  // one ring slot: eight K=64 slabs of 128 channels
 
 struct ChainGeom {
@@ -133,7 +138,7 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
       const int ks = g.ks[0];
       for (int tl = 0; tl < T; tl++) {
         const int buf = tl % g.nbuf0, use = tl / g.nbuf0;
-        if (use >= 1 && !failed && !tc::mbar_wait(&a_empty[buf], (uint32_t)(use - 1) & 1)) failed = true;
+        if (use >= 1 && !failed && !tc::mbar_wait<cTF_L>(&a_empty[buf], (uint32_t)(use - 1) & 1)) failed = true;
         uint8_t* sa = smem + g.a_off[0] + (size_t)buf * g.a_bytes0;
         const uint8_t* src = in + ((size_t)blockIdx.x + (size_t)tl * gridDim.x) * g.a_bytes0;
         for (int q = 0; q < 4; q++) {
@@ -158,7 +163,7 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
         for (int nb = 0; nb < g.nblk[l]; nb++)
           for (int s0 = 0; s0 < ks; s0 += CH_GG, gg++) {
             const int cnt = min(CH_GG, ks - s0);
-            if (gg >= g.ring && !failed && !tc::mbar_wait(&ring_empty[r], rpar)) failed = true;
+            if (gg >= g.ring && !failed && !tc::mbar_wait<cTF_L>(&ring_empty[r], rpar)) failed = true;
             if (s0 == 0) CTR(2, g.blk0[l] + nb, 0);
             if (leader) {
               tc::mbar_expect_tx(&ring_full[r], (uint32_t)(cnt * slab));
@@ -186,12 +191,12 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
         for (int nb = 0; nb < g.nblk[l]; nb++) {
           const int gb = tl * nbt + g.blk0[l] + nb, slot = gb % SLOTS, u = gb / SLOTS;
           CTR(0, g.blk0[l] + nb, 0);
-          if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          if (u >= 1 && !failed && !tc::mbar_wait<cTF_I>(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           CTR(0, g.blk0[l] + nb, 1);
           const uint32_t acc = tmem + (uint32_t)slot * 128;
           for (int s0 = 0; s0 < ks; s0 += CH_GG) {
-            if (!failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
+            if (!failed && !tc::mbar_wait<cTF_I>(&ring_full[r], rpar)) failed = true;
             if (s0 == 0) CTR(0, g.blk0[l] + nb, 2);
             const int cnt = min(CH_GG, ks - s0);
             const uint32_t b_lo = b_lo0 + (uint32_t)r * (CH_SLOT_BYTES / 16);
@@ -214,14 +219,14 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
             } else if (nb == 0 && l > 0 && (cnt & 1) == 0) {
               // the tile's first block runs behind the layer below: slabs 2b, 2b+1 = the 128 channels of its block b
               for (int e = 0; e < cnt; e += 2) {
-                if (!failed && !tc::mbar_wait(&a_ready[l][(s0 + e) >> 1], (uint32_t)tl & 1)) failed = true;
+                if (!failed && !tc::mbar_wait<cTF_I>(&a_ready[l][(s0 + e) >> 1], (uint32_t)tl & 1)) failed = true;
                 tc::fence_after_sync();
                 block(2, e);
               }
             } else if (nb == 0 && l == 0 && (cnt == 8 || cnt == 4)) {
               // the chain's first operand tile arrives in K quarters: the quarters this group reads, then one asm block
               while (qn < 4 && s0 + cnt - 1 >= (qn * ks) / 4) {
-                if (!failed && !tc::mbar_wait(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
+                if (!failed && !tc::mbar_wait<cTF_I>(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
                 qn++;
               }
               tc::fence_after_sync();
@@ -231,11 +236,11 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
                 if (nb == 0) {  // the first operand tile arrives in K quarters
                   if (l == 0) {
                     while (qn < 4 && s >= (qn * ks) / 4) {
-                      if (!failed && !tc::mbar_wait(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
+                      if (!failed && !tc::mbar_wait<cTF_I>(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
                       qn++;
                     }
                   } else if ((s & 1) == 0) {
-                    if (!failed && !tc::mbar_wait(&a_ready[l][s >> 1], (uint32_t)tl & 1)) failed = true;
+                    if (!failed && !tc::mbar_wait<cTF_I>(&a_ready[l][s >> 1], (uint32_t)tl & 1)) failed = true;
                   }
                   tc::fence_after_sync();
                 }
@@ -268,7 +273,7 @@ __global__ void __launch_bounds__(256, 1) k_fc_chain(ChainGeom g, const uint8_t*
         for (int nb = 0; nb < g.nblk[l]; nb++) {
           const int b = g.blk0[l] + nb, gb = tl * nbt + b, slot = gb % SLOTS, u = gb / SLOTS;
           if (warp == 0) CTR(1, b, 0);
-          if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
+          if (!failed && !tc::mbar_wait<cTF_E>(&full[slot], (uint32_t)u & 1)) failed = true;
           tc::fence_after_sync();
           if (warp == 0) CTR(1, b, 1);
           const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * 128;

@@ -34,6 +34,11 @@ constexpr int GG = BNNB_GG;
 #define BNNB_GEMM_STRIP 0
 #endif
 constexpr int kGStrip = BNNB_GEMM_STRIP;
+// test-first mbarrier waits (tcgen05.cuh) by role: 1 loaders, 2 issuer, 4 epilogue
+#ifndef BNNB_GEMM_TFM
+#define BNNB_GEMM_TFM 0
+#endif
+constexpr bool gTF_L = (BNNB_GEMM_TFM & 1) != 0, gTF_I = (BNNB_GEMM_TFM & 2) != 0, gTF_E = (BNNB_GEMM_TFM & 4) != 0;
 constexpr int GF_RING_MAX = 32;
 
 // 8 bits -> 8 nibbles (bit i at position 4i)
@@ -149,7 +154,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
         const uint8_t* in4 = reinterpret_cast<const uint8_t*>(in);
         for (int tl = 0; tl < T; tl++) {
           const int buf = tl % g.nbuf, use = tl / g.nbuf;
-          if (use >= 1 && !failed && !tc::mbar_wait(&a_empty[buf], (uint32_t)(use - 1) & 1)) failed = true;
+          if (use >= 1 && !failed && !tc::mbar_wait<gTF_L>(&a_empty[buf], (uint32_t)(use - 1) & 1)) failed = true;
           uint8_t* sa = smem + (size_t)buf * g.a_bytes;
           const uint8_t* src = in4 + ((size_t)blockIdx.x + (size_t)tl * gridDim.x) * g.a_bytes;
           for (int q = 0; q < 4; q++) {
@@ -168,7 +173,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
     const int total = 128 * g.ks;  // items: (row, pair of chunks = one K=64 slab), row fastest: conflict-free 16-byte stores
     for (int tl = 0; tl < T; tl++) {
       const int buf = tl % g.nbuf, use = tl / g.nbuf;
-      if (use >= 1 && !failed && !tc::mbar_wait(&a_empty[buf], (uint32_t)(use - 1) & 1)) failed = true;
+      if (use >= 1 && !failed && !tc::mbar_wait<gTF_L>(&a_empty[buf], (uint32_t)(use - 1) & 1)) failed = true;
       uint8_t* sa = smem + (size_t)buf * g.a_bytes;
       const long long img0 = ((long long)blockIdx.x + (long long)tl * gridDim.x) * 128;
       int qn = 0;
@@ -216,7 +221,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
       uint32_t rpar = 1;                           // parity to wait for on ring_empty = parity of the slot's previous use
       for (int gg = 0; gg < total; gg++) {
         const int s0 = gi * GG, cnt = min(GG, g.ks - s0);
-        if (gg >= g.ring && !failed && !tc::mbar_wait(&ring_empty[r], rpar)) failed = true;
+        if (gg >= g.ring && !failed && !tc::mbar_wait<gTF_L>(&ring_empty[r], rpar)) failed = true;
         if (leader) {
           if (kGStrip & 8) tc::mbar_arrive(&ring_full[r]);
           else {
@@ -241,7 +246,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
         const uint32_t a_lo = tc::desc_lo(sa_u0 + (uint32_t)buf * g.a_bytes, 2048);
         for (int nb = 0; nb < g.nblk; nb++) {
           const int gb = tl * g.nblk + nb, slot = gb % SLOTS, u = gb / SLOTS;
-          if (u >= 1 && !failed && !tc::mbar_wait(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+          if (u >= 1 && !failed && !tc::mbar_wait<gTF_I>(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
           tc::fence_after_sync();
           const uint32_t acc = tmem + (uint32_t)slot * NB;
           int qn = 0;
@@ -254,7 +259,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
             const int nfull = g.ks / GG;
             uint32_t a = a_lo;
             for (int gi = 0; gi < nfull; gi++) {
-              if (!(g.resident && tl > 0) && !failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
+              if (!(g.resident && tl > 0) && !failed && !tc::mbar_wait<gTF_I>(&ring_full[r], rpar)) failed = true;
               if (leader) {
                 if (!(kGStrip & 1)) tc::mma8_mxf4<256, NB * 2>(acc, a, b_lo + (uint32_t)r * (GG * (SLAB / 16)), d_hi, idesc, sf, (ACC || gi > 0) ? 1u : 0u);
                 if (!g.resident) tc::commit(&ring_empty[r]);
@@ -268,7 +273,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
           }
 #endif
           for (int s0 = s_begin; s0 < g.ks; s0 += GG) {  // one ring slot = GG slabs (fewer at the end of the block)
-            if (!(g.resident && tl > 0) && !failed && !tc::mbar_wait(&ring_full[r], rpar)) failed = true;
+            if (!(g.resident && tl > 0) && !failed && !tc::mbar_wait<gTF_I>(&ring_full[r], rpar)) failed = true;
             const int s1 = min(s0 + GG, g.ks);
 #ifndef BNNB_GEMM_NO_MMA8
             // a full group whose operand quarters are all in (every channel block but a tile's first): one asm block of eight MMAs
@@ -284,7 +289,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
             for (int s = s0; s < s1; s++) {
               // slab s lies in quarter q with ((q+1)*ks)/4 > s: wait for the quarters up to it (first channel block of a tile only)
               while (nb == 0 && qn < 4 && (s >= (qn * g.ks) / 4)) {
-                if (!failed && !tc::mbar_wait(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
+                if (!failed && !tc::mbar_wait<gTF_I>(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
                 tc::fence_after_sync();
                 qn++;
               }
@@ -310,7 +315,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
       int cls_max = 0, cls_arg = 0;  // OUT_SCORE with classes: running arg-max over this row's scores, channel order
       for (int nb = 0; nb < g.nblk; nb++) {
         const int gb = tl * g.nblk + nb, slot = gb % SLOTS, u = gb / SLOTS;
-        if (!failed && !tc::mbar_wait(&full[slot], (uint32_t)u & 1)) failed = true;
+        if (!failed && !tc::mbar_wait<gTF_E>(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const uint32_t trow = tmem + ((uint32_t)(hw * 32) << 16) + (uint32_t)slot * NB;
         uint32_t b0[NW], b1[NW];

@@ -157,7 +157,11 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
 #ifndef BNNB_POLLU
 #define BNNB_POLLU 8
 #endif
-  if (TF) {  // fast path: a barrier that has already completed its phase answers a non-blocking test at once
+#ifndef BNNB_TF_POLLS
+#define BNNB_TF_POLLS 1
+#endif
+#pragma unroll
+  for (int tp = 0; tp < (TF ? BNNB_TF_POLLS : 0); tp++) {  // fast path: a barrier that has already completed its phase answers a non-blocking test at once
     uint32_t ok;
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
     if (ok) return true;
