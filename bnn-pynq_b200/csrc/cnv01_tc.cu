@@ -131,15 +131,16 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
                                                       int n_img, int out_fmt, int* __restrict__ status, Tap01 tp) {
   tc::griddep_launch();  // dependents (programmatic dependent launch) may start their prologues now
   using S = Smem01<OUTM, F4>;
-  // test-first mbarrier waits (tcgen05.cuh), by role: 1 helper warps, 2 layer-0 epilogue, 4 issuers, 8 layer-1 epilogue
-#ifndef BNNB_01_TFM
-#define BNNB_01_TFM 6
+  // test-first mbarrier waits (tcgen05.cuh), by site: bit 0 img_full, 1 p_empty, 2 bits_full (helper warps); 3 abuf_empty, 4 f0 (layer-0
+  // epilogue); 5 p_full, 6 e0, 7 empty, 8 l0_done (issuers); 9 bits_empty, 10 full (layer-1 epilogue)
+#ifndef BNNB_01_TFS
+#define BNNB_01_TFS 0x1f8
 #endif
-#ifndef BNNB_01_TFM_T
-#define BNNB_01_TFM_T 0
+#ifndef BNNB_01_TFS_T
+#define BNNB_01_TFS_T 0
 #endif
-  constexpr int TFM = OUTM == OUT_BIT ? BNNB_01_TFM : BNNB_01_TFM_T;
-  constexpr bool TF_H = (TFM & 1) != 0, TF_E0 = (TFM & 2) != 0, TF_I = (TFM & 4) != 0, TF_E1 = (TFM & 8) != 0;
+  constexpr int TFSM = OUTM == OUT_BIT ? BNNB_01_TFS : BNNB_01_TFS_T;
+#define TFS(n) (((TFSM >> (n)) & 1) != 0)
   constexpr int L1_A = S::L1_A;
   constexpr uint32_t SF_COL = 448;  // TMEM columns of the unit scale factors (F4)
   constexpr uint32_t L0_ACC = 256;  // TMEM columns: layer-1 slots 0,64,128,192; layer-0 slots 256,320
@@ -262,8 +263,8 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     const int hx = tid - 19 * 32;
     const int buf = kk & 1;
     const uint32_t par = (uint32_t)(kk >> 1) & 1;
-    if (!failed && !tc::mbar_wait<TF_H>(&img_full[buf], par)) failed = true;
-    if (kk >= 2 && !failed && !tc::mbar_wait<TF_H>(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
+    if (!failed && !tc::mbar_wait<TFS(0)>(&img_full[buf], par)) failed = true;
+    if (kk >= 2 && !failed && !tc::mbar_wait<TFS(1)>(&p_empty[buf], par ^ 1)) failed = true;  // layer-0 MMAs of image kk-2 are done with this plane
     const uint32_t* iw = reinterpret_cast<const uint32_t*>(sImg + (size_t)buf * IMG_BYTES);
     uint8_t* sPk = sP + (size_t)buf * S::P_STRIDE;
 #pragma unroll PLANEU
@@ -300,14 +301,14 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
       const uint32_t par = (uint32_t)(k >> 1) & 1;
       // the layer-1 MMAs that read this operand buffer two images ago must have completed before it is overwritten
       if (warp == 8) { TR(6, k, 5); }
-      if (k >= 2 && !failed && !tc::mbar_wait<TF_E0>(&abuf_empty[buf], par ^ 1)) failed = true;
+      if (k >= 2 && !failed && !tc::mbar_wait<TFS(3)>(&abuf_empty[buf], par ^ 1)) failed = true;
       if (warp == 8) { TR(6, k, 4); }
       uint8_t* sA = smem + (size_t)buf * L1_A;
 #pragma unroll
       for (int t = 0; t < L0_TILES; t++) {
         const int slot = s0, spar = p0;  // tile u = 8k + t uses slot u % L0_SLOTS for the (u / L0_SLOTS)-th time
         if (++s0 == L0_SLOTS) { s0 = 0; p0 ^= 1u; }
-        if (!failed && !tc::mbar_wait<TF_E0>(&f0[slot], spar)) failed = true;
+        if (!failed && !tc::mbar_wait<TFS(4)>(&f0[slot], spar)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane, y = m >> 5, x = m & 31;
         const bool valid = x < 30 && y < 30;
@@ -410,14 +411,14 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
           tc::mbar_expect_tx(&img_full[k], 3072);
           tc::bulk_g2s(sImg + (size_t)k * IMG_BYTES, in + (first + (long long)k * stride) * 3072, 3072, &img_full[k]);
         }
-      if (CP && !failed && !tc::mbar_wait<TF_I>(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
+      if (CP && !failed && !tc::mbar_wait<TFS(5)>(&pre_done, 0)) failed = true;  // accumulators hold their pre-loads
       int s0 = 0;
       uint32_t p0 = 0;
       auto issue_l0 = [&](int k, int t) {
         const int buf = k & 1;
         if (t == 0) {
           TR(6, k, 0);
-          if (!failed && !tc::mbar_wait<TF_I>(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
+          if (!failed && !tc::mbar_wait<TFS(5)>(&p_full[buf], (uint32_t)(k >> 1) & 1)) failed = true;
           TR(6, k, 1);
           if (k + 2 < K && leader) {  // image buffer `buf` has been consumed: prefetch image k+2 into it
             tc::mbar_expect_tx(&img_full[buf], 3072);
@@ -428,7 +429,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         const uint32_t spar = p0;
         if (++s0 == L0_SLOTS) { s0 = 0; p0 ^= 1u; }
         TR(0, k, t);
-        if (k * L0_TILES + t >= L0_SLOTS && !failed && !tc::mbar_wait<TF_I>(&e0[slot], spar ^ 1u)) failed = true;
+        if (k * L0_TILES + t >= L0_SLOTS && !failed && !tc::mbar_wait<TFS(6)>(&e0[slot], spar ^ 1u)) failed = true;
         tc::fence_after_sync();
         const uint32_t acc = tmem + L0_ACC + (uint32_t)slot * 64;
         const uint32_t a0 = p_lo[buf] + (uint32_t)(t * 128);  // descriptor start fields are in 16-byte units: one row = 1
@@ -447,7 +448,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
         const uint32_t sa_u = sA_u + (uint32_t)buf * L1_A;
         const uint32_t a_lo = a1_lo[buf] + (uint32_t)(t * 128);
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-        if (u >= 1 && !failed && !tc::mbar_wait<TF_I>(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
+        if (u >= 1 && !failed && !tc::mbar_wait<TFS(7)>(&empty[slot], (uint32_t)(u - 1) & 1)) failed = true;
         tc::fence_after_sync();
         const uint32_t acc = tmem + (uint32_t)slot * 64;
         bool firstmma = true;
@@ -494,7 +495,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
           for (int t = 0; t < L1_TILES; t++)
             if (((k * L1_TILES + t) & 1) == w) {
               // layer-1 tile t reads operand rows [128t, 128t+190): complete once layer-0 tile t+1 has been written
-              if (!failed && !tc::mbar_wait<TF_I>(&l0_done[buf][t + 1], (uint32_t)(k >> 1) & 1)) failed = true;
+              if (!failed && !tc::mbar_wait<TFS(8)>(&l0_done[buf][t + 1], (uint32_t)(k >> 1) & 1)) failed = true;
               issue_l1(k, t);
             }
           if (leader) tc::commit(&abuf_empty[buf]);  // this warp's MMAs of the image; the barrier counts both issuers
@@ -543,10 +544,10 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
     for (int k = 0; k < K; k++) {
       const int bb = k & (S::NBITS - 1);  // bit-row buffer: the helpers pool image k while this half is on image k+1
       uint32_t* sbk = sbits + (size_t)bb * (S::BITS / 4);
-      if (k >= S::NBITS && !failed && !tc::mbar_wait<TF_E1>(&bits_empty[bb], (uint32_t)(k / S::NBITS - 1) & 1)) failed = true;
+      if (k >= S::NBITS && !failed && !tc::mbar_wait<TFS(9)>(&bits_empty[bb], (uint32_t)(k / S::NBITS - 1) & 1)) failed = true;
       for (int t = 0; t < L1_TILES; t++) {
         const int g = k * L1_TILES + t, slot = g & 3, u = g >> 2;
-        if (!failed && !tc::mbar_wait<TF_E1>(&full[slot], (uint32_t)u & 1)) failed = true;
+        if (!failed && !tc::mbar_wait<TFS(10)>(&full[slot], (uint32_t)u & 1)) failed = true;
         tc::fence_after_sync();
         const int m = t * 128 + hw * 32 + lane;
         uint32_t r[32];
@@ -619,7 +620,7 @@ __global__ void __launch_bounds__(NT01, 1) k_cnv01_tc(DevLayer L0, DevLayer L1, 
       if (k + 2 < K) build_p(k + 2);
       const int bb = k & (S::NBITS - 1);
       const uint32_t* sbk = sbits + (size_t)bb * (S::BITS / 4);
-      if (!failed && !tc::mbar_wait<TF_H>(&bits_full[bb], (uint32_t)(k / S::NBITS) & 1)) failed = true;
+      if (!failed && !tc::mbar_wait<TFS(2)>(&bits_full[bb], (uint32_t)(k / S::NBITS) & 1)) failed = true;
       // 2x2 max-pool over the 28x28 valid outputs (row index y*30 + x) -> 14x14, bit-packed
 #pragma unroll POOLU
       for (int i = hx; kPool && i < 196 * 2; i += NH * 32) {
