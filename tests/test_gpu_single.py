@@ -69,3 +69,34 @@ def test_single_image_graph_and_ordinary_path_agree():
         assert out.returncode == 0, out.stderr[-2000:]
         got[no_graph] = out.stdout.split("hash")[1].split()[0]
     assert got[0] == got[1]
+
+
+def test_single_image_graph_sees_injected_faults_and_memory_writes():
+    """Faults and MemSet writes rewrite the device operands in place: a graph captured before them must compute with the new
+    parameters (its nodes hold pointers, not values).  Single-image replays against the batch path on the same faulted engine,
+    then against the oracle after the original parameters are loaded again."""
+    from bnn import native
+    net = "cnvW1A1"
+    rt = native.Runtime(net, params_dir(net), devices=[0])
+    imgs = synth_cifar(6, 31)
+    for i in range(3):                                   # capture on clean parameters
+        rt.classify_cifar(imgs[i:i + 1], 10)
+    clean = rt.classify_cifar(imgs, 10, want_scores=True)[1]
+    changed = False
+    for layer, bit in ((8, 5), (7, 1234), (2, 77), (1, 3)):
+        assert rt.weight_layer_bits(layer) > bit
+        rt.inject_fault(0, layer, bit, 1)                # target 0: weights
+        if rt.thresh_layer_bits(layer) > bit % 64:
+            rt.inject_fault(1, layer, bit % 64, 1)       # target 1: thresholds
+        batch = rt.classify_cifar(imgs, 10, want_scores=True)[1]
+        changed = changed or not np.array_equal(batch, clean)
+        for i in range(6):
+            cls, sc = rt.classify_cifar(imgs[i:i + 1], 10, want_scores=True)
+            assert np.array_equal(sc, batch[i:i + 1]), (layer, bit, i)
+    assert changed
+    rt.load_parameters(params_dir(net))
+    o = Oracle(net)
+    for i in range(6):
+        cls, sc = rt.classify_cifar(imgs[i:i + 1], 10, want_scores=True)
+        assert np.array_equal(sc, o.cnv_scores(imgs[i:i + 1]))
+    rt.close()
