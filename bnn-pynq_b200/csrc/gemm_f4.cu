@@ -275,6 +275,27 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
           for (int s0 = s_begin; s0 < g.ks; s0 += GG) {  // one ring slot = GG slabs (fewer at the end of the block)
             if (!(g.resident && tl > 0) && !failed && !tc::mbar_wait<gTF_I>(&ring_full[r], rpar)) failed = true;
             const int s1 = min(s0 + GG, g.ks);
+#ifndef BNNB_GEMM_SLABWISE
+            // The group as asm blocks of 8 / 4 / 2 MMAs (slab by slab with run-time indices the issuing thread spends ~260 clocks per
+            // MMA, fc_chain.cu trace).  A tile's first channel block first waits for the operand quarters the group reads.
+            if (GG == 8) {
+              while (nb == 0 && qn < 4 && s1 - 1 >= (qn * g.ks) / 4) {
+                if (!failed && !tc::mbar_wait<gTF_I>(&a_part[buf][qn], (uint32_t)use & 1)) failed = true;
+                tc::fence_after_sync();
+                qn++;
+              }
+              if (leader && !(kGStrip & 1)) {
+                int e = 0;
+                const int cnt = s1 - s0;
+                const uint32_t a0 = a_lo + (uint32_t)(2 * s0) * 128, b0 = b_lo + (uint32_t)(r * GG) * (SLAB / 16);
+                if (cnt - e >= 8) { tc::mma8_mxf4<256, NB * 2>(acc, a0, b0, d_hi, idesc, sf, (ACC || s0 > 0) ? 1u : 0u); e += 8; }
+                if (cnt - e >= 4) { tc::mma4_mxf4<256, NB * 2>(acc, a0 + (uint32_t)(2 * e) * 128, b0 + (uint32_t)e * (SLAB / 16), d_hi, idesc, sf, (ACC || s0 + e > 0) ? 1u : 0u); e += 4; }
+                if (cnt - e >= 2) { tc::mma2_mxf4<256, NB * 2>(acc, a0 + (uint32_t)(2 * e) * 128, b0 + (uint32_t)e * (SLAB / 16), d_hi, idesc, sf, (ACC || s0 + e > 0) ? 1u : 0u); e += 2; }
+                if (cnt - e >= 1) tc::mma_mxf4_lh(acc, a0 + (uint32_t)(2 * e) * 128, d_hi, b0 + (uint32_t)e * (SLAB / 16), d_hi, idesc, sf, sf, (ACC || s0 + e > 0) ? 1u : 0u);
+              }
+            } else
+#endif
+            {
 #ifndef BNNB_GEMM_NO_MMA8
             // a full group whose operand quarters are all in (every channel block but a tile's first): one asm block of eight MMAs
             if (GG % 8 == 0 && s1 - s0 == GG && (nb > 0 || qn == 4)) {
@@ -295,6 +316,7 @@ __global__ void __launch_bounds__(384, 1) k_gemm_f4(DevLayer L, GemmGeom g, cons
               }
               if (leader && !(kGStrip & 1))
                 tc::mma_mxf4_lh(acc, a_lo + (uint32_t)(2 * s) * 128, d_hi, b_lo + (uint32_t)(r * GG + (s - s0)) * (SLAB / 16), d_hi, idesc, sf, sf, (ACC || s > 0) ? 1u : 0u);
+            }
             }
             if (leader && !g.resident) tc::commit(&ring_empty[r]);
             if (++r == g.ring) { r = 0; rpar ^= 1u; }
